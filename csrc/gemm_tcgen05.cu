@@ -1,0 +1,347 @@
+// Persistent, warp-specialised bf16 GEMM on Blackwell 5th-gen tensor cores.
+//
+//   C[M,N] (+)= A[M,K] * B[N,K]^T          fp32 accumulation in TMEM
+//
+// Each operand may be stored K-major (row-major [rows, K]) or MN-major
+// (row-major [K, rows]); the three combinations a Linear layer needs are
+//   forward  y  = x  W^T      : A K-major,  B K-major
+//   dgrad    dx = dy W        : A K-major,  B MN-major
+//   wgrad    dW = dy^T x      : A MN-major, B MN-major   (optionally dW += ...)
+// so no transposed copies are ever materialised (reference: F.linear + autograd,
+// scaletorch/parallel/tensor_parallel/tensor_parallel.py:240,352, tp_comms.py:265-308).
+//
+// Structure (one CTA per SM, 256 threads):
+//   warp 0      TMA producer  : cp.async.bulk.tensor -> 128B-swizzled smem ring
+//   warp 1      MMA issuer    : one thread issues tcgen05.mma (128 x BN x 16)
+//   warp 2      TMEM allocator
+//   warps 4..7  epilogue      : tcgen05.ld -> registers -> global (bf16 / fp32 / +=)
+// The accumulator is double-buffered in TMEM so the epilogue of tile i overlaps
+// the main loop of tile i+1.
+#include "common/host.h"
+#include "common/ptx.cuh"
+
+namespace stb {
+
+constexpr int kBM = 128;
+constexpr int kBK = 64;  // 64 bf16 = one 128-byte swizzle row
+constexpr int kGemmThreads = 256;
+
+struct GemmParams {
+  void* C;
+  const void* bias;  // unused for now (kept for ABI stability)
+  int M, N, K;
+  int ldc;
+  int tiles_m, tiles_n, num_tiles, k_blocks;
+  int out_fp32;
+  int accumulate;
+};
+
+template <int BN>
+struct GemmCfg {
+  static constexpr int kABytes = kBM * kBK * 2;
+  static constexpr int kBBytes = BN * kBK * 2;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kStages = (BN == 256) ? 4 : 6;
+  static constexpr int kTmemCols = 2 * BN;  // two accumulator stages
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
+};
+
+STB_DEVICE void tile_coords(int tile, int tiles_m, int tiles_n, int& m, int& n) {
+  constexpr int kGroup = 8;
+  const int group_size = kGroup * tiles_n;
+  const int g = tile / group_size;
+  const int first_m = g * kGroup;
+  const int gm = min(tiles_m - first_m, kGroup);
+  const int r = tile - g * group_size;
+  m = first_m + r % gm;
+  n = r / gm;
+}
+
+template <int BN, bool A_MN, bool B_MN>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+    gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                     const GemmParams p) {
+  using Cfg = GemmCfg<BN>;
+  constexpr int kStages = Cfg::kStages;
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~uintptr_t(1023));
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + kStages * Cfg::kABytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kStages * Cfg::kStageBytes);
+  uint64_t* full_bar = bars;
+  uint64_t* empty_bar = bars + kStages;
+  uint64_t* tmem_full = bars + 2 * kStages;
+  uint64_t* tmem_empty = bars + 2 * kStages + 2;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 4);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < kStages; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&tmem_full[i], 1);
+      mbar_init(&tmem_empty[i], 128);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(tmem_ptr, Cfg::kTmemCols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  if (warp == 0) {
+    // ------------------------------------------------------- TMA producer
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+        int tm, tn;
+        tile_coords(tile, p.tiles_m, p.tiles_n, tm, tn);
+        const int m0 = tm * kBM, n0 = tn * BN;
+        for (int kb = 0; kb < p.k_blocks; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          mbar_arrive_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+          uint8_t* a_dst = sA + stage * Cfg::kABytes;
+          uint8_t* b_dst = sB + stage * Cfg::kBBytes;
+          const int k0 = kb * kBK;
+          if constexpr (!A_MN) {
+            tma_load_2d(a_dst, &tmA, &full_bar[stage], k0, m0);
+          } else {
+#pragma unroll
+            for (int j = 0; j < kBM / 64; ++j)
+              tma_load_2d(a_dst + j * (kBK * 128), &tmA, &full_bar[stage], m0 + j * 64, k0);
+          }
+          if constexpr (!B_MN) {
+            tma_load_2d(b_dst, &tmB, &full_bar[stage], k0, n0);
+          } else {
+#pragma unroll
+            for (int j = 0; j < BN / 64; ++j)
+              tma_load_2d(b_dst + j * (kBK * 128), &tmB, &full_bar[stage], n0 + j * 64, k0);
+          }
+          if (++stage == kStages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // --------------------------------------------------------- MMA issuer
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(kBM, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
+      // K-major : 8-row groups are 1024 B apart (SBO); LBO unused.
+      // MN-major: 64-element MN atoms are kBK*128 B apart (LBO); 8-k groups 1024 B apart (SBO).
+      constexpr uint32_t a_lbo = A_MN ? kBK * 128 : 16, b_lbo = B_MN ? kBK * 128 : 16;
+      constexpr uint32_t a_kstep = A_MN ? 16 * 128 : 32, b_kstep = B_MN ? 16 * 128 : 32;
+      int stage = 0;
+      uint32_t phase = 0;
+      int it = 0;
+      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+        const int acc = it & 1;
+        const uint32_t acc_phase = (it >> 1) & 1;
+        mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + acc * BN;
+        for (int kb = 0; kb < p.k_blocks; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t a_addr = smem_u32(sA + stage * Cfg::kABytes);
+          const uint32_t b_addr = smem_u32(sB + stage * Cfg::kBBytes);
+#pragma unroll
+          for (int k = 0; k < kBK / 16; ++k) {
+            const uint64_t da = umma_smem_desc_sw128(a_addr + k * a_kstep, a_lbo, 1024);
+            const uint64_t db = umma_smem_desc_sw128(b_addr + k * b_kstep, b_lbo, 1024);
+            umma_f16_ss(tmem_d, da, db, idesc, (kb | k) != 0);
+          }
+          umma_commit(&empty_bar[stage]);  // frees the smem slot when these MMAs retire
+          if (++stage == kStages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        umma_commit(&tmem_full[acc]);  // accumulator ready for the epilogue
+      }
+    }
+  } else if (warp >= 4) {
+    // ----------------------------------------------------------- epilogue
+    const int ew = warp - 4;  // TMEM lane quarter owned by this warp
+    int it = 0;
+    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+      int tm, tn;
+      tile_coords(tile, p.tiles_m, p.tiles_n, tm, tn);
+      const int acc = it & 1;
+      const uint32_t acc_phase = (it >> 1) & 1;
+      mbar_wait(&tmem_full[acc], acc_phase);
+      tc_fence_after();
+      const int row = tm * kBM + ew * 32 + lane;
+      const uint32_t taddr = tmem_base + (uint32_t(ew * 32) << 16) + acc * BN;
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32b_x32(taddr + c * 32, r);
+        tmem_ld_wait();
+        const int col0 = tn * BN + c * 32;
+        if (row < p.M && col0 < p.N) {
+          const bool full = (col0 + 32 <= p.N);
+          if (p.out_fp32) {
+            float* dst = reinterpret_cast<float*>(p.C) + size_t(row) * p.ldc + col0;
+            if (full && ((p.ldc & 3) == 0)) {
+#pragma unroll
+              for (int v = 0; v < 8; ++v) {
+                float4 o = make_float4(__uint_as_float(r[4 * v]), __uint_as_float(r[4 * v + 1]),
+                                       __uint_as_float(r[4 * v + 2]), __uint_as_float(r[4 * v + 3]));
+                if (p.accumulate) {
+                  const float4 old = *reinterpret_cast<const float4*>(dst + 4 * v);
+                  o.x += old.x; o.y += old.y; o.z += old.z; o.w += old.w;
+                }
+                *reinterpret_cast<float4*>(dst + 4 * v) = o;
+              }
+            } else {
+#pragma unroll
+              for (int v = 0; v < 32; ++v) {
+                if (col0 + v < p.N) {
+                  float o = __uint_as_float(r[v]);
+                  if (p.accumulate) o += dst[v];
+                  dst[v] = o;
+                }
+              }
+            }
+          } else {
+            __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(p.C) + size_t(row) * p.ldc + col0;
+            if (full && ((p.ldc & 7) == 0)) {
+#pragma unroll
+              for (int v = 0; v < 4; ++v) {
+                uint4 o;
+                if (p.accumulate) {
+                  const uint4 old = *reinterpret_cast<const uint4*>(dst + 8 * v);
+                  const float2 a0 = unpack_bf16x2(old.x), a1 = unpack_bf16x2(old.y),
+                               a2 = unpack_bf16x2(old.z), a3 = unpack_bf16x2(old.w);
+                  o.x = pack_bf16x2(__uint_as_float(r[8 * v + 0]) + a0.x, __uint_as_float(r[8 * v + 1]) + a0.y);
+                  o.y = pack_bf16x2(__uint_as_float(r[8 * v + 2]) + a1.x, __uint_as_float(r[8 * v + 3]) + a1.y);
+                  o.z = pack_bf16x2(__uint_as_float(r[8 * v + 4]) + a2.x, __uint_as_float(r[8 * v + 5]) + a2.y);
+                  o.w = pack_bf16x2(__uint_as_float(r[8 * v + 6]) + a3.x, __uint_as_float(r[8 * v + 7]) + a3.y);
+                } else {
+                  o.x = pack_bf16x2(__uint_as_float(r[8 * v + 0]), __uint_as_float(r[8 * v + 1]));
+                  o.y = pack_bf16x2(__uint_as_float(r[8 * v + 2]), __uint_as_float(r[8 * v + 3]));
+                  o.z = pack_bf16x2(__uint_as_float(r[8 * v + 4]), __uint_as_float(r[8 * v + 5]));
+                  o.w = pack_bf16x2(__uint_as_float(r[8 * v + 6]), __uint_as_float(r[8 * v + 7]));
+                }
+                *reinterpret_cast<uint4*>(dst + 8 * v) = o;
+              }
+            } else {
+#pragma unroll
+              for (int v = 0; v < 32; ++v) {
+                if (col0 + v < p.N) {
+                  float o = __uint_as_float(r[v]);
+                  if (p.accumulate) o += __bfloat162float(dst[v]);
+                  dst[v] = __float2bfloat16(o);
+                }
+              }
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(&tmem_empty[acc]);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem_base, Cfg::kTmemCols);
+}
+
+template <int BN, bool A_MN, bool B_MN>
+static int launch_gemm(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb,
+                       int ldc, int out_fp32, int accumulate, cudaStream_t stream) {
+  using Cfg = GemmCfg<BN>;
+  CUtensorMap tmA, tmB;
+  int rc;
+  if (!A_MN)
+    rc = make_tmap_2d(&tmA, A, 2, K, M, uint64_t(lda) * 2, kBK, kBM, 1);
+  else
+    rc = make_tmap_2d(&tmA, A, 2, M, K, uint64_t(lda) * 2, 64, kBK, 1);
+  if (rc) return rc;
+  if (!B_MN)
+    rc = make_tmap_2d(&tmB, B, 2, K, N, uint64_t(ldb) * 2, kBK, BN, 1);
+  else
+    rc = make_tmap_2d(&tmB, B, 2, N, K, uint64_t(ldb) * 2, 64, kBK, 1);
+  if (rc) return rc;
+
+  GemmParams p;
+  p.C = C;
+  p.bias = nullptr;
+  p.M = M; p.N = N; p.K = K; p.ldc = ldc;
+  p.tiles_m = (M + kBM - 1) / kBM;
+  p.tiles_n = (N + BN - 1) / BN;
+  p.num_tiles = p.tiles_m * p.tiles_n;
+  p.k_blocks = (K + kBK - 1) / kBK;
+  p.out_fp32 = out_fp32;
+  p.accumulate = accumulate;
+
+  auto kern = gemm_bf16_kernel<BN, A_MN, B_MN>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    STB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        Cfg::kSmemBytes));
+    attr_set = true;
+  }
+  const int grid = p.num_tiles < sm_count() ? p.num_tiles : sm_count();
+  kern<<<grid, kGemmThreads, Cfg::kSmemBytes, stream>>>(tmA, tmB, p);
+  STB_CHECK_LAUNCH();
+  return 0;
+}
+
+static int pick_bn(int M, int N) {
+  if (N <= 128) return 128;
+  const int sms = sm_count();
+  const long tm = (M + kBM - 1) / kBM;
+  const long t256 = tm * ((N + 255) / 256), t128 = tm * ((N + 127) / 128);
+  // cost ~ waves * tile_work ; 256-wide tiles do twice the work per wave
+  const long c256 = ((t256 + sms - 1) / sms) * 2, c128 = (t128 + sms - 1) / sms;
+  return (c128 < c256) ? 128 : 256;
+}
+
+}  // namespace stb
+
+// C ABI ---------------------------------------------------------------------
+// a_mn / b_mn: 0 = operand stored K-major (row-major [rows, K], ld = row stride),
+//              1 = operand stored MN-major (row-major [K, rows]).
+extern "C" int stb_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, int lda,
+                             int ldb, int ldc, int a_mn, int b_mn, int out_fp32, int accumulate,
+                             int force_bn, cudaStream_t stream) {
+  using namespace stb;
+  STB_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: empty problem %d %d %d", M, N, K);
+  STB_REQUIRE((lda % 8) == 0 && (ldb % 8) == 0, "gemm: lda/ldb must be multiples of 8 elements");
+  STB_REQUIRE((reinterpret_cast<uintptr_t>(A) & 15) == 0 && (reinterpret_cast<uintptr_t>(B) & 15) == 0,
+              "gemm: operands must be 16-byte aligned");
+  STB_REQUIRE(!(a_mn && !b_mn), "gemm: (A MN-major, B K-major) is not instantiated");
+  const int bn = force_bn ? force_bn : pick_bn(M, N);
+#define STB_GEMM_CASE(BN_, AMN_, BMN_)                                                       \
+  return launch_gemm<BN_, AMN_, BMN_>(A, B, C, M, N, K, lda, ldb, ldc, out_fp32, accumulate, \
+                                      stream)
+  if (bn == 256) {
+    if (!a_mn && !b_mn) STB_GEMM_CASE(256, false, false);
+    if (!a_mn && b_mn) STB_GEMM_CASE(256, false, true);
+    STB_GEMM_CASE(256, true, true);
+  } else {
+    if (!a_mn && !b_mn) STB_GEMM_CASE(128, false, false);
+    if (!a_mn && b_mn) STB_GEMM_CASE(128, false, true);
+    STB_GEMM_CASE(128, true, true);
+  }
+#undef STB_GEMM_CASE
+}

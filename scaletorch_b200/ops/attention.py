@@ -1,0 +1,201 @@
+"""Causal flash attention with native GQA, and the fused
+``qkv → (QK-norm) → RoPE → attention`` block used by the decoder layers.
+
+Reference: ``flash_attention`` = ``F.scaled_dot_product_attention`` after an explicit GQA
+expansion of K/V (``scaletorch/models/attention_utils.py:130-152``,
+``scaletorch/models/model_qwen3.py:219-238``).  Here K/V are never expanded: the kernel maps
+``Hq/Hkv`` query heads onto each KV head.  Tensors use the token-major ``[B, S, H, D]`` layout the
+QKV GEMM produces, so no transposes are materialised either.
+
+``flash_attention`` returns ``(out, lse)``; ``lse`` (natural-log sum-exp, ``[B, H, S]`` fp32) is what
+ring attention needs to merge partial results (``scaletorch/parallel/context_parallel/
+context_parallel.py:367-424``).
+"""
+from __future__ import annotations
+
+import math
+
+import torch
+import torch.nn.functional as F
+
+from .. import _native as N
+from . import norm as _norm
+
+
+# --------------------------------------------------------------------------- oracle
+def attention_ref(q, k, v, causal=True, scale=None, q_offset: int = 0):
+    """fp32 eager attention. q ``[B,Sq,Hq,D]``, k/v ``[B,Sk,Hkv,D]`` → (out ``[B,Sq,Hq,D]``, lse ``[B,Hq,Sq]``).
+
+    ``q_offset``: global position of q[0] relative to k[0] (for ring / chunked causal masking).
+    """
+    B, Sq, Hq, D = q.shape
+    Sk, Hkv = k.shape[1], k.shape[2]
+    g = Hq // Hkv
+    scale = scale if scale is not None else 1.0 / math.sqrt(D)
+    qf = q.float().permute(0, 2, 1, 3).reshape(B, Hkv, g, Sq, D)
+    kf = k.float().permute(0, 2, 1, 3)
+    vf = v.float().permute(0, 2, 1, 3)
+    s = torch.einsum("bhgqd,bhkd->bhgqk", qf, kf) * scale
+    if causal:
+        qi = torch.arange(Sq, device=q.device)[:, None] + q_offset
+        ki = torch.arange(Sk, device=q.device)[None, :]
+        s = s.masked_fill(ki > qi, float("-inf"))
+    lse = torch.logsumexp(s, dim=-1)
+    p = torch.exp(s - lse.unsqueeze(-1))
+    p = torch.nan_to_num(p, nan=0.0)
+    o = torch.einsum("bhgqk,bhkd->bhgqd", p, vf)
+    out = o.reshape(B, Hq, Sq, D).permute(0, 2, 1, 3).to(q.dtype)
+    return out, lse.reshape(B, Hq, Sq)
+
+
+def native_attention_available() -> bool:
+    lib = N.load()
+    return lib is not None and hasattr(lib, "stb_flash_attn_fwd")
+
+
+def _flash_fwd(q, k, v, causal, scale):
+    """q/k/v: [B,S,H,D] (last dim contiguous, arbitrary token/head strides)."""
+    B, Sq, Hq, D = q.shape
+    Sk, Hkv = k.shape[1], k.shape[2]
+    out = torch.empty((B, Sq, Hq, D), dtype=q.dtype, device=q.device)
+    lse = torch.empty((B, Hq, Sq), dtype=torch.float32, device=q.device)
+    N.call("stb_flash_attn_fwd", q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr(), lse.data_ptr(),
+           B, Sq, Sk, Hq, Hkv, D,
+           q.stride(0), q.stride(1), q.stride(2), k.stride(0), k.stride(1), k.stride(2),
+           v.stride(0), v.stride(1), v.stride(2), float(scale), int(causal), N.stream_ptr())
+    return out, lse
+
+
+def _flash_bwd(do, q, k, v, out, lse, dq, dk, dv, causal, scale):
+    B, Sq, Hq, D = q.shape
+    Sk, Hkv = k.shape[1], k.shape[2]
+    delta = torch.empty((B, Hq, Sq), dtype=torch.float32, device=q.device)
+    dq_acc = torch.zeros((B, Hq, Sq, D), dtype=torch.float32, device=q.device)
+    N.call("stb_flash_attn_bwd", do.data_ptr(), q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr(),
+           lse.data_ptr(), delta.data_ptr(), dq_acc.data_ptr(), dq.data_ptr(), dk.data_ptr(), dv.data_ptr(),
+           B, Sq, Sk, Hq, Hkv, D,
+           q.stride(0), q.stride(1), q.stride(2), k.stride(0), k.stride(1), k.stride(2),
+           v.stride(0), v.stride(1), v.stride(2),
+           dq.stride(0), dq.stride(1), dq.stride(2), dk.stride(0), dk.stride(1), dk.stride(2),
+           dv.stride(0), dv.stride(1), dv.stride(2), float(scale), int(causal), N.stream_ptr())
+
+
+def _sdpa(q, k, v, causal, scale):
+    """Library attention (PyTorch SDPA) -- used only while the native kernel is absent."""
+    g = q.shape[2] // k.shape[2]
+    o = F.scaled_dot_product_attention(q.transpose(1, 2), k.transpose(1, 2), v.transpose(1, 2),
+                                       is_causal=causal, scale=scale, enable_gqa=g > 1)
+    return o.transpose(1, 2)
+
+
+class _FlashAttention(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, q, k, v, causal, scale):
+        out, lse = _flash_fwd(q, k, v, causal, scale)
+        ctx.save_for_backward(q, k, v, out, lse)
+        ctx.cfg = (causal, scale)
+        ctx.mark_non_differentiable(lse)
+        return out, lse
+
+    @staticmethod
+    def backward(ctx, do, _dlse):
+        q, k, v, out, lse = ctx.saved_tensors
+        causal, scale = ctx.cfg
+        dq, dk, dv = torch.empty_like(q), torch.empty_like(k), torch.empty_like(v)
+        _flash_bwd(do.contiguous(), q, k, v, out, lse, dq, dk, dv, causal, scale)
+        return dq, dk, dv, None, None
+
+
+def flash_attention(q, k, v, causal: bool = True, scale: float | None = None):
+    """q ``[B,Sq,Hq,D]``, k/v ``[B,Sk,Hkv,D]`` → ``(out [B,Sq,Hq,D], lse [B,Hq,Sq])``."""
+    scale = scale if scale is not None else 1.0 / math.sqrt(q.shape[-1])
+    if N.use_native(q) and q.dtype == torch.bfloat16:
+        if native_attention_available() and q.shape[-1] == 128:
+            return _FlashAttention.apply(q, k, v, causal, scale)
+        return _sdpa(q, k, v, causal, scale), None
+    return attention_ref(q, k, v, causal, scale)
+
+
+# ------------------------------------------------- fused qkv -> norm/rope -> attention
+class _QKVAttention(torch.autograd.Function):
+    """One autograd node for ``qkv → QK-norm → RoPE → causal GQA attention``.
+
+    The backward writes dQ/dK/dV straight into one packed ``dqkv`` buffer (the attention kernel
+    takes output strides) and runs the norm/RoPE backward in place on its q,k columns, so the
+    gradient of the packed projection is produced without concatenations or zero-fills.
+    """
+
+    @staticmethod
+    def forward(ctx, qkv, wq, wk, cos, sin, B, S, n_q, n_kv, D, pos_offset, eps, causal, scale):
+        T = B * S
+        use_norm = wq is not None
+        nqk = n_q + n_kv
+        qk = torch.empty((T, nqk * D), dtype=qkv.dtype, device=qkv.device)
+        rstd = torch.empty((T * nqk,), dtype=torch.float32, device=qkv.device) if use_norm else None
+        N.call("stb_qknorm_rope_fwd", qkv.data_ptr(), N.ptr(wq), N.ptr(wk), cos.data_ptr(), sin.data_ptr(),
+               None, qk.data_ptr(), N.ptr(rstd), T, S, n_q, n_kv, D, pos_offset, int(use_norm), float(eps),
+               N.stream_ptr())
+        qk4 = qk.view(B, S, nqk, D)
+        q, k = qk4[:, :, :n_q], qk4[:, :, n_q:]
+        v = qkv.view(B, S, n_q + 2 * n_kv, D)[:, :, nqk:]
+        out, lse = _flash_fwd(q, k, v, causal, scale)
+        ctx.save_for_backward(qkv, qk, wq, wk, cos, sin, rstd, out, lse)
+        ctx.cfg = (B, S, n_q, n_kv, D, pos_offset, use_norm, causal, scale)
+        return out.view(B, S, n_q * D)
+
+    @staticmethod
+    def backward(ctx, do):
+        qkv, qk, wq, wk, cos, sin, rstd, out, lse = ctx.saved_tensors
+        B, S, n_q, n_kv, D, pos_offset, use_norm, causal, scale = ctx.cfg
+        T = B * S
+        nqk = n_q + n_kv
+        qk4 = qk.view(B, S, nqk, D)
+        q, k = qk4[:, :, :n_q], qk4[:, :, n_q:]
+        v = qkv.view(B, S, n_q + 2 * n_kv, D)[:, :, nqk:]
+        dqkv = torch.empty_like(qkv)
+        d4 = dqkv.view(B, S, n_q + 2 * n_kv, D)
+        dqk = torch.empty_like(qk)
+        dqk4 = dqk.view(B, S, nqk, D)
+        do4 = do.reshape(B, S, n_q, D)
+        if not do4.is_contiguous():
+            do4 = do4.contiguous()
+        _flash_bwd(do4, q, k, v, out, lse, dqk4[:, :, :n_q], dqk4[:, :, n_q:], d4[:, :, nqk:], causal, scale)
+        dwq = dwk = None
+        if use_norm:
+            dq_dst, _, q_main = _norm._param_grad_out(wq)
+            dk_dst, _, k_main = _norm._param_grad_out(wk)
+            if not (q_main and getattr(wq, "grad_written", False)):
+                dq_dst.zero_()
+            if not (k_main and getattr(wk, "grad_written", False)):
+                dk_dst.zero_()
+        N.call("stb_qknorm_rope_bwd", dqk.data_ptr(), qkv.data_ptr(), N.ptr(wq), N.ptr(wk), cos.data_ptr(),
+               sin.data_ptr(), None, N.ptr(rstd), dqkv.data_ptr(),
+               dq_dst.data_ptr() if use_norm else None, dk_dst.data_ptr() if use_norm else None,
+               T, S, n_q, n_kv, D, pos_offset, int(use_norm), N.stream_ptr())
+        if use_norm:
+            dwq = _norm._finish_param_grad(wq, dq_dst, q_main)
+            dwk = _norm._finish_param_grad(wk, dk_dst, k_main)
+        return (dqkv, dwq, dwk) + (None,) * 11
+
+
+def qkv_attention(qkv, wq, wk, cos, sin, B, S, n_q, n_kv, head_dim, pos_offset=0, eps=1e-6, causal=True,
+                  scale=None, attn_fn=None):
+    """``qkv [B*S, (Hq+2Hkv)*D]`` → attention output ``[B, S, Hq*D]``.
+
+    ``attn_fn(q, k, v, causal, scale) -> out`` overrides the local attention (ring attention under
+    context parallelism); in that case the norm/RoPE and attention run as separate autograd nodes.
+    """
+    scale = scale if scale is not None else 1.0 / math.sqrt(head_dim)
+    if (attn_fn is None and N.use_native(qkv) and qkv.dtype == torch.bfloat16 and head_dim == 128
+            and native_attention_available()):
+        return _QKVAttention.apply(qkv, wq, wk, cos, sin, B, S, n_q, n_kv, head_dim, pos_offset, eps, causal, scale)
+    nqk = n_q + n_kv
+    qk = _norm.qknorm_rope(qkv, wq, wk, cos, sin, n_q, n_kv, head_dim, S, pos_offset, eps)
+    qk4 = qk.view(B, S, nqk, head_dim)
+    q, k = qk4[:, :, :n_q], qk4[:, :, n_q:]
+    v = qkv.view(B, S, n_q + 2 * n_kv, head_dim)[:, :, nqk:]
+    if attn_fn is not None:
+        out = attn_fn(q, k, v, causal, scale)
+    else:
+        out = flash_attention(q, k, v, causal, scale)[0]
+    return out.reshape(B, S, n_q * head_dim)

@@ -1,0 +1,55 @@
+"""Token embedding gather / scatter-add (vocab-shard aware).
+
+Reference: ``Qwen3Embedding`` (``scaletorch/models/model_qwen3.py:90-110``) and the masked
+lookup of ``VocabParallelEmbedding`` (``scaletorch/parallel/tensor_parallel/
+tensor_parallel.py:464-507``): ids outside ``[vocab_start, vocab_start + V_local)`` yield a zero
+row, which the caller sums across TP ranks.
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn.functional as F
+
+from .. import _native as N
+from .norm import _finish_param_grad, _param_grad_out
+
+
+def embedding_ref(ids: torch.Tensor, weight: torch.Tensor, vocab_start: int = 0) -> torch.Tensor:
+    V = weight.shape[0]
+    local = ids - vocab_start
+    mask = (local >= 0) & (local < V)
+    out = F.embedding(local.clamp(0, V - 1), weight)
+    return out * mask.unsqueeze(-1).to(out.dtype)
+
+
+class _Embedding(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, ids, weight, vocab_start):
+        flat = ids.reshape(-1).contiguous()
+        T, H = flat.numel(), weight.shape[1]
+        out = torch.empty((T, H), dtype=weight.dtype, device=weight.device)
+        N.call("stb_embedding_fwd", flat.data_ptr(), weight.data_ptr(), out.data_ptr(), T, H, vocab_start,
+               weight.shape[0], N.stream_ptr())
+        ctx.save_for_backward(flat, weight)
+        ctx.vocab_start = vocab_start
+        return out.view(*ids.shape, H)
+
+    @staticmethod
+    def backward(ctx, dout):
+        flat, weight = ctx.saved_tensors
+        T, H = flat.numel(), weight.shape[1]
+        d2 = dout.reshape(T, H)
+        if not d2.is_contiguous():
+            d2 = d2.contiguous()
+        dst, acc, is_main = _param_grad_out(weight)
+        if not acc:
+            dst.zero_()
+        N.call("stb_embedding_bwd", flat.data_ptr(), d2.data_ptr(), dst.data_ptr(), T, H, ctx.vocab_start,
+               weight.shape[0], N.stream_ptr())
+        return None, _finish_param_grad(weight, dst, is_main), None
+
+
+def embedding(ids: torch.Tensor, weight: torch.Tensor, vocab_start: int = 0) -> torch.Tensor:
+    if N.use_native(weight) and weight.dtype == torch.bfloat16 and weight.shape[1] % 8 == 0:
+        return _Embedding.apply(ids, weight, int(vocab_start))
+    return embedding_ref(ids, weight, vocab_start)

@@ -1,0 +1,234 @@
+"""Numerics of every sm_100a kernel against a plain PyTorch fp32 reference of the same op."""
+import math
+
+import pytest
+import torch
+
+from scaletorch_b200 import _native as N
+from scaletorch_b200 import ops
+
+pytestmark = pytest.mark.gpu
+
+
+def _bf(*shape, scale=1.0, device="cuda"):
+    return (torch.randn(*shape, device=device, dtype=torch.float32) * scale).to(torch.bfloat16)
+
+
+def _rel_err(a, b):
+    a, b = a.float(), b.float()
+    return ((a - b).norm() / (b.norm() + 1e-12)).item()
+
+
+def test_native_library_loaded():
+    assert N.load(required=True) is not None
+    assert N.available()
+
+
+@pytest.mark.parametrize("M,Nn,K", [(128, 128, 64), (256, 256, 128), (512, 384, 1024), (4096, 3072, 1024),
+                                    (300, 200, 136), (1000, 1544, 72)])
+@pytest.mark.parametrize("bn", [0, 128, 256])
+def test_gemm_nt(M, Nn, K, bn):
+    torch.manual_seed(0)
+    a, b = _bf(M, K), _bf(Nn, K)
+    c = ops.gemm(a, b, force_bn=bn)
+    ref = a.float() @ b.float().t()
+    assert _rel_err(c, ref) < 5e-3
+
+
+@pytest.mark.parametrize("M,Nn,K", [(256, 256, 128), (512, 1024, 384), (300, 200, 136), (4096, 1024, 3072)])
+def test_gemm_dgrad_layout(M, Nn, K):
+    """A K-major, B MN-major:  C = A · B  with B given as [K, N]."""
+    torch.manual_seed(1)
+    a, b = _bf(M, K), _bf(K, Nn)
+    c = ops.gemm(a, b, b_mn=True)
+    ref = a.float() @ b.float()
+    assert _rel_err(c, ref) < 5e-3
+
+
+@pytest.mark.parametrize("M,Nn,K", [(256, 256, 128), (1024, 384, 512), (200, 136, 300), (3072, 1024, 4096)])
+def test_gemm_wgrad_layout(M, Nn, K):
+    """A and B MN-major: C = Aᵀ · B with A [K, M], B [K, N]; fp32 output with accumulation."""
+    torch.manual_seed(2)
+    a, b = _bf(K, M), _bf(K, Nn)
+    ref = a.float().t() @ b.float()
+    c = ops.gemm(a, b, a_mn=True, b_mn=True, out_dtype=torch.float32)
+    assert _rel_err(c, ref) < 5e-3
+    ops.gemm(a, b, a_mn=True, b_mn=True, out=c, accumulate=True)
+    assert _rel_err(c, 2 * ref) < 5e-3
+
+
+def test_gemm_strided_views():
+    torch.manual_seed(3)
+    big = _bf(512, 1024)
+    a = big[:, 256:768]  # lda = 1024, K = 512
+    b = _bf(256, 512)
+    out = torch.zeros(512, 512, device="cuda", dtype=torch.bfloat16)
+    ops.gemm(a, b, out=out[:, 128:384])
+    assert _rel_err(out[:, 128:384], a.float() @ b.float().t()) < 5e-3
+    assert out[:, :128].abs().max() == 0 and out[:, 384:].abs().max() == 0
+
+
+def test_linear_autograd():
+    torch.manual_seed(4)
+    x = _bf(4, 96, 256).requires_grad_()
+    w = _bf(384, 256, scale=0.05).requires_grad_()
+    y = ops.linear(x, w)
+    dy = _bf(4, 96, 384)
+    y.backward(dy)
+    xr = x.detach().float().requires_grad_()
+    wr = w.detach().float().requires_grad_()
+    yr = torch.nn.functional.linear(xr, wr)
+    yr.backward(dy.float())
+    assert _rel_err(y, yr) < 5e-3
+    assert _rel_err(x.grad, xr.grad) < 5e-3
+    assert _rel_err(w.grad, wr.grad) < 5e-3
+
+
+def test_linear_main_grad_accumulation():
+    torch.manual_seed(5)
+    x = _bf(256, 128)
+    w = _bf(192, 128, scale=0.05).requires_grad_()
+    w.main_grad = torch.full((192 * 128,), 7.0, device="cuda")  # garbage: first write must overwrite
+    w.grad_written = False
+    for _ in range(2):
+        ops.linear(x, w).backward(torch.ones(256, 192, device="cuda", dtype=torch.bfloat16))
+    assert w.grad is None
+    ref = 2 * torch.ones(256, 192, device="cuda").t() @ x.float()
+    assert _rel_err(w.main_grad.view(192, 128), ref) < 5e-3
+
+
+@pytest.mark.parametrize("H", [128, 1024, 2048, 4096, 5120])
+@pytest.mark.parametrize("with_res", [False, True])
+def test_rmsnorm(H, with_res):
+    torch.manual_seed(6)
+    rows = 333
+    x = _bf(rows, H).requires_grad_()
+    res = _bf(rows, H).requires_grad_() if with_res else None
+    w = (1 + 0.1 * torch.randn(H, device="cuda")).to(torch.bfloat16).requires_grad_()
+    dy, dh = _bf(rows, H), _bf(rows, H)
+    if with_res:
+        h, y = ops.add_rmsnorm(x, res, w, 1e-6)
+        torch.autograd.backward([h, y], [dh, dy])
+    else:
+        y = ops.rmsnorm(x, w, 1e-6)
+        y.backward(dy)
+    xr = x.detach().float().requires_grad_()
+    wr = w.detach().float().requires_grad_()
+    rr = res.detach().float().requires_grad_() if with_res else None
+    hr = xr + rr if with_res else xr
+    yr = wr * (hr * torch.rsqrt(hr.pow(2).mean(-1, keepdim=True) + 1e-6))
+    if with_res:
+        torch.autograd.backward([hr, yr], [dh.float(), dy.float()])
+        assert _rel_err(h, hr) < 5e-3
+        assert _rel_err(res.grad, rr.grad) < 1e-2
+    else:
+        yr.backward(dy.float())
+    assert _rel_err(y, yr) < 1e-2
+    assert _rel_err(x.grad, xr.grad) < 1e-2
+    assert _rel_err(w.grad, wr.grad) < 2e-2
+
+
+@pytest.mark.parametrize("use_norm", [True, False])
+def test_qknorm_rope(use_norm):
+    torch.manual_seed(7)
+    B, S, Hq, Hkv, D = 2, 96, 4, 2, 128
+    T = B * S
+    qkv = _bf(T, (Hq + 2 * Hkv) * D).requires_grad_()
+    wq = (1 + 0.1 * torch.randn(D, device="cuda")).to(torch.bfloat16).requires_grad_() if use_norm else None
+    wk = (1 + 0.1 * torch.randn(D, device="cuda")).to(torch.bfloat16).requires_grad_() if use_norm else None
+    cos, sin = ops.get_cos_sin(256, D, 1e6, device="cuda")
+    out = ops.qknorm_rope(qkv, wq, wk, cos, sin, Hq, Hkv, D, S, pos_offset=3)
+    g = _bf(T, (Hq + Hkv) * D)
+    out.backward(g)
+
+    qr = qkv.detach().float().requires_grad_()
+    wqr = wq.detach().float().requires_grad_() if use_norm else None
+    wkr = wk.detach().float().requires_grad_() if use_norm else None
+    x = qr[:, : (Hq + Hkv) * D].reshape(T, Hq + Hkv, D)
+    if use_norm:
+        w = torch.cat([wqr.expand(Hq, D), wkr.expand(Hkv, D)], 0)
+        x = w * (x * torch.rsqrt(x.pow(2).mean(-1, keepdim=True) + 1e-6))
+    pos = torch.arange(T, device="cuda") % S + 3
+    c, s = cos[pos].unsqueeze(1), sin[pos].unsqueeze(1)
+    ref = (x * c + ops.rotate_half(x) * s).reshape(T, -1)
+    ref.backward(g.float())
+    assert _rel_err(out, ref) < 1e-2
+    assert _rel_err(qkv.grad[:, : (Hq + Hkv) * D], qr.grad[:, : (Hq + Hkv) * D]) < 1e-2
+    assert qkv.grad[:, (Hq + Hkv) * D:].abs().max() == 0
+    if use_norm:
+        assert _rel_err(wq.grad, wqr.grad) < 2e-2
+        assert _rel_err(wk.grad, wkr.grad) < 2e-2
+
+
+def test_swiglu():
+    torch.manual_seed(8)
+    gu = _bf(3, 100, 2 * 768).requires_grad_()
+    y = ops.swiglu(gu)
+    dy = _bf(3, 100, 768)
+    y.backward(dy)
+    gr = gu.detach().float().requires_grad_()
+    yr = ops.swiglu_ref(gr)
+    yr.backward(dy.float())
+    assert _rel_err(y, yr) < 1e-2
+    assert _rel_err(gu.grad, gr.grad) < 1e-2
+
+
+@pytest.mark.parametrize("V", [1000, 151936 // 8])
+def test_linear_cross_entropy(V):
+    torch.manual_seed(9)
+    T, H = 300, 256
+    x = _bf(T, H).requires_grad_()
+    w = _bf(V, H, scale=0.05).requires_grad_()
+    tgt = torch.randint(0, V, (T,), device="cuda")
+    tgt[::17] = -100
+    loss = ops.linear_cross_entropy(x, w, tgt, loss_scale=0.5)
+    (loss * 2.0).backward()
+    xr = x.detach().float().requires_grad_()
+    wr = w.detach().float().requires_grad_()
+    lr = torch.nn.functional.cross_entropy(xr @ wr.t(), tgt, ignore_index=-100) * 0.5
+    (lr * 2.0).backward()
+    assert abs(loss.item() - lr.item()) < 2e-2 * abs(lr.item())
+    assert _rel_err(x.grad, xr.grad) < 3e-2
+    assert _rel_err(w.grad, wr.grad) < 3e-2
+
+
+def test_embedding():
+    torch.manual_seed(10)
+    V, H = 1000, 256
+    w = _bf(V, H).requires_grad_()
+    ids = torch.randint(0, V, (4, 77), device="cuda")
+    out = ops.embedding(ids, w)
+    dy = _bf(4, 77, H)
+    out.backward(dy)
+    wr = w.detach().float().requires_grad_()
+    outr = torch.nn.functional.embedding(ids, wr)
+    outr.backward(dy.float())
+    assert torch.equal(out.float(), outr)
+    assert _rel_err(w.grad, wr.grad) < 1e-2
+    # vocab shard: ids outside [start, start+V) give zero rows
+    out2 = ops.embedding(ids + 500, w, vocab_start=500)
+    assert torch.equal(out2, out)
+    out3 = ops.embedding(ids, w[:500], vocab_start=0)
+    assert (out3[ids >= 500] == 0).all()
+
+
+def test_adamw_and_gradnorm():
+    from scaletorch_b200.ops.optim import fused_adamw_step, grad_clip_coef
+
+    torch.manual_seed(11)
+    n = 1_000_003
+    p = _bf(n)
+    g = torch.randn(n, device="cuda")
+    m = torch.zeros(n, device="cuda")
+    v = torch.zeros(n, device="cuda")
+    pr = p.float().clone().requires_grad_()
+    opt = torch.optim.AdamW([pr], lr=1e-2, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.1)
+    coef, norm = grad_clip_coef(g, max_norm=1.0)
+    assert abs(norm.item() - g.norm().item()) < 1e-3 * g.norm().item()
+    for step in (1, 2):
+        pr.grad = g * min(1.0, 1.0 / (g.norm().item() + 1e-6))
+        opt.step()
+        fused_adamw_step(p, g, m, v, lr=1e-2, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.1, step=step, clip_coef=coef)
+    assert _rel_err(p, pr.detach()) < 1e-2
+    assert _rel_err(m, opt.state[pr]["exp_avg"]) < 1e-3
+    assert _rel_err(v, opt.state[pr]["exp_avg_sq"]) < 1e-3

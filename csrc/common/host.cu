@@ -63,6 +63,16 @@ static EncodeTiledFn get_encode() {
   return fn;
 }
 
+// cuTensorMapEncodeTiled is a pure driver call: it needs a current context, which a thread that has
+// not yet made any runtime call (e.g. an autograd worker on device 0) does not have.
+static void ensure_context() {
+  static thread_local bool done = false;
+  if (!done) {
+    cudaFree(0);
+    done = true;
+  }
+}
+
 static CUtensorMapDataType dtype_of(int elem_bytes) {
   return elem_bytes == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16
                          : (elem_bytes == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32
@@ -71,6 +81,7 @@ static CUtensorMapDataType dtype_of(int elem_bytes) {
 
 int make_tmap_2d(CUtensorMap* out, const void* base, int elem_bytes, uint64_t dim0, uint64_t dim1,
                  uint64_t stride1_bytes, uint32_t box0, uint32_t box1, int swizzle_128b) {
+  ensure_context();
   EncodeTiledFn enc = get_encode();
   STB_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled entry point unavailable");
   cuuint64_t dims[2] = {dim0, dim1};
@@ -91,6 +102,7 @@ int make_tmap_2d(CUtensorMap* out, const void* base, int elem_bytes, uint64_t di
 int make_tmap_3d(CUtensorMap* out, const void* base, int elem_bytes, uint64_t dim0, uint64_t dim1,
                  uint64_t dim2, uint64_t stride1_bytes, uint64_t stride2_bytes, uint32_t box0,
                  uint32_t box1, uint32_t box2, int swizzle_128b) {
+  ensure_context();
   EncodeTiledFn enc = get_encode();
   STB_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled entry point unavailable");
   cuuint64_t dims[3] = {dim0, dim1, dim2};

@@ -14,7 +14,8 @@
 //   warp 0      TMA producer  : cp.async.bulk.tensor -> 128B-swizzled smem ring
 //   warp 1      MMA issuer    : one thread issues tcgen05.mma (128 x BN x 16)
 //   warp 2      TMEM allocator
-//   warps 4..7  epilogue      : tcgen05.ld -> registers -> global (bf16 / fp32 / +=)
+//   warps 4..7  epilogue      : tcgen05.ld -> registers -> swizzled smem -> TMA store
+//                               (TMA reduce-add when accumulating; direct stores if C is unaligned)
 // The accumulator is double-buffered in TMEM so the epilogue of tile i overlaps
 // the main loop of tile i+1.
 #include "common/host.h"
@@ -43,7 +44,9 @@ struct GemmCfg {
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kStages = (BN == 256) ? 4 : 6;
   static constexpr int kTmemCols = 2 * BN;  // two accumulator stages
-  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
+  // epilogue staging: per epilogue warp two 4 KB slots (32 rows x 128 B, 128B-swizzled)
+  static constexpr int kEpiBytes = 4 * 2 * 4096;
+  static constexpr int kSmemBytes = kStages * kStageBytes + kEpiBytes + 1024 /*align*/ + 256 /*barriers*/;
 };
 
 STB_DEVICE void tile_coords(int tile, int tiles_m, int tiles_n, int& m, int& n) {
@@ -57,10 +60,10 @@ STB_DEVICE void tile_coords(int tile, int tiles_m, int tiles_n, int& m, int& n) 
   n = r / gm;
 }
 
-template <int BN, bool A_MN, bool B_MN>
+template <int BN, bool A_MN, bool B_MN, bool EPI_TMA>
 __global__ void __launch_bounds__(kGemmThreads, 1)
     gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                     const GemmParams p) {
+                     const __grid_constant__ CUtensorMap tmC, const GemmParams p) {
   using Cfg = GemmCfg<BN>;
   constexpr int kStages = Cfg::kStages;
 
@@ -69,7 +72,8 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
                                              ~uintptr_t(1023));
   uint8_t* sA = smem;
   uint8_t* sB = smem + kStages * Cfg::kABytes;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kStages * Cfg::kStageBytes);
+  uint8_t* sEpi = smem + kStages * Cfg::kStageBytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kStages * Cfg::kStageBytes + Cfg::kEpiBytes);
   uint64_t* full_bar = bars;
   uint64_t* empty_bar = bars + kStages;
   uint64_t* tmem_full = bars + 2 * kStages;
@@ -82,6 +86,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
+    if (EPI_TMA) tma_prefetch_desc(&tmC);
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < kStages; ++i) {
@@ -179,6 +184,91 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
   } else if (warp >= 4) {
     // ----------------------------------------------------------- epilogue
     const int ew = warp - 4;  // TMEM lane quarter owned by this warp
+    if constexpr (EPI_TMA) {
+      // TMEM -> registers -> 128B-swizzled smem slot -> TMA store (or TMA reduce-add when
+      // accumulating).  Each warp owns 32 rows and two 4 KB slots, so no cross-warp barrier.
+      uint8_t* slots = sEpi + ew * 8192;
+      int slot = 0;
+      int it = 0;
+      const uint32_t sw = uint32_t(lane & 7);
+      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+        int tm, tn;
+        tile_coords(tile, p.tiles_m, p.tiles_n, tm, tn);
+        const int acc = it & 1;
+        const uint32_t acc_phase = (it >> 1) & 1;
+        mbar_wait(&tmem_full[acc], acc_phase);
+        tc_fence_after();
+        const int row0 = tm * kBM + ew * 32;
+        const uint32_t taddr = tmem_base + (uint32_t(ew * 32) << 16) + acc * BN;
+        if (p.out_fp32) {
+#pragma unroll 1
+          for (int c = 0; c < BN / 32; ++c) {
+            uint32_t r[32];
+            tmem_ld_32x32b_x32(taddr + c * 32, r);
+            tmem_ld_wait();
+            if (c == BN / 32 - 1) {  // accumulator fully drained into registers
+              tc_fence_before();
+              mbar_arrive(&tmem_empty[acc]);
+            }
+            if (lane == 0) tma_store_wait_read<1>();
+            __syncwarp();
+            const uint32_t dst = smem_u32(slots + slot * 4096 + lane * 128);
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+              st_shared_v4(dst + ((uint32_t(j) ^ sw) << 4), r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) {
+              if (p.accumulate)
+                tma_reduce_add_2d(&tmC, slots + slot * 4096, tn * BN + c * 32, row0);
+              else
+                tma_store_2d(&tmC, slots + slot * 4096, tn * BN + c * 32, row0);
+              tma_store_commit();
+            }
+            slot ^= 1;
+          }
+        } else {
+#pragma unroll 1
+          for (int c = 0; c < BN / 64; ++c) {
+            uint32_t r0[32], r1[32];
+            tmem_ld_32x32b_x32(taddr + c * 64, r0);
+            tmem_ld_32x32b_x32(taddr + c * 64 + 32, r1);
+            tmem_ld_wait();
+            if (c == BN / 64 - 1) {
+              tc_fence_before();
+              mbar_arrive(&tmem_empty[acc]);
+            }
+            if (lane == 0) tma_store_wait_read<1>();
+            __syncwarp();
+            const uint32_t dst = smem_u32(slots + slot * 4096 + lane * 128);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              st_shared_v4(dst + ((uint32_t(j) ^ sw) << 4),
+                           pack_bf16x2(__uint_as_float(r0[8 * j + 0]), __uint_as_float(r0[8 * j + 1])),
+                           pack_bf16x2(__uint_as_float(r0[8 * j + 2]), __uint_as_float(r0[8 * j + 3])),
+                           pack_bf16x2(__uint_as_float(r0[8 * j + 4]), __uint_as_float(r0[8 * j + 5])),
+                           pack_bf16x2(__uint_as_float(r0[8 * j + 6]), __uint_as_float(r0[8 * j + 7])));
+              st_shared_v4(dst + ((uint32_t(j + 4) ^ sw) << 4),
+                           pack_bf16x2(__uint_as_float(r1[8 * j + 0]), __uint_as_float(r1[8 * j + 1])),
+                           pack_bf16x2(__uint_as_float(r1[8 * j + 2]), __uint_as_float(r1[8 * j + 3])),
+                           pack_bf16x2(__uint_as_float(r1[8 * j + 4]), __uint_as_float(r1[8 * j + 5])),
+                           pack_bf16x2(__uint_as_float(r1[8 * j + 6]), __uint_as_float(r1[8 * j + 7])));
+            }
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) {
+              if (p.accumulate)
+                tma_reduce_add_2d(&tmC, slots + slot * 4096, tn * BN + c * 64, row0);
+              else
+                tma_store_2d(&tmC, slots + slot * 4096, tn * BN + c * 64, row0);
+              tma_store_commit();
+            }
+            slot ^= 1;
+          }
+        }
+      }
+      if (lane == 0) tma_store_wait<0>();
+    } else {
     int it = 0;
     for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
       int tm, tn;
@@ -258,6 +348,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
       tc_fence_before();
       mbar_arrive(&tmem_empty[acc]);
     }
+    }
   }
 
   tc_fence_before();
@@ -265,7 +356,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
   if (warp == 2) tmem_dealloc(tmem_base, Cfg::kTmemCols);
 }
 
-template <int BN, bool A_MN, bool B_MN>
+template <int BN, bool A_MN, bool B_MN, bool EPI_TMA>
 static int launch_gemm(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb,
                        int ldc, int out_fp32, int accumulate, cudaStream_t stream) {
   using Cfg = GemmCfg<BN>;
@@ -281,6 +372,14 @@ static int launch_gemm(const void* A, const void* B, void* C, int M, int N, int 
   else
     rc = make_tmap_2d(&tmB, B, 2, N, K, uint64_t(ldb) * 2, 64, kBK, 1);
   if (rc) return rc;
+  CUtensorMap tmC = tmA;  // placeholder when the direct-store epilogue is used
+  if (EPI_TMA) {
+    if (out_fp32)
+      rc = make_tmap_2d(&tmC, C, 4, N, M, uint64_t(ldc) * 4, 32, 32, 1);
+    else
+      rc = make_tmap_2d(&tmC, C, 2, N, M, uint64_t(ldc) * 2, 64, 32, 1);
+    if (rc) return rc;
+  }
 
   GemmParams p;
   p.C = C;
@@ -293,7 +392,7 @@ static int launch_gemm(const void* A, const void* B, void* C, int M, int N, int 
   p.out_fp32 = out_fp32;
   p.accumulate = accumulate;
 
-  auto kern = gemm_bf16_kernel<BN, A_MN, B_MN>;
+  auto kern = gemm_bf16_kernel<BN, A_MN, B_MN, EPI_TMA>;
   static bool attr_set = false;
   if (!attr_set) {
     STB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -301,7 +400,7 @@ static int launch_gemm(const void* A, const void* B, void* C, int M, int N, int 
     attr_set = true;
   }
   const int grid = p.num_tiles < sm_count() ? p.num_tiles : sm_count();
-  kern<<<grid, kGemmThreads, Cfg::kSmemBytes, stream>>>(tmA, tmB, p);
+  kern<<<grid, kGemmThreads, Cfg::kSmemBytes, stream>>>(tmA, tmB, tmC, p);
   STB_CHECK_LAUNCH();
   return 0;
 }
@@ -331,9 +430,14 @@ extern "C" int stb_gemm_bf16(const void* A, const void* B, void* C, int M, int N
               "gemm: operands must be 16-byte aligned");
   STB_REQUIRE(!(a_mn && !b_mn), "gemm: (A MN-major, B K-major) is not instantiated");
   const int bn = force_bn ? force_bn : pick_bn(M, N);
-#define STB_GEMM_CASE(BN_, AMN_, BMN_)                                                       \
-  return launch_gemm<BN_, AMN_, BMN_>(A, B, C, M, N, K, lda, ldb, ldc, out_fp32, accumulate, \
-                                      stream)
+  // TMA-store epilogue needs a 16-byte aligned C with a 16-byte multiple row pitch
+  const int celt = out_fp32 ? 4 : 2;
+  const bool epi_tma = ((reinterpret_cast<uintptr_t>(C) & 15) == 0) && ((size_t(ldc) * celt) % 16 == 0);
+#define STB_GEMM_CASE(BN_, AMN_, BMN_)                                                             \
+  return epi_tma ? launch_gemm<BN_, AMN_, BMN_, true>(A, B, C, M, N, K, lda, ldb, ldc, out_fp32,   \
+                                                      accumulate, stream)                          \
+                 : launch_gemm<BN_, AMN_, BMN_, false>(A, B, C, M, N, K, lda, ldb, ldc, out_fp32,  \
+                                                       accumulate, stream)
   if (bn == 256) {
     if (!a_mn && !b_mn) STB_GEMM_CASE(256, false, false);
     if (!a_mn && b_mn) STB_GEMM_CASE(256, false, true);

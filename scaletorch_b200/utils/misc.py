@@ -1,0 +1,119 @@
+"""Miscellaneous helpers (reference: ``scaletorch/utils/misc.py:51-249``)."""
+from __future__ import annotations
+
+import fcntl
+import os
+import random
+from typing import Any
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from ..env import ENV_PRINT_LOCK
+from .device import get_theoretical_flops, manual_seed_all
+
+
+def rank_print(*args: Any, is_print_rank: bool = True, **kwargs: Any) -> None:
+    """``print`` serialised across processes of a node with an ``flock`` (reference ``misc.py:51-85``)."""
+    if not is_print_rank:
+        return
+    lock_path = os.environ.get(ENV_PRINT_LOCK, "/tmp/scaletorch_b200_print.lock")
+    try:
+        with open(lock_path, "a") as fh:
+            fcntl.flock(fh, fcntl.LOCK_EX)
+            try:
+                print(*args, **kwargs, flush=True)
+            finally:
+                fcntl.flock(fh, fcntl.LOCK_UN)
+    except OSError:
+        print(*args, **kwargs, flush=True)
+
+
+def set_all_seed(seed: int, deterministic: bool = False, rank_offset: int = 0) -> None:
+    """Seeds python / numpy / torch.  ``rank_offset`` lets model-parallel shards initialise
+    differently (the reference seeds every rank identically)."""
+    seed = int(seed) + int(rank_offset)
+    random.seed(seed)
+    np.random.seed(seed % (2**32))
+    manual_seed_all(seed)
+    if deterministic:
+        torch.backends.cudnn.deterministic = True
+        torch.backends.cudnn.benchmark = False
+
+
+def to_readable_format(num: int | float, precision: int = 2) -> str:
+    n = float(num)
+    for unit, div in (("T", 1e12), ("B", 1e9), ("M", 1e6), ("K", 1e3)):
+        if abs(n) >= div:
+            return f"{n / div:.{precision}f}{unit}"
+    return f"{n:.{precision}f}"
+
+
+def flops_per_token(num_params: float, num_layers: int, num_heads: int, head_dim: int, seq_len: int) -> float:
+    """Training FLOPs per token ``6N + 12·L·heads·head_dim·S`` (reference ``misc.py:171``)."""
+    return 6.0 * num_params + 12.0 * num_layers * num_heads * head_dim * seq_len
+
+
+def get_mfu(tokens_per_second: float, num_params: float, model_config: Any, theoretical_flops: float | None = None,
+            seq_len: int | None = None) -> float:
+    """Model FLOPs utilisation in percent for *one device's* tokens/s (reference ``misc.py:136-174``)."""
+    L = model_config.num_hidden_layers
+    heads = model_config.num_attention_heads
+    hd = getattr(model_config, "head_dim", None) or model_config.hidden_size // heads
+    S = seq_len if seq_len is not None else getattr(model_config, "max_position_embeddings", 2048)
+    peak = theoretical_flops or get_theoretical_flops()
+    return tokens_per_second * flops_per_token(num_params, L, heads, hd, S) / peak * 100.0
+
+
+_TP_SHARDED_KEYS = ("q_proj", "k_proj", "v_proj", "qkv_proj", "out_proj", "o_proj", "gate_proj", "up_proj",
+                    "gate_up_proj", "down_proj", "embedding", "final_proj")
+
+
+def get_num_params(model: torch.nn.Module) -> int:
+    """Global parameter count: TP-sharded tensors × tp, expert tensors × ep, summed over PP stages
+    (reference ``misc.py:177-207``)."""
+    from ..parallel.process_group import process_group_manager as pgm
+
+    tp = pgm.tp_world_size if pgm else 1
+    ep = pgm.ep_world_size if pgm else 1
+    seen: set[int] = set()
+    total = 0
+    for name, p in model.named_parameters():
+        if id(p) in seen:
+            continue
+        seen.add(id(p))
+        n = p.numel()
+        if ".experts." in name:
+            n *= ep
+        elif any(k in name for k in _TP_SHARDED_KEYS) and "norm" not in name and "router" not in name:
+            n *= tp
+        total += n
+    if pgm and pgm.pp_world_size > 1:
+        t = torch.tensor([total], dtype=torch.int64, device=next(model.parameters()).device)
+        if t.device.type == "meta":
+            t = torch.tensor([total], dtype=torch.int64)
+        dist.all_reduce(t, group=pgm.pp_group)
+        total = int(t.item())
+    return total
+
+
+def assert_no_meta_tensors(model: torch.nn.Module) -> None:
+    bad = [n for n, p in model.named_parameters() if p.device.type == "meta"]
+    bad += [n for n, b in model.named_buffers() if b.device.type == "meta"]
+    if bad:
+        raise RuntimeError(f"tensors still on the meta device: {bad[:8]}{'...' if len(bad) > 8 else ''}")
+
+
+def average_loss_across_dp_cp_ranks(loss: float | torch.Tensor | None, device: torch.device) -> float:
+    """Mean of the step loss over the CP×DP(×EP) group on the last PP stage (reference ``misc.py:229-249``)."""
+    from ..parallel.process_group import process_group_manager as pgm
+
+    if isinstance(loss, torch.Tensor):
+        t = loss.detach().to(device=device, dtype=torch.float32).reshape(1).clone()
+    else:
+        t = torch.tensor([0.0 if loss is None else float(loss)], dtype=torch.float32, device=device)
+    if pgm and pgm.pp_is_last_stage and pgm.grad_sync_world_size > 1:
+        dist.all_reduce(t, group=pgm.grad_sync_group)
+        t /= pgm.grad_sync_world_size
+    return float(t.item())

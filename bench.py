@@ -1,0 +1,264 @@
+#!/usr/bin/env python
+"""Flagship benchmark: Qwen3-0.6B, DP over N GPUs, bf16, seq 2048, micro-batch 2 per GPU.
+
+    python bench.py --gpus 1 --steps 10 --warmup 3
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
+        bench.py --gpus N --steps K --warmup W
+    python bench.py --impl reference ...      # the unmodified reference from baseline/_ref
+
+Prints ONE JSON line on rank 0 (see README "Benchmark contract").  ``value`` is whole-job tokens/s for full
+optimiser steps (forward + backward + gradient all-reduce + clip + AdamW), device-timed with CUDA events
+between barriers, max over ranks.  ``e2e`` is the same metric through the public training API including,
+every step, the pinned-host → device copy of that step's token batch and a device → host read of the loss.
+Synthetic tokens, random-init weights (no network on the box).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+BASELINE_TOK_S_PER_DEVICE = {  # BASELINE.md §2 (Ascend 910B, README.md:48) -- context, other hardware
+    "Qwen3-0.6B": 16422.0,
+}
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--model", default="Qwen3-0.6B")
+    ap.add_argument("--micro_batch_size", type=int, default=2)
+    ap.add_argument("--seq_len", type=int, default=2048)
+    ap.add_argument("--grad_accum", type=int, default=1)
+    ap.add_argument("--tp", type=int, default=1)
+    ap.add_argument("--cp", type=int, default=1)
+    ap.add_argument("--pp", type=int, default=1)
+    ap.add_argument("--ep", type=int, default=1)
+    ap.add_argument("--sequence_parallel", action="store_true")
+    ap.add_argument("--gradient_checkpointing", action="store_true")
+    ap.add_argument("--skip_e2e", action="store_true")
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """Samples SM clocks and throttle reasons with nvidia-smi while the timed region runs."""
+
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.rows, self._stop, self._t = index, [], threading.Event(), None
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                parts = [p.strip() for p in out.strip().split(",")]
+                if len(parts) >= 7:
+                    self.rows.append(parts)
+            except Exception:
+                pass
+            self._stop.wait(0.2)
+
+    def start(self):
+        self._t = threading.Thread(target=self._run, daemon=True)
+        self._t.start()
+
+    def stop(self) -> dict:
+        self._stop.set()
+        if self._t is not None:
+            self._t.join(timeout=6)
+        sm = [float(r[0]) for r in self.rows if r[0].replace(".", "", 1).isdigit()]
+        mx = [float(r[1]) for r in self.rows if r[1].replace(".", "", 1).isdigit()]
+        reasons = set()
+        for r in self.rows:
+            for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(self.rows)}
+
+
+def dist_env():
+    return int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+
+
+def timed_region(torch, dist, world, fn, steps):
+    """barrier+sync, K × fn() between CUDA events, barrier+sync; returns ms (max over ranks)."""
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    ms = torch.tensor([e0.elapsed_time(e1)], device="cuda")
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    return float(ms.item())
+
+
+def build_config_dict(args, world):
+    dp = world // (args.tp * args.cp * args.pp * args.ep)
+    par = "".join(f"{k}{v}" for k, v in (("tp", args.tp), ("cp", args.cp), ("pp", args.pp), ("ep", args.ep)) if v > 1)
+    par = (par + f"dp{dp}") if par else f"dp{dp}"
+    replicas = dp * args.ep
+    return dp, {
+        "model": args.model, "global_batch": replicas * args.micro_batch_size * args.grad_accum, "seq_len": args.seq_len,
+        "micro_batch_size": args.micro_batch_size, "grad_accum": args.grad_accum, "parallelism": par,
+        "sequence_parallel": bool(args.sequence_parallel), "gradient_checkpointing": bool(args.gradient_checkpointing),
+        "optimizer": "adamw + global-norm clip 1.0",
+        "l2_policy": "inputs larger than L2: every step streams >1 GB of weights/activations (126 MB L2); no explicit flush",
+    }
+
+
+# ----------------------------------------------------------------------------------------- ours
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    sys.path.insert(0, ROOT)
+    from scaletorch_b200 import _native
+    from scaletorch_b200.data import MicroBatchDataLoader
+    from scaletorch_b200.trainer import (ScaleTorchArguments, create_model, create_optimizer,
+                                         initialize_distributed_training, train_step)
+    from scaletorch_b200.utils.misc import get_mfu, get_num_params
+
+    rank, local_rank, world = dist_env()
+    if world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run for N>1")
+    dp, cfgd = build_config_dict(args, world)
+    cfg = ScaleTorchArguments(
+        model_name_or_path=args.model, micro_batch_size=args.micro_batch_size, sequence_length=args.seq_len,
+        gradient_accumulation_steps=args.grad_accum, tensor_parallel_size=args.tp, context_parallel_size=args.cp,
+        pipeline_parallel_size=args.pp, expert_parallel_size=args.ep, data_parallel_size=dp,
+        sequence_parallel=args.sequence_parallel, gradient_checkpointing=args.gradient_checkpointing,
+        synthetic_data=True, dtype="bfloat16", learning_rate=3e-4, max_grad_norm=1.0, seed=1)
+    _, _, _, device = initialize_distributed_training(cfg)
+    _native.load(required=True)
+    model, model_config = create_model(cfg, torch.bfloat16, device)
+    model.train()
+    optimizer = create_optimizer(model, cfg, device)
+    num_params = get_num_params(model)
+    loader = MicroBatchDataLoader(args.micro_batch_size, args.seq_len, gradient_accumulation_steps=args.grad_accum,
+                                  synthetic=True, vocab_size=model_config.vocab_size, seed=1 + rank, pin_memory=True,
+                                  num_samples=max(4096, (args.steps + args.warmup + 2) * 4 * args.micro_batch_size * world))
+
+    class DeviceBatches:
+        """Pre-staged device-resident batches for the device-timed region (a fresh batch every step)."""
+
+        def __init__(self, n):
+            self.b = []
+            for _ in range(n):
+                x = next(loader)
+                self.b.append({k: (v.to(device) if torch.is_tensor(v) else v) for k, v in x.items()})
+            self.i = 0
+
+        def __next__(self):
+            x = self.b[self.i % len(self.b)]
+            self.i += 1
+            return x
+
+    def step_with(src):
+        optimizer.zero_grad()
+        if hasattr(model, "reset"):
+            model.reset()
+        loss = train_step(model, src, device, torch.bfloat16, args.grad_accum, args.gradient_checkpointing)
+        optimizer.step()
+        return loss
+
+    staged = DeviceBatches((args.steps + args.warmup) * args.grad_accum)
+    for _ in range(args.warmup):
+        step_with(staged)
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    l0 = _native.launch_count
+    ms = timed_region(torch, dist, world, lambda: step_with(staged), args.steps)
+    launches = _native.launch_count - l0
+    clocks = sampler.stop() if rank == 0 else {}
+
+    # end-to-end: public API, per-step pinned H2D of the batch + D2H read of the loss
+    e2e = None
+    if not args.skip_e2e:
+        losses = []
+
+        def e2e_step():
+            losses.append(float(step_with(loader).item()))
+
+        e2e_step()
+        ms_e2e = timed_region(torch, dist, world, e2e_step, args.steps)
+        tokens = cfgd["global_batch"] * args.seq_len
+        per_rank_tokens = args.micro_batch_size * args.grad_accum * (args.seq_len // args.cp)
+        e2e = {"value": tokens * args.steps / (ms_e2e / 1e3), "unit": "tokens/s", "ms_per_step": ms_e2e / args.steps,
+               "h2d_bytes_per_step": per_rank_tokens * 8 * 3, "d2h_bytes_per_step": 4, "last_loss": losses[-1]}
+
+    if rank == 0:
+        tokens = cfgd["global_batch"] * args.seq_len
+        value = tokens * args.steps / (ms / 1e3)
+        base = BASELINE_TOK_S_PER_DEVICE.get(args.model)
+        out = {
+            "metric": "tokens/s (whole job; tokens/s/GPU = value / n_gpus) + MFU", "value": value, "unit": "tokens/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": (value / (base * world)) if base else None,
+            "dtype": "bf16", "data": "synthetic tokens, random-init weights", "impl": "ours", "config": cfgd,
+            "tokens_per_s_per_gpu": value / world,
+            "mfu_pct_of_nominal_2.25PF": get_mfu(value / world, num_params, model_config, 2.25e15, args.seq_len),
+            "num_params": num_params, "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
+            "native_lib": str(_native.lib_path()),
+        }
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        if peaks.get("bf16_tflops_sustained"):
+            out["mfu_pct_of_measured_sustained"] = get_mfu(value / world, num_params, model_config,
+                                                           peaks["bf16_tflops_sustained"] * 1e12, args.seq_len)
+        print(json.dumps(out), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+# ------------------------------------------------------------------------------------ reference
+def run_reference(args):
+    ref_dir = os.path.join(ROOT, "baseline", "_ref")
+    if not os.path.isdir(os.path.join(ref_dir, "scaletorch")):
+        print(json.dumps({"impl": "reference", "unavailable": "baseline/_ref/scaletorch not installed (pip --target baseline/_ref /root/reference)"}))
+        return
+    sys.path.insert(0, os.path.join(ROOT, "baseline"))  # run_reference.py + the colorama stand-in
+    try:
+        import run_reference
+
+        run_reference.main(args, ROOT, ref_dir, ClockSampler, timed_region, build_config_dict, dist_env,
+                           BASELINE_TOK_S_PER_DEVICE)
+    except Exception as e:  # the reference has known defects at this snapshot
+        import traceback
+
+        traceback.print_exc()
+        rank = int(os.environ.get("RANK", 0))
+        if rank == 0:
+            print(json.dumps({"impl": "reference", "unavailable": f"{type(e).__name__}: {str(e)[:300]}"}))
+
+
+if __name__ == "__main__":
+    a = parse_args()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)

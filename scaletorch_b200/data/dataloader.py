@@ -1,0 +1,114 @@
+"""``MicroBatchDataLoader``: micro-batches with CP slicing, DP sharding and host-side prefetch.
+
+Reference: ``scaletorch/data/dataloader.py:35-292``.  Same constructor vocabulary and the same batch dict
+(``input_ids``, ``target_ids``, ``position_ids``, ``hidden_states``); iteration restarts with
+``set_epoch`` at exhaustion.  Differences: the sampler is keyed on ``pgm.data_rank`` so EP ranks read
+distinct samples unless ``ep_replicate_data``; batches are assembled in *pinned* host
+memory and copied with ``non_blocking=True``; a synthetic token source (random ids of the configured
+shape, regenerated every step on the host) serves the benchmarks on boxes without datasets.
+"""
+from __future__ import annotations
+
+from typing import Any
+
+import torch
+from torch.utils.data import DataLoader, DistributedSampler
+
+from ..parallel.process_group import process_group_manager as pgm
+
+
+class SyntheticTokens(torch.utils.data.Dataset):
+    """``num_samples`` random sequences of ``sequence_length + 1`` ids (deterministic per index)."""
+
+    def __init__(self, vocab_size: int, sequence_length: int, num_samples: int = 1 << 20, seed: int = 0):
+        self.vocab_size, self.sequence_length, self.num_samples, self.seed = vocab_size, sequence_length, num_samples, seed
+
+    def __len__(self) -> int:
+        return self.num_samples
+
+    def __getitem__(self, idx: int):
+        g = torch.Generator().manual_seed(self.seed * 1_000_003 + idx)
+        return {"input_ids": torch.randint(0, self.vocab_size, (self.sequence_length + 1,), generator=g)}
+
+
+class MicroBatchDataLoader(DataLoader):
+    def __init__(self, micro_batch_size: int, sequence_length: int, dataset_name: str | None = None,
+                 tokenizer_name_or_path: str | None = None, gradient_accumulation_steps: int = 1, device=None,
+                 num_workers: int = 0, num_proc: int = 1, num_samples: int | None = None, split: str = "train",
+                 subset_name: str | None = None, pin_memory: bool = True, shuffle: bool = False, seed: int = 0,
+                 synthetic: bool = False, vocab_size: int | None = None, dataset=None, tokenizer=None,
+                 text_column_name: str = "text", strategy: str = "concat_chunk"):
+        self.micro_batch_size = micro_batch_size
+        self.sequence_length = sequence_length
+        self.gradient_accumulation_steps = gradient_accumulation_steps
+        self.cp_world_size = pgm.cp_world_size if pgm else 1
+        self.cp_rank = pgm.cp_rank if pgm else 0
+        self.data_world_size = pgm.data_world_size if pgm else 1
+        self.data_rank = pgm.data_rank if pgm else 0
+        if sequence_length % self.cp_world_size != 0:
+            raise ValueError(f"sequence_length ({sequence_length}) must be divisible by cp size ({self.cp_world_size})")
+        self.sequence_length_per_rank = sequence_length // self.cp_world_size
+        self.global_batch_size = micro_batch_size * gradient_accumulation_steps * self.data_world_size
+        if dataset is None:
+            if synthetic:
+                if vocab_size is None:
+                    raise ValueError("synthetic data needs vocab_size")
+                dataset = SyntheticTokens(vocab_size, sequence_length, num_samples or (1 << 20), seed)
+            else:
+                from .dataset import DatasetProcessor
+
+                proc = DatasetProcessor(tokenizer_name_or_path, tokenizer)
+                raw = proc.load_dataset(dataset_name, split, subset_name, num_samples)
+                dataset = proc.tokenize_dataset(raw, text_column_name, sequence_length, num_proc, strategy)
+        self.tokenized_dataset = dataset
+        if len(dataset) < self.data_world_size * micro_batch_size:
+            raise ValueError(f"dataset has {len(dataset)} samples; need at least {self.data_world_size * micro_batch_size}")
+        self.sampler_ = DistributedSampler(dataset, num_replicas=self.data_world_size, rank=self.data_rank,
+                                           shuffle=shuffle, seed=seed, drop_last=True)
+        use_pin = bool(pin_memory) and torch.cuda.is_available()
+        super().__init__(dataset, batch_size=micro_batch_size, collate_fn=self.collate_batch, pin_memory=use_pin,
+                         num_workers=num_workers, sampler=self.sampler_, shuffle=False, drop_last=True,
+                         persistent_workers=num_workers > 0, prefetch_factor=2 if num_workers > 0 else None)
+        self._iterator = None
+        self._epoch = 0
+        self._prefetched = None
+        self.batches_served = 0
+
+    def collate_batch(self, batch: list[dict[str, Any]]) -> dict[str, Any]:
+        """Stack → CP-slice ``[cp_rank·S/cp, +S/cp)`` → shifted targets and absolute positions."""
+        ids = torch.stack([torch.as_tensor(b["input_ids"], dtype=torch.long) for b in batch])  # [mbs, S+1]
+        lo = self.cp_rank * self.sequence_length_per_rank
+        hi = lo + self.sequence_length_per_rank
+        input_ids = ids[:, lo:hi].contiguous()
+        target_ids = ids[:, lo + 1:hi + 1].contiguous()
+        position_ids = torch.arange(lo, hi, dtype=torch.long).unsqueeze(0).expand(ids.shape[0], -1).contiguous()
+        return {"input_ids": input_ids, "target_ids": target_ids, "position_ids": position_ids, "hidden_states": None}
+
+    def __iter__(self):
+        if self._iterator is None:
+            self.sampler_.set_epoch(self._epoch)
+            self._iterator = super().__iter__()
+        return self
+
+    def _next_raw(self):
+        if self._iterator is None:
+            self.__iter__()
+        try:
+            return next(self._iterator)
+        except StopIteration:
+            self._epoch += 1
+            self.sampler_.set_epoch(self._epoch)
+            self._iterator = super().__iter__()
+            return next(self._iterator)
+
+    def __next__(self):
+        """One-batch software prefetch: the batch returned now was assembled during the previous step."""
+        if self._prefetched is None:
+            self._prefetched = self._next_raw()
+        out = self._prefetched
+        self._prefetched = self._next_raw()
+        self.batches_served += 1
+        return out
+
+    def state_dict(self) -> dict:
+        return {"epoch": self._epoch, "batches_served": self.batches_served}

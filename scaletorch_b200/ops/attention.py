@@ -199,3 +199,49 @@ def qkv_attention(qkv, wq, wk, cos, sin, B, S, n_q, n_kv, head_dim, pos_offset=0
     else:
         out = flash_attention(q, k, v, causal, scale)[0]
     return out.reshape(B, S, n_q * head_dim)
+
+
+# ------------------------------------------------------- block-level API (ring attention)
+def attention_block_bwd_ref(do, q, k, v, out, lse, causal, scale, q_offset: int = 0):
+    """fp32 block backward given the *global* ``out`` / ``lse`` of the query rows (oracle).
+
+    Returns ``(dq, dk, dv)`` contributions of this K/V block: ``P = exp(S - lse)``,
+    ``dS = P ∘ (dO·Vᵀ − rowsum(dO ∘ O))``.
+    """
+    B, Sq, Hq, D = q.shape
+    Sk, Hkv = k.shape[1], k.shape[2]
+    g = Hq // Hkv
+    qf = q.float().permute(0, 2, 1, 3).reshape(B, Hkv, g, Sq, D)
+    kf = k.float().permute(0, 2, 1, 3)
+    vf = v.float().permute(0, 2, 1, 3)
+    dof = do.float().permute(0, 2, 1, 3).reshape(B, Hkv, g, Sq, D)
+    of = out.float().permute(0, 2, 1, 3).reshape(B, Hkv, g, Sq, D)
+    s = torch.einsum("bhgqd,bhkd->bhgqk", qf, kf) * scale
+    if causal:
+        qi = torch.arange(Sq, device=q.device)[:, None] + q_offset
+        ki = torch.arange(Sk, device=q.device)[None, :]
+        s = s.masked_fill(ki > qi, float("-inf"))
+    p = torch.exp(s - lse.reshape(B, Hkv, g, Sq, 1))
+    delta = (dof * of).sum(-1, keepdim=True)
+    dp = torch.einsum("bhgqd,bhkd->bhgqk", dof, vf)
+    ds = p * (dp - delta) * scale
+    dq = torch.einsum("bhgqk,bhkd->bhgqd", ds, kf).reshape(B, Hq, Sq, D).permute(0, 2, 1, 3)
+    dk = torch.einsum("bhgqk,bhgqd->bhkd", ds, qf).permute(0, 2, 1, 3)
+    dv = torch.einsum("bhgqk,bhgqd->bhkd", p, dof).permute(0, 2, 1, 3)
+    return dq.to(q.dtype), dk.to(k.dtype), dv.to(v.dtype)
+
+
+def attention_block_fwd(q, k, v, causal, scale):
+    """(out, lse) of one K/V block -- native flash kernel on CUDA, oracle elsewhere."""
+    if N.use_native(q) and q.dtype == torch.bfloat16 and native_attention_available() and q.shape[-1] == 128:
+        return _flash_fwd(q, k, v, causal, scale)
+    return attention_ref(q, k, v, causal, scale)
+
+
+def attention_block_bwd(do, q, k, v, out, lse, causal, scale):
+    """(dq, dk, dv) of one K/V block given the global out / lse."""
+    if N.use_native(q) and q.dtype == torch.bfloat16 and native_attention_available() and q.shape[-1] == 128:
+        dq, dk, dv = torch.empty_like(q), torch.empty_like(k), torch.empty_like(v)
+        _flash_bwd(do.contiguous(), q, k, v, out, lse, dq, dk, dv, causal, scale)
+        return dq, dk, dv
+    return attention_block_bwd_ref(do, q, k, v, out, lse, causal, scale)

@@ -22,6 +22,24 @@ def embedding_ref(ids: torch.Tensor, weight: torch.Tensor, vocab_start: int = 0)
     return out * mask.unsqueeze(-1).to(out.dtype)
 
 
+def embedding_backward(flat_ids: torch.Tensor, dout2d: torch.Tensor, weight: torch.Tensor, vocab_start: int = 0):
+    """dW[ids - vocab_start] += dout.  Writes into ``weight.main_grad`` when present (returns None)."""
+    T, H = flat_ids.numel(), weight.shape[1]
+    if N.use_native(weight) and weight.dtype == torch.bfloat16 and H % 8 == 0:
+        dst, acc, is_main = _param_grad_out(weight)
+        if not acc:
+            dst.zero_()
+        N.call("stb_embedding_bwd", flat_ids.data_ptr(), dout2d.data_ptr(), dst.data_ptr(), T, H, vocab_start,
+               weight.shape[0], N.stream_ptr())
+        return _finish_param_grad(weight, dst, is_main)
+    V = weight.shape[0]
+    local = flat_ids - vocab_start
+    mask = (local >= 0) & (local < V)
+    grad = torch.zeros(weight.shape, dtype=torch.float32, device=weight.device)
+    grad.index_add_(0, local.clamp(0, V - 1), dout2d.float() * mask.unsqueeze(-1))
+    return grad.to(weight.dtype)
+
+
 class _Embedding(torch.autograd.Function):
     @staticmethod
     def forward(ctx, ids, weight, vocab_start):
@@ -41,12 +59,7 @@ class _Embedding(torch.autograd.Function):
         d2 = dout.reshape(T, H)
         if not d2.is_contiguous():
             d2 = d2.contiguous()
-        dst, acc, is_main = _param_grad_out(weight)
-        if not acc:
-            dst.zero_()
-        N.call("stb_embedding_bwd", flat.data_ptr(), d2.data_ptr(), dst.data_ptr(), T, H, ctx.vocab_start,
-               weight.shape[0], N.stream_ptr())
-        return None, _finish_param_grad(weight, dst, is_main), None
+        return None, embedding_backward(flat, d2, weight, ctx.vocab_start), None
 
 
 def embedding(ids: torch.Tensor, weight: torch.Tensor, vocab_start: int = 0) -> torch.Tensor:

@@ -57,8 +57,8 @@ def rotate_half(x: torch.Tensor) -> torch.Tensor:
 def get_cos_sin(seq_len: int, head_dim: int, base: float = 500000.0, device="cpu") -> tuple[torch.Tensor, torch.Tensor]:
     """fp32 ``[seq_len, head_dim]`` tables, halves duplicated (rotate-half convention)."""
     assert head_dim % 2 == 0
-    inv = 1.0 / (base ** (torch.arange(0, head_dim, 2, dtype=torch.float64) / head_dim))
-    pos = torch.arange(seq_len, dtype=torch.float64)
+    inv = 1.0 / (base ** (torch.arange(0, head_dim, 2, dtype=torch.float64, device="cpu") / head_dim))
+    pos = torch.arange(seq_len, dtype=torch.float64, device="cpu")
     ang = torch.outer(pos, inv)
     cos = torch.cos(ang).repeat(1, 2).float().to(device)
     sin = torch.sin(ang).repeat(1, 2).float().to(device)

@@ -1,0 +1,132 @@
+"""Data parallel wrappers (reference: ``scaletorch/parallel/data_parallel/data_parallel.py:22-388``).
+
+``DataParallelBucket`` overlaps bucketed gradient all-reduces with the backward pass; ``BasicDataParallel``
+reduces per parameter.  Both reduce over ``pgm.grad_sync_group`` (CP×DP, ×EP when EP ranks hold distinct
+data) for dense parameters and ``pgm.expert_grad_sync_group`` for expert parameters.
+
+Fixed relative to the reference: with gradient accumulation the *last* micro-batch synchronises (the
+reference's ``no_sync`` around all micro-steps never syncs nor exposes gradients).
+"""
+from __future__ import annotations
+
+import contextlib
+
+import torch
+import torch.distributed as dist
+import torch.nn as nn
+from torch.autograd import Variable
+
+from ...runtime.flat_params import FlatParamStore
+from ..process_group import process_group_manager as pgm
+from .bucket import BucketManager
+
+
+def _groups(group, expert_group):
+    if group is None and pgm:
+        group = pgm.grad_sync_group
+        expert_group = pgm.expert_grad_sync_group if expert_group is None else expert_group
+    return group, expert_group if expert_group is not None else group
+
+
+def get_store(module: nn.Module) -> FlatParamStore:
+    store = getattr(module, "_stb_store", None)
+    if store is None:
+        store = FlatParamStore(module)
+        module._stb_store = store
+    return store
+
+
+class _DPBase(nn.Module):
+    def __init__(self, module: nn.Module):
+        super().__init__()
+        self.module = module
+        self.require_backward_grad_sync = True
+
+    def forward(self, *args, **kwargs):
+        return self.module(*args, **kwargs)
+
+    def __getattr__(self, name):
+        try:
+            return super().__getattr__(name)
+        except AttributeError:
+            return getattr(super().__getattr__("module"), name)
+
+    @contextlib.contextmanager
+    def no_sync(self):
+        old = self.require_backward_grad_sync
+        self.require_backward_grad_sync = False
+        try:
+            yield
+        finally:
+            self.require_backward_grad_sync = old
+
+
+class BasicDataParallel(_DPBase):
+    """Naive DP: blocking mean all-reduce of each parameter's gradient as soon as it is accumulated."""
+
+    def __init__(self, module: nn.Module, group=None):
+        super().__init__(module)
+        self.group, _ = _groups(group, None)
+        self.world_size = dist.get_world_size(self.group) if self.group is not None else 1
+        for p in module.parameters():
+            if p.requires_grad:
+                p.register_post_accumulate_grad_hook(self._hook)
+
+    def _hook(self, p):
+        if self.require_backward_grad_sync and self.world_size > 1 and p.grad is not None:
+            p.grad.div_(self.world_size)
+            dist.all_reduce(p.grad, group=self.group)
+
+
+class DataParallelBucket(_DPBase):
+    def __init__(self, module: nn.Module, bucket_size: int = 2**24, grad_type: torch.dtype | None = None,
+                 group=None, expert_group=None, wire_dtype: torch.dtype | None = None):
+        super().__init__(module)
+        self.store = get_store(module)
+        self.group, self.expert_group = _groups(group, expert_group)
+        self.grad_type = grad_type or torch.float32
+        self.wire_dtype = wire_dtype or torch.float32
+        self.bucket_manager = BucketManager(self.store, self.group, self.expert_group, bucket_size, self.wire_dtype)
+        self._post_backward_queued = False
+        for s in self.store.slots:
+            s.param.grad_ready_hook = self._make_ready_hook(s.param)
+
+    def _make_ready_hook(self, param):
+        def ready(complete: bool = False):
+            # a parameter used more than once per backward (tied embedding / LM head) is complete only
+            # after all of its kernel-epilogue contributions arrived
+            expected = getattr(param, "_stb_expected_grads", 1)
+            if not complete and expected > 1:
+                param._stb_arrivals = getattr(param, "_stb_arrivals", 0) + 1
+                if param._stb_arrivals < expected:
+                    return
+                param._stb_arrivals = 0
+            if not self.require_backward_grad_sync:
+                return
+            if not self._post_backward_queued:
+                Variable._execution_engine.queue_callback(self._post_backward)
+                self._post_backward_queued = True
+            self.bucket_manager.mark_param_as_ready(param, sync=True)
+
+        return ready
+
+    def _post_backward(self) -> None:
+        """Runs once at the end of a synchronising backward: launch stragglers, wait, re-arm."""
+        self.bucket_manager.sync_all()      # buckets with parameters that never produced a gradient
+        self.bucket_manager.wait()
+        self.bucket_manager.reset()
+        self._post_backward_queued = False
+
+    def sync_grads_manually(self) -> None:
+        """Reduces every bucket now (pipeline-parallel schedules call this after the last micro-batch,
+        reference ``data_parallel.py:325-350``)."""
+        self.bucket_manager.reset()
+        self.bucket_manager.sync_all()
+        self.bucket_manager.wait()
+        self.bucket_manager.reset()
+
+    def reset(self) -> None:
+        """Start of a new optimisation step: forget readiness, mark gradients unwritten."""
+        self.bucket_manager.reset()
+        self.store.zero_grad()
+        self._post_backward_queued = False

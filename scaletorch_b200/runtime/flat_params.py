@@ -1,0 +1,140 @@
+"""Flat parameter / gradient storage.
+
+All trainable parameters of a model replica live in ONE contiguous buffer in the training dtype and
+all gradients in ONE contiguous fp32 buffer (``main_grad``); each ``nn.Parameter`` becomes a view.
+That layout is what makes the optimiser step three kernel launches, lets the wgrad GEMM epilogues
+accumulate straight into ``main_grad`` (TMA reduce-add), and lets data-parallel buckets be plain
+*ranges* of the gradient buffer (no pack / unpack copies).
+
+Reference counterpart: the per-bucket flat buffers + ``param.main_grad`` views of
+``scaletorch/parallel/data_parallel/bucket.py:160-356`` (there only for DP, and always fp32 by accident,
+SURVEY §2.7 #2).  Here fp32 accumulation is the explicit choice (decision D4) and the layout is used
+on a single GPU as well.
+
+Segments: ``dense`` parameters (gradients reduced over DP×CP(×EP)) come first, ``expert`` parameters
+(reduced over DP×CP only) second, so each reduction domain is one contiguous range.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+
+import torch
+import torch.nn as nn
+
+ALIGN = 128  # elements; keeps every parameter 256-byte aligned in bf16 (TMA / vector loads)
+
+
+@dataclass
+class ParamSlot:
+    name: str
+    param: nn.Parameter
+    offset: int
+    numel: int
+    segment: str  # "dense" | "expert"
+
+
+def is_expert_param(name: str) -> bool:
+    return ".experts." in name
+
+
+class FlatParamStore:
+    def __init__(self, module: nn.Module, grad_dtype: torch.dtype = torch.float32):
+        named = []
+        seen: set[int] = set()
+        for name, p in module.named_parameters():
+            if not p.requires_grad or id(p) in seen:
+                continue
+            seen.add(id(p))
+            named.append((name, p))
+        if not named:
+            raise ValueError("module has no trainable parameters")
+        self.device = named[0][1].device
+        self.param_dtype = named[0][1].dtype
+        for n, p in named:
+            if p.dtype != self.param_dtype or p.device != self.device:
+                raise ValueError(f"parameter {n} has dtype/device {p.dtype}/{p.device}; expected "
+                                 f"{self.param_dtype}/{self.device} (cast the module before building the store)")
+        dense = [(n, p) for n, p in named if not is_expert_param(n)]
+        expert = [(n, p) for n, p in named if is_expert_param(n)]
+        self.slots: list[ParamSlot] = []
+        off = 0
+        for seg, items in (("dense", dense), ("expert", expert)):
+            for n, p in items:
+                self.slots.append(ParamSlot(n, p, off, p.numel(), seg))
+                off += (p.numel() + ALIGN - 1) // ALIGN * ALIGN
+            if seg == "dense":
+                self.dense_numel = off
+        self.total_numel = off
+        self.expert_numel = off - self.dense_numel
+        self.param_flat = torch.zeros(off, dtype=self.param_dtype, device=self.device)
+        self.grad_flat = torch.zeros(off, dtype=grad_dtype, device=self.device)
+        for s in self.slots:
+            view = self.param_flat[s.offset:s.offset + s.numel].view(s.param.shape)
+            view.copy_(s.param.data)
+            s.param.data = view
+            s.param.main_grad = self.grad_flat[s.offset:s.offset + s.numel]
+            s.param.grad_written = False
+            s.param._stb_slot = s
+        self._by_param = {id(s.param): s for s in self.slots}
+        self._hooks = []
+        self._install_fallback_hooks()
+
+    # Parameters whose gradient arrives through plain autograd (``.grad``) instead of a kernel epilogue
+    # are folded into main_grad here, exactly like the reference's AccumulateGrad hook
+    # (``data_parallel.py:254-295``): main_grad (+)= grad; grad = None.
+    def _install_fallback_hooks(self) -> None:
+        def make(p: nn.Parameter):
+            def hook(param):
+                if param.grad is None:
+                    return
+                g = param.grad.detach().reshape(-1)
+                if param.grad_written:
+                    param.main_grad.add_(g.to(param.main_grad.dtype))
+                else:
+                    param.main_grad.copy_(g)
+                    param.grad_written = True
+                param.grad = None
+                ready = getattr(param, "grad_ready_hook", None)
+                if ready is not None:
+                    ready(True)  # autograd already summed every use of the parameter
+
+            return hook
+
+        for s in self.slots:
+            self._hooks.append(s.param.register_post_accumulate_grad_hook(make(s.param)))
+
+    # ------------------------------------------------------------------ API
+    def parameters(self) -> list[nn.Parameter]:
+        return [s.param for s in self.slots]
+
+    def slot_of(self, p: nn.Parameter) -> ParamSlot:
+        return self._by_param[id(p)]
+
+    def segment_range(self, segment: str) -> tuple[int, int]:
+        return (0, self.dense_numel) if segment == "dense" else (self.dense_numel, self.total_numel)
+
+    def zero_grad(self, set_to_zero: bool = False) -> None:
+        """Marks every gradient as unwritten: the next backward *overwrites* (β=0 in the GEMM epilogue)
+        instead of accumulating, so no memset is needed.  ``set_to_zero`` additionally clears the buffer."""
+        for s in self.slots:
+            s.param.grad_written = False
+            s.param.grad = None
+        if set_to_zero:
+            self.grad_flat.zero_()
+
+    def finalize_grads(self) -> None:
+        """Zero the slices of parameters that received no gradient this step (unused parameters) so stale
+        values never reach the optimiser."""
+        for s in self.slots:
+            if not s.param.grad_written:
+                s.param.main_grad.zero_()
+
+    def expose_grads(self) -> None:
+        """Points ``param.grad`` at its ``main_grad`` view (for code that expects ``.grad``)."""
+        for s in self.slots:
+            s.param.grad = s.param.main_grad.view(s.param.shape)
+
+    def remove_hooks(self) -> None:
+        for h in self._hooks:
+            h.remove()
+        self._hooks.clear()

@@ -1,0 +1,241 @@
+"""Training configuration dataclasses, parsed with ``transformers.HfArgumentParser``.
+
+Same eight argument groups, field names and defaults as the reference
+(``scaletorch/trainer/config.py:31-475``) so existing launch scripts keep working; every field is a
+``--flag``.  Additions (all optional): ``--sequence_parallel``, ``--ep_replicate_data``,
+``--fused_comm``, ``--grad_wire_dtype``, ``--synthetic_data``, ``--model_config_path``,
+``--aux_loss``.  Validation fixes: ``expert_parallel_size`` is checked, and ``nccl``/``gloo``
+are the only back-ends (Ascend ``hccl`` is dropped).
+"""
+from __future__ import annotations
+
+import os
+from dataclasses import dataclass, field
+
+_VALID_LR_SCHEDULERS = {"linear", "cosine", "polynomial", "step", "onecycle", "constant"}
+_VALID_OPTIMIZERS = {"adamw", "adam", "sgd", "lamb"}
+
+
+@dataclass
+class DataArguments:
+    data_path: str = field(default="./data", metadata={"help": "Dataset download directory"})
+    dataset_name: str = field(default="wikitext2", metadata={"help": "Dataset name or local directory"})
+    tokenizer_name_or_path: str = field(default="facebook/opt-125m", metadata={"help": "Tokenizer name or path"})
+    subset_name: str | None = field(default=None, metadata={"help": "Subset name"})
+    split: str = field(default="train", metadata={"help": "Split name"})
+    num_proc: int = field(default=1, metadata={"help": "Number of processes for data processing"})
+    num_workers: int = field(default=2, metadata={"help": "Number of DataLoader workers"})
+    num_samples: int | None = field(default=None, metadata={"help": "Number of samples to use (None = all)"})
+    pin_memory: bool = field(default=True, metadata={"help": "Whether to pin host memory"})
+    synthetic_data: bool = field(default=False, metadata={"help": "Random tokens of the configured shape (benchmarks; no dataset / tokenizer needed)"})
+
+
+@dataclass
+class ModelArguments:
+    model_name_or_path: str = field(default="facebook/opt-125m", metadata={"help": "Model name, local HF directory or a name under configs/"})
+    num_hidden_layers: int | None = field(default=None, metadata={"help": "Override the number of hidden layers"})
+    num_attention_heads: int | None = field(default=None, metadata={"help": "Override the number of attention heads"})
+    num_key_value_heads: int | None = field(default=None, metadata={"help": "Override the number of key-value heads"})
+    use_flash_attention: bool = field(default=True, metadata={"help": "Use the flash attention kernel (False = eager oracle)"})
+    dtype: str = field(default="bfloat16", metadata={"help": "Training dtype: bfloat16 | float32"})
+
+    def __post_init__(self) -> None:
+        cfg = resolve_model_config(self.model_name_or_path, quiet=True)
+        if cfg is not None:
+            for name in ("num_hidden_layers", "num_attention_heads", "num_key_value_heads"):
+                if getattr(self, name) is None:
+                    setattr(self, name, getattr(cfg, name, None))
+
+
+@dataclass
+class ParallelArguments:
+    tensor_parallel_size: int = field(default=1, metadata={"help": "Size of tensor parallelism"})
+    pipeline_parallel_size: int = field(default=1, metadata={"help": "Size of pipeline parallelism"})
+    data_parallel_size: int = field(default=1, metadata={"help": "Size of data parallelism"})
+    context_parallel_size: int = field(default=1, metadata={"help": "Size of context parallelism"})
+    expert_parallel_size: int = field(default=1, metadata={"help": "Size of expert parallelism"})
+    pipeline_parallel_engine: str = field(default="1f1b", metadata={"help": "Pipeline schedule: 1f1b | afab"})
+    backend: str = field(default="nccl", metadata={"help": "Distributed backend: nccl | gloo"})
+    sequence_parallel: bool = field(default=False, metadata={"help": "Megatron sequence parallelism over the TP group (also enabled by env SEQUENCE_PARALLEL=1)"})
+    ep_replicate_data: bool = field(default=False, metadata={"help": "Reference semantics: every EP rank of a dp_rank reads the same samples"})
+    fused_comm: bool = field(default=True, metadata={"help": "Use the fused compute+collective kernels over NVLink peer memory when available"})
+    grad_wire_dtype: str = field(default="float32", metadata={"help": "dtype of DP gradient buckets on the wire: float32 | bfloat16"})
+
+    def __post_init__(self) -> None:
+        for name in ("data_parallel_size", "tensor_parallel_size", "pipeline_parallel_size", "context_parallel_size",
+                     "expert_parallel_size"):
+            if getattr(self, name) < 1:
+                raise ValueError(f"{name} must be >= 1, got {getattr(self, name)}")
+        if self.pipeline_parallel_engine not in {"1f1b", "afab"}:
+            raise ValueError(f'pipeline_parallel_engine must be "1f1b" or "afab", got {self.pipeline_parallel_engine}')
+        if self.backend not in {"nccl", "gloo"}:
+            raise ValueError(f"backend must be one of {{nccl, gloo}}, got {self.backend}")
+        if self.grad_wire_dtype not in {"float32", "bfloat16"}:
+            raise ValueError(f"grad_wire_dtype must be float32 or bfloat16, got {self.grad_wire_dtype}")
+        if os.environ.get("SEQUENCE_PARALLEL", "0") == "1":
+            self.sequence_parallel = True
+
+
+@dataclass
+class LrSchedulerArguments:
+    lr_scheduler_type: str = field(default="linear", metadata={"help": "Type of learning rate scheduler"})
+    warmup_steps: int = field(default=0, metadata={"help": "Number of warmup steps"})
+    T_max: int | None = field(default=None, metadata={"help": "Maximum number of iterations for cosine annealing"})
+    eta_min: float = field(default=0.0, metadata={"help": "Minimum learning rate for cosine annealing"})
+    power: float = field(default=1.0, metadata={"help": "Power factor for polynomial decay"})
+    step_size: int = field(default=1, metadata={"help": "Step size for step decay"})
+    gamma: float = field(default=0.1, metadata={"help": "Multiplicative factor for step decay"})
+    max_lr: float | None = field(default=None, metadata={"help": "Upper learning rate boundary for OneCycleLR"})
+    pct_start: float = field(default=0.3, metadata={"help": "Fraction of the cycle spent increasing LR (OneCycleLR)"})
+
+    def __post_init__(self) -> None:
+        if self.lr_scheduler_type not in _VALID_LR_SCHEDULERS:
+            from .lr_scheduler import registered_schedulers
+
+            if self.lr_scheduler_type not in registered_schedulers():
+                raise ValueError(f"lr_scheduler_type must be one of {sorted(_VALID_LR_SCHEDULERS)}, got {self.lr_scheduler_type}")
+        if self.warmup_steps < 0:
+            raise ValueError(f"warmup_steps must be >= 0, got {self.warmup_steps}")
+        t = self.lr_scheduler_type
+        if t == "cosine" and self.eta_min < 0:
+            raise ValueError(f"eta_min must be >= 0, got {self.eta_min}")
+        if t == "polynomial" and self.power <= 0:
+            raise ValueError(f"power must be > 0, got {self.power}")
+        if t == "step":
+            if self.step_size <= 0:
+                raise ValueError(f"step_size must be > 0, got {self.step_size}")
+            if self.gamma <= 0 or self.gamma > 1:
+                raise ValueError(f"gamma must be in (0, 1], got {self.gamma}")
+        if t == "onecycle" and not 0 < self.pct_start < 1:
+            raise ValueError(f"pct_start must be in (0, 1), got {self.pct_start}")
+
+
+@dataclass
+class OptimizerArguments:
+    optimizer_type: str = field(default="adamw", metadata={"help": "Type of optimizer"})
+    weight_decay: float = field(default=0.0, metadata={"help": "Weight decay"})
+    use_fused_adam: bool = field(default=True, metadata={"help": "Use the fused AdamW kernel over the flat parameter store"})
+    betas: tuple[float, float] = field(default=(0.9, 0.999), metadata={"help": "Betas for Adam"})
+    learning_rate: float = field(default=1e-3, metadata={"help": "Learning rate"})
+
+    def __post_init__(self) -> None:
+        if self.optimizer_type not in _VALID_OPTIMIZERS:
+            raise ValueError(f"optimizer_type must be one of {sorted(_VALID_OPTIMIZERS)}, got {self.optimizer_type}")
+        if isinstance(self.betas, list):
+            self.betas = tuple(float(b) for b in self.betas)
+
+
+@dataclass
+class TrainingArguments:
+    batch_size: int = field(default=64, metadata={"help": "Training batch size"})
+    test_batch_size: int = field(default=1000, metadata={"help": "Evaluation batch size"})
+    micro_batch_size: int | None = field(default=None, metadata={"help": "Micro batch size"})
+    gradient_accumulation_steps: int = field(default=1, metadata={"help": "Number of gradient accumulation steps"})
+    gradient_checkpointing: bool = field(default=False, metadata={"help": "Recompute decoder layers in backward"})
+    max_grad_norm: float | None = field(default=1.0, metadata={"help": "Max gradient norm (None disables clipping)"})
+    epochs: int = field(default=5, metadata={"help": "Number of training epochs"})
+    seed: int = field(default=1, metadata={"help": "Random seed"})
+    sequence_length: int | None = field(default=1024, metadata={"help": "Sequence length"})
+    log_interval: int = field(default=100, metadata={"help": "Logging frequency"})
+    max_tokens: int | None = field(default=None, metadata={"help": "Stop after this many trained tokens"})
+    total_train_steps: int | None = field(default=None, metadata={"help": "Stop after this many steps"})
+    use_cpu: bool = field(default=False, metadata={"help": "Run on CPU with the gloo backend"})
+    aux_loss: bool = field(default=True, metadata={"help": "Add the MoE load-balancing loss to the training loss"})
+
+    def __post_init__(self) -> None:
+        if self.gradient_accumulation_steps < 1:
+            raise ValueError(f"gradient_accumulation_steps must be >= 1, got {self.gradient_accumulation_steps}")
+        if self.micro_batch_size is not None and self.micro_batch_size < 1:
+            raise ValueError(f"micro_batch_size must be >= 1, got {self.micro_batch_size}")
+        if self.sequence_length is not None and self.sequence_length < 1:
+            raise ValueError(f"sequence_length must be >= 1, got {self.sequence_length}")
+
+
+@dataclass
+class CheckpointArguments:
+    work_dir: str = field(default="./work_dir", metadata={"help": "Directory to save checkpoints"})
+    save_model_checkpoint: bool = field(default=True, metadata={"help": "Whether to save model checkpoints"})
+    save_frequency: int = field(default=300, metadata={"help": "Checkpoint frequency in steps (0 = never)"})
+    resume_path: str = field(default="", metadata={"help": "Checkpoint directory to resume from"})
+    load_pretrained_weights: bool = field(default=False, metadata={"help": "Load and KEEP the HF safetensors weights found in model_name_or_path"})
+
+    def __post_init__(self) -> None:
+        if self.save_frequency < 0:
+            raise ValueError(f"save_frequency must be >= 0, got {self.save_frequency}")
+
+
+@dataclass
+class LoggingArguments:
+    use_wandb: bool = field(default=False, metadata={"help": "Log to Weights & Biases"})
+    project_name: str = field(default="scaletorch", metadata={"help": "Project name for logging"})
+    experiment_name: str | None = field(default=None, metadata={"help": "Experiment name for logging"})
+
+
+@dataclass
+class ScaleTorchArguments(DataArguments, ModelArguments, ParallelArguments, LrSchedulerArguments, OptimizerArguments,
+                          TrainingArguments, CheckpointArguments, LoggingArguments):
+    """All training arguments (multiple inheritance of the eight groups, like the reference)."""
+
+    global_batch_size: int = field(init=False, default=0)
+    global_batch_size_token: int | None = field(init=False, default=None)
+
+    def __post_init__(self) -> None:
+        for cls in (DataArguments, ModelArguments, ParallelArguments, LrSchedulerArguments, OptimizerArguments,
+                    TrainingArguments, CheckpointArguments, LoggingArguments):
+            post = cls.__dict__.get("__post_init__")
+            if post is not None:
+                post(self)
+        if self.micro_batch_size is None:
+            self.micro_batch_size = self.batch_size
+        if self.sequence_length is not None and self.sequence_length % self.context_parallel_size != 0:
+            raise ValueError(f"sequence_length ({self.sequence_length}) must be divisible by context_parallel_size "
+                             f"({self.context_parallel_size})")
+        data_replicas = self.data_parallel_size * (1 if self.ep_replicate_data else self.expert_parallel_size)
+        self.global_batch_size = data_replicas * self.micro_batch_size * self.gradient_accumulation_steps
+        if self.sequence_length is not None:
+            self.global_batch_size_token = self.global_batch_size * self.sequence_length
+
+    def validate_world_size(self, world_size: int) -> None:
+        expected = (self.tensor_parallel_size * self.pipeline_parallel_size * self.data_parallel_size *
+                    self.context_parallel_size * self.expert_parallel_size)
+        if world_size != expected:
+            raise ValueError(
+                f"world_size ({world_size}) != TP ({self.tensor_parallel_size}) * PP ({self.pipeline_parallel_size}) * "
+                f"DP ({self.data_parallel_size}) * CP ({self.context_parallel_size}) * EP ({self.expert_parallel_size}) "
+                f"= {expected}")
+
+
+def validate_config(config: ScaleTorchArguments, world_size: int) -> None:
+    config.validate_world_size(world_size)
+
+
+# --------------------------------------------------------------------------- model config resolution
+_CONFIG_DIR = os.path.join(os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))), "configs")
+
+
+def resolve_model_config(name_or_path: str, quiet: bool = False):
+    """Returns a ``transformers.PretrainedConfig`` for a local HF directory, a vendored config under
+    ``configs/<name>/config.json`` (the GPU box has no network) or, last, the HF hub name."""
+    from transformers import AutoConfig
+
+    candidates = [name_or_path, os.path.join(_CONFIG_DIR, name_or_path), os.path.join(_CONFIG_DIR, os.path.basename(name_or_path.rstrip("/")))]
+    for c in candidates:
+        if os.path.isfile(os.path.join(c, "config.json")):
+            return AutoConfig.from_pretrained(c)
+    try:
+        return AutoConfig.from_pretrained(name_or_path, local_files_only=True)
+    except Exception as e:
+        if not quiet:
+            raise RuntimeError(f"cannot resolve a model config for '{name_or_path}': {e}") from e
+        return None
+
+
+def main() -> None:  # pragma: no cover - CLI helper
+    from transformers import HfArgumentParser
+
+    (cfg,) = HfArgumentParser(ScaleTorchArguments).parse_args_into_dataclasses()
+    print(cfg)
+
+
+if __name__ == "__main__":  # pragma: no cover
+    main()

@@ -1,0 +1,55 @@
+"""Console / wandb metrics (reference: ``scaletorch/trainer/metrics.py:23-114``).
+
+The console line keeps the reference's exact field layout because its benchmark scripts regex-parse it
+(``scripts/benchmark_comprehensive.py:231-239``).
+"""
+from __future__ import annotations
+
+from typing import Any
+
+from ..parallel.process_group import process_group_manager as pgm
+from ..utils.device import memory_reserved
+from ..utils.misc import get_mfu, to_readable_format
+
+
+def is_logging_rank() -> bool:
+    if not pgm:
+        return True
+    return pgm.tp_rank == 0 and pgm.dp_rank == 0 and pgm.cp_rank == 0 and pgm.ep_rank == 0 and pgm.pp_is_last_stage
+
+
+def format_metrics_line(step: int, loss: float, lr: float, grad_norm: float | None, global_batch_size: int,
+                        tokens_per_second: float, tokens_per_second_per_gpu: float, trained_tokens: int,
+                        max_tokens: int | None, mfu: float, memory_gb: float) -> str:
+    parts = [
+        f"Step: {step:<5d}",
+        f"Loss: {loss:6.4f}",
+        f"LR: {lr:.2e}",
+        f"GradNorm: {grad_norm:6.3f}" if grad_norm is not None else "GradNorm: n/a",
+        f"Global batch size: {to_readable_format(global_batch_size):>7s}",
+        f"Tokens/s: {to_readable_format(tokens_per_second):>7s}",
+        f"Tokens/s/GPU: {to_readable_format(tokens_per_second_per_gpu):>7s}",
+        f"Tokens: {to_readable_format(trained_tokens):>7s}" + (f"/{to_readable_format(max_tokens)}" if max_tokens else ""),
+        f"MFU: {mfu:5.2f}%",
+        f"Memory: {memory_gb:6.2f}GB",
+    ]
+    return " | ".join(parts)
+
+
+def log_training_metrics(config: Any, model_config: Any, step: int, loss: float, lr: float, grad_norm: float | None,
+                         step_duration: float, tokens_per_step: int, trained_tokens: int, num_params: int,
+                         world_size: int, logger=None, wandb_run=None) -> dict[str, Any]:
+    tps = tokens_per_step / step_duration if step_duration > 0 else 0.0
+    tps_gpu = tps / max(world_size, 1)
+    mfu = get_mfu(tps_gpu, num_params, model_config, seq_len=config.sequence_length)
+    mem = memory_reserved() / 1e9
+    metrics = {"step": step, "loss": loss, "lr": lr, "grad_norm": grad_norm, "tokens_per_second": tps,
+               "tokens_per_second_per_gpu": tps_gpu, "trained_tokens": trained_tokens, "mfu": mfu,
+               "memory_gb": mem, "step_duration": step_duration}
+    if is_logging_rank():
+        line = format_metrics_line(step, loss, lr, grad_norm, config.global_batch_size_token or tokens_per_step, tps,
+                                   tps_gpu, trained_tokens, config.max_tokens, mfu, mem)
+        (logger.info if logger is not None else print)(line)
+        if wandb_run is not None:
+            wandb_run.log(metrics, step=step)
+    return metrics

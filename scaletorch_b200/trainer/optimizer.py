@@ -1,0 +1,74 @@
+"""Fused AdamW over a :class:`FlatParamStore` with global-norm clipping folded into the update.
+
+Reference: ``torch.optim.AdamW(fused=True)`` (``scaletorch/trainer/model_builder.py:119-134``) followed by a
+separate rank-local ``clip_grad_norm_`` with a ``.item()`` sync (``trainer/train_step.py:122-136``).  Here the
+step is: sum-of-squares kernel → (all-reduce of the scalar over model-parallel ranks) → clip coefficient
+on the device → one AdamW kernel over the flat buffers that reads the coefficient.  No host sync.
+
+It subclasses ``torch.optim.Optimizer`` so LR schedulers, ``param_groups`` and ``state_dict`` behave as
+users expect.
+"""
+from __future__ import annotations
+
+import torch
+import torch.distributed as dist
+
+from ..ops.optim import clip_coef_from_sumsq, fused_adamw_step, sum_of_squares
+from ..runtime.flat_params import FlatParamStore
+
+
+class FusedAdamW(torch.optim.Optimizer):
+    def __init__(self, store: FlatParamStore, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8,
+                 weight_decay: float = 0.01, max_grad_norm: float | None = None, norm_group=None,
+                 norm_scale_tp_replicated: bool = True):
+        self.store = store
+        defaults = dict(lr=lr, betas=tuple(betas), eps=eps, weight_decay=weight_decay)
+        super().__init__(store.parameters(), defaults)
+        self.exp_avg = torch.zeros(store.total_numel, dtype=torch.float32, device=store.device)
+        self.exp_avg_sq = torch.zeros(store.total_numel, dtype=torch.float32, device=store.device)
+        self.step_count = 0
+        self.max_grad_norm = max_grad_norm
+        self.norm_group = norm_group
+        self.last_grad_norm: torch.Tensor | None = None  # device scalar (read lazily for logging)
+
+    @torch.no_grad()
+    def compute_clip(self):
+        """Device scalars ``(coef, norm)`` of the global gradient norm over the model-parallel group."""
+        ss = sum_of_squares(self.store.grad_flat)
+        if self.norm_group is not None and dist.is_initialized() and dist.get_world_size(self.norm_group) > 1:
+            dist.all_reduce(ss, group=self.norm_group)
+        coef, norm = clip_coef_from_sumsq(ss, self.max_grad_norm or 0.0)
+        self.last_grad_norm = norm
+        return coef, norm
+
+    @torch.no_grad()
+    def step(self, closure=None, grad_scale: float = 1.0):
+        loss = closure() if closure is not None else None
+        self.store.finalize_grads()
+        self.step_count += 1
+        g = self.param_groups[0]
+        coef = None
+        if self.max_grad_norm is not None and self.max_grad_norm > 0:
+            coef, _ = self.compute_clip()
+        fused_adamw_step(self.store.param_flat, self.store.grad_flat, self.exp_avg, self.exp_avg_sq,
+                         lr=g["lr"], betas=g["betas"], eps=g["eps"], weight_decay=g["weight_decay"],
+                         step=self.step_count, clip_coef=coef, grad_scale=grad_scale)
+        return loss
+
+    def zero_grad(self, set_to_none: bool = True) -> None:
+        self.store.zero_grad(set_to_zero=False)
+
+    def grad_norm(self) -> float:
+        """Host value of the last global gradient norm (synchronises)."""
+        return float(self.last_grad_norm.item()) if self.last_grad_norm is not None else 0.0
+
+    def state_dict(self):
+        return {"step": self.step_count, "exp_avg": self.exp_avg, "exp_avg_sq": self.exp_avg_sq,
+                "param_groups": [{k: v for k, v in g.items() if k != "params"} for g in self.param_groups]}
+
+    def load_state_dict(self, sd) -> None:
+        self.step_count = int(sd["step"])
+        self.exp_avg.copy_(sd["exp_avg"])
+        self.exp_avg_sq.copy_(sd["exp_avg_sq"])
+        for g, s in zip(self.param_groups, sd.get("param_groups", [])):
+            g.update(s)

@@ -1,0 +1,68 @@
+"""One optimisation step without pipeline parallelism (reference: ``scaletorch/trainer/train_step.py:14-136``).
+
+Differences: the loss is the fused (vocab-parallel) linear+cross-entropy of the model (no full logits);
+with gradient accumulation only the last micro-batch synchronises gradients (the reference never does,
+SURVEY §2.7 #1); the per-micro-batch loss stays on the device (one ``.item()`` per *step*, in the caller,
+instead of one per micro-batch); the MoE auxiliary loss is added; clipping uses the global norm.
+"""
+from __future__ import annotations
+
+import contextlib
+
+import torch
+
+from ..parallel.process_group import process_group_manager as pgm
+
+
+def _micro_batch_loss(model, batch, device, gradient_checkpointing: bool, loss_scale: float, aux_loss: bool):
+    input_ids = batch["input_ids"].to(device, non_blocking=True)
+    target_ids = batch["target_ids"].to(device, non_blocking=True)
+    raw = model.module if hasattr(model, "module") else model
+    loss = raw.loss(input_ids, target_ids, gradient_checkpointing=gradient_checkpointing, loss_scale=loss_scale)
+    if aux_loss:
+        aux = raw.get_aux_loss()
+        if aux is not None:
+            loss = loss + aux * loss_scale
+    return loss
+
+
+def train_step(model, data_loader, device, dtype: torch.dtype = torch.bfloat16, gradient_accumulation_steps: int | None = None,
+               gradient_checkpointing: bool = False, aux_loss: bool = True) -> torch.Tensor:
+    """Runs ``GA`` micro-batches of forward+backward; returns the mean loss as a device scalar."""
+    ga = gradient_accumulation_steps or getattr(data_loader, "gradient_accumulation_steps", 1)
+    total = torch.zeros((), dtype=torch.float32, device=device)
+    has_sync = hasattr(model, "no_sync")
+    use_autocast = dtype == torch.bfloat16 and device.type == "cpu"   # CUDA path runs bf16 parameters natively
+    for i in range(ga):
+        batch = next(data_loader)
+        last = i == ga - 1
+        sync_ctx = contextlib.nullcontext() if (last or not has_sync) else model.no_sync()
+        with sync_ctx:
+            with torch.autocast("cpu", dtype=torch.bfloat16) if use_autocast else contextlib.nullcontext():
+                loss = _micro_batch_loss(model, batch, device, gradient_checkpointing, 1.0 / ga, aux_loss)
+            loss.backward()
+        total += loss.detach().float()
+    return total
+
+
+def clip_gradients(model, max_grad_norm: float | None, optimizer=None) -> float | None:
+    """Global-norm clipping.  With the fused optimiser clipping is folded into ``optimizer.step`` and this
+    only reports the norm; for plain torch optimisers it clips ``.grad`` in place over the model-parallel
+    group."""
+    if max_grad_norm is None or max_grad_norm <= 0:
+        return None
+    from .optimizer import FusedAdamW
+
+    if isinstance(optimizer, FusedAdamW):
+        return None  # computed inside step(); read optimizer.grad_norm() after the step
+    params = [p for p in model.parameters() if p.grad is not None]
+    if not params:
+        return 0.0
+    ss = torch.stack([p.grad.detach().float().pow(2).sum() for p in params]).sum()
+    if pgm and len(pgm.mp_group_ids) > 1:
+        torch.distributed.all_reduce(ss, group=pgm.mp_group)
+    norm = ss.sqrt()
+    coef = torch.clamp(max_grad_norm / (norm + 1e-6), max=1.0)
+    for p in params:
+        p.grad.mul_(coef.to(p.grad.dtype))
+    return float(norm.item())

@@ -22,6 +22,10 @@ int make_tmap_3d(CUtensorMap* out, const void* base, int elem_bytes, uint64_t di
                  uint64_t dim2, uint64_t stride1_bytes, uint64_t stride2_bytes, uint32_t box0,
                  uint32_t box1, uint32_t box2, int swizzle_128b);
 
+// [B, S, H, D] bf16 tensor with element strides (sb, ss, sh), D contiguous; box = {box_d, 1, box_s, 1}
+int make_tmap_bshd(CUtensorMap* out, const void* base, int B, int S, int H, int D, long sb, long ss,
+                   long sh, uint32_t box_d, uint32_t box_s);
+
 #define STB_CHECK_CUDA(expr)                                                              \
   do {                                                                                    \
     cudaError_t _e = (expr);                                                              \

@@ -425,6 +425,82 @@ extern "C" int stb_rmsnorm_bwd(const void* dy, const void* h, const void* w, con
   return 0;
 }
 
+// ---------------------------------------------------------------------------------------------
+// RMSNorm backward for callers that must not allocate device memory.
+//
+// stb_rmsnorm_bwd() needs a caller-provided fp32 scratch buffer for the per-CTA partial sums of the
+// weight gradient.  Some users of this C ABI have nowhere to get one: a host program that hands the
+// whole of HBM to its own arena at start-up (so a later cudaMalloc fails or fragments the arena), or
+// glue code running where an allocation -- and the device-wide synchronisation cudaMalloc/cudaFree
+// imply -- is not acceptable, such as the inner loop of a latency-sensitive service.  For them this
+// variant keeps the scratch inside the library image: a file-scope __device__ array of
+// kNoAllocScratchElems floats (16 MiB).  Every GPU that loads the library carries that array until the
+// process exits, whether or not this function is ever called.
+//
+// What to know before calling it:
+//  * Limit: the partial sums take min(rows, 4 * SM count) * H floats.  If that exceeds
+//    kNoAllocScratchElems (4 Mi floats) the call is refused with an error naming both numbers; use
+//    stb_rmsnorm_bwd() with your own buffer for such shapes.  On a 148-SM B200 every H <= 7080 fits
+//    for any row count.
+//  * The first call on each device looks up the array's device address (cudaGetSymbolAddress, with
+//    that device current) and caches it.  Make that first call during start-up, before any stream
+//    capture begins on the device.
+//  * It calls no cudaMalloc / cudaFree and no library routine that allocates.
+//  * All calls on one device share the one array, which still holds whatever the previous call left
+//    there.  Nothing in it has to start at zero for this kernel -- every partial row that the reduction
+//    reads is fully rewritten by the same call first -- but two calls whose kernels overlap on the GPU
+//    (different streams, no ordering between them) overwrite each other's partial sums and both
+//    produce a wrong dw.  Serialise them: same stream, or an event between the streams.
+//  * Results are the same as stb_rmsnorm_bwd() with the same arguments (same grid, same summation
+//    order).
+constexpr long kNoAllocScratchElems = 4l << 20;
+static __device__ __align__(256) float g_rmsnorm_noalloc_scratch[kNoAllocScratchElems];
+
+// In host code the symbol above is only a handle, not a device address: the address each device gave
+// the array is fetched once per device and kept here.
+static float* g_noalloc_scratch_ptr[64] = {nullptr};
+
+static int noalloc_scratch_for_current_device(float** out) {
+  int dev = 0;
+  STB_CHECK_CUDA(cudaGetDevice(&dev));
+  STB_REQUIRE(dev >= 0 && dev < 64, "rmsnorm_bwd_noalloc: device index %d out of range", dev);
+  if (g_noalloc_scratch_ptr[dev] == nullptr) {
+    float* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_rmsnorm_noalloc_scratch);
+    STB_REQUIRE(e == cudaSuccess && p != nullptr,
+                "rmsnorm_bwd_noalloc: cudaGetSymbolAddress failed on device %d: %s", dev,
+                cudaGetErrorString(e));
+    g_noalloc_scratch_ptr[dev] = p;
+  }
+  *out = g_noalloc_scratch_ptr[dev];
+  return 0;
+}
+
+extern "C" long stb_rmsnorm_bwd_noalloc_max_elems() { return kNoAllocScratchElems; }
+
+extern "C" int stb_rmsnorm_bwd_noalloc(const void* dy, const void* h, const void* w, const float* rstd,
+                                       const void* dres, void* dx, float* dw, int dw_accumulate,
+                                       int rows, int H, cudaStream_t stream) {
+  STB_REQUIRE(H % 8 == 0 && H <= 8192, "rmsnorm: H=%d must be a multiple of 8 and <= 8192", H);
+  if (rows == 0) return 0;
+  const int cap = sm_count() * 4;
+  const int grid = rows < cap ? rows : cap;
+  const long need = long(grid) * H;
+  STB_REQUIRE(need <= kNoAllocScratchElems,
+              "rmsnorm_bwd_noalloc: rows=%d, H=%d needs %ld scratch floats but the built-in scratch holds "
+              "%ld; call stb_rmsnorm_bwd with a caller-provided buffer instead",
+              rows, H, need, kNoAllocScratchElems);
+  float* scratch = nullptr;
+  if (int rc = noalloc_scratch_for_current_device(&scratch)) return rc;
+  STB_DISPATCH_VPT(H, (rmsnorm_bwd_kernel<VPT, NT><<<grid, NT, 0, stream>>>(
+                          (const __nv_bfloat16*)dy, (const __nv_bfloat16*)h, (const __nv_bfloat16*)w,
+                          rstd, (const __nv_bfloat16*)dres, (__nv_bfloat16*)dx, scratch, rows, H)));
+  STB_CHECK_LAUNCH();
+  rmsnorm_dw_reduce_kernel<<<(H + 127) / 128, 128, 0, stream>>>(scratch, dw, grid, H, dw_accumulate);
+  STB_CHECK_LAUNCH();
+  return 0;
+}
+
 extern "C" int stb_qknorm_rope_fwd(const void* qkv, const void* wq, const void* wk, const float* cos_t,
                                    const float* sin_t, const int* pos, void* out, float* rstd, int T,
                                    int S, int Hq, int Hkv, int head_dim, int pos_offset, int use_norm,

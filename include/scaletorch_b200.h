@@ -48,6 +48,20 @@ int stb_rmsnorm_bwd(const void* dy, const void* h, const void* w, const float* r
                     void* dx, float* dw, int dw_accumulate, float* scratch, int rows, int H,
                     cudaStream_t stream);
 
+/* RMSNorm backward without a caller-provided scratch buffer -- this entry point has no counterpart in
+ * the reference; it exists for users of this C ABI who cannot allocate device memory (their process
+ * gave all of HBM to its own arena at start-up, or they run where cudaMalloc's device-wide
+ * synchronisation is not acceptable).  Same arguments and same result as stb_rmsnorm_bwd minus
+ * `scratch`: the partial sums go to a 16 MiB __device__ array inside the library, which every GPU that
+ * loads the library holds until exit.  Shapes with min(rows, 4*SMs) * H > stb_rmsnorm_bwd_noalloc_max_elems()
+ * (4 Mi floats) are refused with an error.  The first call on a device resolves the array's address:
+ * make it before any stream capture.  Never allocates.  Calls that overlap on the GPU share the array
+ * and race; order them on one stream or with events.  csrc/norm_rope.cu. */
+long stb_rmsnorm_bwd_noalloc_max_elems(void);
+int stb_rmsnorm_bwd_noalloc(const void* dy, const void* h, const void* w, const float* rstd,
+                            const void* dres, void* dx, float* dw, int dw_accumulate, int rows, int H,
+                            cudaStream_t stream);
+
 /* ---- per-head QK-RMSNorm + rotate-half RoPE, csrc/norm_rope.cu -----------
  * qkv: [T, (Hq+2Hkv)*128]; out: [T, (Hq+Hkv)*128]; cos/sin: fp32 [max_pos,128];
  * pos: optional int32 [T] (else position = t % S + pos_offset).

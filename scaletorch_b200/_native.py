@@ -28,6 +28,7 @@ _SIGS = {
     "stb_gemm_bf16": [_P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, _P],
     "stb_rmsnorm_fwd": [_P, _P, _P, _P, _P, _P, c_int, c_int, c_float, _P],
     "stb_rmsnorm_bwd": [_P, _P, _P, _P, _P, _P, _P, c_int, _P, c_int, c_int, _P],
+    "stb_rmsnorm_bwd_noalloc": [_P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int, _P],
     "stb_qknorm_rope_fwd": [_P, _P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_float, _P],
     "stb_qknorm_rope_bwd": [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, _P],
     "stb_swiglu_fwd": [_P, _P, c_long, c_int, _P],

@@ -1,0 +1,366 @@
+// Flash-attention forward on tcgen05 tensor cores with native GQA.
+//
+//   out[b,q,h,:] = softmax(scale * Q K^T + causal mask) V        lse[b,h,q] = log sum exp (natural log)
+//
+// Q/K/V are token-major [B, S, H, 128] views with arbitrary batch/token/head strides (they are read
+// straight out of the packed QKV projection), K/V carry Hkv <= Hq heads and are never expanded.
+// (out, lse) is exactly what ring attention needs to merge partial results.
+// Reference: F.scaled_dot_product_attention after an explicit K/V expansion
+// (scaletorch/models/attention_utils.py:130-152, scaletorch/models/model_qwen3.py:219-238) and the eager
+// per-block attention of scaletorch/parallel/context_parallel/context_parallel.py:266-302.
+//
+// One CTA per (batch, q-head, 128-query tile), 10 warps:
+//   warp 0      TMA producer: Q once, K/V tiles of 128 keys through a 2-stage ring (4-D tensor maps)
+//   warp 1      MMA issuer  : S = Q K^T (128x128x128) and O_j = P V (128x128x128), accumulators in TMEM
+//   warps 2..9  softmax     : two threads per query row (64 score columns / 64 output columns each):
+//               tcgen05.ld S -> online max / exp2 -> P (bf16) into 128B-swizzled smem for the PV MMA;
+//               the running output is kept in registers and rescaled when the row max grows.
+// TMEM: S and O_j are both double-buffered (4 x 128 columns) so QK^T of tile j+1 and PV of tile j run
+// while the softmax warps work on tile j / accumulate tile j-1.
+#include <math_constants.h>
+
+#include "common/host.h"
+#include "common/ptx.cuh"
+
+namespace stb {
+
+constexpr int kAttnThreads = 320;
+constexpr int kTile = 128;  // query rows per CTA and keys per step
+constexpr int kHeadDim = 128;
+constexpr int kHalfBytes = kTile * 128;      // one [128 rows][64 bf16] swizzled half tile = 16 KB
+constexpr int kTileBytes = 2 * kHalfBytes;   // 32 KB
+
+struct AttnFwdParams {
+  __nv_bfloat16* out;
+  float* lse;
+  int B, Sq, Sk, Hq, Hkv;
+  int n_qtiles;
+  float scale_log2;
+  int causal;
+};
+
+struct AttnSmem {
+  static constexpr int kQ = 0;
+  static constexpr int kK = kQ + kTileBytes;
+  static constexpr int kV = kK + 2 * kTileBytes;
+  static constexpr int kP = kV + 2 * kTileBytes;
+  static constexpr int kX = kP + kTileBytes;          // float xmax[2][2][128], xsum[2][128]
+  static constexpr int kBar = kX + 3 * 2 * 128 * 4;
+  static constexpr int kBytes = kBar + 256 + 1024;
+};
+
+__global__ void __launch_bounds__(kAttnThreads, 1)
+    flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                          const __grid_constant__ CUtensorMap tmV, const AttnFwdParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sQ = smem + AttnSmem::kQ;
+  uint8_t* sK = smem + AttnSmem::kK;
+  uint8_t* sV = smem + AttnSmem::kV;
+  uint8_t* sP = smem + AttnSmem::kP;
+  float* xmax = reinterpret_cast<float*>(smem + AttnSmem::kX);   // [2 buffers][2 halves][128 rows]
+  float* xsum = xmax + 2 * 2 * 128;                              // [2 halves][128 rows]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + AttnSmem::kBar);
+  uint64_t* q_full = bars + 0;
+  uint64_t* k_full = bars + 1;    // [2]
+  uint64_t* v_full = bars + 3;    // [2]
+  uint64_t* k_empty = bars + 5;   // [2]  K stage reusable once its QK^T retired
+  uint64_t* v_empty = bars + 7;   // [2]  V stage reusable once its PV retired
+  uint64_t* s_full = bars + 9;    // [2]
+  uint64_t* s_free = bars + 11;   // [2]
+  uint64_t* p_full = bars + 13;
+  uint64_t* p_free = bars + 14;
+  uint64_t* o_full = bars + 15;   // [2]
+  uint64_t* o_free = bars + 17;   // [2]
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 19);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  // heavy (late, for causal) query tiles first
+  const int bh = blockIdx.x % (p.B * p.Hq);
+  const int qt = p.n_qtiles - 1 - blockIdx.x / (p.B * p.Hq);
+  const int b = bh / p.Hq, hq = bh % p.Hq;
+  const int hkv = hq / (p.Hq / p.Hkv);
+  const int q0 = qt * kTile;
+  const int causal_shift = p.Sk - p.Sq;  // query i may attend keys <= i + shift
+  int kv_end = p.Sk;
+  if (p.causal) kv_end = min(p.Sk, q0 + kTile + causal_shift);
+  const int n_kv = (kv_end + kTile - 1) / kTile;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmQ);
+    tma_prefetch_desc(&tmK);
+    tma_prefetch_desc(&tmV);
+  }
+  if (warp == 1 && lane == 0) {
+    mbar_init(q_full, 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&k_full[i], 1);
+      mbar_init(&v_full[i], 1);
+      mbar_init(&k_empty[i], 1);
+      mbar_init(&v_empty[i], 1);
+      mbar_init(&s_full[i], 1);
+      mbar_init(&s_free[i], 256);
+      mbar_init(&o_full[i], 1);
+      mbar_init(&o_free[i], 256);
+    }
+    mbar_init(p_full, 256);
+    mbar_init(p_free, 1);
+    fence_barrier_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(tmem_ptr, 512);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------- TMA producer
+    if (lane == 0) {
+      mbar_arrive_expect_tx(q_full, kTileBytes);
+      tma_load_4d(sQ, &tmQ, q_full, 0, hq, q0, b);
+      tma_load_4d(sQ + kHalfBytes, &tmQ, q_full, 64, hq, q0, b);
+      auto load_k = [&](int t) {
+        const int st = t & 1;
+        if (t >= 2) mbar_wait(&k_empty[st], ((t >> 1) - 1) & 1);
+        mbar_arrive_expect_tx(&k_full[st], kTileBytes);
+        tma_load_4d(sK + st * kTileBytes, &tmK, &k_full[st], 0, hkv, t * kTile, b, kEvictLast);
+        tma_load_4d(sK + st * kTileBytes + kHalfBytes, &tmK, &k_full[st], 64, hkv, t * kTile, b, kEvictLast);
+      };
+      load_k(0);
+      // K runs one tile ahead of V: K[j+1] is needed by the QK^T issued right after PV[j-1]
+      for (int j = 0; j < n_kv; ++j) {
+        if (j + 1 < n_kv) load_k(j + 1);
+        const int st = j & 1;
+        if (j >= 2) mbar_wait(&v_empty[st], ((j >> 1) - 1) & 1);
+        mbar_arrive_expect_tx(&v_full[st], kTileBytes);
+        tma_load_4d(sV + st * kTileBytes, &tmV, &v_full[st], 0, hkv, j * kTile, b, kEvictLast);
+        tma_load_4d(sV + st * kTileBytes + kHalfBytes, &tmV, &v_full[st], 64, hkv, j * kTile, b, kEvictLast);
+      }
+    }
+  } else if (warp == 1) {
+    // --------------------------------------------------------------- MMA issuer
+    if (lane == 0) {
+      constexpr uint32_t idesc_qk = umma_idesc_bf16(kTile, kTile, 0, 0);
+      constexpr uint32_t idesc_pv = umma_idesc_bf16(kTile, kHeadDim, 0, 1);
+      const uint32_t q_addr = smem_u32(sQ), p_addr = smem_u32(sP);
+      auto issue_qk = [&](int t) {
+        const int st = t & 1;
+        const uint32_t k_addr = smem_u32(sK + st * kTileBytes);
+        const uint32_t d = tmem_base + st * kTile;
+#pragma unroll
+        for (int kk = 0; kk < 8; ++kk) {
+          const uint32_t off = (kk >> 2) * kHalfBytes + (kk & 3) * 32;
+          umma_f16_ss(d, umma_smem_desc_sw128(q_addr + off, 16, 1024), umma_smem_desc_sw128(k_addr + off, 16, 1024),
+                      idesc_qk, kk != 0);
+        }
+        umma_commit(&s_full[st]);
+        umma_commit(&k_empty[st]);
+      };
+      mbar_wait(q_full, 0);
+      mbar_wait(&k_full[0], 0);
+      tc_fence_after();
+      issue_qk(0);
+      for (int j = 0; j < n_kv; ++j) {
+        if (j + 1 < n_kv) {
+          const int t = j + 1, st = t & 1;
+          mbar_wait(&k_full[st], (t >> 1) & 1);
+          if (t >= 2) mbar_wait(&s_free[st], ((t >> 1) - 1) & 1);
+          tc_fence_after();
+          issue_qk(t);
+        }
+        const int st = j & 1;
+        mbar_wait(&v_full[st], (j >> 1) & 1);
+        mbar_wait(p_full, j & 1);
+        if (j >= 2) mbar_wait(&o_free[st], ((j >> 1) - 1) & 1);
+        tc_fence_after();
+        const uint32_t v_addr = smem_u32(sV + st * kTileBytes);
+        const uint32_t d = tmem_base + 2 * kTile + st * kHeadDim;
+#pragma unroll
+        for (int kk = 0; kk < 8; ++kk) {
+          const uint32_t a_off = (kk >> 2) * kHalfBytes + (kk & 3) * 32;   // P: K-major, 16 keys per step
+          umma_f16_ss(d, umma_smem_desc_sw128(p_addr + a_off, 16, 1024),
+                      umma_smem_desc_sw128(v_addr + kk * 2048, kHalfBytes, 1024),  // V: MN-major
+                      idesc_pv, kk != 0);
+        }
+        umma_commit(&o_full[st]);
+        umma_commit(&v_empty[st]);
+        umma_commit(p_free);
+      }
+    }
+  } else {
+    // ----------------------------------------------------------- softmax warps
+    const int quarter = warp & 3;          // TMEM lane quarter this warp may access
+    const int half = (warp - 2) >> 2;      // which 64 columns of S / O this thread owns
+    const int row = quarter * 32 + lane;
+    const uint32_t lane_addr = uint32_t(quarter * 32) << 16;
+    const int q_pos = q0 + row + causal_shift;
+    float m = -CUDART_INF_F, l = 0.f, alpha_prev = 1.f;
+    float o[64];
+#pragma unroll
+    for (int i = 0; i < 64; ++i) o[i] = 0.f;
+    const uint32_t p_row = smem_u32(sP + half * kHalfBytes + row * 128);
+    const uint32_t sw = uint32_t(row & 7);
+
+    for (int j = 0; j < n_kv; ++j) {
+      const int sb = j & 1;
+      mbar_wait(&s_full[sb], (j >> 1) & 1);
+      tc_fence_after();
+      const uint32_t s_addr = tmem_base + lane_addr + sb * kTile + half * 64;
+      const int key0 = j * kTile + half * 64;
+      const bool need_mask = (p.causal && (key0 + 63 > q_pos)) || (key0 + 64 > p.Sk);
+      uint32_t r[32];
+      // pass 1: row maximum over this thread's 64 columns
+      float mx = -CUDART_INF_F;
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        tmem_ld_32x32b_x32(s_addr + c * 32, r);
+        tmem_ld_wait();
+        if (need_mask) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            const int key = key0 + c * 32 + i;
+            const bool ok = (key < p.Sk) && (!p.causal || key <= q_pos);
+            mx = fmaxf(mx, ok ? __uint_as_float(r[i]) : -CUDART_INF_F);
+          }
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(r[i]));
+        }
+      }
+      mx *= p.scale_log2;  // scale > 0, so max commutes with the scaling
+      float* xm = xmax + sb * 256;
+      xm[half * 128 + row] = mx;
+      named_bar_sync(1, 256);
+      const float m_new = fmaxf(m, fmaxf(mx, xm[(half ^ 1) * 128 + row]));
+      const float m_safe = (m_new == -CUDART_INF_F) ? 0.f : m_new;
+      const float alpha = exp2f(m - m_safe);
+      if (j > 0) mbar_wait(p_free, (j - 1) & 1);  // PV of the previous tile has consumed sP
+      // pass 2: probabilities -> bf16 -> swizzled smem (A operand of the PV MMA)
+      float lsum = 0.f;
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        tmem_ld_32x32b_x32(s_addr + c * 32, r);
+        tmem_ld_wait();
+        float pv[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          float e = exp2f(__uint_as_float(r[i]) * p.scale_log2 - m_safe);
+          if (need_mask) {
+            const int key = key0 + c * 32 + i;
+            const bool ok = (key < p.Sk) && (!p.causal || key <= q_pos);
+            e = ok ? e : 0.f;
+          }
+          pv[i] = e;
+          lsum += e;
+        }
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+          const uint32_t cc = uint32_t(c * 4 + t);
+          st_shared_v4(p_row + ((cc ^ sw) << 4), pack_bf16x2(pv[8 * t + 0], pv[8 * t + 1]),
+                       pack_bf16x2(pv[8 * t + 2], pv[8 * t + 3]), pack_bf16x2(pv[8 * t + 4], pv[8 * t + 5]),
+                       pack_bf16x2(pv[8 * t + 6], pv[8 * t + 7]));
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(&s_free[sb]);
+      fence_proxy_async_smem();
+      mbar_arrive(p_full);
+      l = l * alpha + lsum;
+      // fold in the PV result of the previous tile while the tensor core works on this one
+      if (j > 0) {
+        const int ob = (j - 1) & 1;
+        mbar_wait(&o_full[ob], ((j - 1) >> 1) & 1);
+        tc_fence_after();
+        const uint32_t o_addr = tmem_base + lane_addr + 2 * kTile + ob * kHeadDim + half * 64;
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          tmem_ld_32x32b_x32(o_addr + c * 32, r);
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) o[c * 32 + i] = o[c * 32 + i] * alpha_prev + __uint_as_float(r[i]);
+        }
+        tc_fence_before();
+        mbar_arrive(&o_free[ob]);
+      }
+      alpha_prev = alpha;
+      m = m_new;
+    }
+    {  // last tile's PV result
+      const int ob = (n_kv - 1) & 1;
+      mbar_wait(&o_full[ob], ((n_kv - 1) >> 1) & 1);
+      tc_fence_after();
+      const uint32_t o_addr = tmem_base + lane_addr + 2 * kTile + ob * kHeadDim + half * 64;
+      uint32_t r[32];
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        tmem_ld_32x32b_x32(o_addr + c * 32, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) o[c * 32 + i] = o[c * 32 + i] * alpha_prev + __uint_as_float(r[i]);
+      }
+    }
+    xsum[half * 128 + row] = l;
+    named_bar_sync(1, 256);
+    const float ltot = l + xsum[(half ^ 1) * 128 + row];
+    const float inv = (ltot > 0.f) ? 1.f / ltot : 0.f;
+    const int q = q0 + row;
+    if (q < p.Sq) {
+      __nv_bfloat16* dst = p.out + ((size_t(b) * p.Sq + q) * p.Hq + hq) * kHeadDim + half * 64;
+#pragma unroll
+      for (int t = 0; t < 8; ++t) {
+        *reinterpret_cast<uint4*>(dst + 8 * t) =
+            make_uint4(pack_bf16x2(o[8 * t + 0] * inv, o[8 * t + 1] * inv), pack_bf16x2(o[8 * t + 2] * inv, o[8 * t + 3] * inv),
+                       pack_bf16x2(o[8 * t + 4] * inv, o[8 * t + 5] * inv), pack_bf16x2(o[8 * t + 6] * inv, o[8 * t + 7] * inv));
+      }
+      if (half == 0)
+        p.lse[(size_t(b) * p.Hq + hq) * p.Sq + q] =
+            (ltot > 0.f) ? (m + log2f(ltot)) * 0.6931471805599453f : -CUDART_INF_F;
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem_base, 512);
+}
+
+}  // namespace stb
+
+using namespace stb;
+
+// q: [B,Sq,Hq,128], k/v: [B,Sk,Hkv,128] bf16 with element strides (batch, token, head); out: contiguous
+// [B,Sq,Hq,128] bf16; lse: [B,Hq,Sq] fp32.  causal: query i attends keys <= i + (Sk - Sq).
+extern "C" int stb_flash_attn_fwd(const void* q, const void* k, const void* v, void* out, float* lse, int B,
+                                  int Sq, int Sk, int Hq, int Hkv, int D, long q_sb, long q_ss, long q_sh,
+                                  long k_sb, long k_ss, long k_sh, long v_sb, long v_ss, long v_sh, float scale,
+                                  int causal, cudaStream_t stream) {
+  STB_REQUIRE(D == kHeadDim, "flash_attn: head_dim must be 128 (got %d)", D);
+  STB_REQUIRE(Hq % Hkv == 0, "flash_attn: Hq=%d must be a multiple of Hkv=%d", Hq, Hkv);
+  STB_REQUIRE(!causal || Sq <= Sk, "flash_attn: causal attention needs Sq <= Sk");
+  if (B == 0 || Sq == 0) return 0;
+  CUtensorMap tmQ, tmK, tmV;
+  if (int rc = make_tmap_bshd(&tmQ, q, B, Sq, Hq, D, q_sb, q_ss, q_sh, 64, kTile)) return rc;
+  if (int rc = make_tmap_bshd(&tmK, k, B, Sk, Hkv, D, k_sb, k_ss, k_sh, 64, kTile)) return rc;
+  if (int rc = make_tmap_bshd(&tmV, v, B, Sk, Hkv, D, v_sb, v_ss, v_sh, 64, kTile)) return rc;
+  AttnFwdParams p;
+  p.out = (__nv_bfloat16*)out;
+  p.lse = lse;
+  p.B = B; p.Sq = Sq; p.Sk = Sk; p.Hq = Hq; p.Hkv = Hkv;
+  p.n_qtiles = (Sq + kTile - 1) / kTile;
+  p.scale_log2 = scale * 1.4426950408889634f;
+  p.causal = causal;
+  static bool attr_set = false;
+  if (!attr_set) {
+    STB_CHECK_CUDA(cudaFuncSetAttribute(flash_attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        AttnSmem::kBytes));
+    attr_set = true;
+  }
+  const int grid = B * Hq * p.n_qtiles;
+  flash_attn_fwd_kernel<<<grid, kAttnThreads, AttnSmem::kBytes, stream>>>(tmQ, tmK, tmV, p);
+  STB_CHECK_LAUNCH();
+  return 0;
+}

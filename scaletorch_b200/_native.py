@@ -31,6 +31,11 @@ _SIGS = {
     "stb_rmsnorm_bwd_noalloc": [_P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int, _P],
     "stb_qknorm_rope_fwd": [_P, _P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_float, _P],
     "stb_qknorm_rope_bwd": [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, _P],
+    "stb_flash_attn_fwd": [_P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int, c_long, c_long, c_long, c_long,
+                           c_long, c_long, c_long, c_long, c_long, c_float, c_int, _P],
+    "stb_flash_attn_bwd": [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int,
+                           c_long, c_long, c_long, c_long, c_long, c_long, c_long, c_long, c_long,
+                           c_long, c_long, c_long, c_long, c_long, c_long, c_long, c_long, c_long, c_float, c_int, _P],
     "stb_swiglu_fwd": [_P, _P, c_long, c_int, _P],
     "stb_swiglu_bwd": [_P, _P, _P, c_long, c_int, _P],
     "stb_ce_stats": [_P, _P, _P, c_int, c_int, c_long, c_int, _P],

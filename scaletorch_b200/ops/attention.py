@@ -48,9 +48,15 @@ def attention_ref(q, k, v, causal=True, scale=None, q_offset: int = 0):
     return out, lse.reshape(B, Hq, Sq)
 
 
-def native_attention_available() -> bool:
+def native_attention_fwd_available() -> bool:
     lib = N.load()
     return lib is not None and hasattr(lib, "stb_flash_attn_fwd")
+
+
+def native_attention_available() -> bool:
+    """Forward *and* backward kernels present (what training needs)."""
+    lib = N.load()
+    return lib is not None and hasattr(lib, "stb_flash_attn_fwd") and hasattr(lib, "stb_flash_attn_bwd")
 
 
 def _flash_fwd(q, k, v, causal, scale):

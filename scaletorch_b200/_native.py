@@ -33,7 +33,7 @@ _SIGS = {
     "stb_qknorm_rope_bwd": [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, _P],
     "stb_flash_attn_fwd": [_P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int, c_long, c_long, c_long, c_long,
                            c_long, c_long, c_long, c_long, c_long, c_float, c_int, _P],
-    "stb_flash_attn_bwd": [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int,
+    "stb_flash_attn_bwd": [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int,
                            c_long, c_long, c_long, c_long, c_long, c_long, c_long, c_long, c_long,
                            c_long, c_long, c_long, c_long, c_long, c_long, c_long, c_long, c_long, c_float, c_int, _P],
     "stb_swiglu_fwd": [_P, _P, c_long, c_int, _P],

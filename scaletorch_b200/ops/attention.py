@@ -76,9 +76,8 @@ def _flash_bwd(do, q, k, v, out, lse, dq, dk, dv, causal, scale):
     B, Sq, Hq, D = q.shape
     Sk, Hkv = k.shape[1], k.shape[2]
     delta = torch.empty((B, Hq, Sq), dtype=torch.float32, device=q.device)
-    dq_acc = torch.zeros((B, Hq, Sq, D), dtype=torch.float32, device=q.device)
     N.call("stb_flash_attn_bwd", do.data_ptr(), q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr(),
-           lse.data_ptr(), delta.data_ptr(), dq_acc.data_ptr(), dq.data_ptr(), dk.data_ptr(), dv.data_ptr(),
+           lse.data_ptr(), delta.data_ptr(), dq.data_ptr(), dk.data_ptr(), dv.data_ptr(),
            B, Sq, Sk, Hq, Hkv, D,
            q.stride(0), q.stride(1), q.stride(2), k.stride(0), k.stride(1), k.stride(2),
            v.stride(0), v.stride(1), v.stride(2),

@@ -15,7 +15,8 @@
 //                                and feed dV += P^T dO, dK += dS^T Q whose accumulators stay in TMEM.
 //   3. attn_bwd_dq_kernel        one CTA per (batch, q-head, 128-query tile): Q,dO resident, streams 64-key K/V
 //                                tiles; S = Q K^T, dP = dO V^T, dQ += dS K accumulated in TMEM.
-// Warp roles in 2 and 3: warp 0 TMA producer, warp 1 MMA issuer, warps 2..5 one thread per accumulator row.
+// Warp roles in 2 and 3: warp 0 TMA producer, warp 1 MMA issuer, warps 2..9 elementwise work with two threads
+// per accumulator row (32 of the 64 streamed columns each).
 #include <math_constants.h>
 
 #include "common/host.h"
@@ -23,7 +24,7 @@
 
 namespace stb {
 
-constexpr int kBwdThreads = 192;
+constexpr int kBwdThreads = 320;  // warp 0 TMA, warp 1 MMA, warps 2..9 elementwise (2 threads per row)
 constexpr int kBT = 128;        // resident tile rows
 constexpr int kST = 64;         // streamed tile rows
 constexpr int kBigHalf = kBT * 128;   // [128 rows][64 bf16] = 16 KB
@@ -31,6 +32,7 @@ constexpr int kBigTile = 2 * kBigHalf;
 constexpr int kSmallHalf = kST * 128; // [64 rows][64 bf16] = 8 KB
 constexpr int kSmallTile = 2 * kSmallHalf;
 constexpr float kLog2e = 1.4426950408889634f;
+constexpr int kRing = 3;        // streamed-tile ring depth (2 exposes the TMA latency every iteration)
 
 struct AttnBwdParams {
   const __nv_bfloat16* dout;   // [B,Sq,Hq,128] contiguous
@@ -70,9 +72,9 @@ __global__ void __launch_bounds__(256)
 struct DkvSmem {
   static constexpr int kK = 0;
   static constexpr int kV = kK + kBigTile;
-  static constexpr int kQ = kV + kBigTile;             // 2 stages x 16 KB
-  static constexpr int kDO = kQ + 2 * kSmallTile;      // 2 stages x 16 KB
-  static constexpr int kPT = kDO + 2 * kSmallTile;     // [128 keys][64 q] 16 KB
+  static constexpr int kQ = kV + kBigTile;             // kRing stages x 16 KB
+  static constexpr int kDO = kQ + kRing * kSmallTile;  // kRing stages x 16 KB
+  static constexpr int kPT = kDO + kRing * kSmallTile; // [128 keys][64 q] 16 KB
   static constexpr int kDST = kPT + kBigHalf;          // [128 keys][64 q] 16 KB
   static constexpr int kStat = kDST + kBigHalf;        // float lse2[2][64], delta[2][64]
   static constexpr int kBar = kStat + 4 * 64 * 4;
@@ -95,14 +97,14 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
   float* s_delta = s_lse + 128;                                    // [2][64]
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + DkvSmem::kBar);
   uint64_t* kv_full = bars + 0;
-  uint64_t* qdo_full = bars + 1;   // [2]
-  uint64_t* qdo_empty = bars + 3;  // [2]
-  uint64_t* sdp_full = bars + 5;   // [2]  S^T and dP^T of an iteration are in TMEM
-  uint64_t* st_free = bars + 7;    // [2]  softmax threads have drained that TMEM pair
-  uint64_t* pds_full = bars + 9;   //      P^T / dS^T are in smem
-  uint64_t* pds_free = bars + 10;  //      dV / dK MMAs have consumed them
-  uint64_t* acc_full = bars + 11;  //      all MMAs retired: dV / dK final
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 12);
+  uint64_t* qdo_full = bars + 1;   // [kRing]
+  uint64_t* qdo_empty = bars + 4;  // [kRing]
+  uint64_t* sdp_full = bars + 7;   // [2]  S^T and dP^T of an iteration are in TMEM
+  uint64_t* st_free = bars + 9;    // [2]  softmax threads have drained that TMEM pair
+  uint64_t* pds_full = bars + 11;  //      P^T / dS^T are in smem
+  uint64_t* pds_free = bars + 12;  //      dV / dK MMAs have consumed them
+  uint64_t* acc_full = bars + 13;  //      all MMAs retired: dV / dK final
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 14);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n_kvt = (p.Sk + kBT - 1) / kBT;
@@ -123,13 +125,15 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
   }
   if (warp == 1 && lane == 0) {
     mbar_init(kv_full, 1);
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < kRing; ++i) {
       mbar_init(&qdo_full[i], 1);
       mbar_init(&qdo_empty[i], 1);
-      mbar_init(&sdp_full[i], 1);
-      mbar_init(&st_free[i], 128);
     }
-    mbar_init(pds_full, 128);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&sdp_full[i], 1);
+      mbar_init(&st_free[i], 256);
+    }
+    mbar_init(pds_full, 256);
     mbar_init(pds_free, 1);
     mbar_init(acc_full, 1);
     fence_barrier_init();
@@ -152,10 +156,10 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
       tma_load_4d(sV, &tmV, kv_full, 0, hkv, kv0, b);
       tma_load_4d(sV + kBigHalf, &tmV, kv_full, 64, hkv, kv0, b);
       for (int i = 0; i < n_iter; ++i) {
-        const int st = i & 1;
+        const int st = i % kRing;
         const int hq = hkv * G + i / per_head;
         const int q0 = (qt_start + i % per_head) * kST;
-        if (i >= 2) mbar_wait(&qdo_empty[st], ((i >> 1) - 1) & 1);
+        if (i >= kRing) mbar_wait(&qdo_empty[st], ((i / kRing) - 1) & 1);
         mbar_arrive_expect_tx(&qdo_full[st], 2 * kSmallTile);
         tma_load_4d(sQ + st * kSmallTile, &tmQ, &qdo_full[st], 0, hq, q0, b);
         tma_load_4d(sQ + st * kSmallTile + kSmallHalf, &tmQ, &qdo_full[st], 64, hq, q0, b);
@@ -169,30 +173,30 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
       constexpr uint32_t idesc_g = umma_idesc_bf16(kBT, 128, 0, 1);    // [128 keys] x [128 D], K = q, B MN-major
       const uint32_t k_addr = smem_u32(sK), v_addr = smem_u32(sV), pt_addr = smem_u32(sPT), dst_addr = smem_u32(sDST);
       auto issue_sdp = [&](int i) {
-        const int st = i & 1;
-        mbar_wait(&qdo_full[st], (i >> 1) & 1);
-        if (i >= 2) mbar_wait(&st_free[st], ((i >> 1) - 1) & 1);
+        const int st = i % kRing, tb = i & 1;
+        mbar_wait(&qdo_full[st], (i / kRing) & 1);
+        if (i >= 2) mbar_wait(&st_free[tb], ((i >> 1) - 1) & 1);
         tc_fence_after();
         const uint32_t q_addr = smem_u32(sQ + st * kSmallTile), do_addr = smem_u32(sDO + st * kSmallTile);
 #pragma unroll
         for (int kk = 0; kk < 8; ++kk) {
           const uint32_t a_off = (kk >> 2) * kBigHalf + (kk & 3) * 32, b_off = (kk >> 2) * kSmallHalf + (kk & 3) * 32;
-          umma_f16_ss(tmem_base + st * kST, umma_smem_desc_sw128(k_addr + a_off, 16, 1024),
+          umma_f16_ss(tmem_base + tb * kST, umma_smem_desc_sw128(k_addr + a_off, 16, 1024),
                       umma_smem_desc_sw128(q_addr + b_off, 16, 1024), idesc_s, kk != 0);
         }
 #pragma unroll
         for (int kk = 0; kk < 8; ++kk) {
           const uint32_t a_off = (kk >> 2) * kBigHalf + (kk & 3) * 32, b_off = (kk >> 2) * kSmallHalf + (kk & 3) * 32;
-          umma_f16_ss(tmem_base + 128 + st * kST, umma_smem_desc_sw128(v_addr + a_off, 16, 1024),
+          umma_f16_ss(tmem_base + 128 + tb * kST, umma_smem_desc_sw128(v_addr + a_off, 16, 1024),
                       umma_smem_desc_sw128(do_addr + b_off, 16, 1024), idesc_s, kk != 0);
         }
-        umma_commit(&sdp_full[st]);
+        umma_commit(&sdp_full[tb]);
       };
       mbar_wait(kv_full, 0);
       issue_sdp(0);
       for (int i = 0; i < n_iter; ++i) {
         if (i + 1 < n_iter) issue_sdp(i + 1);
-        const int st = i & 1;
+        const int st = i % kRing;
         mbar_wait(pds_full, i & 1);
         tc_fence_after();
         const uint32_t q_addr = smem_u32(sQ + st * kSmallTile), do_addr = smem_u32(sDO + st * kSmallTile);
@@ -210,10 +214,11 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
       umma_commit(acc_full);
     }
   } else {
-    // one thread per key row
+    // two threads per key row: `half` selects 32 of the 64 query columns of the streamed tile
     const int quarter = warp & 3;
+    const int half = (warp - 2) >> 2;
     const int row = quarter * 32 + lane;
-    const int tid = threadIdx.x - 64;             // 0..127
+    const int tid = threadIdx.x - 64;             // 0..255
     const uint32_t lane_addr = uint32_t(quarter * 32) << 16;
     const int key = kv0 + row;
     const bool key_ok = key < p.Sk;
@@ -224,8 +229,8 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
       const int hq = hkv * G + i / per_head;
       const int q0 = (qt_start + i % per_head) * kST;
       // stage this tile's lse / delta (issued before the wait so the latency hides behind the MMAs)
-      float stat;
-      {
+      float stat = 0.f;
+      if (tid < 128) {
         const int c = tid & 63, q = q0 + c;
         const size_t idx = (size_t(b) * p.Hq + hq) * p.Sq + q;
         if (tid < 64) stat = (q < p.Sq) ? p.lse[idx] * kLog2e : CUDART_INF_F;
@@ -233,48 +238,34 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
       }
       mbar_wait(&sdp_full[sb], (i >> 1) & 1);
       tc_fence_after();
-      if (tid < 64) s_lse[sb * 64 + tid] = stat; else s_delta[sb * 64 + (tid - 64)] = stat;
-      named_bar_sync(2, 128);
-      const float* lse2 = s_lse + sb * 64;
-      const float* dl = s_delta + sb * 64;
-      float pr[64];
-      uint32_t r[32];
-      const int qpos0 = q0 + shift;  // key visible to query column c iff key <= qpos0 + c
+      if (tid < 64) s_lse[sb * 64 + tid] = stat; else if (tid < 128) s_delta[sb * 64 + (tid - 64)] = stat;
+      named_bar_sync(2, 256);
+      const float* lse2 = s_lse + sb * 64 + half * 32;
+      const float* dl = s_delta + sb * 64 + half * 32;
+      uint32_t r0[32], r1[32];
+      tmem_ld_32x32b_x32(tmem_base + lane_addr + sb * kST + half * 32, r0);          // S^T
+      tmem_ld_32x32b_x32(tmem_base + lane_addr + 128 + sb * kST + half * 32, r1);    // dP^T
+      tmem_ld_wait();
+      tc_fence_before();
+      mbar_arrive(&st_free[sb]);
+      float pr[32], ds[32];
+      const int qpos0 = q0 + shift + half * 32;  // key visible to query column c iff key <= qpos0 + c
 #pragma unroll
-      for (int c = 0; c < 2; ++c) {
-        tmem_ld_32x32b_x32(tmem_base + lane_addr + sb * kST + c * 32, r);
-        tmem_ld_wait();
-#pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          const int col = c * 32 + j;
-          float e = exp2f(__uint_as_float(r[j]) * p.scale_log2 - lse2[col]);
-          const bool ok = key_ok && (!p.causal || key <= qpos0 + col);
-          pr[col] = ok ? e : 0.f;
-        }
+      for (int j = 0; j < 32; ++j) {
+        const float e = exp2f(__uint_as_float(r0[j]) * p.scale_log2 - lse2[j]);
+        const bool ok = key_ok && (!p.causal || key <= qpos0 + j);
+        pr[j] = ok ? e : 0.f;
+        ds[j] = pr[j] * (__uint_as_float(r1[j]) - dl[j]) * p.scale;
       }
       if (i > 0) mbar_wait(pds_free, (i - 1) & 1);
 #pragma unroll
-      for (int t = 0; t < 8; ++t)
-        st_shared_v4(pt_row + ((uint32_t(t) ^ sw) << 4), pack_bf16x2(pr[8 * t + 0], pr[8 * t + 1]),
-                     pack_bf16x2(pr[8 * t + 2], pr[8 * t + 3]), pack_bf16x2(pr[8 * t + 4], pr[8 * t + 5]),
-                     pack_bf16x2(pr[8 * t + 6], pr[8 * t + 7]));
-#pragma unroll
-      for (int c = 0; c < 2; ++c) {
-        tmem_ld_32x32b_x32(tmem_base + lane_addr + 128 + sb * kST + c * 32, r);
-        tmem_ld_wait();
-#pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          const int col = c * 32 + j;
-          pr[col] = pr[col] * (__uint_as_float(r[j]) - dl[col]) * p.scale;
-        }
+      for (int t = 0; t < 4; ++t) {
+        const uint32_t cc = (uint32_t(half * 4 + t) ^ sw) << 4;
+        st_shared_v4(pt_row + cc, pack_bf16x2(pr[8 * t + 0], pr[8 * t + 1]), pack_bf16x2(pr[8 * t + 2], pr[8 * t + 3]),
+                     pack_bf16x2(pr[8 * t + 4], pr[8 * t + 5]), pack_bf16x2(pr[8 * t + 6], pr[8 * t + 7]));
+        st_shared_v4(dst_row + cc, pack_bf16x2(ds[8 * t + 0], ds[8 * t + 1]), pack_bf16x2(ds[8 * t + 2], ds[8 * t + 3]),
+                     pack_bf16x2(ds[8 * t + 4], ds[8 * t + 5]), pack_bf16x2(ds[8 * t + 6], ds[8 * t + 7]));
       }
-#pragma unroll
-      for (int t = 0; t < 8; ++t)
-        st_shared_v4(dst_row + ((uint32_t(t) ^ sw) << 4), pack_bf16x2(pr[8 * t + 0], pr[8 * t + 1]),
-                     pack_bf16x2(pr[8 * t + 2], pr[8 * t + 3]), pack_bf16x2(pr[8 * t + 4], pr[8 * t + 5]),
-                     pack_bf16x2(pr[8 * t + 6], pr[8 * t + 7]));
-      tc_fence_before();
-      mbar_arrive(&st_free[sb]);
       fence_proxy_async_smem();
       mbar_arrive(pds_full);
     }
@@ -290,7 +281,7 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
                  sh_ = which == 0 ? p.dv_sh : p.dk_sh;
       __nv_bfloat16* dst = base + b * sb_ + long(key) * ss_ + hkv * sh_;
 #pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
+      for (int c = half * 2; c < half * 2 + 2; ++c) {
         uint32_t r[32];
         if (n_iter > 0) {
           tmem_ld_32x32b_x32(tmem_base + lane_addr + 256 + which * 128 + c * 32, r);
@@ -320,9 +311,9 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
 struct DqSmem {
   static constexpr int kQ = 0;
   static constexpr int kDO = kQ + kBigTile;
-  static constexpr int kK = kDO + kBigTile;            // 2 stages x 16 KB
-  static constexpr int kV = kK + 2 * kSmallTile;       // 2 stages x 16 KB
-  static constexpr int kDS = kV + 2 * kSmallTile;      // [128 q][64 keys] 16 KB
+  static constexpr int kK = kDO + kBigTile;            // kRing stages x 16 KB
+  static constexpr int kV = kK + kRing * kSmallTile;   // kRing stages x 16 KB
+  static constexpr int kDS = kV + kRing * kSmallTile;  // [128 q][64 keys] 16 KB
   static constexpr int kBar = kDS + kBigHalf;
   static constexpr int kBytes = kBar + 256 + 1024;
 };
@@ -340,14 +331,14 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
   uint8_t* sDS = smem + DqSmem::kDS;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + DqSmem::kBar);
   uint64_t* qdo_full = bars + 0;
-  uint64_t* kv_full = bars + 1;    // [2]
-  uint64_t* kv_empty = bars + 3;   // [2]
-  uint64_t* sdp_full = bars + 5;   // [2]
-  uint64_t* st_free = bars + 7;    // [2]
-  uint64_t* ds_full = bars + 9;
-  uint64_t* ds_free = bars + 10;
-  uint64_t* acc_full = bars + 11;
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 12);
+  uint64_t* kv_full = bars + 1;    // [kRing]
+  uint64_t* kv_empty = bars + 4;   // [kRing]
+  uint64_t* sdp_full = bars + 7;   // [2]
+  uint64_t* st_free = bars + 9;    // [2]
+  uint64_t* ds_full = bars + 11;
+  uint64_t* ds_free = bars + 12;
+  uint64_t* acc_full = bars + 13;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 14);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n_qt = (p.Sq + kBT - 1) / kBT;
@@ -366,13 +357,15 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
   }
   if (warp == 1 && lane == 0) {
     mbar_init(qdo_full, 1);
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < kRing; ++i) {
       mbar_init(&kv_full[i], 1);
       mbar_init(&kv_empty[i], 1);
-      mbar_init(&sdp_full[i], 1);
-      mbar_init(&st_free[i], 128);
     }
-    mbar_init(ds_full, 128);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&sdp_full[i], 1);
+      mbar_init(&st_free[i], 256);
+    }
+    mbar_init(ds_full, 256);
     mbar_init(ds_free, 1);
     mbar_init(acc_full, 1);
     fence_barrier_init();
@@ -395,8 +388,8 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
       tma_load_4d(sDO, &tmDO, qdo_full, 0, hq, q0, b);
       tma_load_4d(sDO + kBigHalf, &tmDO, qdo_full, 64, hq, q0, b);
       for (int i = 0; i < n_iter; ++i) {
-        const int st = i & 1;
-        if (i >= 2) mbar_wait(&kv_empty[st], ((i >> 1) - 1) & 1);
+        const int st = i % kRing;
+        if (i >= kRing) mbar_wait(&kv_empty[st], ((i / kRing) - 1) & 1);
         mbar_arrive_expect_tx(&kv_full[st], 2 * kSmallTile);
         tma_load_4d(sK + st * kSmallTile, &tmK, &kv_full[st], 0, hkv, i * kST, b, kEvictLast);
         tma_load_4d(sK + st * kSmallTile + kSmallHalf, &tmK, &kv_full[st], 64, hkv, i * kST, b, kEvictLast);
@@ -410,30 +403,30 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
       constexpr uint32_t idesc_g = umma_idesc_bf16(kBT, 128, 0, 1);   // [128 q] x [128 D], K = keys, B MN-major
       const uint32_t q_addr = smem_u32(sQ), do_addr = smem_u32(sDO), ds_addr = smem_u32(sDS);
       auto issue_sdp = [&](int i) {
-        const int st = i & 1;
-        mbar_wait(&kv_full[st], (i >> 1) & 1);
-        if (i >= 2) mbar_wait(&st_free[st], ((i >> 1) - 1) & 1);
+        const int st = i % kRing, tb = i & 1;
+        mbar_wait(&kv_full[st], (i / kRing) & 1);
+        if (i >= 2) mbar_wait(&st_free[tb], ((i >> 1) - 1) & 1);
         tc_fence_after();
         const uint32_t k_addr = smem_u32(sK + st * kSmallTile), v_addr = smem_u32(sV + st * kSmallTile);
 #pragma unroll
         for (int kk = 0; kk < 8; ++kk) {
           const uint32_t a_off = (kk >> 2) * kBigHalf + (kk & 3) * 32, b_off = (kk >> 2) * kSmallHalf + (kk & 3) * 32;
-          umma_f16_ss(tmem_base + st * kST, umma_smem_desc_sw128(q_addr + a_off, 16, 1024),
+          umma_f16_ss(tmem_base + tb * kST, umma_smem_desc_sw128(q_addr + a_off, 16, 1024),
                       umma_smem_desc_sw128(k_addr + b_off, 16, 1024), idesc_s, kk != 0);
         }
 #pragma unroll
         for (int kk = 0; kk < 8; ++kk) {
           const uint32_t a_off = (kk >> 2) * kBigHalf + (kk & 3) * 32, b_off = (kk >> 2) * kSmallHalf + (kk & 3) * 32;
-          umma_f16_ss(tmem_base + 128 + st * kST, umma_smem_desc_sw128(do_addr + a_off, 16, 1024),
+          umma_f16_ss(tmem_base + 128 + tb * kST, umma_smem_desc_sw128(do_addr + a_off, 16, 1024),
                       umma_smem_desc_sw128(v_addr + b_off, 16, 1024), idesc_s, kk != 0);
         }
-        umma_commit(&sdp_full[st]);
+        umma_commit(&sdp_full[tb]);
       };
       mbar_wait(qdo_full, 0);
       issue_sdp(0);
       for (int i = 0; i < n_iter; ++i) {
         if (i + 1 < n_iter) issue_sdp(i + 1);
-        const int st = i & 1;
+        const int st = i % kRing;
         mbar_wait(ds_full, i & 1);
         tc_fence_after();
         const uint32_t k_addr = smem_u32(sK + st * kSmallTile);
@@ -448,6 +441,7 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
     }
   } else {
     const int quarter = warp & 3;
+    const int half = (warp - 2) >> 2;     // which 32 of the 64 streamed key columns
     const int row = quarter * 32 + lane;
     const uint32_t lane_addr = uint32_t(quarter * 32) << 16;
     const int q = q0 + row;
@@ -460,38 +454,29 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
     const uint32_t sw = uint32_t(row & 7);
     for (int i = 0; i < n_iter; ++i) {
       const int sb = i & 1;
-      const int key0 = i * kST;
+      const int key0 = i * kST + half * 32;
       mbar_wait(&sdp_full[sb], (i >> 1) & 1);
       tc_fence_after();
-      float pr[64];
-      uint32_t r[32];
-#pragma unroll
-      for (int c = 0; c < 2; ++c) {
-        tmem_ld_32x32b_x32(tmem_base + lane_addr + sb * kST + c * 32, r);
-        tmem_ld_wait();
-#pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          const int key = key0 + c * 32 + j;
-          const float e = exp2f(__uint_as_float(r[j]) * p.scale_log2 - lse2);
-          const bool ok = (key < p.Sk) && (!p.causal || key <= q_pos);
-          pr[c * 32 + j] = ok ? e : 0.f;
-        }
-      }
-#pragma unroll
-      for (int c = 0; c < 2; ++c) {
-        tmem_ld_32x32b_x32(tmem_base + lane_addr + 128 + sb * kST + c * 32, r);
-        tmem_ld_wait();
-#pragma unroll
-        for (int j = 0; j < 32; ++j) pr[c * 32 + j] = pr[c * 32 + j] * (__uint_as_float(r[j]) - dl) * p.scale;
-      }
+      uint32_t r0[32], r1[32];
+      tmem_ld_32x32b_x32(tmem_base + lane_addr + sb * kST + half * 32, r0);          // S
+      tmem_ld_32x32b_x32(tmem_base + lane_addr + 128 + sb * kST + half * 32, r1);    // dP
+      tmem_ld_wait();
       tc_fence_before();
       mbar_arrive(&st_free[sb]);
+      float ds[32];
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        const int key = key0 + j;
+        const float e = exp2f(__uint_as_float(r0[j]) * p.scale_log2 - lse2);
+        const bool ok = (key < p.Sk) && (!p.causal || key <= q_pos);
+        ds[j] = (ok ? e : 0.f) * (__uint_as_float(r1[j]) - dl) * p.scale;
+      }
       if (i > 0) mbar_wait(ds_free, (i - 1) & 1);
 #pragma unroll
-      for (int t = 0; t < 8; ++t)
-        st_shared_v4(ds_row + ((uint32_t(t) ^ sw) << 4), pack_bf16x2(pr[8 * t + 0], pr[8 * t + 1]),
-                     pack_bf16x2(pr[8 * t + 2], pr[8 * t + 3]), pack_bf16x2(pr[8 * t + 4], pr[8 * t + 5]),
-                     pack_bf16x2(pr[8 * t + 6], pr[8 * t + 7]));
+      for (int t = 0; t < 4; ++t)
+        st_shared_v4(ds_row + ((uint32_t(half * 4 + t) ^ sw) << 4), pack_bf16x2(ds[8 * t + 0], ds[8 * t + 1]),
+                     pack_bf16x2(ds[8 * t + 2], ds[8 * t + 3]), pack_bf16x2(ds[8 * t + 4], ds[8 * t + 5]),
+                     pack_bf16x2(ds[8 * t + 6], ds[8 * t + 7]));
       fence_proxy_async_smem();
       mbar_arrive(ds_full);
     }
@@ -499,7 +484,7 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
     tc_fence_after();
     __nv_bfloat16* dst = p.dq + b * p.dq_sb + long(q) * p.dq_ss + hq * p.dq_sh;
 #pragma unroll 1
-    for (int c = 0; c < 4; ++c) {
+    for (int c = half * 2; c < half * 2 + 2; ++c) {
       uint32_t r[32];
       tmem_ld_32x32b_x32(tmem_base + lane_addr + 256 + c * 32, r);
       tmem_ld_wait();

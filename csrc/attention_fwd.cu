@@ -9,10 +9,12 @@
 // (scaletorch/models/attention_utils.py:130-152, scaletorch/models/model_qwen3.py:219-238) and the eager
 // per-block attention of scaletorch/parallel/context_parallel/context_parallel.py:266-302.
 //
-// One CTA per (batch, q-head, 128-query tile), 10 warps:
+// One CTA per (batch, q-head, 128-query tile), 12 warps in 3 warpgroups (setmaxnreg moves registers from
+// warpgroup 0 to the softmax warpgroups):
 //   warp 0      TMA producer: Q once, K/V tiles of 128 keys through a 2-stage ring (4-D tensor maps)
 //   warp 1      MMA issuer  : S = Q K^T (128x128x128) and O_j = P V (128x128x128), accumulators in TMEM
-//   warps 2..9  softmax     : two threads per query row (64 score columns / 64 output columns each):
+//   warp 2      TMEM allocation
+//   warps 4..11 softmax     : two threads per query row (64 score columns / 64 output columns each):
 //               tcgen05.ld S -> online max / exp2 -> P (bf16) into 128B-swizzled smem for the PV MMA;
 //               the running output is kept in registers and rescaled when the row max grows.
 // TMEM: S and O_j are both double-buffered (4 x 128 columns) so QK^T of tile j+1 and PV of tile j run
@@ -24,7 +26,7 @@
 
 namespace stb {
 
-constexpr int kAttnThreads = 320;
+constexpr int kAttnThreads = 384;  // warpgroup 0: TMA / MMA / TMEM-alloc warps; warpgroups 1,2: softmax
 constexpr int kTile = 128;  // query rows per CTA and keys per step
 constexpr int kHeadDim = 128;
 constexpr int kHalfBytes = kTile * 128;      // one [128 rows][64 bf16] swizzled half tile = 16 KB
@@ -118,6 +120,8 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
 
+  if (warp < 4) {
+  setmaxnreg_dec<40>();
   if (warp == 0) {
     // ------------------------------------------------------------- TMA producer
     if (lane == 0) {
@@ -192,10 +196,12 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
         umma_commit(p_free);
       }
     }
+  }
   } else {
+    setmaxnreg_inc<224>();
     // ----------------------------------------------------------- softmax warps
     const int quarter = warp & 3;          // TMEM lane quarter this warp may access
-    const int half = (warp - 2) >> 2;      // which 64 columns of S / O this thread owns
+    const int half = (warp - 4) >> 2;      // which 64 columns of S / O this thread owns
     const int row = quarter * 32 + lane;
     const uint32_t lane_addr = uint32_t(quarter * 32) << 16;
     const int q_pos = q0 + row + causal_shift;
@@ -213,61 +219,53 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
       const uint32_t s_addr = tmem_base + lane_addr + sb * kTile + half * 64;
       const int key0 = j * kTile + half * 64;
       const bool need_mask = (p.causal && (key0 + 63 > q_pos)) || (key0 + 64 > p.Sk);
-      uint32_t r[32];
-      // pass 1: row maximum over this thread's 64 columns
-      float mx = -CUDART_INF_F;
+      // one TMEM read of this thread's 64 score columns; everything else happens in registers
+      uint32_t r0[32], r1[32];
+      tmem_ld_32x32b_x32(s_addr, r0);
+      tmem_ld_32x32b_x32(s_addr + 32, r1);
+      tmem_ld_wait();
+      tc_fence_before();
+      mbar_arrive(&s_free[sb]);          // S buffer may be overwritten by QK^T of tile j+2
+      float sc[64];   // raw scores; the softmax scale is folded into the exp2 FFMA below
 #pragma unroll
-      for (int c = 0; c < 2; ++c) {
-        tmem_ld_32x32b_x32(s_addr + c * 32, r);
-        tmem_ld_wait();
-        if (need_mask) {
+      for (int i = 0; i < 32; ++i) {
+        sc[i] = __uint_as_float(r0[i]);
+        sc[32 + i] = __uint_as_float(r1[i]);
+      }
+      if (need_mask) {
 #pragma unroll
-          for (int i = 0; i < 32; ++i) {
-            const int key = key0 + c * 32 + i;
-            const bool ok = (key < p.Sk) && (!p.causal || key <= q_pos);
-            mx = fmaxf(mx, ok ? __uint_as_float(r[i]) : -CUDART_INF_F);
-          }
-        } else {
-#pragma unroll
-          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(r[i]));
+        for (int i = 0; i < 64; ++i) {
+          const int key = key0 + i;
+          const bool ok = (key < p.Sk) && (!p.causal || key <= q_pos);
+          sc[i] = ok ? sc[i] : -CUDART_INF_F;
         }
       }
-      mx *= p.scale_log2;  // scale > 0, so max commutes with the scaling
+      float mx = sc[0];
+#pragma unroll
+      for (int i = 1; i < 64; ++i) mx = fmaxf(mx, sc[i]);
+      mx *= p.scale_log2;   // scale > 0: max commutes with the scaling
       float* xm = xmax + sb * 256;
       xm[half * 128 + row] = mx;
       named_bar_sync(1, 256);
       const float m_new = fmaxf(m, fmaxf(mx, xm[(half ^ 1) * 128 + row]));
       const float m_safe = (m_new == -CUDART_INF_F) ? 0.f : m_new;
       const float alpha = exp2f(m - m_safe);
-      if (j > 0) mbar_wait(p_free, (j - 1) & 1);  // PV of the previous tile has consumed sP
-      // pass 2: probabilities -> bf16 -> swizzled smem (A operand of the PV MMA)
-      float lsum = 0.f;
+      float ls0 = 0.f, ls1 = 0.f, ls2 = 0.f, ls3 = 0.f;
+      const float neg_m = -m_safe;
 #pragma unroll
-      for (int c = 0; c < 2; ++c) {
-        tmem_ld_32x32b_x32(s_addr + c * 32, r);
-        tmem_ld_wait();
-        float pv[32];
-#pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          float e = exp2f(__uint_as_float(r[i]) * p.scale_log2 - m_safe);
-          if (need_mask) {
-            const int key = key0 + c * 32 + i;
-            const bool ok = (key < p.Sk) && (!p.causal || key <= q_pos);
-            e = ok ? e : 0.f;
-          }
-          pv[i] = e;
-          lsum += e;
-        }
-#pragma unroll
-        for (int t = 0; t < 4; ++t) {
-          const uint32_t cc = uint32_t(c * 4 + t);
-          st_shared_v4(p_row + ((cc ^ sw) << 4), pack_bf16x2(pv[8 * t + 0], pv[8 * t + 1]),
-                       pack_bf16x2(pv[8 * t + 2], pv[8 * t + 3]), pack_bf16x2(pv[8 * t + 4], pv[8 * t + 5]),
-                       pack_bf16x2(pv[8 * t + 6], pv[8 * t + 7]));
-        }
+      for (int i = 0; i < 64; i += 4) {   // masked entries: exp2(-inf) = 0
+        sc[i + 0] = exp2f(fmaf(sc[i + 0], p.scale_log2, neg_m)); ls0 += sc[i + 0];
+        sc[i + 1] = exp2f(fmaf(sc[i + 1], p.scale_log2, neg_m)); ls1 += sc[i + 1];
+        sc[i + 2] = exp2f(fmaf(sc[i + 2], p.scale_log2, neg_m)); ls2 += sc[i + 2];
+        sc[i + 3] = exp2f(fmaf(sc[i + 3], p.scale_log2, neg_m)); ls3 += sc[i + 3];
       }
-      tc_fence_before();
-      mbar_arrive(&s_free[sb]);
+      const float lsum = (ls0 + ls1) + (ls2 + ls3);
+      if (j > 0) mbar_wait(p_free, (j - 1) & 1);  // PV of the previous tile has consumed sP
+#pragma unroll
+      for (int t = 0; t < 8; ++t)
+        st_shared_v4(p_row + ((uint32_t(t) ^ sw) << 4), pack_bf16x2(sc[8 * t + 0], sc[8 * t + 1]),
+                     pack_bf16x2(sc[8 * t + 2], sc[8 * t + 3]), pack_bf16x2(sc[8 * t + 4], sc[8 * t + 5]),
+                     pack_bf16x2(sc[8 * t + 6], sc[8 * t + 7]));
       fence_proxy_async_smem();
       mbar_arrive(p_full);
       l = l * alpha + lsum;
@@ -277,15 +275,16 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
         mbar_wait(&o_full[ob], ((j - 1) >> 1) & 1);
         tc_fence_after();
         const uint32_t o_addr = tmem_base + lane_addr + 2 * kTile + ob * kHeadDim + half * 64;
-#pragma unroll
-        for (int c = 0; c < 2; ++c) {
-          tmem_ld_32x32b_x32(o_addr + c * 32, r);
-          tmem_ld_wait();
-#pragma unroll
-          for (int i = 0; i < 32; ++i) o[c * 32 + i] = o[c * 32 + i] * alpha_prev + __uint_as_float(r[i]);
-        }
+        tmem_ld_32x32b_x32(o_addr, r0);
+        tmem_ld_32x32b_x32(o_addr + 32, r1);
+        tmem_ld_wait();
         tc_fence_before();
         mbar_arrive(&o_free[ob]);
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          o[i] = o[i] * alpha_prev + __uint_as_float(r0[i]);
+          o[32 + i] = o[32 + i] * alpha_prev + __uint_as_float(r1[i]);
+        }
       }
       alpha_prev = alpha;
       m = m_new;

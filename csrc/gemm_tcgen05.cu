@@ -406,13 +406,16 @@ static int launch_gemm(const void* A, const void* B, void* C, int M, int N, int 
 }
 
 static int pick_bn(int M, int N) {
+  // ncu (profiles/ncu_r1a_summary.md): the 128x128 tile needs 128 B/cycle/SM from L2 and starves the tensor
+  // pipe; 128x256 needs 96 B/cycle.  Use the wide tile whenever N allows it and the narrow one only when it
+  // avoids a mostly idle last wave on small problems.
   if (N <= 128) return 128;
   const int sms = sm_count();
   const long tm = (M + kBM - 1) / kBM;
-  const long t256 = tm * ((N + 255) / 256), t128 = tm * ((N + 127) / 128);
-  // cost ~ waves * tile_work ; 256-wide tiles do twice the work per wave
-  const long c256 = ((t256 + sms - 1) / sms) * 2, c128 = (t128 + sms - 1) / sms;
-  return (c128 < c256) ? 128 : 256;
+  const long t256 = tm * ((N + 255) / 256);
+  if (t256 >= sms) return 256;
+  const long t128 = tm * ((N + 127) / 128);
+  return (t128 <= sms) ? 128 : 256;
 }
 
 }  // namespace stb

@@ -27,7 +27,7 @@ def gemm(
     a_mn: bool = False,
     b_mn: bool = False,
     out: torch.Tensor | None = None,
-    out_dtype: torch.dtype = torch.bfloat16,
+    out_dtype: torch.dtype | None = None,
     accumulate: bool = False,
     force_bn: int = 0,
 ) -> torch.Tensor:
@@ -41,7 +41,7 @@ def gemm(
     assert K == Kb, f"K mismatch {K} vs {Kb}"
     if out is None:
         assert not accumulate
-        out = torch.empty((M, Nn), dtype=out_dtype, device=a.device)
+        out = torch.empty((M, Nn), dtype=out_dtype or a.dtype, device=a.device)
     if not N.use_native(a):
         af = (a.t() if a_mn else a).float()
         bf = (b.t() if b_mn else b).float()

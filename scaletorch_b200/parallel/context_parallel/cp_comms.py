@@ -36,7 +36,7 @@ class ContextCommunicator:
         if self._reqs is not None:
             raise RuntimeError("send_recv() after commit(): call wait() first")
         if recv_tensor is None:
-            recv_tensor = torch.empty_like(tensor_to_send)
+            recv_tensor = torch.empty(tensor_to_send.shape, dtype=tensor_to_send.dtype, device=tensor_to_send.device)
         send = tensor_to_send.contiguous()
         if self.world_size > 1:
             self._ops.append(dist.P2POp(dist.isend, send, self.send_rank, group=self.group))

@@ -55,10 +55,12 @@ class _GatherLastDim(torch.autograd.Function):
         ws = _ws(group)
         if ws == 1:
             return x
-        x = x.contiguous()
-        out = torch.empty((ws,) + tuple(x.shape), dtype=x.dtype, device=x.device)
-        dist.all_gather_into_tensor(out, x, group=group)
-        return out.movedim(0, -2).reshape(*x.shape[:-1], ws * x.shape[-1])
+        n = x.shape[-1]
+        x2 = x.contiguous().view(-1, n)
+        out = torch.empty((ws * x2.shape[0], n), dtype=x.dtype, device=x.device)
+        dist.all_gather_into_tensor(out, x2, group=group)
+        out = out.view(ws, x2.shape[0], n).permute(1, 0, 2).reshape(x2.shape[0], ws * n)
+        return out.view(*x.shape[:-1], ws * n)
 
     @staticmethod
     def backward(ctx, g):

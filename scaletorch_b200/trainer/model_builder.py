@@ -100,4 +100,7 @@ def create_optimizer(model: torch.nn.Module, config, device: torch.device):
 
 def get_tensor_shapes(config, model_config) -> tuple[int, int, int]:
     """Shape of the activation exchanged between pipeline stages: ``(mbs, S/cp, hidden)``."""
-    return (config.micro_batch_size, config.sequence_length // config.context_parallel_size, model_config.hidden_size)
+    s_local = config.sequence_length // config.context_parallel_size
+    if getattr(config, "sequence_parallel", False) and config.tensor_parallel_size > 1:
+        s_local //= config.tensor_parallel_size   # the boundary tensor is the TP rank's token shard
+    return (config.micro_batch_size, s_local, model_config.hidden_size)

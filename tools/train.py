@@ -1,0 +1,167 @@
+#!/usr/bin/env python
+"""Training entry point.
+
+    torchrun --nproc_per_node 8 --master-addr 127.0.0.1 tools/train.py \
+        --model_name_or_path Qwen3-8B --tensor_parallel_size 2 --context_parallel_size 2 --data_parallel_size 2 \
+        --sequence_parallel True --micro_batch_size 1 --sequence_length 4096 --synthetic_data True \
+        --total_train_steps 20
+
+Same flags and console output as the reference trainer (``tools/train.py:55-453``: config → dist init →
+data loader → model → optimiser / scheduler → loop with clip, step, log, checkpoint → cleanup with
+``performance_logs_{rank}_{ts}.json``).  Differences: device-timed steps (CUDA events), one host sync per
+step (the loss), global-norm clipping folded into the fused optimiser, RNG / data position in checkpoints.
+"""
+from __future__ import annotations
+
+import gc
+import os
+import sys
+import time
+from pathlib import Path
+
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+from transformers import HfArgumentParser  # noqa: E402
+
+from scaletorch_b200.data import MicroBatchDataLoader  # noqa: E402
+from scaletorch_b200.parallel.process_group import process_group_manager as pgm  # noqa: E402
+from scaletorch_b200.trainer import (ScaleTorchArguments, cleanup_distributed, clip_gradients, create_lr_scheduler,  # noqa: E402
+                                     create_model, create_optimizer, get_dtype, get_tensor_shapes,
+                                     initialize_distributed_training, log_training_metrics, train_step,
+                                     validate_config)
+from scaletorch_b200.trainer.metrics import is_logging_rank  # noqa: E402
+from scaletorch_b200.trainer.optimizer import FusedAdamW  # noqa: E402
+from scaletorch_b200.utils.checkpoint import CheckpointManager  # noqa: E402
+from scaletorch_b200.utils.device import empty_cache, is_accelerator_available  # noqa: E402
+from scaletorch_b200.utils.logger_utils import get_logger  # noqa: E402
+from scaletorch_b200.utils.misc import (average_loss_across_dp_cp_ranks, get_num_params, rank_print, set_all_seed,  # noqa: E402
+                                        to_readable_format)
+from scaletorch_b200.utils.monitor import PerformanceMonitor  # noqa: E402
+
+logger = get_logger("scaletorch_b200.train")
+
+try:  # optional
+    import wandb
+except Exception:  # pragma: no cover
+    wandb = None
+
+
+def build_data_loader(config, model_config, device):
+    return MicroBatchDataLoader(
+        micro_batch_size=config.micro_batch_size, sequence_length=config.sequence_length,
+        dataset_name=config.dataset_name, tokenizer_name_or_path=config.tokenizer_name_or_path
+        if config.tokenizer_name_or_path != "facebook/opt-125m" else config.model_name_or_path,
+        gradient_accumulation_steps=config.gradient_accumulation_steps, device=device,
+        num_workers=config.num_workers if not config.synthetic_data else 0, num_proc=config.num_proc,
+        num_samples=config.num_samples, subset_name=config.subset_name, split=config.split,
+        pin_memory=config.pin_memory, synthetic=config.synthetic_data, vocab_size=model_config.vocab_size,
+        seed=config.seed)
+
+
+def main(argv=None) -> None:
+    world_size, monitor, run = 1, None, None
+    try:
+        (config,) = HfArgumentParser(ScaleTorchArguments).parse_args_into_dataclasses(args=argv)
+        dtype = get_dtype(config)
+        local_rank, global_rank, world_size, device = initialize_distributed_training(config)
+        validate_config(config, world_size)
+        log_rank = is_logging_rank()
+        set_all_seed(config.seed)
+        logger.info("dtype=%s device=%s world_size=%d layout=%s", dtype, device, world_size, pgm if pgm else "single")
+
+        t0 = time.time()
+        model, model_config = create_model(config, dtype, device)
+        model.train()
+        data_loader = build_data_loader(config, model_config, device)
+        if world_size > 1:
+            dist.barrier()
+        tokens_per_step = data_loader.global_batch_size * config.sequence_length
+        rank_print(f"init time: {time.time() - t0:.2f}s | Tokens per step: {to_readable_format(tokens_per_step)}",
+                   is_print_rank=log_rank)
+        if log_rank and config.use_wandb and wandb is not None:
+            run = wandb.init(project=config.project_name, name=f"{config.experiment_name}_{to_readable_format(tokens_per_step)}",
+                             config={k: getattr(config, k) for k in ("tensor_parallel_size", "context_parallel_size",
+                                     "pipeline_parallel_size", "data_parallel_size", "expert_parallel_size",
+                                     "model_name_or_path", "learning_rate", "seed", "micro_batch_size",
+                                     "gradient_accumulation_steps", "sequence_length")})
+        num_params = get_num_params(model)
+        rank_print(f"Number of parameters: {to_readable_format(num_params)}", is_print_rank=log_rank)
+        optimizer = create_optimizer(model, config, device)
+        total_steps = config.total_train_steps
+        if total_steps is None and config.max_tokens is not None and tokens_per_step > 0:
+            total_steps = config.max_tokens // tokens_per_step
+        lr_scheduler = create_lr_scheduler(optimizer, config, total_steps)
+        ckpt = CheckpointManager()
+        monitor = PerformanceMonitor(config=config, log_dir=config.work_dir)
+        trained_tokens, step = 0, 0
+        if config.resume_path:
+            step, trained_tokens = ckpt.load_checkpoint(model, optimizer, config.resume_path)
+            sched_path = os.path.join(config.resume_path, "scheduler.pt")
+            if os.path.exists(sched_path):
+                lr_scheduler.load_state_dict(torch.load(sched_path, weights_only=False))
+            rank_print(f"Loaded checkpoint at step {step}, trained_tokens={trained_tokens}", is_print_rank=log_rank)
+        if world_size > 1:
+            dist.barrier()
+        tensor_shapes = get_tensor_shapes(config, model_config) if (pgm and pgm.pp_world_size > 1) else None
+
+        monitor.start()
+        max_steps = config.total_train_steps or float("inf")
+        while config.max_tokens is None or trained_tokens < config.max_tokens:
+            monitor.start_iteration(tokens_processed=tokens_per_step)
+            optimizer.zero_grad(set_to_none=True)
+            if hasattr(model, "reset"):
+                model.reset()
+            if pgm and pgm.pp_world_size > 1:
+                from scaletorch_b200.parallel.pipeline_parallel.pipeline_parallel import (train_step_pipeline_1f1b,
+                                                                                          train_step_pipeline_afab)
+
+                fn = train_step_pipeline_afab if config.pipeline_parallel_engine == "afab" else train_step_pipeline_1f1b
+                loss_t = fn(model, data_loader, tensor_shapes, device, dtype, config.gradient_checkpointing)
+            else:
+                loss_t = train_step(model, data_loader, device, dtype, config.gradient_accumulation_steps,
+                                    config.gradient_checkpointing, config.aux_loss)
+            grad_norm = clip_gradients(model, config.max_grad_norm, optimizer)
+            optimizer.step()
+            lr_scheduler.step()
+            stats = monitor.end_iteration()           # CUDA-event timed, syncs once per step
+            loss = average_loss_across_dp_cp_ranks(loss_t, device)
+            if isinstance(optimizer, FusedAdamW) and config.max_grad_norm:
+                grad_norm = optimizer.grad_norm()
+            trained_tokens += tokens_per_step
+            step += 1
+            if step % 100 == 0 and is_accelerator_available():
+                empty_cache()
+                if step % 1000 == 0:
+                    gc.collect()
+            log_training_metrics(config, model_config, step, loss, lr_scheduler.get_last_lr()[0], grad_norm,
+                                 stats["iteration_time"], tokens_per_step, trained_tokens, num_params, world_size,
+                                 logger=logger, wandb_run=run)
+            if config.save_model_checkpoint and config.save_frequency > 0 and step % config.save_frequency == 0:
+                out_dir = Path(config.work_dir) / f"{step}"
+                ckpt.save_checkpoint(model, optimizer, step, trained_tokens, str(out_dir),
+                                     extra={"data_loader": data_loader.state_dict()})
+                if log_rank:
+                    torch.save(lr_scheduler.state_dict(), out_dir / "scheduler.pt")
+            if step >= max_steps:
+                break
+    except Exception:
+        logger.error("training failed", exc_info=True)
+        raise
+    finally:
+        if run is not None:
+            run.finish()
+        if monitor is not None:
+            try:
+                monitor.save_stats()
+                if is_logging_rank():
+                    monitor.print_summary()
+            except Exception:
+                pass
+        cleanup_distributed()
+
+
+if __name__ == "__main__":
+    main()

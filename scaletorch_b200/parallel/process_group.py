@@ -200,6 +200,10 @@ class ProcessGroupManagerProxy:
         inst = object.__getattribute__(self, "_instance")
         return "ProcessGroupManagerProxy(<uninitialised>)" if inst is None else repr(inst)
 
+    def __str__(self) -> str:
+        inst = object.__getattribute__(self, "_instance")
+        return "ProcessGroupManagerProxy(<uninitialised>)" if inst is None else str(inst)
+
 
 process_group_manager = ProcessGroupManagerProxy()
 

@@ -115,14 +115,15 @@ class OptimizerArguments:
     optimizer_type: str = field(default="adamw", metadata={"help": "Type of optimizer"})
     weight_decay: float = field(default=0.0, metadata={"help": "Weight decay"})
     use_fused_adam: bool = field(default=True, metadata={"help": "Use the fused AdamW kernel over the flat parameter store"})
-    betas: tuple[float, float] = field(default=(0.9, 0.999), metadata={"help": "Betas for Adam"})
+    betas: list[float] = field(default_factory=lambda: [0.9, 0.999], metadata={"help": "Betas for Adam (two floats: --betas 0.9 0.95)"})
     learning_rate: float = field(default=1e-3, metadata={"help": "Learning rate"})
 
     def __post_init__(self) -> None:
         if self.optimizer_type not in _VALID_OPTIMIZERS:
             raise ValueError(f"optimizer_type must be one of {sorted(_VALID_OPTIMIZERS)}, got {self.optimizer_type}")
-        if isinstance(self.betas, list):
-            self.betas = tuple(float(b) for b in self.betas)
+        self.betas = tuple(float(b) for b in self.betas)   # parsed as a list (nargs="+"), used as a 2-tuple
+        if len(self.betas) != 2:
+            raise ValueError(f"betas must be two floats, got {self.betas}")
 
 
 @dataclass

@@ -49,7 +49,11 @@ def log_training_metrics(config: Any, model_config: Any, step: int, loss: float,
     if is_logging_rank():
         line = format_metrics_line(step, loss, lr, grad_norm, config.global_batch_size_token or tokens_per_step, tps,
                                    tps_gpu, trained_tokens, config.max_tokens, mfu, mem)
-        (logger.info if logger is not None else print)(line)
+        # the logging rank is the last PP stage, which is not global rank 0 under PP: its logger is muted
+        if logger is not None and logger.isEnabledFor(20):
+            logger.info(line)
+        else:
+            print(line, flush=True)
         if wandb_run is not None:
             wandb_run.log(metrics, step=step)
     return metrics

@@ -73,10 +73,10 @@ def _find_safetensors(save_dir: str) -> tuple[str | None, dict | None]:
 
 
 def _rebuild_rope(model: nn.Module) -> None:
-    """RoPE tables are plain buffers computed in ``__init__``; under the meta context they come out as
-    meta tensors and are recomputed here."""
+    """RoPE tables are plain buffers computed in ``__init__``; ``to_empty`` re-allocates every buffer
+    uninitialised (and the meta context may have produced meta tensors), so they are always recomputed."""
     for m in model.modules():
-        if hasattr(m, "cos") and isinstance(getattr(m, "cos"), torch.Tensor) and m.cos.device.type == "meta":
+        if isinstance(m.__dict__.get("_buffers", {}).get("cos"), torch.Tensor) and hasattr(m, "head_dim"):
             from ..ops.norm import get_cos_sin
 
             cfg = m.config

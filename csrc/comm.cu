@@ -1,0 +1,351 @@
+// Communication kernels over NVLink peer memory (symmetric buffers: the same allocation size on every rank,
+// every peer's copy mapped into this process, optionally one NVLS multicast address for all of them).
+//
+//   stb_symm_barrier      all ranks of the group rendezvous on the device (release/acquire flags in peer memory)
+//   stb_allreduce_f32     in-place sum (x scale) of an fp32 range of the symmetric buffer: each rank reduces its
+//                         1/world slice by loading it from every peer and stores the result back to every peer
+//                         (two-shot, one kernel); with an NVLS multicast mapping the loads/stores become
+//                         multimem.ld_reduce / multimem.st and the reduction happens inside the switch.
+//                         Used for the data-parallel gradient buckets (the 1/world scale is fused) and the
+//                         non-SP tensor-parallel all-reduce.
+//   stb_allreduce_bf16    same for bf16 ranges (tensor-parallel activations), fp32 accumulation.
+//   stb_allgather_pull    each rank pulls the other ranks' shards out of their symmetric buffers into a local
+//                         contiguous buffer and raises one ready flag per row block (consumed by the AG->GEMM
+//                         producer warp of stb_gemm_bf16_ex).
+//
+// Reference counterparts: dist.all_reduce / all_gather / reduce_scatter through c10d-NCCL in
+// scaletorch/parallel/data_parallel/bucket.py:73-78, tensor_parallel/tp_comms.py:144-147,
+// sequence_parallel/sp_comms.py:46-47,79-82.
+//
+// Flags are monotonically increasing epochs (never reset), so consecutive calls need no re-zeroing.
+// Every kernel here is launched with a grid that is fully resident (<= SM count), because its blocks wait
+// on one another / on other GPUs.
+#include "common/host.h"
+#include "common/ptx.cuh"
+
+namespace stb {
+
+STB_DEVICE void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+STB_DEVICE uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+STB_DEVICE uint32_t ld_acquire_gpu(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+STB_DEVICE void st_release_gpu(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// Flag layout inside each rank's flag page (uint32): [slot][world] arrival epochs written by the peers,
+// followed by one local "go" word per slot at index kMaxSlots*kMaxWorld + slot.
+constexpr int kMaxWorld = 16;
+constexpr int kMaxSlots = 8;
+
+// Cross-GPU barrier executed by one warp of one block: rank r writes `epoch` into slot[r] of every peer,
+// then waits until every peer has written `epoch` (or later) into its own page.
+STB_DEVICE void cross_gpu_barrier(uint32_t* const* flag_pages, int rank, int world, int slot, uint32_t epoch) {
+  const int t = threadIdx.x;
+  if (t < world) {
+    __threadfence_system();
+    st_release_sys(flag_pages[t] + slot * kMaxWorld + rank, epoch);
+    const uint32_t* mine = flag_pages[rank] + slot * kMaxWorld + t;
+    while (int32_t(ld_acquire_sys(mine) - epoch) < 0) {
+    }
+  }
+}
+
+__global__ void symm_barrier_kernel(uint32_t* const* flag_pages, int rank, int world, int slot, uint32_t epoch) {
+  cross_gpu_barrier(flag_pages, rank, world, slot, epoch);
+}
+
+// Grid-wide: block 0 performs the cross-GPU barrier and releases the other blocks through a local word.
+STB_DEVICE void grid_cross_gpu_barrier(uint32_t* const* flag_pages, int rank, int world, int slot, uint32_t epoch) {
+  uint32_t* go = flag_pages[rank] + kMaxSlots * kMaxWorld + slot;
+  if (blockIdx.x == 0) {
+    if (threadIdx.x < 32) cross_gpu_barrier(flag_pages, rank, world, slot, epoch);
+    __syncthreads();
+    if (threadIdx.x == 0) st_release_gpu(go, epoch);
+  } else {
+    if (threadIdx.x == 0) {
+      while (int32_t(ld_acquire_gpu(go) - epoch) < 0) {
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// End-of-kernel variant: every block reports completion; block 0 waits for all of them, then runs the
+// cross-GPU barrier.  The kernel (hence the stream) completes only after every rank finished its part.
+STB_DEVICE void grid_finish_cross_gpu_barrier(uint32_t* const* flag_pages, int rank, int world, int slot,
+                                              uint32_t epoch) {
+  uint32_t* done = flag_pages[rank] + kMaxSlots * kMaxWorld + kMaxSlots + slot;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence_system();
+    atomicAdd(done, 1u);
+  }
+  if (blockIdx.x == 0) {
+    if (threadIdx.x == 0) {
+      while (ld_acquire_gpu(done) < gridDim.x) {
+      }
+      *done = 0;   // re-arm: the next kernel using this slot starts after this one has completed
+    }
+    __syncthreads();
+    if (threadIdx.x < 32) cross_gpu_barrier(flag_pages, rank, world, slot, epoch);
+  }
+}
+
+STB_DEVICE float4 ld_peer_f4(const float* p) {
+  float4 v;
+  asm volatile("ld.global.relaxed.sys.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(p)
+               : "memory");
+  return v;
+}
+STB_DEVICE void st_peer_f4(float* p, const float4& v) {
+  asm volatile("st.global.relaxed.sys.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z),
+               "f"(v.w)
+               : "memory");
+}
+STB_DEVICE float4 multimem_ld_reduce_f4(const float* mc) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(mc)
+               : "memory");
+  return v;
+}
+STB_DEVICE void multimem_st_f4(float* mc, const float4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc), "f"(v.x), "f"(v.y),
+               "f"(v.z), "f"(v.w)
+               : "memory");
+}
+STB_DEVICE uint4 multimem_ld_reduce_bf16x8(const void* mc) {
+  uint4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "l"(mc)
+               : "memory");
+  return v;
+}
+STB_DEVICE void multimem_st_u4(void* mc, const uint4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc), "r"(v.x), "r"(v.y),
+               "r"(v.z), "r"(v.w)
+               : "memory");
+}
+
+// In-place all-reduce of `n` fp32 elements starting `offset` elements into every rank's symmetric buffer.
+template <bool MULTIMEM>
+__global__ void __launch_bounds__(512)
+    allreduce_f32_kernel(float* const* bufs, float* mc, uint32_t* const* flag_pages, long offset, long n, float scale,
+                         int rank, int world, int slot, uint32_t epoch) {
+  grid_cross_gpu_barrier(flag_pages, rank, world, slot, epoch);   // every rank's data is in place
+  const long nvec = n >> 2;
+  const long per = (nvec + world - 1) / world;
+  const long lo = per * rank, hi = min(nvec, lo + per);
+  for (long i = lo + long(blockIdx.x) * blockDim.x + threadIdx.x; i < hi; i += long(gridDim.x) * blockDim.x) {
+    const long e = offset + (i << 2);
+    float4 acc;
+    if (MULTIMEM) {
+      acc = multimem_ld_reduce_f4(mc + e);
+    } else {
+      acc = ld_peer_f4(bufs[rank] + e);
+      for (int p = 1; p < world; ++p) {
+        const float4 v = ld_peer_f4(bufs[(rank + p) % world] + e);
+        acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+      }
+    }
+    acc.x *= scale; acc.y *= scale; acc.z *= scale; acc.w *= scale;
+    if (MULTIMEM) {
+      multimem_st_f4(mc + e, acc);
+    } else {
+      for (int p = 0; p < world; ++p) st_peer_f4(bufs[(rank + p) % world] + e, acc);
+    }
+  }
+  if (rank == 0) {  // scalar tail (n % 4) handled by rank 0
+    for (long i = (nvec << 2) + long(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += long(gridDim.x) * blockDim.x) {
+      float acc = 0.f;
+      for (int p = 0; p < world; ++p) acc += bufs[p][offset + i];
+      acc *= scale;
+      for (int p = 0; p < world; ++p) bufs[p][offset + i] = acc;
+    }
+  }
+  grid_finish_cross_gpu_barrier(flag_pages, rank, world, slot, epoch + 1);  // results have landed everywhere
+}
+
+template <bool MULTIMEM>
+__global__ void __launch_bounds__(512)
+    allreduce_bf16_kernel(__nv_bfloat16* const* bufs, __nv_bfloat16* mc, uint32_t* const* flag_pages, long offset,
+                          long n, int rank, int world, int slot, uint32_t epoch) {
+  grid_cross_gpu_barrier(flag_pages, rank, world, slot, epoch);
+  const long nvec = n >> 3;
+  const long per = (nvec + world - 1) / world;
+  const long lo = per * rank, hi = min(nvec, lo + per);
+  for (long i = lo + long(blockIdx.x) * blockDim.x + threadIdx.x; i < hi; i += long(gridDim.x) * blockDim.x) {
+    const long e = offset + (i << 3);
+    uint4 out;
+    if (MULTIMEM) {
+      out = multimem_ld_reduce_bf16x8(mc + e);
+      multimem_st_u4(mc + e, out);
+    } else {
+      float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+      for (int p = 0; p < world; ++p) {
+        const float4 vf = ld_peer_f4(reinterpret_cast<const float*>(bufs[(rank + p) % world] + e));
+        const uint32_t u[4] = {__float_as_uint(vf.x), __float_as_uint(vf.y), __float_as_uint(vf.z),
+                               __float_as_uint(vf.w)};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float2 f = unpack_bf16x2(u[j]);
+          acc[2 * j] += f.x; acc[2 * j + 1] += f.y;
+        }
+      }
+      out = make_uint4(pack_bf16x2(acc[0], acc[1]), pack_bf16x2(acc[2], acc[3]), pack_bf16x2(acc[4], acc[5]),
+                       pack_bf16x2(acc[6], acc[7]));
+      for (int p = 0; p < world; ++p) *reinterpret_cast<uint4*>(bufs[(rank + p) % world] + e) = out;
+    }
+  }
+  grid_finish_cross_gpu_barrier(flag_pages, rank, world, slot, epoch + 1);
+}
+
+// out (local, fresh) <- sum over ranks of bufs[p][offset .. offset+n): every rank reads all peers (one-shot).
+__global__ void __launch_bounds__(512)
+    allreduce_oneshot_bf16_kernel(const __nv_bfloat16* const* bufs, uint32_t* const* flag_pages, long offset,
+                                  __nv_bfloat16* out, long n, int rank, int world, int slot, uint32_t epoch) {
+  grid_cross_gpu_barrier(flag_pages, rank, world, slot, epoch);
+  const long nvec = n >> 3;
+  for (long i = long(blockIdx.x) * blockDim.x + threadIdx.x; i < nvec; i += long(gridDim.x) * blockDim.x) {
+    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (int p = 0; p < world; ++p) {
+      const uint4 v = ld_nc_v4(bufs[(rank + p) % world] + offset + (i << 3));
+      const uint32_t u[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 f = unpack_bf16x2(u[j]);
+        acc[2 * j] += f.x; acc[2 * j + 1] += f.y;
+      }
+    }
+    *reinterpret_cast<uint4*>(out + (i << 3)) = make_uint4(pack_bf16x2(acc[0], acc[1]), pack_bf16x2(acc[2], acc[3]),
+                                                           pack_bf16x2(acc[4], acc[5]), pack_bf16x2(acc[6], acc[7]));
+  }
+  // the partial buffers may be overwritten only after every rank has read them
+  grid_finish_cross_gpu_barrier(flag_pages, rank, world, slot, epoch + 1);
+}
+
+// dst[world * rows_per_rank, row_bytes] <- shard of every rank (rank r's shard sits at offset_bytes of its buffer).
+// One ready flag (epoch) per block of `flag_rows` rows is released in `ready` (local memory) when its bytes landed.
+__global__ void __launch_bounds__(512)
+    allgather_pull_kernel(const uint8_t* const* bufs, uint32_t* const* flag_pages, long offset_bytes, uint8_t* dst,
+                          long rows_per_rank, long row_bytes, int flag_rows, uint32_t* ready, int rank, int world,
+                          int slot, uint32_t epoch) {
+  grid_cross_gpu_barrier(flag_pages, rank, world, slot, epoch);   // every rank's shard is written
+  const long blocks_per_rank = (rows_per_rank + flag_rows - 1) / flag_rows;
+  const long total_blocks = blocks_per_rank * world;
+  const long vec_per_row = row_bytes >> 4;
+  for (long blk = blockIdx.x; blk < total_blocks; blk += gridDim.x) {
+    // local shard first, then the peers in ring order
+    const int src = int((rank + blk / blocks_per_rank) % world);
+    const long rb = blk % blocks_per_rank;
+    const long r0 = rb * flag_rows, r1 = min(rows_per_rank, r0 + flag_rows);
+    const uint4* s = reinterpret_cast<const uint4*>(bufs[src] + offset_bytes + r0 * row_bytes);
+    uint4* d = reinterpret_cast<uint4*>(dst + (long(src) * rows_per_rank + r0) * row_bytes);
+    const long nv = (r1 - r0) * vec_per_row;
+    for (long i = threadIdx.x; i < nv; i += blockDim.x) d[i] = ld_nc_v4(s + i);
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) st_release_gpu(ready + long(src) * blocks_per_rank + rb, epoch);
+  }
+  // peers may reuse their shard buffers only after everybody has pulled them
+  grid_finish_cross_gpu_barrier(flag_pages, rank, world, slot, epoch + 1);
+}
+
+static int comm_grid(int sm_budget) {
+  const int sms = sm_count();
+  if (sm_budget <= 0 || sm_budget > sms) sm_budget = sms;
+  return sm_budget;
+}
+
+}  // namespace stb
+
+using namespace stb;
+
+extern "C" int stb_symm_flag_page_bytes() { return (kMaxSlots * kMaxWorld + 2 * kMaxSlots) * 4; }
+
+extern "C" int stb_symm_barrier(const void* flag_pages_dev, int rank, int world, int slot, unsigned epoch,
+                                cudaStream_t stream) {
+  STB_REQUIRE(world <= kMaxWorld && slot < kMaxSlots, "symm_barrier: world %d / slot %d out of range", world, slot);
+  symm_barrier_kernel<<<1, 32, 0, stream>>>((uint32_t* const*)flag_pages_dev, rank, world, slot, epoch);
+  STB_CHECK_LAUNCH();
+  return 0;
+}
+
+// Consumes epochs `epoch` and `epoch + 1` of `slot`.
+extern "C" int stb_allreduce_f32(const void* bufs_dev, void* multicast_ptr, const void* flag_pages_dev,
+                                 long offset_elems, long n, float scale, int rank, int world, int slot,
+                                 unsigned epoch, int sm_budget, cudaStream_t stream) {
+  STB_REQUIRE(world <= kMaxWorld && slot < kMaxSlots, "allreduce: world %d / slot %d out of range", world, slot);
+  STB_REQUIRE(offset_elems % 4 == 0, "allreduce_f32: offset must be a multiple of 4 elements");
+  if (n == 0) return 0;
+  const int grid = comm_grid(sm_budget);
+  if (multicast_ptr != nullptr)
+    allreduce_f32_kernel<true><<<grid, 512, 0, stream>>>((float* const*)bufs_dev, (float*)multicast_ptr,
+                                                         (uint32_t* const*)flag_pages_dev, offset_elems, n, scale, rank,
+                                                         world, slot, epoch);
+  else
+    allreduce_f32_kernel<false><<<grid, 512, 0, stream>>>((float* const*)bufs_dev, nullptr,
+                                                          (uint32_t* const*)flag_pages_dev, offset_elems, n, scale, rank,
+                                                          world, slot, epoch);
+  STB_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int stb_allreduce_bf16(const void* bufs_dev, void* multicast_ptr, const void* flag_pages_dev,
+                                  long offset_elems, long n, int rank, int world, int slot, unsigned epoch,
+                                  int sm_budget, cudaStream_t stream) {
+  STB_REQUIRE(world <= kMaxWorld && slot < kMaxSlots, "allreduce: world %d / slot %d out of range", world, slot);
+  STB_REQUIRE(offset_elems % 8 == 0 && n % 8 == 0, "allreduce_bf16: offset and n must be multiples of 8 elements");
+  if (n == 0) return 0;
+  const int grid = comm_grid(sm_budget);
+  if (multicast_ptr != nullptr)
+    allreduce_bf16_kernel<true><<<grid, 512, 0, stream>>>((__nv_bfloat16* const*)bufs_dev, (__nv_bfloat16*)multicast_ptr,
+                                                          (uint32_t* const*)flag_pages_dev, offset_elems, n, rank, world,
+                                                          slot, epoch);
+  else
+    allreduce_bf16_kernel<false><<<grid, 512, 0, stream>>>((__nv_bfloat16* const*)bufs_dev, nullptr,
+                                                           (uint32_t* const*)flag_pages_dev, offset_elems, n, rank,
+                                                           world, slot, epoch);
+  STB_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int stb_allreduce_oneshot_bf16(const void* bufs_dev, const void* flag_pages_dev, long offset_elems, void* out,
+                                          long n, int rank, int world, int slot, unsigned epoch, int sm_budget,
+                                          cudaStream_t stream) {
+  STB_REQUIRE(world <= kMaxWorld && slot < kMaxSlots, "allreduce: world %d / slot %d out of range", world, slot);
+  STB_REQUIRE(offset_elems % 8 == 0 && n % 8 == 0, "allreduce_oneshot_bf16: offset and n must be multiples of 8");
+  if (n == 0) return 0;
+  allreduce_oneshot_bf16_kernel<<<comm_grid(sm_budget), 512, 0, stream>>>(
+      (const __nv_bfloat16* const*)bufs_dev, (uint32_t* const*)flag_pages_dev, offset_elems, (__nv_bfloat16*)out, n,
+      rank, world, slot, epoch);
+  STB_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int stb_allgather_pull(const void* bufs_dev, const void* flag_pages_dev, long offset_bytes, void* dst,
+                                  long rows_per_rank, long row_bytes, int flag_rows, void* ready, int rank, int world,
+                                  int slot, unsigned epoch, int sm_budget, cudaStream_t stream) {
+  STB_REQUIRE(world <= kMaxWorld && slot < kMaxSlots, "allgather: world %d / slot %d out of range", world, slot);
+  STB_REQUIRE(row_bytes % 16 == 0 && offset_bytes % 16 == 0, "allgather: rows must be 16-byte multiples");
+  const int grid = comm_grid(sm_budget);
+  allgather_pull_kernel<<<grid, 512, 0, stream>>>((const uint8_t* const*)bufs_dev, (uint32_t* const*)flag_pages_dev,
+                                                  offset_bytes, (uint8_t*)dst, rows_per_rank, row_bytes, flag_rows,
+                                                  (uint32_t*)ready, rank, world, slot, epoch);
+  STB_CHECK_LAUNCH();
+  return 0;
+}

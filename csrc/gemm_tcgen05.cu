@@ -35,6 +35,25 @@ struct GemmParams {
   int tiles_m, tiles_n, num_tiles, k_blocks;
   int out_fp32;
   int accumulate;
+  // ---- fused collectives (0 / nullptr = plain GEMM)
+  int m_rotate;                 // tile-row rotation: tiles of other ranks first, local tiles last
+  int rows_per_dest;            // GEMM->reduce-scatter: rows [d*rows_per_dest, ...) go to tensor map d
+  const uint32_t* a_ready;      // all-gather->GEMM: one flag per a_flag_rows rows of A, ready when >= a_epoch
+  uint32_t a_epoch;
+  int a_flag_rows;
+  // copy CTAs of the all-gather->GEMM kernel (blockIdx < n_copy): pull the peers' A shards over NVLink
+  int n_copy;
+  const uint8_t* const* ag_bufs;      // device array [world]: base of every rank's symmetric buffer
+  uint32_t* const* ag_flag_pages;     // device array [world]: flag pages (see comm.cu)
+  long ag_offset_bytes;               // shard offset inside each symmetric buffer
+  uint8_t* ag_dst;                    // local A_full
+  uint32_t* ag_ready;                 // same memory as a_ready, written here
+  int ag_rank, ag_world, ag_slot;
+};
+
+constexpr int kMaxDest = 8;
+struct CMaps {
+  CUtensorMap m[kMaxDest];
 };
 
 template <int BN>
@@ -60,12 +79,98 @@ STB_DEVICE void tile_coords(int tile, int tiles_m, int tiles_n, int& m, int& n) 
   n = r / gm;
 }
 
+// ---- copy role of the all-gather->GEMM kernel --------------------------------------------------------
+// Flag-page layout and barrier protocol are shared with csrc/comm.cu (kMaxWorld = 16, kMaxSlots = 8).
+STB_DEVICE void ag_cross_gpu_barrier(uint32_t* const* pages, int rank, int world, int slot, uint32_t epoch) {
+  const int t = threadIdx.x;
+  if (t < world) {
+    __threadfence_system();
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(pages[t] + slot * 16 + rank), "r"(epoch) : "memory");
+    const uint32_t* mine = pages[rank] + slot * 16 + t;
+    uint32_t v;
+    do {
+      asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(mine) : "memory");
+    } while (int32_t(v - epoch) < 0);
+  }
+}
+
+STB_DEVICE void ag_copy_role(const GemmParams& p) {
+  uint32_t* go = p.ag_flag_pages[p.ag_rank] + 8 * 16 + p.ag_slot;
+  uint32_t* done = p.ag_flag_pages[p.ag_rank] + 8 * 16 + 8 + p.ag_slot;
+  // 1. every rank has written its shard (cross-GPU barrier by copy CTA 0, released locally to the others)
+  if (blockIdx.x == 0) {
+    if (threadIdx.x < 32) ag_cross_gpu_barrier(p.ag_flag_pages, p.ag_rank, p.ag_world, p.ag_slot, p.a_epoch);
+    __syncthreads();
+    if (threadIdx.x == 0) asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(go), "r"(p.a_epoch) : "memory");
+  } else {
+    if (threadIdx.x == 0) {
+      uint32_t v;
+      do {
+        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(go) : "memory");
+      } while (int32_t(v - p.a_epoch) < 0);
+    }
+    __syncthreads();
+  }
+  // 2. pull row blocks: own shard first, then the peers in ring order (the order the compute CTAs consume)
+  const long rows_per_rank = p.M / p.ag_world;
+  const long row_bytes = long(p.K) * 2;
+  const long blocks_per_rank = (rows_per_rank + p.a_flag_rows - 1) / p.a_flag_rows;
+  const long total = blocks_per_rank * p.ag_world;
+  const long vec_per_row = row_bytes >> 4;
+  for (long blk = blockIdx.x; blk < total; blk += p.n_copy) {
+    const int src = int((p.ag_rank + blk / blocks_per_rank) % p.ag_world);
+    const long rb = blk % blocks_per_rank;
+    const long r0 = rb * p.a_flag_rows, r1 = min(rows_per_rank, r0 + long(p.a_flag_rows));
+    const uint4* s = reinterpret_cast<const uint4*>(p.ag_bufs[src] + p.ag_offset_bytes + r0 * row_bytes);
+    uint4* d = reinterpret_cast<uint4*>(p.ag_dst + (long(src) * rows_per_rank + r0) * row_bytes);
+    const long nv = (r1 - r0) * vec_per_row;
+    long i = threadIdx.x;
+    for (; i + 7 * kGemmThreads < nv; i += 8 * kGemmThreads) {   // 8 x 16 B in flight per thread
+      uint4 v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) v[u] = ld_nc_v4(s + i + u * kGemmThreads);
+#pragma unroll
+      for (int u = 0; u < 8; ++u) d[i + u * kGemmThreads] = v[u];
+    }
+    for (; i < nv; i += kGemmThreads) d[i] = ld_nc_v4(s + i);
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0)
+      asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p.ag_ready + long(src) * blocks_per_rank + rb),
+                   "r"(p.a_epoch)
+                   : "memory");
+  }
+  // 3. tell the peers their shard buffers may be reused: all copy CTAs done -> cross-GPU barrier
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence_system();
+    atomicAdd(done, 1u);
+  }
+  if (blockIdx.x == 0) {
+    if (threadIdx.x == 0) {
+      uint32_t v;
+      do {
+        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(done) : "memory");
+      } while (v < uint32_t(p.n_copy));
+      *done = 0;
+    }
+    __syncthreads();
+    if (threadIdx.x < 32) ag_cross_gpu_barrier(p.ag_flag_pages, p.ag_rank, p.ag_world, p.ag_slot, p.a_epoch + 1);
+  }
+}
+
 template <int BN, bool A_MN, bool B_MN, bool EPI_TMA>
 __global__ void __launch_bounds__(kGemmThreads, 1)
     gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                     const __grid_constant__ CUtensorMap tmC, const GemmParams p) {
+                     const __grid_constant__ CMaps tmCs, const GemmParams p) {
   using Cfg = GemmCfg<BN>;
   constexpr int kStages = Cfg::kStages;
+  if (int(blockIdx.x) < p.n_copy) {   // all-gather->GEMM: communication CTAs (no TMEM, no smem pipeline)
+    ag_copy_role(p);
+    return;
+  }
+  const int cta = int(blockIdx.x) - p.n_copy;
+  const int ncta = int(gridDim.x) - p.n_copy;
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
@@ -86,7 +191,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
-    if (EPI_TMA) tma_prefetch_desc(&tmC);
+    if (EPI_TMA) tma_prefetch_desc(&tmCs.m[0]);
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < kStages; ++i) {
@@ -113,10 +218,24 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+      for (int tile = cta; tile < p.num_tiles; tile += ncta) {
         int tm, tn;
         tile_coords(tile, p.tiles_m, p.tiles_n, tm, tn);
+        tm = (tm + p.m_rotate) % p.tiles_m;
         const int m0 = tm * kBM, n0 = tn * BN;
+        if (p.a_ready != nullptr) {
+          // all-gather->GEMM: these rows of A are being pulled from a peer by the copy kernel running
+          // next to us; wait until every flag block covering them has landed
+          const int last_row = min(m0 + kBM, p.M) - 1;
+          for (int fb = m0 / p.a_flag_rows; fb <= last_row / p.a_flag_rows; ++fb) {
+            const uint32_t* f = p.a_ready + fb;
+            uint32_t v;
+            do {
+              asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
+            } while (int32_t(v - p.a_epoch) < 0);
+          }
+          asm volatile("fence.proxy.async.global;" ::: "memory");  // generic-proxy writes -> TMA (async proxy) reads
+        }
         for (int kb = 0; kb < p.k_blocks; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
           mbar_arrive_expect_tx(&full_bar[stage], Cfg::kStageBytes);
@@ -155,7 +274,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
       int stage = 0;
       uint32_t phase = 0;
       int it = 0;
-      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+      for (int tile = cta; tile < p.num_tiles; tile += ncta, ++it) {
         const int acc = it & 1;
         const uint32_t acc_phase = (it >> 1) & 1;
         mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
@@ -191,14 +310,23 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
       int slot = 0;
       int it = 0;
       const uint32_t sw = uint32_t(lane & 7);
-      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+      for (int tile = cta; tile < p.num_tiles; tile += ncta, ++it) {
         int tm, tn;
         tile_coords(tile, p.tiles_m, p.tiles_n, tm, tn);
+        tm = (tm + p.m_rotate) % p.tiles_m;
         const int acc = it & 1;
         const uint32_t acc_phase = (it >> 1) & 1;
         mbar_wait(&tmem_full[acc], acc_phase);
         tc_fence_after();
-        const int row0 = tm * kBM + ew * 32;
+        int row0 = tm * kBM + ew * 32;
+        // GEMM->reduce-scatter: the tile's rows belong to rank `dest`; its tensor map addresses that
+        // rank's output buffer (peer memory), so the TMA reduce-add below travels over NVLink
+        const CUtensorMap* tmC = &tmCs.m[0];
+        if (p.rows_per_dest > 0) {
+          const int dest = row0 / p.rows_per_dest;
+          tmC = &tmCs.m[dest];
+          row0 -= dest * p.rows_per_dest;
+        }
         const uint32_t taddr = tmem_base + (uint32_t(ew * 32) << 16) + acc * BN;
         if (p.out_fp32) {
 #pragma unroll 1
@@ -220,9 +348,9 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
             __syncwarp();
             if (lane == 0) {
               if (p.accumulate)
-                tma_reduce_add_2d(&tmC, slots + slot * 4096, tn * BN + c * 32, row0);
+                tma_reduce_add_2d(tmC, slots + slot * 4096, tn * BN + c * 32, row0);
               else
-                tma_store_2d(&tmC, slots + slot * 4096, tn * BN + c * 32, row0);
+                tma_store_2d(tmC, slots + slot * 4096, tn * BN + c * 32, row0);
               tma_store_commit();
             }
             slot ^= 1;
@@ -258,9 +386,9 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
             __syncwarp();
             if (lane == 0) {
               if (p.accumulate)
-                tma_reduce_add_2d(&tmC, slots + slot * 4096, tn * BN + c * 64, row0);
+                tma_reduce_add_2d(tmC, slots + slot * 4096, tn * BN + c * 64, row0);
               else
-                tma_store_2d(&tmC, slots + slot * 4096, tn * BN + c * 64, row0);
+                tma_store_2d(tmC, slots + slot * 4096, tn * BN + c * 64, row0);
               tma_store_commit();
             }
             slot ^= 1;
@@ -270,9 +398,10 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
       if (lane == 0) tma_store_wait<0>();
     } else {
     int it = 0;
-    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+    for (int tile = cta; tile < p.num_tiles; tile += ncta, ++it) {
       int tm, tn;
       tile_coords(tile, p.tiles_m, p.tiles_n, tm, tn);
+      tm = (tm + p.m_rotate) % p.tiles_m;
       const int acc = it & 1;
       const uint32_t acc_phase = (it >> 1) & 1;
       mbar_wait(&tmem_full[acc], acc_phase);
@@ -356,9 +485,24 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
   if (warp == 2) tmem_dealloc(tmem_base, Cfg::kTmemCols);
 }
 
+struct GemmFused {
+  int m_rotate = 0;
+  int n_dest = 0;                 // > 0: GEMM->reduce-scatter into c_dest[d] (each [M / n_dest, N], ld = ldc)
+  void* c_dest[kMaxDest] = {nullptr};
+  const uint32_t* a_ready = nullptr;
+  uint32_t a_epoch = 0;
+  int a_flag_rows = 0;
+  int n_copy = 0;
+  const uint8_t* const* ag_bufs = nullptr;
+  uint32_t* const* ag_flag_pages = nullptr;
+  long ag_offset_bytes = 0;
+  uint8_t* ag_dst = nullptr;
+  int ag_rank = 0, ag_world = 1, ag_slot = 0;
+};
+
 template <int BN, bool A_MN, bool B_MN, bool EPI_TMA>
 static int launch_gemm(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb,
-                       int ldc, int out_fp32, int accumulate, cudaStream_t stream) {
+                       int ldc, int out_fp32, int accumulate, cudaStream_t stream, const GemmFused& fx) {
   using Cfg = GemmCfg<BN>;
   CUtensorMap tmA, tmB;
   int rc;
@@ -372,13 +516,19 @@ static int launch_gemm(const void* A, const void* B, void* C, int M, int N, int 
   else
     rc = make_tmap_2d(&tmB, B, 2, N, K, uint64_t(ldb) * 2, 64, kBK, 1);
   if (rc) return rc;
-  CUtensorMap tmC = tmA;  // placeholder when the direct-store epilogue is used
+  CMaps tmCs;
+  for (int d = 0; d < kMaxDest; ++d) tmCs.m[d] = tmA;  // placeholders
   if (EPI_TMA) {
-    if (out_fp32)
-      rc = make_tmap_2d(&tmC, C, 4, N, M, uint64_t(ldc) * 4, 32, 32, 1);
-    else
-      rc = make_tmap_2d(&tmC, C, 2, N, M, uint64_t(ldc) * 2, 64, 32, 1);
-    if (rc) return rc;
+    const int nd = fx.n_dest > 0 ? fx.n_dest : 1;
+    const int rows = fx.n_dest > 0 ? M / fx.n_dest : M;
+    for (int d = 0; d < nd; ++d) {
+      void* base = fx.n_dest > 0 ? fx.c_dest[d] : C;
+      if (out_fp32)
+        rc = make_tmap_2d(&tmCs.m[d], base, 4, N, rows, uint64_t(ldc) * 4, 32, 32, 1);
+      else
+        rc = make_tmap_2d(&tmCs.m[d], base, 2, N, rows, uint64_t(ldc) * 2, 64, 32, 1);
+      if (rc) return rc;
+    }
   }
 
   GemmParams p;
@@ -391,6 +541,18 @@ static int launch_gemm(const void* A, const void* B, void* C, int M, int N, int 
   p.k_blocks = (K + kBK - 1) / kBK;
   p.out_fp32 = out_fp32;
   p.accumulate = accumulate;
+  p.m_rotate = fx.m_rotate % p.tiles_m;
+  p.rows_per_dest = fx.n_dest > 0 ? M / fx.n_dest : 0;
+  p.a_ready = fx.a_ready;
+  p.a_epoch = fx.a_epoch;
+  p.a_flag_rows = fx.a_flag_rows;
+  p.n_copy = fx.n_copy;
+  p.ag_bufs = fx.ag_bufs;
+  p.ag_flag_pages = fx.ag_flag_pages;
+  p.ag_offset_bytes = fx.ag_offset_bytes;
+  p.ag_dst = fx.ag_dst;
+  p.ag_ready = const_cast<uint32_t*>(fx.a_ready);
+  p.ag_rank = fx.ag_rank; p.ag_world = fx.ag_world; p.ag_slot = fx.ag_slot;
 
   auto kern = gemm_bf16_kernel<BN, A_MN, B_MN, EPI_TMA>;
   static bool attr_set = false;
@@ -399,8 +561,10 @@ static int launch_gemm(const void* A, const void* B, void* C, int M, int N, int 
                                         Cfg::kSmemBytes));
     attr_set = true;
   }
-  const int grid = p.num_tiles < sm_count() ? p.num_tiles : sm_count();
-  kern<<<grid, kGemmThreads, Cfg::kSmemBytes, stream>>>(tmA, tmB, tmC, p);
+  // all CTAs (compute + copy) must be co-resident: one CTA per SM
+  const int compute_cap = sm_count() - fx.n_copy;
+  const int grid = (p.num_tiles < compute_cap ? p.num_tiles : compute_cap) + fx.n_copy;
+  kern<<<grid, kGemmThreads, Cfg::kSmemBytes, stream>>>(tmA, tmB, tmCs, p);
   STB_CHECK_LAUNCH();
   return 0;
 }
@@ -423,9 +587,9 @@ static int pick_bn(int M, int N) {
 // C ABI ---------------------------------------------------------------------
 // a_mn / b_mn: 0 = operand stored K-major (row-major [rows, K], ld = row stride),
 //              1 = operand stored MN-major (row-major [K, rows]).
-extern "C" int stb_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, int lda,
-                             int ldb, int ldc, int a_mn, int b_mn, int out_fp32, int accumulate,
-                             int force_bn, cudaStream_t stream) {
+static int gemm_dispatch(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc,
+                         int a_mn, int b_mn, int out_fp32, int accumulate, int force_bn, cudaStream_t stream,
+                         const stb::GemmFused& fx) {
   using namespace stb;
   STB_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: empty problem %d %d %d", M, N, K);
   STB_REQUIRE((lda % 8) == 0 && (ldb % 8) == 0, "gemm: lda/ldb must be multiples of 8 elements");
@@ -435,12 +599,14 @@ extern "C" int stb_gemm_bf16(const void* A, const void* B, void* C, int M, int N
   const int bn = force_bn ? force_bn : pick_bn(M, N);
   // TMA-store epilogue needs a 16-byte aligned C with a 16-byte multiple row pitch
   const int celt = out_fp32 ? 4 : 2;
-  const bool epi_tma = ((reinterpret_cast<uintptr_t>(C) & 15) == 0) && ((size_t(ldc) * celt) % 16 == 0);
+  const void* c0 = fx.n_dest > 0 ? fx.c_dest[0] : C;
+  const bool epi_tma = ((reinterpret_cast<uintptr_t>(c0) & 15) == 0) && ((size_t(ldc) * celt) % 16 == 0);
+  STB_REQUIRE(epi_tma || fx.n_dest == 0, "gemm_rs: destination buffers must be 16-byte aligned");
 #define STB_GEMM_CASE(BN_, AMN_, BMN_)                                                             \
   return epi_tma ? launch_gemm<BN_, AMN_, BMN_, true>(A, B, C, M, N, K, lda, ldb, ldc, out_fp32,   \
-                                                      accumulate, stream)                          \
+                                                      accumulate, stream, fx)                      \
                  : launch_gemm<BN_, AMN_, BMN_, false>(A, B, C, M, N, K, lda, ldb, ldc, out_fp32,  \
-                                                       accumulate, stream)
+                                                       accumulate, stream, fx)
   if (bn == 256) {
     if (!a_mn && !b_mn) STB_GEMM_CASE(256, false, false);
     if (!a_mn && b_mn) STB_GEMM_CASE(256, false, true);
@@ -451,4 +617,57 @@ extern "C" int stb_gemm_bf16(const void* A, const void* B, void* C, int M, int N
     STB_GEMM_CASE(128, true, true);
   }
 #undef STB_GEMM_CASE
+}
+
+extern "C" int stb_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, int lda,
+                             int ldb, int ldc, int a_mn, int b_mn, int out_fp32, int accumulate,
+                             int force_bn, cudaStream_t stream) {
+  stb::GemmFused fx;
+  return gemm_dispatch(A, B, C, M, N, K, lda, ldb, ldc, a_mn, b_mn, out_fp32, accumulate, force_bn, stream, fx);
+}
+
+// GEMM -> reduce-scatter in one kernel.  Rank `rank` of `world` computes the partial product
+// P[M,N] = A * op(B)^T and adds row block d (M/world rows) of it into c_dest[d] -- rank d's output buffer,
+// mapped into this process (symmetric memory) -- with TMA reduce-add issued from the epilogue, tile by
+// tile, remote ranks first.  Every destination buffer must be zeroed and every rank must have passed a
+// barrier before the first add; a barrier after the kernel makes the sums visible (see runtime/fused_ops.py).
+extern "C" int stb_gemm_rs_bf16(const void* A, const void* B, void* const* c_dest, int M, int N, int K, int lda,
+                                int ldb, int ldc, int b_mn, int rank, int world, cudaStream_t stream) {
+  using namespace stb;
+  STB_REQUIRE(world >= 1 && world <= kMaxDest, "gemm_rs: world %d out of range", world);
+  STB_REQUIRE(M % world == 0 && (M / world) % kBM == 0, "gemm_rs: M / world must be a multiple of %d", kBM);
+  GemmFused fx;
+  fx.n_dest = world;
+  for (int d = 0; d < world; ++d) fx.c_dest[d] = c_dest[d];
+  fx.m_rotate = ((rank + 1) % world) * (M / world / kBM);   // start with the next rank's rows, end with our own
+  return gemm_dispatch(A, B, nullptr, M, N, K, lda, ldb, ldc, 0, b_mn, 0, 1, 0, stream, fx);
+}
+
+// all-gather -> GEMM in one kernel: C[M,N] = A_full[M,K] * op(B)^T where row block r of A_full is rank r's
+// shard, living at `shard_offset_bytes` of that rank's symmetric buffer.  `n_copy` CTAs of the grid pull the
+// shards over NVLink into the local `A_full` buffer (own shard first, then the peers in ring order) and raise
+// one flag per `flag_rows` rows; the remaining CTAs are the usual persistent GEMM, whose TMA producer waits
+// on the flags of the rows it is about to load.  A_full is returned to the caller (wgrad needs it).
+// Consumes epochs `epoch` and `epoch + 1` of flag slot `slot`.
+extern "C" int stb_ag_gemm_bf16(void* A_full, const void* B, void* C, int M, int N, int K, int ldb, int ldc,
+                                int b_mn, const void* bufs_dev, const void* flag_pages_dev, long shard_offset_bytes,
+                                void* ready_flags, unsigned epoch, int flag_rows, int n_copy, int rank, int world,
+                                int slot, cudaStream_t stream) {
+  using namespace stb;
+  STB_REQUIRE(M % world == 0 && (M / world) % kBM == 0, "ag_gemm: M / world must be a multiple of %d", kBM);
+  STB_REQUIRE(flag_rows % kBM == 0 || kBM % flag_rows == 0, "ag_gemm: flag_rows must divide or be a multiple of %d", kBM);
+  STB_REQUIRE(n_copy >= 1 && n_copy < sm_count() / 2, "ag_gemm: n_copy %d out of range", n_copy);
+  STB_REQUIRE((long(K) * 2) % 16 == 0 && shard_offset_bytes % 16 == 0, "ag_gemm: rows must be 16-byte multiples");
+  GemmFused fx;
+  fx.a_ready = (const uint32_t*)ready_flags;
+  fx.a_epoch = epoch;
+  fx.a_flag_rows = flag_rows;
+  fx.m_rotate = rank * (M / world / kBM);   // local rows first, then the peers in ring order
+  fx.n_copy = n_copy;
+  fx.ag_bufs = (const uint8_t* const*)bufs_dev;
+  fx.ag_flag_pages = (uint32_t* const*)flag_pages_dev;
+  fx.ag_offset_bytes = shard_offset_bytes;
+  fx.ag_dst = (uint8_t*)A_full;
+  fx.ag_rank = rank; fx.ag_world = world; fx.ag_slot = slot;
+  return gemm_dispatch(A_full, B, C, M, N, K, K, ldb, ldc, 0, b_mn, 0, 0, 0, stream, fx);
 }

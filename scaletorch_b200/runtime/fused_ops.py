@@ -1,0 +1,202 @@
+"""Python side of the fused compute+collective kernels (csrc/comm.cu, csrc/gemm_tcgen05.cu).
+
+One :class:`SymmGroup` per process group owns
+* a *flag page* per rank (monotonic epochs, 8 slots) used by the on-device cross-GPU barriers, and
+* a *data window* per rank, carved into fixed regions (all-gather shards / reduce-scatter destinations /
+  all-reduce partials / gradient buckets),
+both allocated with ``torch.distributed._symmetric_memory`` so every peer's copy is mapped into this process
+(and, when the fabric supports it, one NVLS multicast address covers all copies).  The kernels receive the
+device array of peer base pointers; nothing goes through NCCL.
+
+Ops (all stream-ordered on the current stream, no host synchronisation):
+    all_gather_gemm      y = all_gather(x_shard) · Wᵀ in one kernel (copy CTAs + GEMM CTAs)      [column-parallel fwd, row-parallel bwd]
+    gemm_reduce_scatter  y_shard = reduce_scatter(x · Wᵀ): epilogue TMA reduce-adds into peer memory [row-parallel fwd, column-parallel bwd]
+    gemm_all_reduce      y = all_reduce(x · Wᵀ): GEMM into the window + one-shot peer reduction       [row-parallel fwd without SP]
+    all_reduce_f32_      in-place mean/sum of a range of the gradient window (two-shot / NVLS)         [data-parallel buckets]
+"""
+from __future__ import annotations
+
+import ctypes
+
+import torch
+import torch.distributed as dist
+
+from .. import _native as N
+
+_groups: dict[int, "SymmGroup"] = {}
+_P, _I, _L, _U, _F = ctypes.c_void_p, ctypes.c_int, ctypes.c_long, ctypes.c_uint, ctypes.c_float
+N.register("stb_symm_barrier", [_P, _I, _I, _I, _U, _P])
+N.register("stb_allreduce_f32", [_P, _P, _P, _L, _L, _F, _I, _I, _I, _U, _I, _P])
+N.register("stb_allreduce_bf16", [_P, _P, _P, _L, _L, _I, _I, _I, _U, _I, _P])
+N.register("stb_allreduce_oneshot_bf16", [_P, _P, _L, _P, _L, _I, _I, _I, _U, _I, _P])
+N.register("stb_allgather_pull", [_P, _P, _L, _P, _L, _L, _I, _P, _I, _I, _I, _U, _I, _P])
+N.register("stb_gemm_rs_bf16", [_P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _I, _P])
+N.register("stb_ag_gemm_bf16", [_P, _P, _P, _I, _I, _I, _I, _I, _I, _P, _P, _L, _P, _U, _I, _I, _I, _I, _I, _P])
+
+# flag slots (each op family has its own so families on different streams never share an epoch counter)
+SLOT_BARRIER, SLOT_AG, SLOT_RS, SLOT_AR, SLOT_DP = 0, 1, 2, 3, 4
+
+MB = 1 << 20
+
+
+class SymmGroup:
+    """Symmetric flag pages + data window of one process group."""
+
+    def __init__(self, group, window_bytes: int = 512 * MB):
+        import torch.distributed._symmetric_memory as sm
+
+        self.group = group
+        self.rank = dist.get_rank(group)
+        self.world = dist.get_world_size(group)
+        dev = torch.device("cuda", torch.cuda.current_device())
+        self.device = dev
+        self.flags = sm.empty(4096, dtype=torch.uint8, device=dev)
+        self.flags.zero_()
+        self.flags_h = sm.rendezvous(self.flags, group=group)
+        self.window = sm.empty(window_bytes, dtype=torch.uint8, device=dev)
+        self.window_h = sm.rendezvous(self.window, group=group)
+        self.window_bytes = window_bytes
+        self.flag_pages_dev = int(self.flags_h.buffer_ptrs_dev)
+        self.bufs_dev = int(self.window_h.buffer_ptrs_dev)
+        self.peer_ptrs = [int(p) for p in self.window_h.buffer_ptrs]
+        try:
+            self.mc_ptr = int(self.window_h.multicast_ptr or 0) if self.window_h.has_multicast_support() else 0
+        except Exception:
+            self.mc_ptr = 0
+        self.epoch = [1] * 8
+        # region layout (bytes): [AG shards | RS destinations | all-reduce partials | spare]
+        q = window_bytes // 4
+        self.off_ag, self.off_rs, self.off_ar, self.off_spare = 0, q, 2 * q, 3 * q
+        self.region_bytes = q
+        self.ready_flags = torch.zeros(1 << 16, dtype=torch.int32, device=dev)   # AG->GEMM row-block flags (local)
+        torch.cuda.synchronize()
+        dist.barrier(group)            # flag pages are zero everywhere before the first device barrier
+
+    def take_epochs(self, slot: int, n: int = 1) -> int:
+        e = self.epoch[slot]
+        self.epoch[slot] += n
+        return e
+
+    def view(self, offset: int, shape, dtype) -> torch.Tensor:
+        n = 1
+        for s in shape:
+            n *= s
+        nbytes = n * torch.empty((), dtype=dtype).element_size()
+        return self.window[offset:offset + nbytes].view(dtype).view(*shape)
+
+    def peer_ptr_array(self, offset: int):
+        arr = (ctypes.c_void_p * self.world)(*[p + offset for p in self.peer_ptrs])
+        return arr
+
+    def barrier(self, slot: int = SLOT_BARRIER) -> None:
+        N.call("stb_symm_barrier", self.flag_pages_dev, self.rank, self.world, slot, self.take_epochs(slot), N.stream_ptr())
+
+
+def get_group(group, window_bytes: int | None = None) -> SymmGroup:
+    key = id(group)
+    g = _groups.get(key)
+    if g is None:
+        g = SymmGroup(group, window_bytes or 512 * MB)
+        _groups[key] = g
+    return g
+
+
+def reset() -> None:
+    _groups.clear()
+
+
+# ------------------------------------------------------------------------------------------ ops
+def all_gather_gemm(x_shard: torch.Tensor, weight: torch.Tensor, group, b_mn: bool = False, n_copy: int = 16,
+                    flag_rows: int = 128):
+    """``(y [T, N], x_full [T, K])`` with ``T = world · T_shard``; weight ``[N, K]`` (or ``[K, N]`` if ``b_mn``)."""
+    g = get_group(group)
+    Ts, K = x_shard.shape
+    T = Ts * g.world
+    Nn = weight.shape[1] if b_mn else weight.shape[0]
+    assert Ts * K * 2 <= g.region_bytes, "all-gather shard does not fit the symmetric window region"
+    shard = g.view(g.off_ag, (Ts, K), torch.bfloat16)
+    shard.copy_(x_shard)
+    x_full = torch.empty((T, K), dtype=torch.bfloat16, device=x_shard.device)
+    y = torch.empty((T, Nn), dtype=torch.bfloat16, device=x_shard.device)
+    epoch = g.take_epochs(SLOT_AG, 2)
+    N.call("stb_ag_gemm_bf16", x_full.data_ptr(), weight.data_ptr(), y.data_ptr(), T, Nn, K, weight.stride(0),
+           y.stride(0), int(b_mn), g.bufs_dev, g.flag_pages_dev, g.off_ag, g.ready_flags.data_ptr(), epoch, flag_rows,
+           n_copy, g.rank, g.world, SLOT_AG, N.stream_ptr())
+    return y, x_full
+
+
+def gemm_reduce_scatter(x: torch.Tensor, weight: torch.Tensor, group, b_mn: bool = False) -> torch.Tensor:
+    """``reduce_scatter_rows(x · op(W)ᵀ)``: returns this rank's ``[T / world, N]`` row block of the summed product."""
+    g = get_group(group)
+    T, K = x.shape
+    Nn = weight.shape[1] if b_mn else weight.shape[0]
+    rows = T // g.world
+    assert rows * Nn * 2 <= g.region_bytes, "reduce-scatter destination does not fit the symmetric window region"
+    dest = g.view(g.off_rs, (rows, Nn), torch.bfloat16)
+    dest.zero_()
+    g.barrier(SLOT_RS)                                   # every destination is zeroed
+    ptrs = g.peer_ptr_array(g.off_rs)
+    N.call("stb_gemm_rs_bf16", x.data_ptr(), weight.data_ptr(), ptrs, T, Nn, K, x.stride(0), weight.stride(0), Nn,
+           int(b_mn), g.rank, g.world, N.stream_ptr())
+    g.barrier(SLOT_RS)                                   # every rank's adds have landed
+    return dest.clone()
+
+
+def gemm_all_reduce(x: torch.Tensor, weight: torch.Tensor, group, b_mn: bool = False) -> torch.Tensor:
+    """``all_reduce(x · op(W)ᵀ)``: the GEMM writes its partial into the window, then every rank sums the peers'
+    partials straight out of their memory (one-shot) into a fresh local tensor."""
+    from ..ops.gemm import gemm
+
+    g = get_group(group)
+    T = x.shape[0]
+    Nn = weight.shape[1] if b_mn else weight.shape[0]
+    assert T * Nn * 2 <= g.region_bytes
+    part = g.view(g.off_ar, (T, Nn), torch.bfloat16)
+    gemm(x, weight, b_mn=b_mn, out=part)
+    return all_reduce_window_bf16(g, g.off_ar, T * Nn).view(T, Nn)
+
+
+def all_reduce_window_bf16(g: SymmGroup, offset_bytes: int, n: int, sm_budget: int = 0) -> torch.Tensor:
+    out = torch.empty(n, dtype=torch.bfloat16, device=g.device)
+    epoch = g.take_epochs(SLOT_AR, 2)
+    N.call("stb_allreduce_oneshot_bf16", g.bufs_dev, g.flag_pages_dev, offset_bytes // 2, out.data_ptr(), n, g.rank,
+           g.world, SLOT_AR, epoch, sm_budget, N.stream_ptr())
+    return out
+
+
+def all_reduce_(t: torch.Tensor, group) -> torch.Tensor:
+    """Sum ``t`` (bf16, contiguous) over the group through the window; returns a new tensor."""
+    g = get_group(group)
+    n = t.numel()
+    assert n * 2 <= g.region_bytes and n % 8 == 0
+    g.view(g.off_ar, (n,), torch.bfloat16).copy_(t.reshape(-1))
+    return all_reduce_window_bf16(g, g.off_ar, n).view(t.shape)
+
+
+class GradWindow:
+    """fp32 gradient buffer allocated in symmetric memory so data-parallel buckets are reduced in place by
+    ``stb_allreduce_f32`` (two-shot over peer memory, NVLS multimem when available) with the 1/world scale fused."""
+
+    def __init__(self, group, numel: int):
+        import torch.distributed._symmetric_memory as sm
+
+        self.g = get_group(group)
+        dev = self.g.device
+        nbytes = (numel * 4 + (1 << 21) - 1) // (1 << 21) * (1 << 21)
+        self.raw = sm.empty(nbytes, dtype=torch.uint8, device=dev)
+        self.h = sm.rendezvous(self.raw, group=group)
+        self.bufs_dev = int(self.h.buffer_ptrs_dev)
+        try:
+            self.mc_ptr = int(self.h.multicast_ptr or 0) if self.h.has_multicast_support() else 0
+        except Exception:
+            self.mc_ptr = 0
+        self.grad = self.raw[: numel * 4].view(torch.float32)
+        self.grad.zero_()
+        torch.cuda.synchronize()
+        dist.barrier(group)
+
+    def all_reduce_range_(self, start: int, numel: int, scale: float, sm_budget: int = 32) -> None:
+        g = self.g
+        epoch = g.take_epochs(SLOT_DP, 2)
+        N.call("stb_allreduce_f32", self.bufs_dev, self.mc_ptr or None, g.flag_pages_dev, start, numel, float(scale),
+               g.rank, g.world, SLOT_DP, epoch, sm_budget, N.stream_ptr())

@@ -17,7 +17,8 @@ from ...runtime.flat_params import FlatParamStore, ParamSlot
 
 
 class Bucket:
-    def __init__(self, slots: list[ParamSlot], grad_flat: torch.Tensor, group, wire_dtype: torch.dtype = torch.float32):
+    def __init__(self, slots: list[ParamSlot], grad_flat: torch.Tensor, group, wire_dtype: torch.dtype = torch.float32,
+                 grad_window=None, comm_stream=None, sm_budget: int = 32):
         self.slots = slots
         self.params = [s.param for s in slots]
         self.start = min(s.offset for s in slots)
@@ -29,6 +30,11 @@ class Bucket:
         self.params_with_grad_ready: set[int] = set()
         self.handle = None
         self._wire: torch.Tensor | None = None
+        # fused path: the gradient buffer lives in symmetric memory and the bucket is reduced in place by
+        # stb_allreduce_f32 (two-shot over NVLink peer memory / NVLS, 1/world scale fused) on a side stream
+        self.grad_window = grad_window
+        self.comm_stream = comm_stream
+        self.sm_budget = sm_budget
 
     @property
     def numel(self) -> int:
@@ -45,6 +51,17 @@ class Bucket:
                 p.main_grad.zero_()
                 p.grad_written = True
         inv = 1.0 / self.world_size
+        if self.grad_window is not None:
+            cur = torch.cuda.current_stream()
+            ready = torch.cuda.Event()
+            ready.record(cur)
+            self.comm_stream.wait_event(ready)
+            with torch.cuda.stream(self.comm_stream):
+                self.grad_window.all_reduce_range_(self.start, self.numel, inv, self.sm_budget)
+                done = torch.cuda.Event()
+                done.record(self.comm_stream)
+            self.handle = _EventHandle(done)
+            return
         if self.wire_dtype == torch.bfloat16 and self.grad_data.is_cuda:
             if self._wire is None:
                 self._wire = torch.empty(self.numel, dtype=torch.bfloat16, device=self.grad_data.device)
@@ -79,13 +96,26 @@ class Bucket:
         return len(self.params_with_grad_ready) == len(self.params)
 
 
+class _EventHandle:
+    """``wait()`` makes the current stream wait for the side-stream all-reduce (no host blocking)."""
+
+    def __init__(self, event):
+        self.event = event
+
+    def wait(self):
+        torch.cuda.current_stream().wait_event(self.event)
+
+
 class BucketManager:
     """Partitions the store's parameters into buckets of at most ``bucket_size`` elements per reduction
     domain (dense / expert).  Oversize parameters get a bucket of their own."""
 
     def __init__(self, store: FlatParamStore, dense_group, expert_group=None, bucket_size: int = 2**24,
-                 wire_dtype: torch.dtype = torch.float32):
+                 wire_dtype: torch.dtype = torch.float32, grad_window=None, sm_budget: int = 32):
         self.store = store
+        self.grad_window = grad_window
+        self.sm_budget = sm_budget
+        self.comm_stream = torch.cuda.Stream() if grad_window is not None else None
         self.bucket_size = int(bucket_size)
         self.buckets: list[Bucket] = []
         self.param_to_bucket: dict[int, Bucket] = {}
@@ -95,15 +125,16 @@ class BucketManager:
             cur_n = 0
             for s in reversed(slots):
                 if cur and cur_n + s.numel > self.bucket_size:
-                    self._add(cur, group, wire_dtype)
+                    self._add(cur, group, wire_dtype, seg)
                     cur, cur_n = [], 0
                 cur.append(s)
                 cur_n += s.numel
             if cur:
-                self._add(cur, group, wire_dtype)
+                self._add(cur, group, wire_dtype, seg)
 
-    def _add(self, slots, group, wire_dtype) -> None:
-        b = Bucket(slots, self.store.grad_flat, group, wire_dtype)
+    def _add(self, slots, group, wire_dtype, seg="dense") -> None:
+        gw = self.grad_window if seg == "dense" else None   # the window is registered with the dense sync group
+        b = Bucket(slots, self.store.grad_flat, group, wire_dtype, gw, self.comm_stream, self.sm_budget)
         self.buckets.append(b)
         for s in slots:
             self.param_to_bucket[id(s.param)] = b

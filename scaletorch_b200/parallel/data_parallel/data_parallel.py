@@ -28,10 +28,30 @@ def _groups(group, expert_group):
     return group, expert_group if expert_group is not None else group
 
 
-def get_store(module: nn.Module) -> FlatParamStore:
+def get_store(module: nn.Module, grad_sync_group=None, fused_comm: bool = True) -> FlatParamStore:
+    """Builds (once) the flat parameter / gradient store.  With a multi-rank NCCL ``grad_sync_group`` and the
+    fused collectives enabled, the gradient buffer is allocated in symmetric memory (``GradWindow``)."""
     store = getattr(module, "_stb_store", None)
     if store is None:
-        store = FlatParamStore(module)
+        window = None
+        p0 = next(module.parameters())
+        if grad_sync_group is not None and fused_comm and p0.is_cuda:
+            from ...runtime import symm
+
+            if symm.group_ready(grad_sync_group) and symm.has_kernel("stb_allreduce_f32"):
+                from ...runtime.fused_ops import GradWindow
+
+                holder = {}
+
+                def alloc(numel):
+                    holder["w"] = GradWindow(grad_sync_group, numel)
+                    return holder["w"].grad[:numel]
+
+                store = FlatParamStore(module, grad_alloc=alloc)
+                window = holder["w"]
+        if store is None:
+            store = FlatParamStore(module)
+        store.grad_window = window
         module._stb_store = store
     return store
 
@@ -86,7 +106,8 @@ class DataParallelBucket(_DPBase):
         self.group, self.expert_group = _groups(group, expert_group)
         self.grad_type = grad_type or torch.float32
         self.wire_dtype = wire_dtype or torch.float32
-        self.bucket_manager = BucketManager(self.store, self.group, self.expert_group, bucket_size, self.wire_dtype)
+        self.bucket_manager = BucketManager(self.store, self.group, self.expert_group, bucket_size, self.wire_dtype,
+                                            grad_window=getattr(self.store, "grad_window", None))
         self._post_backward_queued = False
         for s in self.store.slots:
             s.param.grad_ready_hook = self._make_ready_hook(s.param)

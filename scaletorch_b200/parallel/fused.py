@@ -1,9 +1,9 @@
 """Dispatch layer for the fused compute+collective kernels over symmetric memory.
 
-Each ``*_available`` predicate answers "can the fused sm_100a kernel serve this call?" (CUDA bf16
-tensors, NCCL group fully inside one NVSwitch domain, symmetric-memory runtime initialised, shapes
-supported).  When it returns False the callers in ``tensor_parallel`` / ``data_parallel`` /
-``expert_parallel`` / ``context_parallel`` run the c10d path, which is also the measured baseline.
+Each ``*_available`` predicate answers "can the fused sm_100a kernel serve this call?" (CUDA bf16 tensors, an
+NCCL group inside one NVSwitch domain, shapes the kernels support, window large enough).  When it returns
+False the callers in ``tensor_parallel`` / ``data_parallel`` run the c10d path, which is also the measured
+baseline (``--fused_comm False`` or ``SCALETORCH_B200_FUSED_COMM=0`` forces it).
 """
 from __future__ import annotations
 
@@ -13,19 +13,35 @@ from ..runtime import symm
 
 
 def _ok(t: torch.Tensor, group) -> bool:
-    return t.is_cuda and t.dtype == torch.bfloat16 and symm.group_ready(group)
+    return t.is_cuda and t.dtype == torch.bfloat16 and t.is_contiguous() and symm.group_ready(group)
 
 
-def ag_gemm_available(x2d: torch.Tensor, group) -> bool:
-    return _ok(x2d, group) and symm.has_kernel("stb_ag_gemm_bf16")
+def _world(group) -> int:
+    import torch.distributed as dist
+
+    return dist.get_world_size(group)
 
 
-def gemm_rs_available(x2d: torch.Tensor, group) -> bool:
-    return _ok(x2d, group) and symm.has_kernel("stb_gemm_rs_bf16")
+def ag_gemm_available(x_shard: torch.Tensor, group) -> bool:
+    """x_shard ``[T/world, K]``: every rank's row block must be a multiple of the 128-row tile."""
+    return (_ok(x_shard, group) and symm.has_kernel("stb_ag_gemm_bf16") and x_shard.shape[0] % 128 == 0
+            and x_shard.numel() * 2 <= symm.region_bytes(group) and _world(group) <= 8)
+
+
+def gemm_rs_available(x_full: torch.Tensor, group) -> bool:
+    """x_full ``[T, K]`` with ``T / world`` a multiple of 128."""
+    w = _world(group)
+    return (_ok(x_full, group) and symm.has_kernel("stb_gemm_rs_bf16") and x_full.shape[0] % (128 * w) == 0 and w <= 8)
+
+
+def gemm_ar_available(x: torch.Tensor, n_out: int, group) -> bool:
+    return (_ok(x, group) and symm.has_kernel("stb_allreduce_oneshot_bf16")
+            and x.shape[0] * n_out * 2 <= symm.region_bytes(group) and (x.shape[0] * n_out) % 8 == 0)
 
 
 def allreduce_available(t: torch.Tensor, group) -> bool:
-    return _ok(t, group) and symm.has_kernel("stb_allreduce_bf16")
+    return (_ok(t, group) and symm.has_kernel("stb_allreduce_oneshot_bf16") and t.numel() % 8 == 0
+            and t.numel() * 2 <= symm.region_bytes(group))
 
 
 def all_gather_gemm(x2d, weight, group, b_mn: bool = False):
@@ -38,6 +54,12 @@ def gemm_reduce_scatter(x2d, weight, group, b_mn: bool = False):
     from ..runtime import fused_ops
 
     return fused_ops.gemm_reduce_scatter(x2d, weight, group, b_mn=b_mn)
+
+
+def gemm_all_reduce(x2d, weight, group, b_mn: bool = False):
+    from ..runtime import fused_ops
+
+    return fused_ops.gemm_all_reduce(x2d, weight, group, b_mn=b_mn)
 
 
 def all_reduce_(t, group):

@@ -85,7 +85,7 @@ class _ColumnParallelFn(torch.autograd.Function):
             x_full = torch.empty((ws * x2.shape[0], x2.shape[1]), dtype=x2.dtype, device=x2.device)
             hx = dist.all_gather_into_tensor(x_full, x2.contiguous(), group=group, async_op=True)
             if F_ is not None and F_.gemm_rs_available(dy2, group):
-                dx = F_.gemm_reduce_scatter(dy2, weight, group, b_mn=True)
+                dx = F_.gemm_reduce_scatter(dy2, weight, group, b_mn=True)   # dgrad GEMM -> reduce-scatter, one kernel
                 hr = None
             else:
                 dx_full = gemm(dy2, weight, b_mn=True)
@@ -101,6 +101,11 @@ class _ColumnParallelFn(torch.autograd.Function):
             dw = wgrad_into(weight, dy2, x_full) if ctx.needs_input_grad[1] else None
             if hr is not None:
                 hr.wait()
+            return dx.view(ctx.x_shape), dw, None, None, None
+        F_ = _fused() if (ctx.fused and ws > 1) else None
+        if F_ is not None and F_.gemm_ar_available(dy2, weight.shape[1], group):
+            dx = F_.gemm_all_reduce(dy2, weight, group, b_mn=True)
+            dw = wgrad_into(weight, dy2, x2) if ctx.needs_input_grad[1] else None
             return dx.view(ctx.x_shape), dw, None, None, None
         dx = gemm(dy2, weight, b_mn=True)
         h = dist.all_reduce(dx, group=group, async_op=True) if ws > 1 else None
@@ -126,12 +131,12 @@ class _RowParallelFn(torch.autograd.Function):
                 return F_.gemm_reduce_scatter(x2, weight, group)
             y = gemm(x2, weight)
             return C._reduce_scatter_dim0(y, group) if ws > 1 else y
-        y = gemm(x2, weight)
-        if ws > 1:
-            F_ = _fused() if fused_comm else None
-            if F_ is not None and F_.allreduce_available(y, group):
-                y = F_.all_reduce_(y, group)
-            else:
+        F_ = _fused() if (fused_comm and ws > 1) else None
+        if F_ is not None and F_.gemm_ar_available(x2, weight.shape[0], group):
+            y = F_.gemm_all_reduce(x2, weight, group)   # GEMM into the window + one-shot peer reduction
+        else:
+            y = gemm(x2, weight)
+            if ws > 1:
                 dist.all_reduce(y, group=group)
         return y.view(*x.shape[:-1], weight.shape[0])
 

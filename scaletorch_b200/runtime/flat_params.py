@@ -38,7 +38,9 @@ def is_expert_param(name: str) -> bool:
 
 
 class FlatParamStore:
-    def __init__(self, module: nn.Module, grad_dtype: torch.dtype = torch.float32):
+    def __init__(self, module: nn.Module, grad_dtype: torch.dtype = torch.float32, grad_alloc=None):
+        """``grad_alloc(numel) -> fp32 tensor`` lets the caller place the gradient buffer in symmetric memory
+        (data-parallel buckets are then reduced in place over NVLink)."""
         named = []
         seen: set[int] = set()
         for name, p in module.named_parameters():
@@ -67,7 +69,8 @@ class FlatParamStore:
         self.total_numel = off
         self.expert_numel = off - self.dense_numel
         self.param_flat = torch.zeros(off, dtype=self.param_dtype, device=self.device)
-        self.grad_flat = torch.zeros(off, dtype=grad_dtype, device=self.device)
+        self.grad_flat = grad_alloc(off) if grad_alloc is not None else torch.zeros(off, dtype=grad_dtype, device=self.device)
+        assert self.grad_flat.numel() >= off and self.grad_flat.dtype == grad_dtype
         for s in self.slots:
             view = self.param_flat[s.offset:s.offset + s.numel].view(s.param.shape)
             view.copy_(s.param.data)

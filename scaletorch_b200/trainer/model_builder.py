@@ -55,8 +55,10 @@ def create_model(config, dtype: torch.dtype, device: torch.device):
         model, model_config, save_dir=config.model_name_or_path,
         load_weights=getattr(config, "load_pretrained_weights", False))
     model.to(dtype).to(device)
-    get_store(model)  # flat parameter / main-grad buffers (also on a single GPU)
     grad_sync = pgm.grad_sync_world_size if pgm else 1
+    # flat parameter / main-grad buffers (also on a single GPU); in symmetric memory when gradients are
+    # all-reduced over NVLink by our own kernel
+    get_store(model, pgm.grad_sync_group if (pgm and grad_sync > 1) else None, getattr(config, "fused_comm", True))
     if pgm and (grad_sync > 1 or pgm.expert_grad_sync_world_size > 1):
         wire = torch.bfloat16 if getattr(config, "grad_wire_dtype", "float32") == "bfloat16" else torch.float32
         model = DataParallelBucket(model, wire_dtype=wire)

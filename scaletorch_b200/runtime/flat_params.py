@@ -79,6 +79,14 @@ class FlatParamStore:
             s.param.grad_written = False
             s.param._stb_slot = s
         self._by_param = {id(s.param): s for s in self.slots}
+        # a parameter reachable under several names (tied embedding / LM head) receives one kernel-epilogue
+        # gradient contribution per use; data-parallel buckets wait for all of them.  (Set here rather than in
+        # the model constructor because ``to_empty`` re-creates Parameter objects and drops attributes.)
+        uses: dict[int, int] = {}
+        for _n, p in module.named_parameters(remove_duplicate=False):
+            uses[id(p)] = uses.get(id(p), 0) + 1
+        for s in self.slots:
+            s.param._stb_expected_grads = uses.get(id(s.param), 1)
         self._hooks = []
         self._install_fallback_hooks()
 

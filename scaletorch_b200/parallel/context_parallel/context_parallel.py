@@ -114,6 +114,11 @@ def ring_attention(q, k, v, sm_scale: float, is_causal: bool = True, group=None)
             return ops.flash_attention(q, k, v, is_causal, sm_scale)[0]
         group, send_rank, recv_rank = pgm.cp_group, pgm.cp_send_rank, pgm.cp_recv_rank
         cp_rank, cp_size = pgm.cp_rank, pgm.cp_world_size
+        if q.is_cuda and os.environ.get("SCALETORCH_B200_FUSED_COMM", "1") == "1":
+            from . import fused_ring
+
+            if fused_ring.available(q, k, group):   # K/V pulled from the peers' HBM by the attention kernel itself
+                return fused_ring.fused_ring_attention(q, k, v, sm_scale, is_causal, group)
     else:
         import torch.distributed as dist
 

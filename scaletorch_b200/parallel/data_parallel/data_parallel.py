@@ -106,8 +106,12 @@ class DataParallelBucket(_DPBase):
         self.group, self.expert_group = _groups(group, expert_group)
         self.grad_type = grad_type or torch.float32
         self.wire_dtype = wire_dtype or torch.float32
+        import os
+
+        bucket_size = int(os.environ.get("SCALETORCH_B200_DP_BUCKET", bucket_size))
+        sm_budget = int(os.environ.get("SCALETORCH_B200_DP_SM_BUDGET", 148))  # profiles/dp_allreduce_sweep.md
         self.bucket_manager = BucketManager(self.store, self.group, self.expert_group, bucket_size, self.wire_dtype,
-                                            grad_window=getattr(self.store, "grad_window", None))
+                                            grad_window=getattr(self.store, "grad_window", None), sm_budget=sm_budget)
         self._post_backward_queued = False
         for s in self.store.slots:
             s.param.grad_ready_hook = self._make_ready_hook(s.param)

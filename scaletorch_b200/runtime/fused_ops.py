@@ -190,6 +190,12 @@ class GradWindow:
             self.mc_ptr = int(self.h.multicast_ptr or 0) if self.h.has_multicast_support() else 0
         except Exception:
             self.mc_ptr = 0
+        import os
+
+        if os.environ.get("SCALETORCH_B200_NO_MULTIMEM", "0") == "1":
+            self.mc_ptr = 0
+        if self.g.rank == 0 and os.environ.get("SCALETORCH_B200_VERBOSE", "0") == "1":
+            print(f"[GradWindow] {nbytes >> 20} MiB, world {self.g.world}, multicast_ptr={'yes' if self.mc_ptr else 'no'}", flush=True)
         self.grad = self.raw[: numel * 4].view(torch.float32)
         self.grad.zero_()
         torch.cuda.synchronize()

@@ -65,6 +65,29 @@ def _worker(rank, world, port, mode, fused):
                     continue      # partial over heads / tokens: summed across TP by the trainer
                 ref = shard_tensor(n, fg[n], cfg, world, rank, 1, 0)
                 assert _rel(p.grad, ref) < 6e-2, (n, _rel(p.grad, ref))
+        elif mode == "cp":
+            setup_process_group_manager(tp_size=1, cp_size=world, pp_size=1, dp_size=1)
+            par = Qwen3(cfg, ParallelContext.from_pgm(fused_comm=fused)).to(torch.bfloat16).to(dev)
+            par.load_state_dict(full.state_dict())
+            S2 = 1024
+            ids2 = torch.randint(0, cfg.vocab_size, (B, S2 + 1), device=dev)
+            dist.broadcast(ids2, 0)
+            x2, y2 = ids2[:, :-1].contiguous(), ids2[:, 1:].contiguous()
+            lf = full.loss(x2, y2)
+            lf.backward()
+            n = S2 // world
+            for _ in range(2):
+                par.zero_grad()
+                lp = par.loss(x2[:, rank * n:(rank + 1) * n].contiguous(), y2[:, rank * n:(rank + 1) * n].contiguous())
+                lp.backward()
+                tot = lp.detach().float().clone()
+                dist.all_reduce(tot)
+                assert abs(tot.item() / world - lf.item()) < 3e-2 * abs(lf.item()), (tot.item() / world, lf.item())
+                fg = {nm: p.grad for nm, p in full.named_parameters()}
+                for nm, p in par.named_parameters():
+                    gsum = p.grad.float().clone()
+                    dist.all_reduce(gsum)
+                    assert _rel(gsum / world, fg[nm]) < 8e-2, (nm, _rel(gsum / world, fg[nm]))
         else:  # dp
             setup_process_group_manager(tp_size=1, cp_size=1, pp_size=1, dp_size=world)
             par = Qwen3(cfg, ParallelContext.from_pgm(fused_comm=fused)).to(torch.bfloat16).to(dev)
@@ -85,7 +108,7 @@ def _worker(rank, world, port, mode, fused):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("mode,fused", [("tp", False), ("tp", True), ("tp_sp", False), ("tp_sp", True), ("dp", False), ("dp", True)])
+@pytest.mark.parametrize("mode,fused", [("tp", False), ("tp", True), ("tp_sp", False), ("tp_sp", True), ("dp", False), ("dp", True), ("cp", False), ("cp", True)])
 def test_two_gpu_model_equality(mode, fused):
     if torch.cuda.device_count() < 2:
         pytest.skip("needs at least 2 GPUs")

@@ -88,8 +88,16 @@ class _GroupedLinear(torch.autograd.Function):
         return dx, dw, None
 
 
+def _use_native(x_sorted, *weights) -> bool:
+    if not (native_grouped_available() and N.use_native(x_sorted) and x_sorted.dtype == torch.bfloat16):
+        return False
+    from .grouped_native import supported
+
+    return all(supported(w) for w in weights)
+
+
 def grouped_linear(x_sorted: torch.Tensor, weight: torch.Tensor, tokens_per_expert: torch.Tensor) -> torch.Tensor:
-    if native_grouped_available() and N.use_native(x_sorted) and x_sorted.dtype == torch.bfloat16:
+    if _use_native(x_sorted, weight):
         from .grouped_native import grouped_linear_native
 
         return grouped_linear_native(x_sorted, weight, tokens_per_expert)
@@ -98,5 +106,9 @@ def grouped_linear(x_sorted: torch.Tensor, weight: torch.Tensor, tokens_per_expe
 
 def grouped_mlp(x_sorted, tokens_per_expert, gate_up_proj, down_proj) -> torch.Tensor:
     """SwiGLU expert MLP over expert-sorted rows: ``down(silu(gate(x)) * up(x))`` per expert."""
+    if _use_native(x_sorted, gate_up_proj, down_proj):
+        from .grouped_native import grouped_mlp_native
+
+        return grouped_mlp_native(x_sorted, tokens_per_expert, gate_up_proj, down_proj)
     gu = grouped_linear(x_sorted, gate_up_proj, tokens_per_expert)
     return grouped_linear(swiglu(gu), down_proj, tokens_per_expert)

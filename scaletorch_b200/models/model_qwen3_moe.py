@@ -95,6 +95,9 @@ class MoELayer(nn.Module):
                                 aux_loss_coef=getattr(config, "router_aux_loss_coef", 0.001))
         self.experts = MoEExperts(self.experts_per_rank, config.hidden_size, config.moe_intermediate_size)
         self._aux_loss: torch.Tensor | None = None
+        self.use_fused_ep = True                     # peer-memory dispatch/combine when the fabric allows it
+        self.ep_capacity_factor = getattr(config, "ep_capacity_factor", None)
+        self.dropped_pairs: torch.Tensor | None = None   # device counter of over-capacity pairs (fused EP path)
 
     def reset_parameters(self) -> None:
         self.router.reset_parameters()
@@ -111,7 +114,13 @@ class MoELayer(nn.Module):
             x = tp_comms.gather_from_sequence_parallel_region(x, ctx.tp_group)
         weights, idx, aux = self.router(x)
         self._aux_loss = aux
-        if self.ep_size > 1:
+        if self.ep_size > 1 and self.use_fused_ep and self._fused_ep_ok(x):
+            from ..parallel.expert_parallel import fused_ep
+
+            out, st = fused_ep.fused_moe_ep(x, weights, idx, self.experts.gate_up_proj, self.experts.down_proj,
+                                            self.num_experts, ctx.ep_group, self.ep_capacity_factor)
+            self.dropped_pairs = st.dropped if self.dropped_pairs is None else self.dropped_pairs + st.dropped
+        elif self.ep_size > 1:
             recv, tokens_per_expert, state = dispatch_tokens(x, idx, self.num_experts, self.ep_size, ctx.ep_group)
             y = self.experts(recv, tokens_per_expert)
             out = gather_tokens(y, weights, state, ctx.ep_group)
@@ -124,6 +133,13 @@ class MoELayer(nn.Module):
             # every TP rank holds the full, identical output: keep the local token shard
             out = _SplitKeepGrad.apply(out, ctx.tp_group)
         return out
+
+    def _fused_ep_ok(self, x) -> bool:
+        if not x.is_cuda:
+            return False
+        from ..parallel.expert_parallel import fused_ep
+
+        return fused_ep.available(self.ctx.ep_group, x, self.experts.gate_up_proj, self.experts.down_proj)
 
     def _forward_local(self, x, weights, idx):
         T, H = x.shape

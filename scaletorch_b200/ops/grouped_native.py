@@ -39,6 +39,18 @@ class GroupedLayout:
         self.dest = rows - self.offs[row_e] + offs_pad[row_e]          # padded position of every sorted row
         self.num_rows, self.E = num_rows, E
 
+    @classmethod
+    def from_padded_offsets(cls, offs_pad: torch.Tensor, r_max: int, num_experts: int) -> "GroupedLayout":
+        """Layout for rows that already sit at their padded positions (EP receive regions): ``offs_pad [E+1]``."""
+        self = cls.__new__(cls)
+        offs_pad = offs_pad.to(torch.int64)
+        self.offs_pad = offs_pad.to(torch.int32).contiguous()
+        self.r_max, self.E, self.num_rows = r_max, num_experts, None
+        tiles = torch.arange(r_max // 128, device=offs_pad.device, dtype=torch.int64) * 128
+        te = torch.searchsorted(offs_pad[1:].contiguous(), tiles, right=True)
+        self.tile_expert = torch.where(tiles < offs_pad[-1], te, torch.full_like(te, -1)).to(torch.int32).contiguous()
+        return self
+
     def pad(self, x_sorted: torch.Tensor) -> torch.Tensor:
         out = torch.zeros((self.r_max, x_sorted.shape[1]), dtype=x_sorted.dtype, device=x_sorted.device)
         return out.index_copy(0, self.dest, x_sorted)
@@ -56,9 +68,16 @@ class _GroupedLinearPadded(torch.autograd.Function):
     """``y_pad = x_pad · W[e]ᵀ`` on padded rows; dX / dW through the dgrad / ragged-wgrad modes."""
 
     @staticmethod
-    def forward(ctx, x_pad, weight, layout):
+    def forward(ctx, x_pad, weight, layout, bufs=None):
+        """``bufs``: optional ``{"out": tensor, "dx": tensor}`` preallocated destinations (the EP path points them
+        at its symmetric return region so the combine / dispatch-backward pull needs no staging copy).  They travel
+        in a dict so autograd does not treat them as inputs."""
         E, Nn, K = weight.shape
-        y = torch.empty((layout.r_max, Nn), dtype=x_pad.dtype, device=x_pad.device)
+        bufs = bufs or {}
+        y = bufs.get("out")
+        if y is None:
+            y = torch.empty((layout.r_max, Nn), dtype=x_pad.dtype, device=x_pad.device)
+        ctx.dx_out = bufs.get("dx")
         _call(0, x_pad, weight, y, layout, Nn, K)
         ctx.save_for_backward(x_pad, weight)
         ctx.layout = layout
@@ -72,7 +91,7 @@ class _GroupedLinearPadded(torch.autograd.Function):
         dy = dy.contiguous()
         dx = None
         if ctx.needs_input_grad[0]:
-            dx = torch.empty_like(x_pad)
+            dx = ctx.dx_out if ctx.dx_out is not None else torch.empty_like(x_pad)
             _call(1, dy, weight, dx, layout, Nn, K)
         dw = None
         if ctx.needs_input_grad[1]:
@@ -88,7 +107,7 @@ class _GroupedLinearPadded(torch.autograd.Function):
                 dw32 = torch.empty((E, Nn, K), dtype=torch.float32, device=x_pad.device)
                 _call(2, dy, x_pad, dw32, layout, Nn, K, out_fp32=1, accumulate=0)
                 dw = dw32.to(weight.dtype)
-        return dx, dw, None
+        return dx, dw, None, None
 
 
 def supported(weight: torch.Tensor) -> bool:

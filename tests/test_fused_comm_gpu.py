@@ -81,12 +81,40 @@ def _worker(rank, world, port, which):
                 y, x_full = F.all_gather_gemm(xs, w, group)
                 assert torch.equal(x_full, gathered)
                 assert _rel(y, ref) < 2e-2, _rel(y, ref)
+        elif which == "ep_moe":
+            from types import SimpleNamespace
+
+            from scaletorch_b200.models.model_qwen3_moe import MoELayer
+
+            cfg = SimpleNamespace(num_experts=8, num_experts_per_tok=2, hidden_size=256, moe_intermediate_size=128,
+                                  norm_topk_prob=True, router_aux_loss_coef=0.0)
+            ctx = SimpleNamespace(sp=False, ep_size=world, ep_rank=rank, ep_group=group, tp_group=None)
+            torch.manual_seed(7)
+            layer = MoELayer(cfg, ctx).to(dev).bfloat16()
+            torch.manual_seed(50 + rank)
+            x = (torch.randn(600, 256, device=dev)).bfloat16().requires_grad_()
+            gout = torch.randn(600, 256, device=dev).bfloat16()
+            res = {}
+            for fused in (True, False, True):
+                layer.use_fused_ep = fused
+                layer.zero_grad()
+                x.grad = None
+                y = layer(x)
+                y.backward(gout)
+                res[fused] = (y.detach().clone(), x.grad.clone(), {n: p.grad.clone() for n, p in layer.named_parameters()})
+            assert layer.dropped_pairs is not None and int(layer.dropped_pairs) == 0
+            yf, xf, gf = res[True]
+            yr, xr, gr = res[False]
+            assert _rel(yf, yr) < 2e-2, _rel(yf, yr)
+            assert _rel(xf, xr) < 3e-2, _rel(xf, xr)
+            for n in gf:
+                assert _rel(gf[n], gr[n]) < 3e-2, (n, _rel(gf[n], gr[n]))
         dist.barrier()
     finally:
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("which", ["barrier_allreduce", "gemm_rs", "ag_gemm"])
+@pytest.mark.parametrize("which", ["barrier_allreduce", "gemm_rs", "ag_gemm", "ep_moe"])
 def test_fused_collectives_two_gpus(which):
     if torch.cuda.device_count() < 2:
         pytest.skip("needs at least 2 GPUs")

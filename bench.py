@@ -135,7 +135,7 @@ def run_ours(args):
     from scaletorch_b200 import _native
     from scaletorch_b200.data import MicroBatchDataLoader
     from scaletorch_b200.trainer import (ScaleTorchArguments, create_model, create_optimizer,
-                                         initialize_distributed_training, train_step)
+                                         initialize_distributed_training, training_step)
     from scaletorch_b200.utils.misc import get_mfu, get_num_params
 
     rank, local_rank, world = dist_env()
@@ -167,6 +167,7 @@ def run_ours(args):
                 x = next(loader)
                 self.b.append({k: (v.to(device) if torch.is_tensor(v) else v) for k, v in x.items()})
             self.i = 0
+            self.gradient_accumulation_steps = args.grad_accum
 
         def __next__(self):
             x = self.b[self.i % len(self.b)]
@@ -177,7 +178,7 @@ def run_ours(args):
         optimizer.zero_grad()
         if hasattr(model, "reset"):
             model.reset()
-        loss = train_step(model, src, device, torch.bfloat16, args.grad_accum, args.gradient_checkpointing)
+        loss = training_step(model, src, device, torch.bfloat16, cfg)
         optimizer.step()
         return loss
 
@@ -187,6 +188,21 @@ def run_ours(args):
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
+    if os.environ.get("SCALETORCH_B200_PROFILE"):
+        # diagnosis only (kernel-time table of rank 0 -> file); numbers of a profiled run are never reported
+        from torch.profiler import ProfilerActivity, profile
+
+        with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA]) as prof:
+            for _ in range(2):
+                step_with(staged)
+            torch.cuda.synchronize()
+        if rank == 0:
+            with open(os.environ["SCALETORCH_B200_PROFILE"], "w") as f:
+                f.write(prof.key_averages().table(sort_by="cuda_time_total", row_limit=45, max_name_column_width=90))
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        return
     l0 = _native.launch_count
     ms = timed_region(torch, dist, world, lambda: step_with(staged), args.steps)
     launches = _native.launch_count - l0

@@ -45,6 +45,22 @@ def train_step(model, data_loader, device, dtype: torch.dtype = torch.bfloat16, 
     return total
 
 
+def training_step(model, data_loader, device, dtype, config, tensor_shapes=None) -> torch.Tensor:
+    """Schedule dispatch used by ``tools/train.py`` and ``bench.py``: AFAB / 1F1B when the model is pipeline-parallel
+    (reference ``train.py:351-363``), the plain accumulate loop otherwise."""
+    if pgm and pgm.pp_world_size > 1:
+        from ..parallel.pipeline_parallel.pipeline_parallel import train_step_pipeline_1f1b, train_step_pipeline_afab
+        from .model_builder import get_tensor_shapes
+
+        if tensor_shapes is None:
+            raw = model.module if hasattr(model, "module") else model
+            tensor_shapes = get_tensor_shapes(config, raw.config)
+        fn = train_step_pipeline_afab if getattr(config, "pipeline_parallel_engine", "1f1b") == "afab" else train_step_pipeline_1f1b
+        return fn(model, data_loader, tensor_shapes, device, dtype, config.gradient_checkpointing)
+    return train_step(model, data_loader, device, dtype, config.gradient_accumulation_steps, config.gradient_checkpointing,
+                      getattr(config, "aux_loss", True))
+
+
 def clip_gradients(model, max_grad_norm: float | None, optimizer=None) -> float | None:
     """Global-norm clipping.  With the fused optimiser clipping is folded into ``optimizer.step`` and this
     only reports the norm; for plain torch optimisers it clips ``.grad`` in place over the model-parallel

@@ -63,7 +63,22 @@ def get_mfu(tokens_per_second: float, num_params: float, model_config: Any, theo
     hd = getattr(model_config, "head_dim", None) or model_config.hidden_size // heads
     S = seq_len if seq_len is not None else getattr(model_config, "max_position_embeddings", 2048)
     peak = theoretical_flops or get_theoretical_flops()
-    return tokens_per_second * flops_per_token(num_params, L, heads, hd, S) / peak * 100.0
+    return tokens_per_second * flops_per_token(active_params(num_params, model_config), L, heads, hd, S) / peak * 100.0
+
+
+def active_params(num_params: float, model_config: Any) -> float:
+    """Parameters that take part in one token's forward: for MoE models only ``top_k / num_experts`` of the expert
+    weights count (the reference's formula uses all of them, which overstates MoE MFU by ~10x)."""
+    E = getattr(model_config, "num_experts", 0) or 0
+    k = getattr(model_config, "num_experts_per_tok", 0) or 0
+    inter = getattr(model_config, "moe_intermediate_size", 0) or 0
+    if E <= 0 or k <= 0 or inter <= 0:
+        return num_params
+    step = getattr(model_config, "decoder_sparse_step", 1) or 1
+    mlp_only = getattr(model_config, "mlp_only_layers", None) or []
+    n_moe = sum(1 for i in range(model_config.num_hidden_layers) if i not in mlp_only and (i + 1) % step == 0)
+    expert_total = n_moe * E * 3 * model_config.hidden_size * inter
+    return num_params - expert_total * (1.0 - k / E)
 
 
 _TP_SHARDED_KEYS = ("q_proj", "k_proj", "v_proj", "qkv_proj", "out_proj", "o_proj", "gate_proj", "up_proj",

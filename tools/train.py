@@ -30,7 +30,7 @@ from scaletorch_b200.data import MicroBatchDataLoader  # noqa: E402
 from scaletorch_b200.parallel.process_group import process_group_manager as pgm  # noqa: E402
 from scaletorch_b200.trainer import (ScaleTorchArguments, cleanup_distributed, clip_gradients, create_lr_scheduler,  # noqa: E402
                                      create_model, create_optimizer, get_dtype, get_tensor_shapes,
-                                     initialize_distributed_training, log_training_metrics, train_step,
+                                     initialize_distributed_training, log_training_metrics, training_step,
                                      validate_config)
 from scaletorch_b200.trainer.metrics import is_logging_rank  # noqa: E402
 from scaletorch_b200.trainer.optimizer import FusedAdamW  # noqa: E402
@@ -114,15 +114,7 @@ def main(argv=None) -> None:
             optimizer.zero_grad(set_to_none=True)
             if hasattr(model, "reset"):
                 model.reset()
-            if pgm and pgm.pp_world_size > 1:
-                from scaletorch_b200.parallel.pipeline_parallel.pipeline_parallel import (train_step_pipeline_1f1b,
-                                                                                          train_step_pipeline_afab)
-
-                fn = train_step_pipeline_afab if config.pipeline_parallel_engine == "afab" else train_step_pipeline_1f1b
-                loss_t = fn(model, data_loader, tensor_shapes, device, dtype, config.gradient_checkpointing)
-            else:
-                loss_t = train_step(model, data_loader, device, dtype, config.gradient_accumulation_steps,
-                                    config.gradient_checkpointing, config.aux_loss)
+            loss_t = training_step(model, data_loader, device, dtype, config, tensor_shapes)
             grad_norm = clip_gradients(model, config.max_grad_norm, optimizer)
             optimizer.step()
             lr_scheduler.step()

@@ -115,6 +115,80 @@ int stb_embedding_fwd(const long* ids, const void* W, void* out, long T, int H, 
 int stb_embedding_bwd(const long* ids, const void* dout, float* dW, long T, int H, int vocab_start,
                       int vocab_local, cudaStream_t stream);
 
+/* ---- flash attention (tcgen05, head_dim 128, GQA, causal), csrc/attention_fwd.cu / attention_bwd.cu ------------
+ * Tensors are [B, S, H, D] views described by element strides (sb, ss, sh); D is contiguous. lse / delta are
+ * [B, Hq, Sq] fp32. The backward runs three kernels (delta, dK/dV, dQ) and writes dq/dk/dv through their own strides
+ * (so a packed dqkv buffer can be filled in place).
+ * Reference: F.scaled_dot_product_attention in scaletorch/models/attention_utils.py:130-152 and the eager per-block
+ * ring attention in scaletorch/parallel/context_parallel/context_parallel.py:266-364. */
+int stb_flash_attn_fwd(const void* q, const void* k, const void* v, void* out, float* lse, int B, int Sq, int Sk,
+                       int Hq, int Hkv, int D, long q_sb, long q_ss, long q_sh, long k_sb, long k_ss, long k_sh,
+                       long v_sb, long v_ss, long v_sh, float scale, int causal, cudaStream_t stream);
+int stb_flash_attn_bwd(const void* dout, const void* q, const void* k, const void* v, const void* out,
+                       const float* lse, float* delta, void* dq, void* dk, void* dv, int B, int Sq, int Sk, int Hq,
+                       int Hkv, int D, long q_sb, long q_ss, long q_sh, long k_sb, long k_ss, long k_sh, long v_sb,
+                       long v_ss, long v_sh, long dq_sb, long dq_ss, long dq_sh, long dk_sb, long dk_ss, long dk_sh,
+                       long dv_sb, long dv_ss, long dv_sh, float scale, int causal, cudaStream_t stream);
+
+/* ---- collectives over NVLink peer memory, csrc/comm.cu ---------------------------------------------------------
+ * `bufs_dev` / `flag_pages_dev`: device arrays of `world` peer base pointers of a symmetric data buffer / of the 4 KiB
+ * flag page (stb_symm_flag_page_bytes) of every rank. Flags are monotonically increasing epochs per `slot` (< 8):
+ * the caller passes the next unused epoch; the comment of each function says how many it consumes. Grids are sized
+ * <= SM count (`sm_budget`, 0 = all) because blocks wait on other GPUs.
+ * Reference: dist.all_reduce / all_gather / reduce_scatter through c10d-NCCL (scaletorch/parallel/data_parallel/
+ * bucket.py:73-78, tensor_parallel/tp_comms.py:144-147, sequence_parallel/sp_comms.py:46-47,79-82). */
+int stb_symm_flag_page_bytes(void);
+int stb_symm_barrier(const void* flag_pages_dev, int rank, int world, int slot, unsigned epoch,
+                     cudaStream_t stream);                                                   /* 1 epoch  */
+int stb_allreduce_f32(const void* bufs_dev, void* multicast_ptr, const void* flag_pages_dev, long offset_elems,
+                      long n, float scale, int rank, int world, int slot, unsigned epoch, int sm_budget,
+                      cudaStream_t stream);                                                  /* 2 epochs; in place, x scale */
+int stb_allreduce_bf16(const void* bufs_dev, void* multicast_ptr, const void* flag_pages_dev, long offset_elems,
+                       long n, int rank, int world, int slot, unsigned epoch, int sm_budget,
+                       cudaStream_t stream);                                                 /* 2 epochs */
+int stb_allreduce_oneshot_bf16(const void* bufs_dev, const void* flag_pages_dev, long offset_elems, void* out,
+                               long n, int rank, int world, int slot, unsigned epoch, int sm_budget,
+                               cudaStream_t stream);                                         /* 2 epochs; out is local */
+int stb_allgather_pull(const void* bufs_dev, const void* flag_pages_dev, long offset_bytes, void* dst,
+                       long rows_per_rank, long row_bytes, int flag_rows, void* ready, int rank, int world, int slot,
+                       unsigned epoch, int sm_budget, cudaStream_t stream);                  /* 2 epochs */
+
+/* ---- GEMM fused with its collective, csrc/gemm_tcgen05.cu -------------------------------------------------------
+ * stb_gemm_rs_bf16: C = A . op(B) whose epilogue TMA-reduce-adds row block d of the product into `c_dest[d]` (rank d's
+ *   zeroed [M / world, N] bf16 buffer, peer-mapped) -> GEMM + reduce-scatter in one kernel; tiles are visited
+ *   starting at the caller's own block + 1 so the NVLink traffic is spread over the peers.
+ * stb_ag_gemm_bf16: `n_copy` CTAs of the grid pull the other ranks' [M / world, K] shards out of their symmetric
+ *   windows into A_full and raise one flag per `flag_rows` rows; the GEMM CTAs' TMA producer waits on the flags of the
+ *   tile it is about to load (own shard first) -> all-gather + GEMM in one kernel. Consumes 2 epochs.
+ * Reference: ColumnParallelLinear / RowParallelLinear + separate NCCL calls (tensor_parallel.py:196-362). */
+int stb_gemm_rs_bf16(const void* A, const void* B, void* const* c_dest, int M, int N, int K, int lda, int ldb,
+                     int ldc, int b_mn, int rank, int world, cudaStream_t stream);
+int stb_ag_gemm_bf16(void* A_full, const void* B, void* C, int M, int N, int K, int ldb, int ldc, int b_mn,
+                     const void* bufs_dev, const void* flag_pages_dev, long shard_offset_bytes, void* ready_flags,
+                     unsigned epoch, int flag_rows, int n_copy, int rank, int world, int slot, cudaStream_t stream);
+
+/* ---- MoE: ragged grouped GEMM, csrc/grouped_gemm.cu -------------------------------------------------------------
+ * Rows are expert-major with every expert segment padded to 128 rows (padding rows zero). `offs_pad` [E + 1] and
+ * `tile_expert` [R_max / 128] (-1 = unused tile) live on the device: no host synchronisation.
+ *   mode 0 (fprop)  C[R, N]   = A[R, K]  . B[e][N, K]^T        mode 1 (dgrad)  C[R, K] = A[R, N] . B[e][N, K]
+ *   mode 2 (wgrad)  C[e][N,K] (+)= A[rows of e, N]^T . B[rows of e, K]   (fp32 or bf16 C, optional accumulate)
+ * Reference: per-expert Python loop, scaletorch/models/model_qwen3_moe.py:129-171. */
+int stb_grouped_gemm_bf16(int mode, const void* A, const void* B, void* C, const int* tile_expert,
+                          const int* offs_pad, int R_max, int N, int K, int E, int out_fp32, int accumulate,
+                          cudaStream_t stream);
+
+/* ---- MoE: expert-parallel dispatch / combine over peer memory, csrc/ep_dispatch.cu ------------------------------
+ * Reference: scaletorch/parallel/expert_parallel/ep_comms.py:30-171 (all_to_all_single x5, two host syncs). */
+int stb_ep_exchange_counts(const void* bufs_dev, const void* flag_pages_dev, long table_off, const int* counts,
+                           int E, int* out, int rank, int world, int slot, unsigned epoch,
+                           cudaStream_t stream);                                             /* 1 epoch  */
+int stb_ep_push(const void* bufs_dev, const void* flag_pages_dev, long region_off, const void* src,
+                const int* dst_rank, const int* dst_row, const float* scale, long P, int k, int H, int rank,
+                int world, int slot, unsigned epoch, int sm_budget, cudaStream_t stream);    /* 2 epochs */
+int stb_ep_pull(const void* bufs_dev, const void* flag_pages_dev, long region_off, void* out, void* rows_out,
+                const int* src_rank, const int* src_row, const float* weights, long T, int k, int H, int rank,
+                int world, int slot, unsigned epoch, int sm_budget, cudaStream_t stream);    /* 2 epochs */
+
 #ifdef __cplusplus
 }
 #endif

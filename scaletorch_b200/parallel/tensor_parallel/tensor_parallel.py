@@ -358,3 +358,35 @@ def apply_tensor_parallel(model: nn.Module, enable_sequence_parallel: bool = Fal
         model.final_proj = ColumnParallelLinear(fp.in_features, fp.out_features, bias=getattr(fp, "bias", None) is not None,
                                                 gather_output=True)
     return model
+
+
+def mark_tp_partial_params(model: nn.Module, tp_group, sequence_parallel: bool) -> list[str]:
+    """Flag replicated parameters whose gradient is only partial on each TP rank (see
+    ``FlatParamStore.sync_tp_partial_grads``); returns their names."""
+    import torch.distributed as dist
+
+    if tp_group is None or dist.get_world_size(tp_group) <= 1:
+        return []
+    names = []
+    for n, p in model.named_parameters():
+        leaf = n.rsplit(".", 2)
+        is_norm = "norm" in n.split(".")[-2] if len(leaf) >= 2 else False
+        if ("q_norm" in n or "k_norm" in n) or (sequence_parallel and is_norm):
+            p._stb_tp_partial = True
+            names.append(n)
+    return names
+
+
+def sync_tp_partial_grads(model: nn.Module, tp_group) -> None:
+    """``.grad``-based variant for plain torch optimisers."""
+    import torch.distributed as dist
+
+    ps = [p for p in model.parameters() if getattr(p, "_stb_tp_partial", False) and p.grad is not None]
+    if tp_group is None or not ps:
+        return
+    flat = torch.cat([p.grad.reshape(-1).float() for p in ps])
+    dist.all_reduce(flat, group=tp_group)
+    off = 0
+    for p in ps:
+        p.grad.copy_(flat[off:off + p.numel()].view_as(p.grad))
+        off += p.numel()

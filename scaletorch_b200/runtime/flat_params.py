@@ -140,6 +140,27 @@ class FlatParamStore:
             if not s.param.grad_written:
                 s.param.main_grad.zero_()
 
+    def sync_tp_partial_grads(self) -> None:
+        """Sum, over the TP group, the gradients of replicated parameters that every TP rank computes from only a
+        part of the data: q_norm / k_norm weights (each rank holds a subset of the heads) and, under sequence
+        parallelism, every norm weight (each rank sees a token shard).  Marked by ``mark_tp_partial_params``.  The
+        reference has no such step (its SP path is incomplete, SURVEY §2.7 #3-4)."""
+        group = getattr(self, "tp_group", None)
+        slots = getattr(self, "_tp_partial_slots", None)
+        if slots is None:
+            slots = self._tp_partial_slots = [s for s in self.slots if getattr(s.param, "_stb_tp_partial", False)]
+        if group is None or not slots:
+            return
+        import torch.distributed as dist
+
+        flat = torch.cat([s.param.main_grad.reshape(-1) for s in slots])
+        dist.all_reduce(flat, group=group)
+        off = 0
+        for s in slots:
+            n = s.param.main_grad.numel()
+            s.param.main_grad.copy_(flat[off:off + n].view_as(s.param.main_grad))
+            off += n
+
     def expose_grads(self) -> None:
         """Points ``param.grad`` at its ``main_grad`` view (for code that expects ``.grad``)."""
         for s in self.slots:

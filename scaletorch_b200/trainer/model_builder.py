@@ -55,10 +55,16 @@ def create_model(config, dtype: torch.dtype, device: torch.device):
         model, model_config, save_dir=config.model_name_or_path,
         load_weights=getattr(config, "load_pretrained_weights", False))
     model.to(dtype).to(device)
+    if pgm and pgm.tp_world_size > 1:
+        from ..parallel.tensor_parallel.tensor_parallel import mark_tp_partial_params
+
+        mark_tp_partial_params(model, pgm.tp_group, ctx.sp)
     grad_sync = pgm.grad_sync_world_size if pgm else 1
     # flat parameter / main-grad buffers (also on a single GPU); in symmetric memory when gradients are
     # all-reduced over NVLink by our own kernel
-    get_store(model, pgm.grad_sync_group if (pgm and grad_sync > 1) else None, getattr(config, "fused_comm", True))
+    store = get_store(model, pgm.grad_sync_group if (pgm and grad_sync > 1) else None, getattr(config, "fused_comm", True))
+    if pgm and pgm.tp_world_size > 1 and store is not None:
+        store.tp_group = pgm.tp_group
     if pgm and (grad_sync > 1 or pgm.expert_grad_sync_world_size > 1):
         wire = torch.bfloat16 if getattr(config, "grad_wire_dtype", "float32") == "bfloat16" else torch.float32
         model = DataParallelBucket(model, wire_dtype=wire)

@@ -45,6 +45,7 @@ class FusedAdamW(torch.optim.Optimizer):
     def step(self, closure=None, grad_scale: float = 1.0):
         loss = closure() if closure is not None else None
         self.store.finalize_grads()
+        self.store.sync_tp_partial_grads()
         self.step_count += 1
         g = self.param_groups[0]
         coef = None

@@ -71,6 +71,10 @@ def clip_gradients(model, max_grad_norm: float | None, optimizer=None) -> float 
 
     if isinstance(optimizer, FusedAdamW):
         return None  # computed inside step(); read optimizer.grad_norm() after the step
+    if pgm and pgm.tp_world_size > 1:
+        from ..parallel.tensor_parallel.tensor_parallel import sync_tp_partial_grads
+
+        sync_tp_partial_grads(model, pgm.tp_group)
     params = [p for p in model.parameters() if p.grad is not None]
     if not params:
         return 0.0

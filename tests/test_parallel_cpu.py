@@ -54,13 +54,13 @@ def _tp_worker(rank, world, model_name, sp):
     lp = par.loss(x, y)
     lp.backward()
     assert abs(lf.item() - lp.item()) < 1e-4, (lf.item(), lp.item())
-    # norm / q_norm / k_norm weights are replicated but see only partial tokens (SP) or heads: sum over TP
-    import torch.distributed as dist
+    # norm / q_norm / k_norm weights are replicated but see only partial tokens (SP) or heads: the framework sums
+    # their gradients over TP (mark_tp_partial_params + sync_tp_partial_grads, used by the trainer)
+    from scaletorch_b200.parallel.tensor_parallel.tensor_parallel import mark_tp_partial_params, sync_tp_partial_grads
 
-    for n, p in par.named_parameters():
-        partial = ("q_norm" in n or "k_norm" in n) or (sp and "norm" in n)
-        if partial:
-            dist.all_reduce(p.grad, group=pgm.tp_group)
+    marked = mark_tp_partial_params(par, pgm.tp_group, sp)
+    assert (model_name == "qwen3" or sp) == bool(marked), marked
+    sync_tp_partial_grads(par, pgm.tp_group)
     _compare_sharded_grads(full, par, cfg, world, rank)
     # full logits through the reference-compatible forward
     assert rel_err(par(x), full(x)) < 1e-4

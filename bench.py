@@ -211,13 +211,22 @@ def run_ours(args):
     # end-to-end: public API, per-step pinned H2D of the batch + D2H read of the loss
     e2e = None
     if not args.skip_e2e:
+        from scaletorch_b200.trainer import AsyncScalarReader
+
         losses = []
+        reader = AsyncScalarReader(slots=4)
 
         def e2e_step():
-            losses.append(float(step_with(loader).item()))
+            # every step: pinned H2D of the batch (inside the loader / train step), D2H copy of the loss into pinned
+            # host memory.  The host consumes step i's loss after enqueueing step i+1 (one-step lag), as the trainer
+            # CLI does, so the device queue never drains; all K copies land inside the timed region.
+            reader.push(step_with(loader))
+            if len(reader) > 1:
+                losses.append(reader.pop())
 
         e2e_step()
         ms_e2e = timed_region(torch, dist, world, e2e_step, args.steps)
+        losses.extend(reader.drain())
         tokens = cfgd["global_batch"] * args.seq_len
         per_rank_tokens = args.micro_batch_size * args.grad_accum * (args.seq_len // args.cp)
         e2e = {"value": tokens * args.steps / (ms_e2e / 1e3), "unit": "tokens/s", "ms_per_step": ms_e2e / args.steps,

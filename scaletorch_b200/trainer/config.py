@@ -139,6 +139,7 @@ class TrainingArguments:
     sequence_length: int | None = field(default=1024, metadata={"help": "Sequence length"})
     log_interval: int = field(default=100, metadata={"help": "Logging frequency"})
     max_tokens: int | None = field(default=None, metadata={"help": "Stop after this many trained tokens"})
+    log_lag: int = field(default=1, metadata={"help": "Log step i after enqueueing step i+lag (0 = synchronous logging)"})
     total_train_steps: int | None = field(default=None, metadata={"help": "Stop after this many steps"})
     use_cpu: bool = field(default=False, metadata={"help": "Run on CPU with the gloo backend"})
     aux_loss: bool = field(default=True, metadata={"help": "Add the MoE load-balancing loss to the training loss"})

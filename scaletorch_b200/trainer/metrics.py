@@ -57,3 +57,49 @@ def log_training_metrics(config: Any, model_config: Any, step: int, loss: float,
         if wandb_run is not None:
             wandb_run.log(metrics, step=step)
     return metrics
+
+
+class AsyncScalarReader:
+    """Device→host readback of per-step scalars (loss, grad norm) without draining the GPU queue.
+
+    ``push(t)`` enqueues a copy of the device scalar into a pinned host slot followed by an event; ``pop()`` returns the
+    oldest pushed value, waiting only for *its* event.  With ``lag = 1`` the training loop reads step ``i``'s loss after
+    it has already enqueued step ``i + 1``, so the host keeps running ahead of the device (the reference calls
+    ``.item()`` on every micro-batch, ``trainer/train_step.py:113``).  On CPU tensors it degrades to plain reads.
+    """
+
+    def __init__(self, slots: int = 4):
+        import torch
+
+        self._torch = torch
+        self._cuda = torch.cuda.is_available()
+        self._host = torch.zeros(slots, dtype=torch.float32, pin_memory=self._cuda)
+        self._events = [torch.cuda.Event() for _ in range(slots)] if self._cuda else [None] * slots
+        self._head = self._tail = 0
+        self._slots = slots
+
+    def __len__(self) -> int:
+        return self._head - self._tail
+
+    def push(self, t) -> None:
+        if len(self) == self._slots:
+            raise RuntimeError("AsyncScalarReader is full: pop() before pushing more")
+        i = self._head % self._slots
+        if t.is_cuda:
+            self._host[i:i + 1].copy_(t.detach().reshape(1).float(), non_blocking=True)
+            self._events[i].record()
+        else:
+            self._host[i] = float(t)
+        self._head += 1
+
+    def pop(self) -> float:
+        if len(self) == 0:
+            raise RuntimeError("AsyncScalarReader is empty")
+        i = self._tail % self._slots
+        if self._events[i] is not None and self._cuda:
+            self._events[i].synchronize()
+        self._tail += 1
+        return float(self._host[i])
+
+    def drain(self) -> list[float]:
+        return [self.pop() for _ in range(len(self))]

@@ -120,8 +120,9 @@ def assert_no_meta_tensors(model: torch.nn.Module) -> None:
         raise RuntimeError(f"tensors still on the meta device: {bad[:8]}{'...' if len(bad) > 8 else ''}")
 
 
-def average_loss_across_dp_cp_ranks(loss: float | torch.Tensor | None, device: torch.device) -> float:
-    """Mean of the step loss over the CP×DP(×EP) group on the last PP stage (reference ``misc.py:229-249``)."""
+def average_loss_across_dp_cp_ranks(loss: float | torch.Tensor | None, device: torch.device, as_tensor: bool = False):
+    """Mean of the step loss over the CP×DP(×EP) group on the last PP stage (reference ``misc.py:229-249``).
+    ``as_tensor=True`` returns the device scalar without synchronising (for lagged logging)."""
     from ..parallel.process_group import process_group_manager as pgm
 
     if isinstance(loss, torch.Tensor):
@@ -131,4 +132,4 @@ def average_loss_across_dp_cp_ranks(loss: float | torch.Tensor | None, device: t
     if pgm and pgm.pp_is_last_stage and pgm.grad_sync_world_size > 1:
         dist.all_reduce(t, group=pgm.grad_sync_group)
         t /= pgm.grad_sync_world_size
-    return float(t.item())
+    return t if as_tensor else float(t.item())

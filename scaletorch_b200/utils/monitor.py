@@ -79,13 +79,37 @@ class PerformanceMonitor:
                 dt = time.time() - self._iter_t0
         else:
             dt = time.time() - self._iter_t0
+        self._iter_t0 = None
+        return self._record(dt, self._tokens)
+
+    def end_iteration_deferred(self):
+        """Record the end-of-step event without waiting for it; pass the handle to :meth:`resolve_iteration` later (the
+        trainer resolves step ``i`` after it has enqueued step ``i + 1``, so the device queue never drains)."""
+        if self._iter_t0 is None:
+            raise RuntimeError("end_iteration_deferred() called before start_iteration()")
+        if self._ev1 is not None:
+            self._ev1.record()
+        h = (self._ev0, self._ev1, self._tokens, self._iter_t0, time.time())
+        self._iter_t0 = None
+        return h
+
+    def resolve_iteration(self, handle) -> dict[str, Any]:
+        ev0, ev1, tokens, t0, t1 = handle
+        if ev1 is not None:
+            ev1.synchronize()
+            dt = ev0.elapsed_time(ev1) / 1e3
+        else:
+            dt = t1 - t0
+        return self._record(dt, tokens)
+
+    def _record(self, dt: float, tokens: int) -> dict[str, Any]:
         self.iteration += 1
-        self.total_tokens += self._tokens
+        self.total_tokens += tokens
         stats: dict[str, Any] = {
             "iteration": self.iteration,
             "iteration_time": dt,
-            "tokens": self._tokens,
-            "tokens_per_second": (self._tokens / dt) if dt > 0 else 0.0,
+            "tokens": tokens,
+            "tokens_per_second": (tokens / dt) if dt > 0 else 0.0,
             "memory_allocated_gb": memory_allocated() / 1e9,
             "memory_reserved_gb": memory_reserved() / 1e9,
             "max_memory_allocated_gb": max_memory_allocated() / 1e9,
@@ -104,7 +128,6 @@ class PerformanceMonitor:
         self.history.append(stats)
         if len(self.history) > MAX_HISTORY:
             self.history = self.history[-TRIM_TO:]
-        self._iter_t0 = None
         return stats
 
     # ------------------------------------------------------------------ reporting

@@ -14,6 +14,7 @@ step (the loss), global-norm clipping folded into the fused optimiser, RNG / dat
 from __future__ import annotations
 
 import gc
+from collections import deque
 import os
 import sys
 import time
@@ -28,7 +29,7 @@ from transformers import HfArgumentParser  # noqa: E402
 
 from scaletorch_b200.data import MicroBatchDataLoader  # noqa: E402
 from scaletorch_b200.parallel.process_group import process_group_manager as pgm  # noqa: E402
-from scaletorch_b200.trainer import (ScaleTorchArguments, cleanup_distributed, clip_gradients, create_lr_scheduler,  # noqa: E402
+from scaletorch_b200.trainer import (AsyncScalarReader, ScaleTorchArguments, cleanup_distributed, clip_gradients, create_lr_scheduler,  # noqa: E402
                                      create_model, create_optimizer, get_dtype, get_tensor_shapes,
                                      initialize_distributed_training, log_training_metrics, training_step,
                                      validate_config)
@@ -109,6 +110,18 @@ def main(argv=None) -> None:
 
         monitor.start()
         max_steps = config.total_train_steps or float("inf")
+        log_lag = max(0, int(getattr(config, "log_lag", 1)))
+        pending: deque = deque()
+        loss_reader, norm_reader = AsyncScalarReader(log_lag + 2), AsyncScalarReader(log_lag + 2)
+
+        def flush_one():
+            st, lr_, gn, handle, tokens_ = pending.popleft()
+            stats = monitor.resolve_iteration(handle)
+            loss = loss_reader.pop()
+            gn = norm_reader.pop() if gn == "reader" else gn
+            log_training_metrics(config, model_config, st, loss, lr_, gn, stats["iteration_time"], tokens_per_step, tokens_,
+                                 num_params, world_size, logger=logger, wandb_run=run)
+
         while config.max_tokens is None or trained_tokens < config.max_tokens:
             monitor.start_iteration(tokens_processed=tokens_per_step)
             optimizer.zero_grad(set_to_none=True)
@@ -118,19 +131,22 @@ def main(argv=None) -> None:
             grad_norm = clip_gradients(model, config.max_grad_norm, optimizer)
             optimizer.step()
             lr_scheduler.step()
-            stats = monitor.end_iteration()           # CUDA-event timed, syncs once per step
-            loss = average_loss_across_dp_cp_ranks(loss_t, device)
-            if isinstance(optimizer, FusedAdamW) and config.max_grad_norm:
-                grad_norm = optimizer.grad_norm()
+            # lagged logging: step i is resolved (events, loss, grad norm read back) after step i+1 has been enqueued,
+            # so the host never drains the device queue; --log_lag 0 restores fully synchronous logging
+            handle = monitor.end_iteration_deferred()
+            loss_reader.push(average_loss_across_dp_cp_ranks(loss_t, device, as_tensor=True))
+            if isinstance(optimizer, FusedAdamW) and config.max_grad_norm and optimizer.last_grad_norm is not None:
+                norm_reader.push(optimizer.last_grad_norm)
+                grad_norm = "reader"
             trained_tokens += tokens_per_step
             step += 1
+            pending.append((step, lr_scheduler.get_last_lr()[0], grad_norm, handle, trained_tokens))
             if step % 100 == 0 and is_accelerator_available():
                 empty_cache()
                 if step % 1000 == 0:
                     gc.collect()
-            log_training_metrics(config, model_config, step, loss, lr_scheduler.get_last_lr()[0], grad_norm,
-                                 stats["iteration_time"], tokens_per_step, trained_tokens, num_params, world_size,
-                                 logger=logger, wandb_run=run)
+            while len(pending) > log_lag:
+                flush_one()
             if config.save_model_checkpoint and config.save_frequency > 0 and step % config.save_frequency == 0:
                 out_dir = Path(config.work_dir) / f"{step}"
                 ckpt.save_checkpoint(model, optimizer, step, trained_tokens, str(out_dir),
@@ -139,6 +155,8 @@ def main(argv=None) -> None:
                     torch.save(lr_scheduler.state_dict(), out_dir / "scheduler.pt")
             if step >= max_steps:
                 break
+        while pending:
+            flush_one()
     except Exception:
         logger.error("training failed", exc_info=True)
         raise

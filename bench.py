@@ -46,6 +46,7 @@ def parse_args():
     ap.add_argument("--sequence_parallel", action="store_true")
     ap.add_argument("--gradient_checkpointing", action="store_true")
     ap.add_argument("--skip_e2e", action="store_true")
+    ap.add_argument("--cuda_graph", type=int, default=1, help="capture the whole step in a CUDA graph when supported (ours)")
     return ap.parse_args()
 
 
@@ -174,7 +175,21 @@ def run_ours(args):
             self.i += 1
             return x
 
+    from scaletorch_b200.trainer import GraphedTrainStep
+
+    graphed = None
+    if args.cuda_graph and GraphedTrainStep.supported(cfg, optimizer):
+        graphed = GraphedTrainStep(model, optimizer, cfg, device, warmup=2)
+    launches_per_graph = [0]
+
     def step_with(src):
+        if graphed is not None:
+            was_captured = graphed.graph is not None
+            c0 = _native.launch_count
+            loss = graphed(src)
+            if not was_captured and graphed.graph is not None:
+                launches_per_graph[0] = _native.launch_count - c0      # kernels recorded into the graph
+            return loss
         optimizer.zero_grad()
         if hasattr(model, "reset"):
             model.reset()
@@ -184,6 +199,8 @@ def run_ours(args):
 
     staged = DeviceBatches((args.steps + args.warmup) * args.grad_accum)
     for _ in range(args.warmup):
+        step_with(staged)
+    while graphed is not None and graphed.graph is None:      # the capture itself never falls into the timed region
         step_with(staged)
     sampler = ClockSampler(local_rank)
     if rank == 0:
@@ -203,9 +220,32 @@ def run_ours(args):
             dist.barrier()
             dist.destroy_process_group()
         return
+    if os.environ.get("SCALETORCH_B200_DP_SWEEP"):
+        # diagnosis: time the same model under several (transport, CTA budget) settings of the gradient all-reduce
+        dp = model if hasattr(model, "bucket_manager") else None
+        gw = getattr(getattr(dp, "store", None), "grad_window", None)
+        if dp is not None and gw is not None:
+            mc = gw.mc_ptr
+            for spec in os.environ["SCALETORCH_B200_DP_SWEEP"].split(","):
+                kind, budget = spec.split(":")
+                gw.mc_ptr = mc if kind == "nvls" else 0
+                for b in dp.bucket_manager.buckets:
+                    b.sm_budget = int(budget)
+                for _ in range(2):
+                    step_with(staged)
+                t = timed_region(torch, dist, world, lambda: step_with(staged), args.steps) / args.steps
+                if rank == 0:
+                    print(f"DP_SWEEP {kind} budget {budget}: {t:.3f} ms/step", flush=True)
+            gw.mc_ptr = mc
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        return
     l0 = _native.launch_count
     ms = timed_region(torch, dist, world, lambda: step_with(staged), args.steps)
     launches = _native.launch_count - l0
+    if graphed is not None and graphed.graph is not None:
+        launches = launches_per_graph[0] * args.steps              # replayed from the graph: same kernels every step
     clocks = sampler.stop() if rank == 0 else {}
 
     # end-to-end: public API, per-step pinned H2D of the batch + D2H read of the loss
@@ -244,6 +284,7 @@ def run_ours(args):
             "tokens_per_s_per_gpu": value / world,
             "mfu_pct_of_nominal_2.25PF": get_mfu(value / world, num_params, model_config, 2.25e15, args.seq_len),
             "num_params": num_params, "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
+            "cuda_graph": bool(graphed is not None and graphed.graph is not None),
             "native_lib": str(_native.lib_path()),
         }
         peaks = {}

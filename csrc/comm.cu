@@ -26,8 +26,11 @@
 
 namespace stb {
 
-__global__ void symm_barrier_kernel(uint32_t* const* flag_pages, int rank, int world, int slot, uint32_t epoch) {
+__global__ void symm_barrier_kernel(uint32_t* const* flag_pages, int rank, int world, int slot, uint32_t epoch_arg) {
+  const uint32_t epoch = symm_epoch_load(flag_pages, rank, slot, epoch_arg);
   cross_gpu_barrier(flag_pages, rank, world, slot, epoch);
+  __syncwarp();
+  if (threadIdx.x == 0) symm_epoch_store(flag_pages, rank, slot, epoch_arg, epoch + 1);
 }
 
 STB_DEVICE float4 ld_peer_f4(const float* p) {
@@ -74,27 +77,42 @@ STB_DEVICE void multimem_st_u4(void* mc, const uint4& v) {
 template <bool MULTIMEM>
 __global__ void __launch_bounds__(512)
     allreduce_f32_kernel(float* const* bufs, float* mc, uint32_t* const* flag_pages, long offset, long n, float scale,
-                         int rank, int world, int slot, uint32_t epoch) {
+                         int rank, int world, int slot, uint32_t epoch_arg) {
+  const uint32_t epoch = symm_epoch_load(flag_pages, rank, slot, epoch_arg);
   grid_cross_gpu_barrier(flag_pages, rank, world, slot, epoch);   // every rank's data is in place
   const long nvec = n >> 2;
   const long per = (nvec + world - 1) / world;
   const long lo = per * rank, hi = min(nvec, lo + per);
-  for (long i = lo + long(blockIdx.x) * blockDim.x + threadIdx.x; i < hi; i += long(gridDim.x) * blockDim.x) {
-    const long e = offset + (i << 2);
-    float4 acc;
-    if (MULTIMEM) {
-      acc = multimem_ld_reduce_f4(mc + e);
-    } else {
-      acc = ld_peer_f4(bufs[rank] + e);
+  if (MULTIMEM) {
+    // NVLS: the switch reduces; per thread 8 independent 16-byte ld_reduce in flight, then 8 broadcast stores, so a
+    // few CTAs saturate the link and the rest of the SMs stay with the backward pass
+    constexpr int U = 8;
+    const long stride = long(gridDim.x) * blockDim.x;
+    for (long i0 = lo + long(blockIdx.x) * blockDim.x + threadIdx.x; i0 < hi; i0 += stride * U) {
+      float4 acc[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long i = i0 + u * stride;
+        if (i < hi) acc[u] = multimem_ld_reduce_f4(mc + offset + (i << 2));
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long i = i0 + u * stride;
+        if (i < hi) {
+          acc[u].x *= scale; acc[u].y *= scale; acc[u].z *= scale; acc[u].w *= scale;
+          multimem_st_f4(mc + offset + (i << 2), acc[u]);
+        }
+      }
+    }
+  } else {
+    for (long i = lo + long(blockIdx.x) * blockDim.x + threadIdx.x; i < hi; i += long(gridDim.x) * blockDim.x) {
+      const long e = offset + (i << 2);
+      float4 acc = ld_peer_f4(bufs[rank] + e);
       for (int p = 1; p < world; ++p) {
         const float4 v = ld_peer_f4(bufs[(rank + p) % world] + e);
         acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
       }
-    }
-    acc.x *= scale; acc.y *= scale; acc.z *= scale; acc.w *= scale;
-    if (MULTIMEM) {
-      multimem_st_f4(mc + e, acc);
-    } else {
+      acc.x *= scale; acc.y *= scale; acc.z *= scale; acc.w *= scale;
       for (int p = 0; p < world; ++p) st_peer_f4(bufs[(rank + p) % world] + e, acc);
     }
   }
@@ -106,13 +124,14 @@ __global__ void __launch_bounds__(512)
       for (int p = 0; p < world; ++p) bufs[p][offset + i] = acc;
     }
   }
-  grid_finish_cross_gpu_barrier(flag_pages, rank, world, slot, epoch + 1);  // results have landed everywhere
+  grid_finish_cross_gpu_barrier(flag_pages, rank, world, slot, epoch + 1, epoch_arg);  // results have landed everywhere
 }
 
 template <bool MULTIMEM>
 __global__ void __launch_bounds__(512)
     allreduce_bf16_kernel(__nv_bfloat16* const* bufs, __nv_bfloat16* mc, uint32_t* const* flag_pages, long offset,
-                          long n, int rank, int world, int slot, uint32_t epoch) {
+                          long n, int rank, int world, int slot, uint32_t epoch_arg) {
+  const uint32_t epoch = symm_epoch_load(flag_pages, rank, slot, epoch_arg);
   grid_cross_gpu_barrier(flag_pages, rank, world, slot, epoch);
   const long nvec = n >> 3;
   const long per = (nvec + world - 1) / world;
@@ -140,13 +159,14 @@ __global__ void __launch_bounds__(512)
       for (int p = 0; p < world; ++p) *reinterpret_cast<uint4*>(bufs[(rank + p) % world] + e) = out;
     }
   }
-  grid_finish_cross_gpu_barrier(flag_pages, rank, world, slot, epoch + 1);
+  grid_finish_cross_gpu_barrier(flag_pages, rank, world, slot, epoch + 1, epoch_arg);
 }
 
 // out (local, fresh) <- sum over ranks of bufs[p][offset .. offset+n): every rank reads all peers (one-shot).
 __global__ void __launch_bounds__(512)
     allreduce_oneshot_bf16_kernel(const __nv_bfloat16* const* bufs, uint32_t* const* flag_pages, long offset,
-                                  __nv_bfloat16* out, long n, int rank, int world, int slot, uint32_t epoch) {
+                                  __nv_bfloat16* out, long n, int rank, int world, int slot, uint32_t epoch_arg) {
+  const uint32_t epoch = symm_epoch_load(flag_pages, rank, slot, epoch_arg);
   grid_cross_gpu_barrier(flag_pages, rank, world, slot, epoch);
   const long nvec = n >> 3;
   for (long i = long(blockIdx.x) * blockDim.x + threadIdx.x; i < nvec; i += long(gridDim.x) * blockDim.x) {
@@ -164,7 +184,7 @@ __global__ void __launch_bounds__(512)
                                                            pack_bf16x2(acc[4], acc[5]), pack_bf16x2(acc[6], acc[7]));
   }
   // the partial buffers may be overwritten only after every rank has read them
-  grid_finish_cross_gpu_barrier(flag_pages, rank, world, slot, epoch + 1);
+  grid_finish_cross_gpu_barrier(flag_pages, rank, world, slot, epoch + 1, epoch_arg);
 }
 
 // dst[world * rows_per_rank, row_bytes] <- shard of every rank (rank r's shard sits at offset_bytes of its buffer).
@@ -172,7 +192,8 @@ __global__ void __launch_bounds__(512)
 __global__ void __launch_bounds__(512)
     allgather_pull_kernel(const uint8_t* const* bufs, uint32_t* const* flag_pages, long offset_bytes, uint8_t* dst,
                           long rows_per_rank, long row_bytes, int flag_rows, uint32_t* ready, int rank, int world,
-                          int slot, uint32_t epoch) {
+                          int slot, uint32_t epoch_arg) {
+  const uint32_t epoch = symm_epoch_load(flag_pages, rank, slot, epoch_arg);
   grid_cross_gpu_barrier(flag_pages, rank, world, slot, epoch);   // every rank's shard is written
   const long blocks_per_rank = (rows_per_rank + flag_rows - 1) / flag_rows;
   const long total_blocks = blocks_per_rank * world;
@@ -191,7 +212,7 @@ __global__ void __launch_bounds__(512)
     if (threadIdx.x == 0) st_release_gpu(ready + long(src) * blocks_per_rank + rb, epoch);
   }
   // peers may reuse their shard buffers only after everybody has pulled them
-  grid_finish_cross_gpu_barrier(flag_pages, rank, world, slot, epoch + 1);
+  grid_finish_cross_gpu_barrier(flag_pages, rank, world, slot, epoch + 1, epoch_arg);
 }
 
 static int comm_grid(int sm_budget) {
@@ -204,7 +225,7 @@ static int comm_grid(int sm_budget) {
 
 using namespace stb;
 
-extern "C" int stb_symm_flag_page_bytes() { return (kMaxSlots * kMaxWorld + 2 * kMaxSlots) * 4; }
+extern "C" int stb_symm_flag_page_bytes() { return kFlagPageWords * 4; }
 
 extern "C" int stb_symm_barrier(const void* flag_pages_dev, int rank, int world, int slot, unsigned epoch,
                                 cudaStream_t stream) {

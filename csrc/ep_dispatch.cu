@@ -26,7 +26,8 @@ namespace stb {
 
 __global__ void __launch_bounds__(256)
 ep_counts_kernel(char* const* bufs, uint32_t* const* flag_pages, long table_off, const int* __restrict__ counts, int E,
-                 int* __restrict__ out, int rank, int world, int slot, uint32_t epoch) {
+                 int* __restrict__ out, int rank, int world, int slot, uint32_t epoch_arg) {
+  const uint32_t epoch = symm_epoch_load(flag_pages, rank, slot, epoch_arg);
   for (int peer = 0; peer < world; ++peer) {
     int* tbl = reinterpret_cast<int*>(bufs[peer] + table_off) + long(rank) * E;
     for (int e = threadIdx.x; e < E; e += blockDim.x) tbl[e] = counts[e];
@@ -36,12 +37,14 @@ ep_counts_kernel(char* const* bufs, uint32_t* const* flag_pages, long table_off,
   __syncthreads();
   const volatile int* mine = reinterpret_cast<const volatile int*>(bufs[rank] + table_off);
   for (int i = threadIdx.x; i < world * E; i += blockDim.x) out[i] = mine[i];
+  if (threadIdx.x == 0) symm_epoch_store(flag_pages, rank, slot, epoch_arg, epoch + 1);
 }
 
 __global__ void __launch_bounds__(256)
 ep_push_kernel(char* const* bufs, uint32_t* const* flag_pages, long region_off, const __nv_bfloat16* __restrict__ src,
                const int* __restrict__ dst_rank, const int* __restrict__ dst_row, const float* __restrict__ scale,
-               long P, int k, int H, int rank, int world, int slot, uint32_t epoch) {
+               long P, int k, int H, int rank, int world, int slot, uint32_t epoch_arg) {
+  const uint32_t epoch = symm_epoch_load(flag_pages, rank, slot, epoch_arg);
   grid_cross_gpu_barrier(flag_pages, rank, world, slot, epoch);   // every destination region is zeroed / free
   const int warps = blockDim.x >> 5, lane = threadIdx.x & 31;
   const int vec = H >> 3;                                           // uint4 (8 bf16) per row
@@ -66,7 +69,7 @@ ep_push_kernel(char* const* bufs, uint32_t* const* flag_pages, long region_off, 
       }
     }
   }
-  grid_finish_cross_gpu_barrier(flag_pages, rank, world, slot, epoch + 1);   // every rank's rows have landed
+  grid_finish_cross_gpu_barrier(flag_pages, rank, world, slot, epoch + 1, epoch_arg);   // every rank's rows have landed
 }
 
 template <int K>
@@ -74,7 +77,8 @@ __global__ void __launch_bounds__(256)
 ep_pull_kernel(char* const* bufs, uint32_t* const* flag_pages, long region_off, __nv_bfloat16* __restrict__ out,
                __nv_bfloat16* __restrict__ rows_out, const int* __restrict__ src_rank, const int* __restrict__ src_row,
                const float* __restrict__ weights, long T, int k_rt, int H, int rank, int world, int slot,
-               uint32_t epoch) {
+               uint32_t epoch_arg) {
+  const uint32_t epoch = symm_epoch_load(flag_pages, rank, slot, epoch_arg);
   grid_cross_gpu_barrier(flag_pages, rank, world, slot, epoch);   // every rank's expert outputs are complete
   const int k = K > 0 ? K : k_rt;
   const int warps = blockDim.x >> 5, lane = threadIdx.x & 31;
@@ -116,7 +120,7 @@ ep_pull_kernel(char* const* bufs, uint32_t* const* flag_pages, long region_off, 
       reinterpret_cast<uint4*>(out + t * long(H))[c] = o;
     }
   }
-  grid_finish_cross_gpu_barrier(flag_pages, rank, world, slot, epoch + 1);   // owners may overwrite their regions
+  grid_finish_cross_gpu_barrier(flag_pages, rank, world, slot, epoch + 1, epoch_arg);   // owners may overwrite their regions
 }
 
 static int ep_grid(int sm_budget) {

@@ -94,20 +94,20 @@ STB_DEVICE void ag_cross_gpu_barrier(uint32_t* const* pages, int rank, int world
   }
 }
 
-STB_DEVICE void ag_copy_role(const GemmParams& p) {
+STB_DEVICE void ag_copy_role(const GemmParams& p, const uint32_t a_epoch) {
   uint32_t* go = p.ag_flag_pages[p.ag_rank] + 8 * 16 + p.ag_slot;
   uint32_t* done = p.ag_flag_pages[p.ag_rank] + 8 * 16 + 8 + p.ag_slot;
   // 1. every rank has written its shard (cross-GPU barrier by copy CTA 0, released locally to the others)
   if (blockIdx.x == 0) {
-    if (threadIdx.x < 32) ag_cross_gpu_barrier(p.ag_flag_pages, p.ag_rank, p.ag_world, p.ag_slot, p.a_epoch);
+    if (threadIdx.x < 32) ag_cross_gpu_barrier(p.ag_flag_pages, p.ag_rank, p.ag_world, p.ag_slot, a_epoch);
     __syncthreads();
-    if (threadIdx.x == 0) asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(go), "r"(p.a_epoch) : "memory");
+    if (threadIdx.x == 0) asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(go), "r"(a_epoch) : "memory");
   } else {
     if (threadIdx.x == 0) {
       uint32_t v;
       do {
         asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(go) : "memory");
-      } while (int32_t(v - p.a_epoch) < 0);
+      } while (int32_t(v - a_epoch) < 0);
     }
     __syncthreads();
   }
@@ -137,7 +137,7 @@ STB_DEVICE void ag_copy_role(const GemmParams& p) {
     __syncthreads();
     if (threadIdx.x == 0)
       asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p.ag_ready + long(src) * blocks_per_rank + rb),
-                   "r"(p.a_epoch)
+                   "r"(a_epoch)
                    : "memory");
   }
   // 3. tell the peers their shard buffers may be reused: all copy CTAs done -> cross-GPU barrier
@@ -155,7 +155,19 @@ STB_DEVICE void ag_copy_role(const GemmParams& p) {
       *done = 0;
     }
     __syncthreads();
-    if (threadIdx.x < 32) ag_cross_gpu_barrier(p.ag_flag_pages, p.ag_rank, p.ag_world, p.ag_slot, p.a_epoch + 1);
+    if (threadIdx.x < 32) ag_cross_gpu_barrier(p.ag_flag_pages, p.ag_rank, p.ag_world, p.ag_slot, a_epoch + 1);
+    if (p.a_epoch == 0 && threadIdx.x == 0) {
+      // device-driven epochs: advance the slot counter once every CTA of the grid has read it
+      uint32_t* checkin = p.ag_flag_pages[p.ag_rank] + 8 * 16 + 24 + p.ag_slot;
+      uint32_t v;
+      do {
+        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(checkin) : "memory");
+      } while (v < gridDim.x);
+      *checkin = 0;
+      asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p.ag_flag_pages[p.ag_rank] + 8 * 16 + 16 + p.ag_slot),
+                   "r"(a_epoch + 2)
+                   : "memory");
+    }
   }
 }
 
@@ -165,8 +177,17 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
                      const __grid_constant__ CMaps tmCs, const GemmParams p) {
   using Cfg = GemmCfg<BN>;
   constexpr int kStages = Cfg::kStages;
+  // all-gather->GEMM with device-driven epochs (a_epoch == 0: graph-replayable): every CTA reads the slot's counter
+  // (csrc/common/symm.cuh) and checks in; copy CTA 0 advances the counter after all of them have
+  uint32_t a_epoch = p.a_epoch;
+  if (p.a_ready != nullptr && p.a_epoch == 0) {
+    uint32_t* page = p.ag_flag_pages[p.ag_rank];
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(a_epoch) : "l"(page + 8 * 16 + 16 + p.ag_slot) : "memory");
+    __syncthreads();
+    if (threadIdx.x == 0) atomicAdd(page + 8 * 16 + 24 + p.ag_slot, 1u);
+  }
   if (int(blockIdx.x) < p.n_copy) {   // all-gather->GEMM: communication CTAs (no TMEM, no smem pipeline)
-    ag_copy_role(p);
+    ag_copy_role(p, a_epoch);
     return;
   }
   const int cta = int(blockIdx.x) - p.n_copy;
@@ -232,7 +253,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
             uint32_t v;
             do {
               asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
-            } while (int32_t(v - p.a_epoch) < 0);
+            } while (int32_t(v - a_epoch) < 0);
           }
           asm volatile("fence.proxy.async.global;" ::: "memory");  // generic-proxy writes -> TMA (async proxy) reads
         }

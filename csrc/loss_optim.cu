@@ -145,7 +145,12 @@ __global__ void __launch_bounds__(256)
     adamw_kernel(PT* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
                  float* __restrict__ v, long n, float lr, float beta1, float beta2, float eps,
                  float weight_decay, float bc1, float bc2, const float* __restrict__ clip_coef_ptr,
-                 float grad_scale) {
+                 float grad_scale, const float* __restrict__ hyper) {
+  if (hyper != nullptr) {   // step-dependent scalars from device memory: the launch is replayable from a CUDA graph
+    lr = hyper[0];
+    bc1 = hyper[1];
+    bc2 = hyper[2];
+  }
   const float clip = (clip_coef_ptr ? *clip_coef_ptr : 1.f) * grad_scale;
   const long nvec = n >> 2;
   const float inv_bc1 = 1.f / bc1, inv_sqrt_bc2 = rsqrtf(bc2);
@@ -354,11 +359,30 @@ extern "C" int stb_adamw(void* p, int p_is_fp32, const float* g, float* m, float
   const int grid = ew_grid(n / 4 + 1, 256, 8);
   if (p_is_fp32)
     adamw_kernel<float><<<grid, 256, 0, stream>>>((float*)p, g, m, v, n, lr, beta1, beta2, eps,
-                                                  weight_decay, bc1, bc2, clip_coef, grad_scale);
+                                                  weight_decay, bc1, bc2, clip_coef, grad_scale, nullptr);
   else
     adamw_kernel<__nv_bfloat16><<<grid, 256, 0, stream>>>((__nv_bfloat16*)p, g, m, v, n, lr, beta1,
                                                           beta2, eps, weight_decay, bc1, bc2,
-                                                          clip_coef, grad_scale);
+                                                          clip_coef, grad_scale, nullptr);
+  STB_CHECK_LAUNCH();
+  return 0;
+}
+
+// Same update with the step-dependent scalars read from device memory: hyper = {lr, 1 - beta1^step, 1 - beta2^step}.
+// The host refreshes `hyper` (a 12-byte copy) before each step, so the launch itself never changes and can live in a
+// CUDA graph.
+extern "C" int stb_adamw_dyn(void* p, int p_is_fp32, const float* g, float* m, float* v, long n, float beta1,
+                             float beta2, float eps, float weight_decay, const float* clip_coef,
+                             float grad_scale, const float* hyper, cudaStream_t stream) {
+  if (n == 0) return 0;
+  STB_REQUIRE(hyper != nullptr, "adamw_dyn: hyper must point at {lr, bc1, bc2} in device memory");
+  const int grid = ew_grid(n / 4 + 1, 256, 8);
+  if (p_is_fp32)
+    adamw_kernel<float><<<grid, 256, 0, stream>>>((float*)p, g, m, v, n, 0.f, beta1, beta2, eps, weight_decay,
+                                                  1.f, 1.f, clip_coef, grad_scale, hyper);
+  else
+    adamw_kernel<__nv_bfloat16><<<grid, 256, 0, stream>>>((__nv_bfloat16*)p, g, m, v, n, 0.f, beta1, beta2, eps,
+                                                          weight_decay, 1.f, 1.f, clip_coef, grad_scale, hyper);
   STB_CHECK_LAUNCH();
   return 0;
 }

@@ -101,6 +101,10 @@ int stb_ce_grad(void* logits, const long* targets, const float* lse, int rows, i
 int stb_adamw(void* p, int p_is_fp32, const float* g, float* m, float* v, long n, float lr,
               float beta1, float beta2, float eps, float weight_decay, int step,
               const float* clip_coef, float grad_scale, cudaStream_t stream);
+/* graph-replayable variant: hyper = {lr, 1 - beta1^step, 1 - beta2^step} in device memory */
+int stb_adamw_dyn(void* p, int p_is_fp32, const float* g, float* m, float* v, long n, float beta1, float beta2,
+                  float eps, float weight_decay, const float* clip_coef, float grad_scale, const float* hyper,
+                  cudaStream_t stream);
 long stb_sumsq_scratch_bytes(void);
 int stb_sumsq(const float* g, long n, void* scratch, float* out, cudaStream_t stream);
 int stb_clip_coef(const float* sumsq, float max_norm, float* coef, float* norm_out,

@@ -42,6 +42,7 @@ _SIGS = {
     "stb_ce_finalize": [_P, _P, _P, _P, c_int, c_long, _P],
     "stb_ce_grad": [_P, _P, _P, c_int, c_int, c_long, c_int, c_float, _P, c_long, _P],
     "stb_adamw": [_P, c_int, _P, _P, _P, c_long, c_float, c_float, c_float, c_float, c_float, c_int, _P, c_float, _P],
+    "stb_adamw_dyn": [_P, c_int, _P, _P, _P, c_long, c_float, c_float, c_float, c_float, _P, c_float, _P, _P],
     "stb_sumsq": [_P, c_long, _P, _P, _P],
     "stb_clip_coef": [_P, c_float, _P, _P, _P],
     "stb_cast_scale_f32_bf16": [_P, _P, c_long, c_float, _P],

@@ -22,7 +22,7 @@ import torch.nn as nn
 import torch.nn.functional as F
 
 from .. import ops
-from ..ops.grouped import grouped_mlp
+from ..ops.grouped import expert_counts, grouped_mlp
 from ..parallel.context import ParallelContext
 from ..parallel.expert_parallel.ep_comms import dispatch_tokens, gather_tokens
 from .transformer import MLP, DecoderLM
@@ -52,7 +52,7 @@ class MoERouter(nn.Module):
         aux = logits.new_zeros(())
         if self.training and self.aux_loss_coef > 0:
             probs = F.softmax(logits, dim=-1)
-            f = torch.bincount(topk_idx.reshape(-1), minlength=self.num_experts).to(probs.dtype) / x.shape[0]
+            f = expert_counts(topk_idx, self.num_experts).to(probs.dtype) / x.shape[0]
             aux = self.aux_loss_coef * self.num_experts * (f * probs.mean(dim=0)).sum()
         return weights, topk_idx, aux
 
@@ -148,7 +148,7 @@ class MoELayer(nn.Module):
         sort_idx = torch.argsort(flat, stable=True)
         token_of = torch.div(sort_idx, k, rounding_mode="floor")
         xs = x.index_select(0, token_of)
-        counts = torch.bincount(flat, minlength=self.num_experts)
+        counts = expert_counts(flat, self.num_experts)
         ys = self.experts(xs, counts)
         w = weights.reshape(-1).index_select(0, sort_idx).to(ys.dtype)
         ys = ys * w.unsqueeze(-1)

@@ -21,6 +21,14 @@ from .activation import swiglu
 from .gemm import gemm
 
 
+def expert_counts(expert_ids: torch.Tensor, num_experts: int) -> torch.Tensor:
+    """``bincount(expert_ids, minlength=num_experts)`` without the host synchronisation ``torch.bincount`` performs on
+    CUDA to size its output (it reads ``max(input)`` back): the output size is static here."""
+    flat = expert_ids.reshape(-1)
+    out = torch.zeros(num_experts, dtype=torch.int64, device=flat.device)
+    return out.scatter_add_(0, flat, torch.ones_like(flat, dtype=torch.int64))
+
+
 def _offsets(tokens_per_expert: torch.Tensor) -> list[int]:
     c = tokens_per_expert.tolist()  # host sync (path b only)
     off = [0]

@@ -59,10 +59,17 @@ def grad_clip_coef(g: torch.Tensor, max_norm: float, group=None) -> tuple[torch.
     return clip_coef_from_sumsq(ss, max_norm)
 
 
-def fused_adamw_step(p, g, m, v, *, lr, betas, eps, weight_decay, step, clip_coef=None, grad_scale=1.0):
-    """In-place AdamW on flat tensors: ``p`` bf16/fp32, ``g``/``m``/``v`` fp32."""
+def fused_adamw_step(p, g, m, v, *, lr, betas, eps, weight_decay, step, clip_coef=None, grad_scale=1.0, hyper=None):
+    """In-place AdamW on flat tensors: ``p`` bf16/fp32, ``g``/``m``/``v`` fp32.  ``hyper``: device tensor
+    ``[lr, 1-β1^step, 1-β2^step]`` -- when given the launch takes those scalars from device memory (CUDA-graph safe)
+    and ``lr`` / ``step`` are ignored."""
     if N.use_native(p):
         assert g.dtype == torch.float32 and m.dtype == torch.float32 and v.dtype == torch.float32
+        if hyper is not None:
+            N.call("stb_adamw_dyn", p.data_ptr(), int(p.dtype == torch.float32), g.data_ptr(), m.data_ptr(), v.data_ptr(),
+                   p.numel(), float(betas[0]), float(betas[1]), float(eps), float(weight_decay), N.ptr(clip_coef),
+                   float(grad_scale), hyper.data_ptr(), N.stream_ptr())
+            return
         N.call("stb_adamw", p.data_ptr(), int(p.dtype == torch.float32), g.data_ptr(), m.data_ptr(), v.data_ptr(),
                p.numel(), float(lr), float(betas[0]), float(betas[1]), float(eps), float(weight_decay), int(step),
                N.ptr(clip_coef), float(grad_scale), N.stream_ptr())

@@ -19,6 +19,8 @@ from __future__ import annotations
 import torch
 import torch.distributed as dist
 
+from ...ops.grouped import expert_counts
+
 
 def _a2a_single(out: torch.Tensor, inp: torch.Tensor, out_splits, in_splits, group) -> None:
     if dist.get_backend(group) == "gloo":
@@ -98,7 +100,7 @@ def dispatch_tokens(hidden_states: torch.Tensor, topk_indices: torch.Tensor, num
     sort_idx = torch.argsort(flat, stable=True)          # (token,k) pairs ordered by global expert id
     token_of = torch.div(sort_idx, k, rounding_mode="floor")
     send = hidden_states.index_select(0, token_of)       # [T*k, H], differentiable gather
-    counts = torch.bincount(flat, minlength=num_experts).view(ep_size, e_local)
+    counts = expert_counts(flat, num_experts).view(ep_size, e_local)
     recv_counts = exchange_counts(counts, group)          # [src_rank, local expert]
     send_splits = counts.sum(1).tolist()                  # host sync (c10d needs host-side splits)
     recv_splits = recv_counts.sum(1).tolist()

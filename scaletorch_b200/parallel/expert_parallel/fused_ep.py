@@ -29,6 +29,7 @@ import torch.distributed as dist
 
 from ... import _native as N
 from ...ops.activation import swiglu
+from ...ops.grouped import expert_counts
 from ...ops.grouped_native import GroupedLayout, _GroupedLinearPadded
 from ...runtime import fused_ops
 
@@ -91,7 +92,7 @@ class FusedEPState:
         e_local = num_experts // ep
         P = T * k
         flat = idx.reshape(-1)
-        counts = torch.bincount(flat, minlength=num_experts).to(torch.int32)
+        counts = expert_counts(flat, num_experts).to(torch.int32)
         table = torch.empty((ep, num_experts), dtype=torch.int32, device=idx.device)
         N.call("stb_ep_exchange_counts", win.bufs_dev, g.flag_pages_dev, win.off_table, counts.data_ptr(), num_experts,
                table.data_ptr(), rank, ep, SLOT_EP, g.take_epochs(SLOT_EP, 1), N.stream_ptr())

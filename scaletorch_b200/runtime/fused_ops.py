@@ -39,6 +39,23 @@ SLOT_BARRIER, SLOT_AG, SLOT_RS, SLOT_AR, SLOT_DP = 0, 1, 2, 3, 4
 MB = 1 << 20
 
 
+def _no_multimem() -> bool:
+    import os
+
+    return os.environ.get("SCALETORCH_B200_NO_MULTIMEM", "0") == "1"
+
+
+def _multicast_ptr(handle) -> int:
+    """NVLS multicast address of a rendezvoused symmetric buffer (0 when the fabric has no multicast support).
+    ``handle.multicast_ptr`` is the source of truth; ``has_multicast_support`` is a static method taking
+    ``(device_type, device_index)`` -- calling it without arguments raises, which an earlier version of this file
+    swallowed and so never used NVLS."""
+    try:
+        return int(getattr(handle, "multicast_ptr", 0) or 0)
+    except Exception:  # pragma: no cover - very old torch
+        return 0
+
+
 class SymmGroup:
     """Symmetric flag pages + data window of one process group."""
 
@@ -52,6 +69,9 @@ class SymmGroup:
         self.device = dev
         self.flags = sm.empty(4096, dtype=torch.uint8, device=dev)
         self.flags.zero_()
+        # device-driven epochs (csrc/common/symm.cuh): one counter word per slot at [144 + slot], starting at 1.  The
+        # kernels read and advance it themselves, so every launch passes epoch 0 and is replayable from a CUDA graph.
+        self.flags.view(torch.int32)[144:152] = 1
         self.flags_h = sm.rendezvous(self.flags, group=group)
         self.window = sm.empty(window_bytes, dtype=torch.uint8, device=dev)
         self.window_h = sm.rendezvous(self.window, group=group)
@@ -59,10 +79,7 @@ class SymmGroup:
         self.flag_pages_dev = int(self.flags_h.buffer_ptrs_dev)
         self.bufs_dev = int(self.window_h.buffer_ptrs_dev)
         self.peer_ptrs = [int(p) for p in self.window_h.buffer_ptrs]
-        try:
-            self.mc_ptr = int(self.window_h.multicast_ptr or 0) if self.window_h.has_multicast_support() else 0
-        except Exception:
-            self.mc_ptr = 0
+        self.mc_ptr = _multicast_ptr(self.window_h)
         self.epoch = [1] * 8
         # region layout (bytes): [AG shards | RS destinations | all-reduce partials | spare]
         q = window_bytes // 4
@@ -73,9 +90,10 @@ class SymmGroup:
         dist.barrier(group)            # flag pages are zero everywhere before the first device barrier
 
     def take_epochs(self, slot: int, n: int = 1) -> int:
-        e = self.epoch[slot]
+        """Epoch argument for the next launch on ``slot``: always 0 = "use the device counter" (the host-side count is
+        kept only for debugging)."""
         self.epoch[slot] += n
-        return e
+        return 0
 
     def view(self, offset: int, shape, dtype) -> torch.Tensor:
         n = 1
@@ -157,6 +175,12 @@ def gemm_all_reduce(x: torch.Tensor, weight: torch.Tensor, group, b_mn: bool = F
 
 
 def all_reduce_window_bf16(g: SymmGroup, offset_bytes: int, n: int, sm_budget: int = 0) -> torch.Tensor:
+    if g.mc_ptr and n % 8 == 0 and not _no_multimem():
+        # NVLS: in-switch reduction + broadcast in place on the window (each rank handles 1/world of the range)
+        epoch = g.take_epochs(SLOT_AR, 2)
+        N.call("stb_allreduce_bf16", g.bufs_dev, g.mc_ptr, g.flag_pages_dev, offset_bytes // 2, n, g.rank, g.world,
+               SLOT_AR, epoch, sm_budget or 64, N.stream_ptr())
+        return g.view(offset_bytes, (n,), torch.bfloat16).clone()
     out = torch.empty(n, dtype=torch.bfloat16, device=g.device)
     epoch = g.take_epochs(SLOT_AR, 2)
     N.call("stb_allreduce_oneshot_bf16", g.bufs_dev, g.flag_pages_dev, offset_bytes // 2, out.data_ptr(), n, g.rank,
@@ -186,10 +210,7 @@ class GradWindow:
         self.raw = sm.empty(nbytes, dtype=torch.uint8, device=dev)
         self.h = sm.rendezvous(self.raw, group=group)
         self.bufs_dev = int(self.h.buffer_ptrs_dev)
-        try:
-            self.mc_ptr = int(self.h.multicast_ptr or 0) if self.h.has_multicast_support() else 0
-        except Exception:
-            self.mc_ptr = 0
+        self.mc_ptr = _multicast_ptr(self.h)
         import os
 
         if os.environ.get("SCALETORCH_B200_NO_MULTIMEM", "0") == "1":

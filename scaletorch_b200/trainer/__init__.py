@@ -1,5 +1,6 @@
 from .config import (CheckpointArguments, DataArguments, LoggingArguments, LrSchedulerArguments, ModelArguments,
                      OptimizerArguments, ParallelArguments, ScaleTorchArguments, TrainingArguments, validate_config)
+from .graphed import GraphedTrainStep
 from .dist_setup import cleanup_distributed, get_dtype, initialize_distributed_training
 from .lr_scheduler import create_lr_scheduler, register_scheduler
 from .metrics import AsyncScalarReader, log_training_metrics
@@ -7,7 +8,7 @@ from .model_builder import create_model, create_optimizer, get_tensor_shapes
 from .train_step import clip_gradients, train_step, training_step
 
 __all__ = [
-    "AsyncScalarReader", "CheckpointArguments", "DataArguments", "LoggingArguments", "LrSchedulerArguments", "ModelArguments",
+    "AsyncScalarReader", "CheckpointArguments", "GraphedTrainStep", "DataArguments", "LoggingArguments", "LrSchedulerArguments", "ModelArguments",
     "OptimizerArguments", "ParallelArguments", "ScaleTorchArguments", "TrainingArguments", "cleanup_distributed",
     "clip_gradients", "create_lr_scheduler", "create_model", "create_optimizer", "get_dtype", "get_tensor_shapes",
     "initialize_distributed_training", "log_training_metrics", "register_scheduler", "train_step", "training_step", "validate_config",

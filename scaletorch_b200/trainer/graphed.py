@@ -1,0 +1,104 @@
+"""Whole-step CUDA-graph capture of the training step.
+
+A Qwen3-0.6B step is ~650 kernel launches issued from ~900 Python autograd nodes: the host needs about as long to
+issue them (≈26-30 ms) as the GPU needs to run them (≈31 ms), and with eight ranks sharing one host the step becomes
+launch-bound.  Everything in the step is already shaped for capture: every kernel takes raw pointers and a stream and
+allocates nothing, the gradient clip coefficient and the loss scale stay on the device, AdamW reads its
+step-dependent scalars from device memory (``stb_adamw_dyn``), the peer-memory collectives advance their epochs on
+the device (``csrc/common/symm.cuh``), and MoE routing never synchronises with the host.  So the whole
+zero-grad → GA × (forward, backward, bucket all-reduce) → clip → AdamW sequence is captured once and replayed.
+
+The reference has no counterpart (eager PyTorch; ``tools/optimize_mfu.py`` tries ``torch.compile``).
+
+Not captured: pipeline-parallel schedules (NCCL p2p with data-dependent ordering across micro-batches) and the c10d
+fallback collectives; ``GraphedTrainStep.supported`` says whether a configuration qualifies.
+"""
+from __future__ import annotations
+
+import torch
+
+from ..parallel.process_group import process_group_manager as pgm
+from .train_step import training_step
+
+
+class _StaticBatches:
+    """Iterator over the static device buffers the captured step reads (one per micro-batch)."""
+
+    def __init__(self, buffers, grad_accum: int):
+        self.buffers, self.gradient_accumulation_steps, self._i = buffers, grad_accum, 0
+
+    def __next__(self):
+        b = self.buffers[self._i % len(self.buffers)]
+        self._i += 1
+        return b
+
+
+class GraphedTrainStep:
+    """``step = GraphedTrainStep(model, optimizer, config, device); loss = step(data_loader)``.
+
+    The first call runs ``warmup`` eager steps on a side stream (real optimiser steps on real batches), captures the next
+    one, and from then on every call copies the batch into the static buffers, refreshes the optimiser scalars and
+    replays the graph.  The returned loss is a device scalar owned by the graph (valid until the next call).
+    """
+
+    def __init__(self, model, optimizer, config, device, warmup: int = 3):
+        self.model, self.optimizer, self.config, self.device = model, optimizer, config, device
+        self.warmup = warmup
+        self.graph: torch.cuda.CUDAGraph | None = None
+        self.static_loss: torch.Tensor | None = None
+        self._buffers: list[dict] | None = None
+        self._steps_seen = 0
+        self.ga = config.gradient_accumulation_steps
+
+    @staticmethod
+    def supported(config, optimizer) -> bool:
+        from .optimizer import FusedAdamW
+
+        if not torch.cuda.is_available() or not isinstance(optimizer, FusedAdamW):
+            return False
+        if pgm and pgm.pp_world_size > 1:
+            return False
+        if pgm and pgm.world_size > 1 and not getattr(config, "fused_comm", True):
+            return False
+        return True
+
+    # ------------------------------------------------------------------------------------------------------
+    def _eager(self, src) -> torch.Tensor:
+        self.optimizer.zero_grad()
+        if hasattr(self.model, "reset"):
+            self.model.reset()
+        loss = training_step(self.model, src, self.device, torch.bfloat16, self.config)
+        self.optimizer.step()
+        return loss
+
+    def _fetch(self, data_loader) -> list[dict]:
+        return [next(data_loader) for _ in range(self.ga)]
+
+    def _stage(self, batches: list[dict]) -> None:
+        if self._buffers is None:
+            self._buffers = [{k: torch.empty_like(v, device=self.device) for k, v in b.items() if torch.is_tensor(v)}
+                             for b in batches]
+        for buf, b in zip(self._buffers, batches):
+            for k, dst in buf.items():
+                dst.copy_(b[k], non_blocking=True)
+
+    def __call__(self, data_loader) -> torch.Tensor:
+        batches = self._fetch(data_loader)
+        self._stage(batches)
+        src = _StaticBatches(self._buffers, self.ga)
+        if self.graph is None:
+            if self._steps_seen < self.warmup:
+                self._steps_seen += 1
+                return self._eager(src)
+            # capture; the captured work also *runs* once?  No: capture only records, so run the step for this batch by
+            # replaying right after the capture.
+            torch.cuda.synchronize()
+            torch.cuda.empty_cache()          # the eager warm-up pool is not needed again: the graph owns its memory
+            self.graph = torch.cuda.CUDAGraph()
+            # thread_local: the loader's prefetch thread may pin memory while we capture; kernels launched into the
+            # capturing stream by the autograd thread are captured in either mode
+            with torch.cuda.graph(self.graph, capture_error_mode="thread_local"):
+                self.static_loss = self._eager(src)
+        self.optimizer.prepare_step()
+        self.graph.replay()
+        return self.static_loss

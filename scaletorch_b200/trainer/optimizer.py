@@ -30,6 +30,11 @@ class FusedAdamW(torch.optim.Optimizer):
         self.max_grad_norm = max_grad_norm
         self.norm_group = norm_group
         self.last_grad_norm: torch.Tensor | None = None  # device scalar (read lazily for logging)
+        # step-dependent scalars {lr, 1-β1^t, 1-β2^t} live in device memory so the whole step can sit in a CUDA graph
+        self._hyper_dev = self._hyper_host = None
+        if store.device.type == "cuda":
+            self._hyper_dev = torch.zeros(4, dtype=torch.float32, device=store.device)
+            self._hyper_host = torch.zeros(4, dtype=torch.float32, pin_memory=True)
 
     @torch.no_grad()
     def compute_clip(self):
@@ -41,19 +46,33 @@ class FusedAdamW(torch.optim.Optimizer):
         self.last_grad_norm = norm
         return coef, norm
 
+    def prepare_step(self) -> None:
+        """Advance the step counter and refresh the device-side scalars.  Called by :meth:`step` in eager mode; under
+        CUDA-graph replay the caller invokes it before every ``graph.replay()`` (``trainer/graphed.py``)."""
+        self.step_count += 1
+        if self._hyper_dev is not None:
+            g = self.param_groups[0]
+            b1, b2 = g["betas"]
+            self._hyper_host[0] = float(g["lr"])
+            self._hyper_host[1] = 1.0 - b1 ** self.step_count
+            self._hyper_host[2] = 1.0 - b2 ** self.step_count
+            self._hyper_dev.copy_(self._hyper_host, non_blocking=True)
+
     @torch.no_grad()
     def step(self, closure=None, grad_scale: float = 1.0):
         loss = closure() if closure is not None else None
         self.store.finalize_grads()
         self.store.sync_tp_partial_grads()
-        self.step_count += 1
+        capturing = self._hyper_dev is not None and torch.cuda.is_current_stream_capturing()
+        if not capturing:
+            self.prepare_step()
         g = self.param_groups[0]
         coef = None
         if self.max_grad_norm is not None and self.max_grad_norm > 0:
             coef, _ = self.compute_clip()
         fused_adamw_step(self.store.param_flat, self.store.grad_flat, self.exp_avg, self.exp_avg_sq,
                          lr=g["lr"], betas=g["betas"], eps=g["eps"], weight_decay=g["weight_decay"],
-                         step=self.step_count, clip_coef=coef, grad_scale=grad_scale)
+                         step=max(self.step_count, 1), clip_coef=coef, grad_scale=grad_scale, hyper=self._hyper_dev)
         return loss
 
     def zero_grad(self, set_to_none: bool = True) -> None:

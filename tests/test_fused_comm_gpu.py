@@ -44,8 +44,20 @@ def _worker(rank, world, port, which):
                 dist.all_reduce(ref)
                 out = F.all_reduce_(t, group)
                 assert _rel(out, ref) < 1e-2, _rel(out, ref)
+            # both transports of the bf16 all-reduce (NVLS multimem when the fabric has it, one-shot peer loads)
+            for no_mm in ("0", "1"):
+                os.environ["SCALETORCH_B200_NO_MULTIMEM"] = no_mm
+                t = torch.randn(1 << 18, device=dev).bfloat16()
+                ref = t.clone()
+                dist.all_reduce(ref)
+                assert _rel(F.all_reduce_(t, group), ref) < 1e-2
+            os.environ["SCALETORCH_B200_NO_MULTIMEM"] = "0"
             gw = F.GradWindow(group, 1 << 20)
-            for it in range(2):
+            if rank == 0:
+                print(f"multicast available: {bool(g.mc_ptr)} (window) {bool(gw.mc_ptr)} (grad window)", flush=True)
+            for it in range(4):
+                if it == 2:
+                    gw.mc_ptr = 0            # second half: two-shot peer-memory path
                 gw.grad.copy_(torch.randn(1 << 20, device=dev))
                 ref = gw.grad.clone()
                 dist.all_reduce(ref)

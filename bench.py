@@ -90,6 +90,13 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(self.rows)}
 
 
+def fused_mc(gw) -> int:
+    """NVLS multicast address of the gradient window even when the default transport choice disabled it."""
+    from scaletorch_b200.runtime.fused_ops import _multicast_ptr
+
+    return _multicast_ptr(gw.h)
+
+
 def dist_env():
     return int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
 
@@ -225,12 +232,14 @@ def run_ours(args):
         dp = model if hasattr(model, "bucket_manager") else None
         gw = getattr(getattr(dp, "store", None), "grad_window", None)
         if dp is not None and gw is not None:
-            mc = gw.mc_ptr
+            mc = gw.mc_ptr or fused_mc(gw)
             for spec in os.environ["SCALETORCH_B200_DP_SWEEP"].split(","):
                 kind, budget = spec.split(":")
                 gw.mc_ptr = mc if kind == "nvls" else 0
                 for b in dp.bucket_manager.buckets:
                     b.sm_budget = int(budget)
+                if graphed is not None:            # the transport and the CTA budget are baked into the graph: re-capture
+                    graphed.graph = None
                 for _ in range(2):
                     step_with(staged)
                 t = timed_region(torch, dist, world, lambda: step_with(staged), args.steps) / args.steps

@@ -105,15 +105,43 @@ __global__ void __launch_bounds__(512)
       }
     }
   } else {
-    for (long i = lo + long(blockIdx.x) * blockDim.x + threadIdx.x; i < hi; i += long(gridDim.x) * blockDim.x) {
-      const long e = offset + (i << 2);
-      float4 acc = ld_peer_f4(bufs[rank] + e);
-      for (int p = 1; p < world; ++p) {
-        const float4 v = ld_peer_f4(bufs[(rank + p) % world] + e);
-        acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+    // peer loads/stores: 8 independent 16-byte loads in flight per thread and peer (64 KB per CTA), so ~24 CTAs keep
+    // the NVLink ports busy and the remaining SMs stay with the backward pass (one load in flight per thread needed
+    // all 148 SMs to reach the same bandwidth)
+    constexpr int U = 8;
+    const long stride = long(gridDim.x) * blockDim.x;
+    for (long i0 = lo + long(blockIdx.x) * blockDim.x + threadIdx.x; i0 < hi; i0 += stride * U) {
+      float4 acc[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long i = i0 + u * stride;
+        acc[u] = (i < hi) ? ld_peer_f4(bufs[rank] + offset + (i << 2)) : make_float4(0.f, 0.f, 0.f, 0.f);
       }
-      acc.x *= scale; acc.y *= scale; acc.z *= scale; acc.w *= scale;
-      for (int p = 0; p < world; ++p) st_peer_f4(bufs[(rank + p) % world] + e, acc);
+      for (int p = 1; p < world; ++p) {
+        const float* src = bufs[(rank + p) % world] + offset;
+        float4 v[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const long i = i0 + u * stride;
+          v[u] = (i < hi) ? ld_peer_f4(src + (i << 2)) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          acc[u].x += v[u].x; acc[u].y += v[u].y; acc[u].z += v[u].z; acc[u].w += v[u].w;
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        acc[u].x *= scale; acc[u].y *= scale; acc[u].z *= scale; acc[u].w *= scale;
+      }
+      for (int p = 0; p < world; ++p) {
+        float* dst = bufs[(rank + p) % world] + offset;
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const long i = i0 + u * stride;
+          if (i < hi) st_peer_f4(dst + (i << 2), acc[u]);
+        }
+      }
     }
   }
   if (rank == 0) {  // scalar tail (n % 4) handled by rank 0

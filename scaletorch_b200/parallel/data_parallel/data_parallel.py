@@ -109,7 +109,7 @@ class DataParallelBucket(_DPBase):
         import os
 
         bucket_size = int(os.environ.get("SCALETORCH_B200_DP_BUCKET", bucket_size))
-        sm_budget = int(os.environ.get("SCALETORCH_B200_DP_SM_BUDGET", 148))  # profiles/dp_allreduce_sweep.md
+        sm_budget = int(os.environ.get("SCALETORCH_B200_DP_SM_BUDGET", 16))  # profiles/dp_allreduce_sweep.md
         self.bucket_manager = BucketManager(self.store, self.group, self.expert_group, bucket_size, self.wire_dtype,
                                             grad_window=getattr(self.store, "grad_window", None), sm_budget=sm_budget)
         self._post_backward_queued = False

@@ -213,6 +213,8 @@ class GradWindow:
         self.mc_ptr = _multicast_ptr(self.h)
         import os
 
+        # transport (profiles/dp_allreduce_sweep.md): NVLS multimem with 16 CTAs was the fastest setting at 2 and at 8
+        # ranks once the step is replayed from a CUDA graph; SCALETORCH_B200_NO_MULTIMEM=1 selects the peer-load path
         if os.environ.get("SCALETORCH_B200_NO_MULTIMEM", "0") == "1":
             self.mc_ptr = 0
         if self.g.rank == 0 and os.environ.get("SCALETORCH_B200_VERBOSE", "0") == "1":

@@ -108,8 +108,10 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n_kvt = (p.Sk + kBT - 1) / kBT;
-  const int kvt = blockIdx.x % n_kvt;
-  const int bh = blockIdx.x / n_kvt;
+  // heavy tiles first: under a causal mask key tile 0 streams every query tile and the last one only a few, so CTAs are
+  // ordered by key tile across all (batch, head) pairs and the SMs that finish early pick up the light tail
+  const int kvt = blockIdx.x / (p.B * p.Hkv);
+  const int bh = blockIdx.x % (p.B * p.Hkv);
   const int b = bh / p.Hkv, hkv = bh % p.Hkv;
   const int G = p.Hq / p.Hkv;
   const int kv0 = kvt * kBT;
@@ -240,8 +242,18 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
       tc_fence_after();
       if (tid < 64) s_lse[sb * 64 + tid] = stat; else if (tid < 128) s_delta[sb * 64 + (tid - 64)] = stat;
       named_bar_sync(2, 256);
-      const float* lse2 = s_lse + sb * 64 + half * 32;
-      const float* dl = s_delta + sb * 64 + half * 32;
+      // per-column statistics of this thread's 32 query columns: 16 x LDS.128 (broadcast) instead of 64 x LDS.32
+      float lse2[32], dl[32];
+      {
+        const float4* l4 = reinterpret_cast<const float4*>(s_lse + sb * 64 + half * 32);
+        const float4* d4 = reinterpret_cast<const float4*>(s_delta + sb * 64 + half * 32);
+#pragma unroll
+        for (int t = 0; t < 8; ++t) {
+          const float4 a = l4[t], c = d4[t];
+          lse2[4 * t] = a.x; lse2[4 * t + 1] = a.y; lse2[4 * t + 2] = a.z; lse2[4 * t + 3] = a.w;
+          dl[4 * t] = c.x; dl[4 * t + 1] = c.y; dl[4 * t + 2] = c.z; dl[4 * t + 3] = c.w;
+        }
+      }
       uint32_t r0[32], r1[32];
       tmem_ld_32x32b_x32(tmem_base + lane_addr + sb * kST + half * 32, r0);          // S^T
       tmem_ld_32x32b_x32(tmem_base + lane_addr + 128 + sb * kST + half * 32, r1);    // dP^T
@@ -250,12 +262,23 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
       mbar_arrive(&st_free[sb]);
       float pr[32], ds[32];
       const int qpos0 = q0 + shift + half * 32;  // key visible to query column c iff key <= qpos0 + c
+      // tiles strictly below the diagonal (and inside Sk / Sq) need no mask: uniform branch, 3 instructions fewer per
+      // element.  dS is left unscaled here; the softmax scale is applied once per dK element in the epilogue.
+      const bool full_tile = (kv0 + kBT <= p.Sk) && (q0 + kST <= p.Sq) && (!p.causal || kv0 + kBT - 1 <= q0 + shift);
+      if (full_tile) {
 #pragma unroll
-      for (int j = 0; j < 32; ++j) {
-        const float e = exp2f(__uint_as_float(r0[j]) * p.scale_log2 - lse2[j]);
-        const bool ok = key_ok && (!p.causal || key <= qpos0 + j);
-        pr[j] = ok ? e : 0.f;
-        ds[j] = pr[j] * (__uint_as_float(r1[j]) - dl[j]) * p.scale;
+        for (int j = 0; j < 32; ++j) {
+          pr[j] = exp2f(fmaf(__uint_as_float(r0[j]), p.scale_log2, -lse2[j]));
+          ds[j] = pr[j] * (__uint_as_float(r1[j]) - dl[j]);
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          const float e = exp2f(fmaf(__uint_as_float(r0[j]), p.scale_log2, -lse2[j]));
+          const bool ok = key_ok && (!p.causal || key <= qpos0 + j);
+          pr[j] = ok ? e : 0.f;
+          ds[j] = pr[j] * (__uint_as_float(r1[j]) - dl[j]);
+        }
       }
       if (i > 0) mbar_wait(pds_free, (i - 1) & 1);
 #pragma unroll
@@ -291,13 +314,14 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
           for (int j = 0; j < 32; ++j) r[j] = 0;
         }
         if (key_ok) {
+          const float osc = which == 0 ? 1.f : p.scale;     // dK = scale * dS^T Q (dS was accumulated unscaled)
 #pragma unroll
           for (int t = 0; t < 4; ++t)
-            *reinterpret_cast<uint4*>(dst + c * 32 + 8 * t) =
-                make_uint4(pack_bf16x2(__uint_as_float(r[8 * t + 0]), __uint_as_float(r[8 * t + 1])),
-                           pack_bf16x2(__uint_as_float(r[8 * t + 2]), __uint_as_float(r[8 * t + 3])),
-                           pack_bf16x2(__uint_as_float(r[8 * t + 4]), __uint_as_float(r[8 * t + 5])),
-                           pack_bf16x2(__uint_as_float(r[8 * t + 6]), __uint_as_float(r[8 * t + 7])));
+            *reinterpret_cast<uint4*>(dst + c * 32 + 8 * t) = make_uint4(
+                pack_bf16x2(__uint_as_float(r[8 * t + 0]) * osc, __uint_as_float(r[8 * t + 1]) * osc),
+                pack_bf16x2(__uint_as_float(r[8 * t + 2]) * osc, __uint_as_float(r[8 * t + 3]) * osc),
+                pack_bf16x2(__uint_as_float(r[8 * t + 4]) * osc, __uint_as_float(r[8 * t + 5]) * osc),
+                pack_bf16x2(__uint_as_float(r[8 * t + 6]) * osc, __uint_as_float(r[8 * t + 7]) * osc));
         }
       }
     }
@@ -464,12 +488,21 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
       tc_fence_before();
       mbar_arrive(&st_free[sb]);
       float ds[32];
+      // tiles strictly below the diagonal need no mask (uniform branch); the softmax scale is applied once per dQ
+      // element in the epilogue instead of once per dS element
+      const bool full_tile = (i * kST + kST <= p.Sk) && (!p.causal || i * kST + kST - 1 <= q0 + shift);
+      if (full_tile) {
 #pragma unroll
-      for (int j = 0; j < 32; ++j) {
-        const int key = key0 + j;
-        const float e = exp2f(__uint_as_float(r0[j]) * p.scale_log2 - lse2);
-        const bool ok = (key < p.Sk) && (!p.causal || key <= q_pos);
-        ds[j] = (ok ? e : 0.f) * (__uint_as_float(r1[j]) - dl) * p.scale;
+        for (int j = 0; j < 32; ++j)
+          ds[j] = exp2f(fmaf(__uint_as_float(r0[j]), p.scale_log2, -lse2)) * (__uint_as_float(r1[j]) - dl);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          const int key = key0 + j;
+          const float e = exp2f(fmaf(__uint_as_float(r0[j]), p.scale_log2, -lse2));
+          const bool ok = (key < p.Sk) && (!p.causal || key <= q_pos);
+          ds[j] = (ok ? e : 0.f) * (__uint_as_float(r1[j]) - dl);
+        }
       }
       if (i > 0) mbar_wait(ds_free, (i - 1) & 1);
 #pragma unroll
@@ -489,13 +522,14 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
       tmem_ld_32x32b_x32(tmem_base + lane_addr + 256 + c * 32, r);
       tmem_ld_wait();
       if (q_ok) {
+        const float osc = p.scale;                           // dQ = scale * dS K
 #pragma unroll
         for (int t = 0; t < 4; ++t)
-          *reinterpret_cast<uint4*>(dst + c * 32 + 8 * t) =
-              make_uint4(pack_bf16x2(__uint_as_float(r[8 * t + 0]), __uint_as_float(r[8 * t + 1])),
-                         pack_bf16x2(__uint_as_float(r[8 * t + 2]), __uint_as_float(r[8 * t + 3])),
-                         pack_bf16x2(__uint_as_float(r[8 * t + 4]), __uint_as_float(r[8 * t + 5])),
-                         pack_bf16x2(__uint_as_float(r[8 * t + 6]), __uint_as_float(r[8 * t + 7])));
+          *reinterpret_cast<uint4*>(dst + c * 32 + 8 * t) = make_uint4(
+              pack_bf16x2(__uint_as_float(r[8 * t + 0]) * osc, __uint_as_float(r[8 * t + 1]) * osc),
+              pack_bf16x2(__uint_as_float(r[8 * t + 2]) * osc, __uint_as_float(r[8 * t + 3]) * osc),
+              pack_bf16x2(__uint_as_float(r[8 * t + 4]) * osc, __uint_as_float(r[8 * t + 5]) * osc),
+              pack_bf16x2(__uint_as_float(r[8 * t + 6]) * osc, __uint_as_float(r[8 * t + 7]) * osc));
       }
     }
   }

@@ -39,6 +39,21 @@ SLOT_BARRIER, SLOT_AG, SLOT_RS, SLOT_AR, SLOT_DP = 0, 1, 2, 3, 4
 MB = 1 << 20
 
 
+def _poison() -> bool:
+    import os
+
+    return os.environ.get("SCALETORCH_B200_POISON", "0") == "1"
+
+
+def _empty(shape, dtype, device) -> torch.Tensor:
+    """Output buffers of the fused collectives.  Debug mode ``SCALETORCH_B200_POISON=1`` fills them with NaN first, so a
+    row block a kernel failed to write (a missed flag, a wrong peer offset) shows up as NaN in the very next op instead
+    of as plausible stale data (the reference has no race / ordering diagnostics)."""
+    if _poison():
+        return torch.full(shape, float("nan"), dtype=dtype, device=device)
+    return torch.empty(shape, dtype=dtype, device=device)
+
+
 def _no_multimem() -> bool:
     import os
 
@@ -134,8 +149,8 @@ def all_gather_gemm(x_shard: torch.Tensor, weight: torch.Tensor, group, b_mn: bo
     assert Ts * K * 2 <= g.region_bytes, "all-gather shard does not fit the symmetric window region"
     shard = g.view(g.off_ag, (Ts, K), torch.bfloat16)
     shard.copy_(x_shard)
-    x_full = torch.empty((T, K), dtype=torch.bfloat16, device=x_shard.device)
-    y = torch.empty((T, Nn), dtype=torch.bfloat16, device=x_shard.device)
+    x_full = _empty((T, K), torch.bfloat16, x_shard.device)
+    y = _empty((T, Nn), torch.bfloat16, x_shard.device)
     epoch = g.take_epochs(SLOT_AG, 2)
     N.call("stb_ag_gemm_bf16", x_full.data_ptr(), weight.data_ptr(), y.data_ptr(), T, Nn, K, weight.stride(0),
            y.stride(0), int(b_mn), g.bufs_dev, g.flag_pages_dev, g.off_ag, g.ready_flags.data_ptr(), epoch, flag_rows,
@@ -181,7 +196,7 @@ def all_reduce_window_bf16(g: SymmGroup, offset_bytes: int, n: int, sm_budget: i
         N.call("stb_allreduce_bf16", g.bufs_dev, g.mc_ptr, g.flag_pages_dev, offset_bytes // 2, n, g.rank, g.world,
                SLOT_AR, epoch, sm_budget or 64, N.stream_ptr())
         return g.view(offset_bytes, (n,), torch.bfloat16).clone()
-    out = torch.empty(n, dtype=torch.bfloat16, device=g.device)
+    out = _empty((n,), torch.bfloat16, g.device)
     epoch = g.take_epochs(SLOT_AR, 2)
     N.call("stb_allreduce_oneshot_bf16", g.bufs_dev, g.flag_pages_dev, offset_bytes // 2, out.data_ptr(), n, g.rank,
            g.world, SLOT_AR, epoch, sm_budget, N.stream_ptr())

@@ -139,6 +139,7 @@ class TrainingArguments:
     sequence_length: int | None = field(default=1024, metadata={"help": "Sequence length"})
     log_interval: int = field(default=100, metadata={"help": "Logging frequency"})
     max_tokens: int | None = field(default=None, metadata={"help": "Stop after this many trained tokens"})
+    use_cuda_graph: bool = field(default=False, metadata={"help": "Replay the whole step from a CUDA graph (trainer/graphed.py)"})
     log_lag: int = field(default=1, metadata={"help": "Log step i after enqueueing step i+lag (0 = synchronous logging)"})
     total_train_steps: int | None = field(default=None, metadata={"help": "Stop after this many steps"})
     use_cpu: bool = field(default=False, metadata={"help": "Run on CPU with the gloo backend"})
@@ -171,6 +172,11 @@ class LoggingArguments:
     use_wandb: bool = field(default=False, metadata={"help": "Log to Weights & Biases"})
     project_name: str = field(default="scaletorch", metadata={"help": "Project name for logging"})
     experiment_name: str | None = field(default=None, metadata={"help": "Experiment name for logging"})
+    profile_start_step: int | None = field(default=None, metadata={"help": "First step of the torch.profiler window"})
+    profile_end_step: int | None = field(default=None, metadata={"help": "Step at which the profiler window closes"})
+    trace_dir: str = field(default="traces", metadata={"help": "Where Chrome traces / kernel tables are written"})
+    nvtx: bool = field(default=False, metadata={"help": "Emit NVTX ranges (step / phase) for Nsight Systems"})
+    step_timeout_s: float = field(default=0.0, metadata={"help": "Watchdog: abort if a step takes longer (0 = off)"})
 
 
 @dataclass

@@ -32,6 +32,7 @@ def _worker(rank, world, port, which):
         from scaletorch_b200.runtime import fused_ops as F
 
         group = dist.group.WORLD
+        os.environ["SCALETORCH_B200_POISON"] = "1"      # unwritten output rows would surface as NaN
         torch.manual_seed(100 + rank)
         dev = torch.device("cuda", rank)
         if which == "barrier_allreduce":

@@ -108,6 +108,18 @@ def main(argv=None) -> None:
             dist.barrier()
         tensor_shapes = get_tensor_shapes(config, model_config) if (pgm and pgm.pp_world_size > 1) else None
 
+        from scaletorch_b200.trainer import GraphedTrainStep
+        from scaletorch_b200.utils.tracing import ProfilerWindow, enable_nvtx, nvtx_range
+        from scaletorch_b200.utils.watchdog import StepWatchdog, maybe_inject_fault
+
+        if config.nvtx:
+            enable_nvtx()
+        prof = ProfilerWindow(config.profile_start_step, config.profile_end_step, config.trace_dir, global_rank)
+        watchdog = StepWatchdog(config.step_timeout_s, config.work_dir or ".", global_rank).start()
+        graphed = None
+        if config.use_cuda_graph and GraphedTrainStep.supported(config, optimizer):
+            graphed = GraphedTrainStep(model, optimizer, config, device)
+            rank_print("whole-step CUDA graph replay enabled", is_print_rank=log_rank)
         monitor.start()
         max_steps = config.total_train_steps or float("inf")
         log_lag = max(0, int(getattr(config, "log_lag", 1)))
@@ -123,13 +135,21 @@ def main(argv=None) -> None:
                                  num_params, world_size, logger=logger, wandb_run=run)
 
         while config.max_tokens is None or trained_tokens < config.max_tokens:
+            prof.step(step)
+            maybe_inject_fault(global_rank, step)
             monitor.start_iteration(tokens_processed=tokens_per_step)
-            optimizer.zero_grad(set_to_none=True)
-            if hasattr(model, "reset"):
-                model.reset()
-            loss_t = training_step(model, data_loader, device, dtype, config, tensor_shapes)
-            grad_norm = clip_gradients(model, config.max_grad_norm, optimizer)
-            optimizer.step()
+            with nvtx_range(f"step {step}"):
+                if graphed is not None:
+                    loss_t, grad_norm = graphed(data_loader), None
+                else:
+                    optimizer.zero_grad(set_to_none=True)
+                    if hasattr(model, "reset"):
+                        model.reset()
+                    with nvtx_range("fwd+bwd"):
+                        loss_t = training_step(model, data_loader, device, dtype, config, tensor_shapes)
+                    grad_norm = clip_gradients(model, config.max_grad_norm, optimizer)
+                    with nvtx_range("optimizer"):
+                        optimizer.step()
             lr_scheduler.step()
             # lagged logging: step i is resolved (events, loss, grad norm read back) after step i+1 has been enqueued,
             # so the host never drains the device queue; --log_lag 0 restores fully synchronous logging
@@ -147,6 +167,7 @@ def main(argv=None) -> None:
                     gc.collect()
             while len(pending) > log_lag:
                 flush_one()
+            watchdog.beat(step)
             if config.save_model_checkpoint and config.save_frequency > 0 and step % config.save_frequency == 0:
                 out_dir = Path(config.work_dir) / f"{step}"
                 ckpt.save_checkpoint(model, optimizer, step, trained_tokens, str(out_dir),
@@ -157,6 +178,8 @@ def main(argv=None) -> None:
                 break
         while pending:
             flush_one()
+        prof.close()
+        watchdog.stop()
     except Exception:
         logger.error("training failed", exc_info=True)
         raise

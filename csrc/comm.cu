@@ -243,6 +243,42 @@ __global__ void __launch_bounds__(512)
   grid_finish_cross_gpu_barrier(flag_pages, rank, world, slot, epoch + 1, epoch_arg);
 }
 
+// Embedding gradient as token rows: every rank has staged (ids[T], dout[T, H]) in its symmetric window; each rank walks
+// the rows of *all* ranks and scatter-adds scale * dout into its local fp32 gradient of the (vocab-shard of the)
+// embedding matrix.  The gradient of an embedding touches at most T rows per rank, so exchanging the rows costs
+// world * T * H * 2 bytes where all-reducing the [V, H] fp32 gradient costs V * H * 4 bytes (8 MB vs 622 MB per rank
+// for Qwen3-0.6B) -- and that all-reduce sat at the very end of backward where nothing can hide it.
+// Reference: the embedding weight goes through the same bucket all-reduce as every other parameter
+// (scaletorch/parallel/data_parallel/bucket.py:58-78).
+__global__ void __launch_bounds__(256)
+    embedding_bwd_peers_kernel(const uint8_t* const* bufs, uint32_t* const* flag_pages, long ids_off, long dout_off,
+                               float* __restrict__ dW, long T, int H, int vocab_start, int vocab_local, float scale,
+                               int rank, int world, int slot, uint32_t epoch_arg) {
+  const uint32_t epoch = symm_epoch_load(flag_pages, rank, slot, epoch_arg);
+  grid_cross_gpu_barrier(flag_pages, rank, world, slot, epoch);       // every rank has staged its rows
+  const int vec_per_row = H >> 3;
+  const long per_rank = T * vec_per_row;
+  const long total = per_rank * world;
+  for (long i = long(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += long(gridDim.x) * blockDim.x) {
+    const int src = int((rank + i / per_rank) % world);               // own rows first, then the peers in ring order
+    const long r = i % per_rank;
+    const long t = r / vec_per_row;
+    const int c = int(r % vec_per_row) * 8;
+    const long id = reinterpret_cast<const long*>(bufs[src] + ids_off)[t] - vocab_start;
+    if (id < 0 || id >= vocab_local) continue;
+    const uint4 d = ld_nc_v4(reinterpret_cast<const __nv_bfloat16*>(bufs[src] + dout_off) + t * H + c);
+    const uint32_t du[4] = {d.x, d.y, d.z, d.w};
+    float* dst = dW + id * H + c;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float2 f = unpack_bf16x2(du[j]);
+      atomicAdd(dst + 2 * j, f.x * scale);
+      atomicAdd(dst + 2 * j + 1, f.y * scale);
+    }
+  }
+  grid_finish_cross_gpu_barrier(flag_pages, rank, world, slot, epoch + 1, epoch_arg);   // staging areas may be reused
+}
+
 static int comm_grid(int sm_budget) {
   const int sms = sm_count();
   if (sm_budget <= 0 || sm_budget > sms) sm_budget = sms;
@@ -324,6 +360,21 @@ extern "C" int stb_allgather_pull(const void* bufs_dev, const void* flag_pages_d
   allgather_pull_kernel<<<grid, 512, 0, stream>>>((const uint8_t* const*)bufs_dev, (uint32_t* const*)flag_pages_dev,
                                                   offset_bytes, (uint8_t*)dst, rows_per_rank, row_bytes, flag_rows,
                                                   (uint32_t*)ready, rank, world, slot, epoch);
+  STB_CHECK_LAUNCH();
+  return 0;
+}
+
+// Consumes 2 epochs.  ids (int64 [T]) at ids_off and dout (bf16 [T, H]) at dout_off of every rank's symmetric buffer;
+// dW: local fp32 [vocab_local, H], accumulated into (the caller zeroes it when this is the first contribution).
+extern "C" int stb_embedding_bwd_peers(const void* bufs_dev, const void* flag_pages_dev, long ids_off, long dout_off,
+                                       float* dW, long T, int H, int vocab_start, int vocab_local, float scale,
+                                       int rank, int world, int slot, unsigned epoch, int sm_budget,
+                                       cudaStream_t stream) {
+  STB_REQUIRE(world <= kMaxWorld && slot < kMaxSlots, "embedding_bwd_peers: world %d / slot %d out of range", world, slot);
+  STB_REQUIRE(H % 8 == 0 && ids_off % 8 == 0 && dout_off % 16 == 0, "embedding_bwd_peers: H %% 8 and aligned offsets required");
+  embedding_bwd_peers_kernel<<<comm_grid(sm_budget), 256, 0, stream>>>(
+      (const uint8_t* const*)bufs_dev, (uint32_t* const*)flag_pages_dev, ids_off, dout_off, dW, T, H, vocab_start,
+      vocab_local, scale, rank, world, slot, epoch);
   STB_CHECK_LAUNCH();
   return 0;
 }

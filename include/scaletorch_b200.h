@@ -157,6 +157,11 @@ int stb_allgather_pull(const void* bufs_dev, const void* flag_pages_dev, long of
                        long rows_per_rank, long row_bytes, int flag_rows, void* ready, int rank, int world, int slot,
                        unsigned epoch, int sm_budget, cudaStream_t stream);                  /* 2 epochs */
 
+/* embedding gradient exchanged as token rows instead of all-reducing the [V, H] matrix; 2 epochs */
+int stb_embedding_bwd_peers(const void* bufs_dev, const void* flag_pages_dev, long ids_off, long dout_off, float* dW,
+                            long T, int H, int vocab_start, int vocab_local, float scale, int rank, int world,
+                            int slot, unsigned epoch, int sm_budget, cudaStream_t stream);
+
 /* ---- GEMM fused with its collective, csrc/gemm_tcgen05.cu -------------------------------------------------------
  * stb_gemm_rs_bf16: C = A . op(B) whose epilogue TMA-reduce-adds row block d of the product into `c_dest[d]` (rank d's
  *   zeroed [M / world, N] bf16 buffer, peer-mapped) -> GEMM + reduce-scatter in one kernel; tiles are visited

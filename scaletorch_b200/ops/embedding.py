@@ -29,6 +29,13 @@ def embedding_backward(flat_ids: torch.Tensor, dout2d: torch.Tensor, weight: tor
         dst, acc, is_main = _param_grad_out(weight)
         if not acc:
             dst.zero_()
+        sync = getattr(weight, "_stb_sparse_sync", None)
+        if sync is not None and is_main and sync.fits(T, H):
+            # data-parallel ranks exchange the token rows; the result already holds every rank's contribution (mean),
+            # so the parameter takes no part in the dense bucket all-reduce for this gradient
+            sync.accumulate(flat_ids, dout2d, dst, vocab_start, weight.shape[0])
+            weight.grad_written = True
+            return None
         N.call("stb_embedding_bwd", flat_ids.data_ptr(), dout2d.data_ptr(), dst.data_ptr(), T, H, vocab_start,
                weight.shape[0], N.stream_ptr())
         return _finish_param_grad(weight, dst, is_main)

@@ -29,6 +29,8 @@ class Bucket:
         self.wire_dtype = wire_dtype
         self.params_with_grad_ready: set[int] = set()
         self.handle = None
+        self.launched = False          # sync_gradient() ran in this backward (the handle may already have been waited on)
+        self.skip_sync = False         # every parameter of the bucket synchronises by itself (embedding row exchange)
         self._wire: torch.Tensor | None = None
         # fused path: the gradient buffer lives in symmetric memory and the bucket is reduced in place by
         # stb_allreduce_f32 (two-shot over NVLink peer memory / NVLS, 1/world scale fused) on a side stream
@@ -42,9 +44,10 @@ class Bucket:
 
     def sync_gradient(self) -> None:
         """Launches the (asynchronous) mean all-reduce of this bucket."""
-        if self.handle is not None:
+        if self.handle is not None or self.launched:
             raise RuntimeError("bucket gradient sync launched twice")
-        if self.world_size == 1:
+        self.launched = True
+        if self.world_size == 1 or self.skip_sync:
             return
         for p in self.params:            # parameters that got no gradient contribute zeros
             if not p.grad_written:
@@ -80,8 +83,14 @@ class Bucket:
         if self._wire is not None and self.wire_dtype == torch.bfloat16 and self.world_size > 1:
             self.grad_data.copy_(self._wire)
 
+    def wait_stream(self) -> None:
+        """Order the current stream after this bucket's all-reduce if one is in flight (does not consume the handle)."""
+        if isinstance(self.handle, _EventHandle):
+            self.handle.wait()
+
     def reset(self) -> None:
         self.handle = None
+        self.launched = False
         self.params_with_grad_ready.clear()
 
     def mark_param_as_ready(self, param, sync: bool = True) -> None:
@@ -153,5 +162,5 @@ class BucketManager:
     def sync_all(self) -> None:
         """Launches the reduction of every bucket that has not been launched yet."""
         for b in self.buckets:
-            if b.handle is None:
+            if not b.launched:
                 b.sync_gradient()

@@ -115,6 +115,39 @@ class DataParallelBucket(_DPBase):
         self._post_backward_queued = False
         for s in self.store.slots:
             s.param.grad_ready_hook = self._make_ready_hook(s.param)
+        self._install_embedding_row_exchange(module)
+
+    def _install_embedding_row_exchange(self, module: nn.Module) -> None:
+        """Embedding gradients touch at most ``tokens`` rows per rank: exchange those rows between the gradient-sync
+        ranks (``runtime.fused_ops.EmbeddingGradExchange``) instead of all-reducing the ``[V, H]`` matrix, whose
+        reduction would sit at the very end of backward.  Needs the peer-memory gradient window and no pipeline split
+        (tied weights across stages are handled by the PP wrapper)."""
+        import os
+
+        from ...parallel.process_group import process_group_manager as pgm
+        from ...parallel.tensor_parallel.tensor_parallel import VocabParallelEmbedding
+
+        if getattr(self.store, "grad_window", None) is None or os.environ.get("SCALETORCH_B200_EMB_ROW_EXCHANGE", "1") != "1":
+            return
+        if pgm and pgm.pp_world_size > 1:
+            return
+        from ...runtime.fused_ops import EmbeddingGradExchange
+
+        world = dist.get_world_size(self.group)
+        for m in module.modules():
+            if not isinstance(m, VocabParallelEmbedding):
+                continue
+            w = m.weight
+            bucket = self.bucket_manager.param_to_bucket.get(id(w))
+            if bucket is None or bucket.grad_window is None:
+                continue
+            tied = getattr(w, "_stb_expected_grads", 1) > 1
+            if tied:
+                w._stb_expected_grads -= 1        # only the LM-head wgrad arrival marks the parameter ready
+                w._stb_sparse_sync = EmbeddingGradExchange(self.group, 1.0 / world, wait_for=bucket.wait_stream)
+            elif len(bucket.params) == 1:
+                bucket.skip_sync = True           # nothing dense to reduce for this parameter
+                w._stb_sparse_sync = EmbeddingGradExchange(self.group, 1.0 / world)
 
     def _make_ready_hook(self, param):
         def ready(complete: bool = False):

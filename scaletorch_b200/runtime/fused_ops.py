@@ -30,11 +30,13 @@ N.register("stb_allreduce_f32", [_P, _P, _P, _L, _L, _F, _I, _I, _I, _U, _I, _P]
 N.register("stb_allreduce_bf16", [_P, _P, _P, _L, _L, _I, _I, _I, _U, _I, _P])
 N.register("stb_allreduce_oneshot_bf16", [_P, _P, _L, _P, _L, _I, _I, _I, _U, _I, _P])
 N.register("stb_allgather_pull", [_P, _P, _L, _P, _L, _L, _I, _P, _I, _I, _I, _U, _I, _P])
+N.register("stb_embedding_bwd_peers", [_P, _P, _L, _L, _P, _L, _I, _I, _I, _F, _I, _I, _I, _U, _I, _P])
 N.register("stb_gemm_rs_bf16", [_P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _I, _P])
 N.register("stb_ag_gemm_bf16", [_P, _P, _P, _I, _I, _I, _I, _I, _I, _P, _P, _L, _P, _U, _I, _I, _I, _I, _I, _P])
 
 # flag slots (each op family has its own so families on different streams never share an epoch counter)
 SLOT_BARRIER, SLOT_AG, SLOT_RS, SLOT_AR, SLOT_DP = 0, 1, 2, 3, 4
+SLOT_EMB = 7     # (5 = context-parallel ring, 6 = expert-parallel dispatch/combine)
 
 MB = 1 << 20
 
@@ -244,3 +246,34 @@ class GradWindow:
         epoch = g.take_epochs(SLOT_DP, 2)
         N.call("stb_allreduce_f32", self.bufs_dev, self.mc_ptr or None, g.flag_pages_dev, start, numel, float(scale),
                g.rank, g.world, SLOT_DP, epoch, sm_budget, N.stream_ptr())
+
+
+class EmbeddingGradExchange:
+    """Data-parallel synchronisation of an embedding gradient by exchanging token rows (``stb_embedding_bwd_peers``).
+
+    Installed on the embedding weight by ``DataParallelBucket`` (attribute ``_stb_sparse_sync``);
+    ``ops.embedding.embedding_backward`` calls :meth:`accumulate` instead of scatter-adding locally.  Every
+    micro-batch is exchanged, also under ``no_sync``: the contributions are identical on all ranks afterwards, so a
+    later mean all-reduce of the same range (tied LM head) leaves them unchanged.
+    """
+
+    def __init__(self, group, scale: float, wait_for=None):
+        self.g = get_group(group)
+        self.scale = float(scale)
+        self.wait_for = wait_for          # callable: make the current stream wait for the dense all-reduce of the range
+
+    def fits(self, T: int, H: int) -> bool:
+        return T * 8 + T * H * 2 + 4096 <= self.g.region_bytes
+
+    def accumulate(self, flat_ids: torch.Tensor, dout2d: torch.Tensor, dst: torch.Tensor, vocab_start: int, vocab_local: int):
+        g = self.g
+        T, H = dout2d.shape
+        ids_off = g.off_ag
+        dout_off = g.off_ag + (T * 8 + 4095) // 4096 * 4096
+        g.view(ids_off, (T,), torch.int64).copy_(flat_ids)
+        g.view(dout_off, (T, H), torch.bfloat16).copy_(dout2d)
+        if self.wait_for is not None:
+            self.wait_for()
+        N.call("stb_embedding_bwd_peers", g.bufs_dev, g.flag_pages_dev, ids_off, dout_off, dst.data_ptr(), T, H,
+               int(vocab_start), int(vocab_local), self.scale, g.rank, g.world, SLOT_EMB, g.take_epochs(SLOT_EMB, 2), 32,
+               N.stream_ptr())

@@ -42,6 +42,7 @@ def _worker(rank, world, port, mode, fused):
         from scaletorch_b200.utils.sharding import load_from_unsharded, shard_tensor
 
         cfg = Cfg()
+        cfg.tie_word_embeddings = mode == "dp_tied"
         torch.manual_seed(1234)
         full = Qwen3(cfg, ParallelContext()).to(torch.bfloat16).to(dev)
         torch.manual_seed(7)
@@ -96,6 +97,9 @@ def _worker(rank, world, port, mode, fused):
             get_store(par, pgm.grad_sync_group, fused)
             assert (getattr(par._stb_store, "grad_window", None) is not None) == fused
             dp = DataParallelBucket(par, bucket_size=4_000_000)
+            # fused path: the embedding gradient is exchanged as token rows (tied: after the LM-head all-reduce)
+            emb_w = next(p for n, p in par.named_parameters() if "embedding" in n)
+            assert (getattr(emb_w, "_stb_sparse_sync", None) is not None) == fused
             full.loss(x, y).backward()
             for _ in range(2):   # second round checks epoch / flag re-use
                 dp.reset()
@@ -108,7 +112,7 @@ def _worker(rank, world, port, mode, fused):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("mode,fused", [("tp", False), ("tp", True), ("tp_sp", False), ("tp_sp", True), ("dp", False), ("dp", True), ("cp", False), ("cp", True)])
+@pytest.mark.parametrize("mode,fused", [("tp", False), ("tp", True), ("tp_sp", False), ("tp_sp", True), ("dp", False), ("dp", True), ("dp_tied", True), ("cp", False), ("cp", True)])
 def test_two_gpu_model_equality(mode, fused):
     if torch.cuda.device_count() < 2:
         pytest.skip("needs at least 2 GPUs")

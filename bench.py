@@ -46,6 +46,7 @@ def parse_args():
     ap.add_argument("--sequence_parallel", action="store_true")
     ap.add_argument("--gradient_checkpointing", action="store_true")
     ap.add_argument("--skip_e2e", action="store_true")
+    ap.add_argument("--cp_zigzag", type=int, default=1, help="load-balanced causal context parallelism (ours)")
     ap.add_argument("--cuda_graph", type=int, default=1, help="capture the whole step in a CUDA graph when supported (ours)")
     return ap.parse_args()
 
@@ -155,7 +156,7 @@ def run_ours(args):
         gradient_accumulation_steps=args.grad_accum, tensor_parallel_size=args.tp, context_parallel_size=args.cp,
         pipeline_parallel_size=args.pp, expert_parallel_size=args.ep, data_parallel_size=dp,
         sequence_parallel=args.sequence_parallel, gradient_checkpointing=args.gradient_checkpointing,
-        synthetic_data=True, dtype="bfloat16", learning_rate=3e-4, max_grad_norm=1.0, seed=1)
+        cp_zigzag=bool(args.cp_zigzag), synthetic_data=True, dtype="bfloat16", learning_rate=3e-4, max_grad_norm=1.0, seed=1)
     _, _, _, device = initialize_distributed_training(cfg)
     _native.load(required=True)
     model, model_config = create_model(cfg, torch.bfloat16, device)

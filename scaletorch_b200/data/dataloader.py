@@ -77,6 +77,16 @@ class MicroBatchDataLoader(DataLoader):
     def collate_batch(self, batch: list[dict[str, Any]]) -> dict[str, Any]:
         """Stack → CP-slice ``[cp_rank·S/cp, +S/cp)`` → shifted targets and absolute positions."""
         ids = torch.stack([torch.as_tensor(b["input_ids"], dtype=torch.long) for b in batch])  # [mbs, S+1]
+        if self.cp_world_size > 1:
+            from ..parallel.context_parallel import zigzag
+
+            if zigzag.enabled():   # load-balanced causal CP: chunks cp_rank and 2·cp−1−cp_rank of 2·cp
+                S = self.sequence_length_per_rank * self.cp_world_size
+                input_ids = zigzag.take(ids, S, self.cp_world_size, self.cp_rank).contiguous()
+                target_ids = zigzag.take(ids, S, self.cp_world_size, self.cp_rank, shift=1).contiguous()
+                pos = zigzag.local_positions(self.sequence_length_per_rank, self.cp_world_size, self.cp_rank)
+                position_ids = pos.unsqueeze(0).expand(ids.shape[0], -1).contiguous()
+                return {"input_ids": input_ids, "target_ids": target_ids, "position_ids": position_ids, "hidden_states": None}
         lo = self.cp_rank * self.sequence_length_per_rank
         hi = lo + self.sequence_length_per_rank
         input_ids = ids[:, lo:hi].contiguous()

@@ -69,8 +69,10 @@ class Attention(nn.Module):
             self.q_norm.reset_parameters()
             self.k_norm.reset_parameters()
 
-    def forward(self, x: torch.Tensor, B: int, S: int, cos: torch.Tensor, sin: torch.Tensor, pos_offset: int = 0):
-        """x: ``[T(/tp), H]`` → ``[T(/tp), H]`` with ``T = B*S`` local (CP-sharded) tokens."""
+    def forward(self, x: torch.Tensor, B: int, S: int, cos: torch.Tensor, sin: torch.Tensor, pos_offset: int = 0,
+                positions: torch.Tensor | None = None):
+        """x: ``[T(/tp), H]`` → ``[T(/tp), H]`` with ``T = B*S`` local (CP-sharded) tokens.  ``positions [T]``: explicit
+        token positions (zig-zag context parallelism), otherwise ``pos_offset + t mod S``."""
         qkv = self.qkv_proj(x)  # [T, (Hq_l + 2 Hkv_l) * D]
         attn_fn = None
         if self._attn_backend_name != "flash":
@@ -79,7 +81,7 @@ class Attention(nn.Module):
             qkv, self.q_norm.weight if self.q_norm is not None else None,
             self.k_norm.weight if self.k_norm is not None else None, cos, sin, B, S,
             self.num_local_heads, self.num_local_kv_heads, self.head_dim, pos_offset, self.eps,
-            causal=True, scale=1.0 / math.sqrt(self.head_dim), attn_fn=attn_fn)
+            causal=True, scale=1.0 / math.sqrt(self.head_dim), attn_fn=attn_fn, positions=positions)
         return self.out_proj(a.reshape(B * S, self.num_local_heads * self.head_dim))
 
 
@@ -130,13 +132,14 @@ class DecoderLayer(nn.Module):
         self.attention.reset_parameters()
         self.ffn.reset_parameters()
 
-    def forward(self, h: torch.Tensor, delta: torch.Tensor | None, B: int, S: int, cos, sin, pos_offset: int = 0):
+    def forward(self, h: torch.Tensor, delta: torch.Tensor | None, B: int, S: int, cos, sin, pos_offset: int = 0,
+                positions: torch.Tensor | None = None):
         """``(h, delta)`` is the residual stream and the not-yet-added branch output."""
         if delta is None:
             y = ops.rmsnorm(h, self.input_layernorm.weight, self.input_layernorm.eps)
         else:
             h, y = ops.add_rmsnorm(delta, h, self.input_layernorm.weight, self.input_layernorm.eps)
-        a = self.attention(y, B, S, cos, sin, pos_offset)
+        a = self.attention(y, B, S, cos, sin, pos_offset, positions)
         h, y = ops.add_rmsnorm(a, h, self.post_attention_layernorm.weight, self.post_attention_layernorm.eps)
         return h, self.ffn(y)
 
@@ -229,12 +232,19 @@ class DecoderLM(nn.Module):
 
     def run_layers(self, h, delta, B: int, S: int, layers=None, gradient_checkpointing: bool = False):
         pos_offset = self.ctx.cp_rank * S if self.ctx.cp_size > 1 else 0
+        positions = None
+        if self.ctx.cp_size > 1:
+            from ..parallel.context_parallel import zigzag
+
+            if zigzag.enabled():   # this rank holds chunks cp_rank and 2·cp−1−cp_rank: RoPE needs explicit positions
+                positions = zigzag.local_positions(S, self.ctx.cp_size, self.ctx.cp_rank, h.device).repeat(B)
         layers = self.decoder_layers if layers is None else layers
         for layer in layers:
             if gradient_checkpointing and torch.is_grad_enabled():
-                h, delta = torch_checkpoint(layer, h, delta, B, S, self.cos, self.sin, pos_offset, use_reentrant=False)
+                h, delta = torch_checkpoint(layer, h, delta, B, S, self.cos, self.sin, pos_offset, positions,
+                                            use_reentrant=False)
             else:
-                h, delta = layer(h, delta, B, S, self.cos, self.sin, pos_offset)
+                h, delta = layer(h, delta, B, S, self.cos, self.sin, pos_offset, positions)
         return h, delta
 
     def finalize(self, h, delta):

@@ -184,18 +184,18 @@ class _QKVAttention(torch.autograd.Function):
 
 
 def qkv_attention(qkv, wq, wk, cos, sin, B, S, n_q, n_kv, head_dim, pos_offset=0, eps=1e-6, causal=True,
-                  scale=None, attn_fn=None):
+                  scale=None, attn_fn=None, positions=None):
     """``qkv [B*S, (Hq+2Hkv)*D]`` → attention output ``[B, S, Hq*D]``.
 
     ``attn_fn(q, k, v, causal, scale) -> out`` overrides the local attention (ring attention under
     context parallelism); in that case the norm/RoPE and attention run as separate autograd nodes.
     """
     scale = scale if scale is not None else 1.0 / math.sqrt(head_dim)
-    if (attn_fn is None and N.use_native(qkv) and qkv.dtype == torch.bfloat16 and head_dim == 128
+    if (attn_fn is None and positions is None and N.use_native(qkv) and qkv.dtype == torch.bfloat16 and head_dim == 128
             and native_attention_available()):
         return _QKVAttention.apply(qkv, wq, wk, cos, sin, B, S, n_q, n_kv, head_dim, pos_offset, eps, causal, scale)
     nqk = n_q + n_kv
-    qk = _norm.qknorm_rope(qkv, wq, wk, cos, sin, n_q, n_kv, head_dim, S, pos_offset, eps)
+    qk = _norm.qknorm_rope(qkv, wq, wk, cos, sin, n_q, n_kv, head_dim, S, pos_offset, eps, positions)
     qk4 = qk.view(B, S, nqk, head_dim)
     q, k = qk4[:, :, :n_q], qk4[:, :, n_q:]
     v = qkv.view(B, S, n_q + 2 * n_kv, head_dim)[:, :, nqk:]

@@ -46,9 +46,23 @@ def update_output_and_lse(out, lse, block_out, block_lse):
     return out * w_old + block_out.float() * w_new, new_lse
 
 
+def update_rows(out, lse, block_out, block_lse, q_lo: int):
+    """:func:`update_output_and_lse` restricted to query rows ``[q_lo:]`` (zig-zag partial blocks)."""
+    if q_lo == 0:
+        return update_output_and_lse(out, lse, block_out, block_lse)
+    o2, l2 = update_output_and_lse(out[:, q_lo:], lse[:, :, q_lo:], block_out, block_lse)
+    out[:, q_lo:] = o2
+    lse[:, :, q_lo:] = l2
+    return out, lse
+
+
 class RingAttentionFunc(torch.autograd.Function):
     @staticmethod
     def forward(ctx, q, k, v, sm_scale, is_causal, group, send_rank, recv_rank, cp_rank, cp_size):
+        from . import zigzag
+
+        zz = zigzag.enabled() and is_causal
+        S = q.shape[1]
         comm = ContextCommunicator("kv", group, send_rank, recv_rank)
         k_cur, v_cur = k.contiguous(), v.contiguous()
         out, lse = None, None
@@ -57,21 +71,26 @@ class RingAttentionFunc(torch.autograd.Function):
                 k_next = comm.send_recv(k_cur)
                 v_next = comm.send_recv(v_cur)
                 comm.commit()
-            if not is_causal or step <= cp_rank:
-                b_out, b_lse = ops.attention.attention_block_fwd(q, k_cur, v_cur, is_causal and step == 0, sm_scale)
-                out, lse = update_output_and_lse(out, lse, b_out, b_lse)
+            plan = zigzag.block_plan(step, cp_rank, cp_size, S, is_causal, zz)
+            if plan is not None:
+                q_lo, k_hi, cf = plan
+                b_out, b_lse = ops.attention.attention_block_fwd(q[:, q_lo:], k_cur[:, :k_hi], v_cur[:, :k_hi], cf, sm_scale)
+                out, lse = update_rows(out, lse, b_out, b_lse, q_lo)
             if step + 1 != cp_size:
                 comm.wait()
                 k_cur, v_cur = k_next, v_next
         out = out.to(q.dtype)
         ctx.save_for_backward(q, k, v, out, lse)
-        ctx.cfg = (sm_scale, is_causal, group, send_rank, recv_rank, cp_rank, cp_size)
+        ctx.cfg = (sm_scale, is_causal, group, send_rank, recv_rank, cp_rank, cp_size, zz)
         return out
 
     @staticmethod
     def backward(ctx, dout):
         q, k, v, out, lse = ctx.saved_tensors
-        sm_scale, is_causal, group, send_rank, recv_rank, cp_rank, cp_size = ctx.cfg
+        from . import zigzag
+
+        sm_scale, is_causal, group, send_rank, recv_rank, cp_rank, cp_size, zz = ctx.cfg
+        S = q.shape[1]
         kv_comm = ContextCommunicator("kv-bwd", group, send_rank, recv_rank)
         d_comm = ContextCommunicator("dkv", group, send_rank, recv_rank)
         dout = dout.contiguous()
@@ -83,11 +102,22 @@ class RingAttentionFunc(torch.autograd.Function):
                 k_next = kv_comm.send_recv(k_cur)
                 v_next = kv_comm.send_recv(v_cur)
                 kv_comm.commit()
-            if not is_causal or step <= cp_rank:
-                b_dq, b_dk, b_dv = ops.attention.attention_block_bwd(dout, q, k_cur, v_cur, out, lse,
-                                                                     is_causal and step == 0, sm_scale)
-                dq += b_dq.float()
-                b_dk, b_dv = b_dk.float(), b_dv.float()
+            plan = zigzag.block_plan(step, cp_rank, cp_size, S, is_causal, zz)
+            if plan is not None:
+                q_lo, k_hi, cf = plan
+                if q_lo == 0 and k_hi == S:
+                    b_dq, b_dk, b_dv = ops.attention.attention_block_bwd(dout, q, k_cur, v_cur, out, lse, cf, sm_scale)
+                    dq += b_dq.float()
+                    b_dk, b_dv = b_dk.float(), b_dv.float()
+                else:
+                    p_dq, p_dk, p_dv = ops.attention.attention_block_bwd(
+                        dout[:, q_lo:].contiguous(), q[:, q_lo:], k_cur[:, :k_hi], v_cur[:, :k_hi],
+                        out[:, q_lo:].contiguous(), lse[:, :, q_lo:].contiguous(), cf, sm_scale)
+                    dq[:, q_lo:] += p_dq.float()
+                    b_dk = torch.zeros_like(k_cur, dtype=torch.float32)
+                    b_dv = torch.zeros_like(v_cur, dtype=torch.float32)
+                    b_dk[:, :k_hi] = p_dk.float()
+                    b_dv[:, :k_hi] = p_dv.float()
             else:
                 b_dk = torch.zeros_like(k_cur, dtype=torch.float32)
                 b_dv = torch.zeros_like(v_cur, dtype=torch.float32)

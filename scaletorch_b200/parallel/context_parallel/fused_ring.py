@@ -21,7 +21,8 @@ import torch.distributed as dist
 from ... import ops
 from ...runtime import fused_ops as F
 from ...runtime import symm
-from .context_parallel import update_output_and_lse
+from . import zigzag
+from .context_parallel import update_output_and_lse, update_rows
 
 SLOT_CP = 5
 _pull_streams: dict[int, torch.cuda.Stream] = {}
@@ -81,26 +82,30 @@ class FusedRingAttention(torch.autograd.Function):
         kw.copy_(k)
         vw.copy_(v)
         g.barrier(SLOT_CP)                      # every rank's K/V block is published
-        # blocks in the future of every local query are skipped under a causal mask
-        steps = {s_: (r - s_) % cp for s_ in range(1, cp) if not (is_causal and s_ > r)}
+        # contiguous split: blocks in the future of every local query are skipped under a causal mask; zig-zag split:
+        # every peer block contributes half a block (zigzag.block_plan)
+        zz = zigzag.enabled() and is_causal
+        plans = {s_: zigzag.block_plan(s_, r, cp, S, is_causal, zz) for s_ in range(1, cp)}
+        steps = {s_: (r - s_) % cp for s_ in range(1, cp) if plans[s_] is not None}
         staged = _stage_peer_blocks(g, steps, (B, S, Hkv, D), n)
         out, lse = ops.attention.attention_block_fwd(q, k, v, is_causal, sm_scale)
         out, lse = update_output_and_lse(None, None, out, lse)
         for step in steps:
             kb, vb, ev = staged[step]
             torch.cuda.current_stream().wait_event(ev)
-            b_out, b_lse = ops.attention.attention_block_fwd(q, kb, vb, False, sm_scale)
-            out, lse = update_output_and_lse(out, lse, b_out, b_lse)
+            q_lo, k_hi, cf = plans[step]
+            b_out, b_lse = ops.attention.attention_block_fwd(q[:, q_lo:], kb[:, :k_hi], vb[:, :k_hi], cf, sm_scale)
+            out, lse = update_rows(out, lse, b_out, b_lse, q_lo)
         g.barrier(SLOT_CP)                      # every pull has completed: windows may be overwritten
         out = out.to(q.dtype)
         ctx.save_for_backward(q, k, v, out, lse)
-        ctx.cfg = (sm_scale, is_causal, group)
+        ctx.cfg = (sm_scale, is_causal, group, zz)
         return out
 
     @staticmethod
     def backward(ctx, dout):
         q, k, v, out, lse = ctx.saved_tensors
-        sm_scale, is_causal, group = ctx.cfg
+        sm_scale, is_causal, group, zz = ctx.cfg
         g = F.get_group(group)
         r, cp = g.rank, g.world
         B, S, Hkv, D = k.shape
@@ -120,25 +125,39 @@ class FusedRingAttention(torch.autograd.Function):
             return dk, dv
 
         g.barrier(SLOT_CP)
-        steps = {s_: (r - s_) % cp for s_ in range(1, cp) if not (is_causal and s_ > r)}
+        plans = {s_: zigzag.block_plan(s_, r, cp, S, is_causal, zz) for s_ in range(1, cp)}
+        steps = {s_: (r - s_) % cp for s_ in range(1, cp) if plans[s_] is not None}
         staged = _stage_peer_blocks(g, steps, (B, S, Hkv, D), n)
         dq = torch.zeros(q.shape, dtype=torch.float32, device=q.device)
         for step in [0] + list(steps):
             src = (r - step) % cp
             if step == 0:
                 kb, vb = k, v
+                q_lo, k_hi, cf = 0, S, is_causal
             else:
                 kb, vb, ev = staged[step]
                 torch.cuda.current_stream().wait_event(ev)
+                q_lo, k_hi, cf = plans[step]
             dkj, dvj = slot(src)
-            dqj = torch.empty_like(q)
-            ops.attention._flash_bwd(dout, q, kb, vb, out, lse, dqj, dkj, dvj, is_causal and step == 0, sm_scale)
-            dq += dqj.float()
+            if q_lo == 0 and k_hi == S:
+                dqj = torch.empty_like(q)
+                ops.attention._flash_bwd(dout, q, kb, vb, out, lse, dqj, dkj, dvj, cf, sm_scale)
+                dq += dqj.float()
+            else:                       # zig-zag half block: queries [q_lo:] x keys [:k_hi]
+                qs = q[:, q_lo:]
+                dqj = torch.empty_like(qs)
+                if k_hi < S:            # the untouched half of the contribution slot must read as zero
+                    dkj[:, k_hi:].zero_()
+                    dvj[:, k_hi:].zero_()
+                ops.attention._flash_bwd(dout[:, q_lo:].contiguous(), qs, kb[:, :k_hi], vb[:, :k_hi],
+                                         out[:, q_lo:].contiguous(), lse[:, :, q_lo:].contiguous(), dqj,
+                                         dkj[:, :k_hi], dvj[:, :k_hi], cf, sm_scale)
+                dq[:, q_lo:] += dqj.float()
         g.barrier(SLOT_CP)                      # all contributions are written
         # block r was used by ranks r, r+1, ..., cp-1 (causal) or by everyone
         dk = torch.zeros(k.shape, dtype=torch.float32, device=k.device)
         dv = torch.zeros(v.shape, dtype=torch.float32, device=v.device)
-        users = range(r, cp) if is_causal else range(cp)
+        users = range(cp) if (zz or not is_causal) else range(r, cp)
         for u in users:
             off = base + r * slot_bytes
             if u == r:

@@ -107,14 +107,20 @@ class PipelineParallel(nn.Module):
             B, S = hidden_states.shape[0], hidden_states.shape[1] * sp_f
             h = hidden_states.reshape(-1, self.hidden_size)
         pos_offset = self.ctx.cp_rank * S if self.ctx.cp_size > 1 else 0
+        positions = None
+        if self.ctx.cp_size > 1:
+            from ..context_parallel import zigzag
+
+            if zigzag.enabled():
+                positions = zigzag.local_positions(S, self.ctx.cp_size, self.ctx.cp_rank, h.device).repeat(B)
         delta = None
         for layer in self.decoder_layers:
             if gradient_checkpointing and torch.is_grad_enabled():
                 from torch.utils.checkpoint import checkpoint
 
-                h, delta = checkpoint(layer, h, delta, B, S, self.cos, self.sin, pos_offset, use_reentrant=False)
+                h, delta = checkpoint(layer, h, delta, B, S, self.cos, self.sin, pos_offset, positions, use_reentrant=False)
             else:
-                h, delta = layer(h, delta, B, S, self.cos, self.sin, pos_offset)
+                h, delta = layer(h, delta, B, S, self.cos, self.sin, pos_offset, positions)
         if self.is_last:
             from ... import ops
 

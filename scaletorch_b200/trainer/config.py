@@ -57,6 +57,7 @@ class ParallelArguments:
     pipeline_parallel_engine: str = field(default="1f1b", metadata={"help": "Pipeline schedule: 1f1b | afab"})
     backend: str = field(default="nccl", metadata={"help": "Distributed backend: nccl | gloo"})
     sequence_parallel: bool = field(default=False, metadata={"help": "Megatron sequence parallelism over the TP group (also enabled by env SEQUENCE_PARALLEL=1)"})
+    cp_zigzag: bool = field(default=True, metadata={"help": "Load-balanced (zig-zag) causal context parallelism: rank r owns chunks r and 2cp-1-r (needs S % 2cp == 0; falls back to the contiguous split otherwise)"})
     ep_replicate_data: bool = field(default=False, metadata={"help": "Reference semantics: every EP rank of a dp_rank reads the same samples"})
     fused_comm: bool = field(default=True, metadata={"help": "Use the fused compute+collective kernels over NVLink peer memory when available"})
     grad_wire_dtype: str = field(default="float32", metadata={"help": "dtype of DP gradient buckets on the wire: float32 | bfloat16"})

@@ -40,6 +40,12 @@ def initialize_distributed_training(config) -> tuple[int, int, int, torch.device
     device = get_current_device(use_cpu)
     if not use_cpu:
         set_device(device)
+    # zig-zag context parallelism is a job-wide switch read by the loader, the RoPE positions and the ring attention
+    from ..parallel.context_parallel import zigzag
+
+    cp = getattr(config, "context_parallel_size", 1)
+    seq = getattr(config, "sequence_length", None) or 0
+    zigzag.set_enabled(bool(getattr(config, "cp_zigzag", False)) and cp > 1 and seq % (2 * cp) == 0)
     if world_size == 1:
         return local_rank, global_rank, world_size, device
     backend = "gloo" if use_cpu else getattr(config, "backend", "nccl")

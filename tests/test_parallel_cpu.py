@@ -72,12 +72,15 @@ def test_tensor_parallel_matches_single_process(model_name, sp):
 
 
 # ------------------------------------------------------------------ CP (ring attention)
-def _cp_worker(rank, world, causal_model):
+def _cp_worker(rank, world, causal_model, zz=False):
     from scaletorch_b200.parallel.context import ParallelContext
     from scaletorch_b200.parallel.process_group import process_group_manager as pgm
     from scaletorch_b200.parallel.process_group import setup_process_group_manager
     import torch.distributed as dist
 
+    from scaletorch_b200.parallel.context_parallel import zigzag
+
+    zigzag.set_enabled(zz)
     setup_process_group_manager(tp_size=1, cp_size=world, pp_size=1, dp_size=1)
     cfg = TinyCfg(model_type=causal_model)
     ctx = ParallelContext.from_pgm()
@@ -90,7 +93,11 @@ def _cp_worker(rank, world, causal_model):
     lf = full.loss(x, y)
     lf.backward()
     n = S // world
-    lp = par.loss(x[:, rank * n:(rank + 1) * n].contiguous(), y[:, rank * n:(rank + 1) * n].contiguous())
+    if zz:   # rank r owns chunks r and 2·cp−1−r: every rank does one causal block + (cp − 1) half blocks
+        xs, ys = zigzag.take(x, S, world, rank).contiguous(), zigzag.take(y, S, world, rank).contiguous()
+    else:
+        xs, ys = x[:, rank * n:(rank + 1) * n].contiguous(), y[:, rank * n:(rank + 1) * n].contiguous()
+    lp = par.loss(xs, ys)
     lp.backward()
     tot = lp.detach().clone()
     dist.all_reduce(tot, group=pgm.cp_group)
@@ -105,6 +112,31 @@ def _cp_worker(rank, world, causal_model):
 @pytest.mark.parametrize("world", [2, 4])
 def test_context_parallel_ring_attention_matches_single_process(world):
     run_distributed(_cp_worker, world, "qwen3")
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_context_parallel_zigzag_matches_single_process(world):
+    run_distributed(_cp_worker, world, "qwen3", True)
+
+
+def test_zigzag_loader_slices_and_positions():
+    from scaletorch_b200.parallel.context_parallel import zigzag
+
+    S, cp = 32, 4
+    seen = []
+    for r in range(cp):
+        (a0, a1), (b0, b1) = zigzag.chunk_ranges(S, cp, r)
+        pos = zigzag.local_positions(S // cp, cp, r)
+        assert pos.tolist() == list(range(a0, a1)) + list(range(b0, b1))
+        seen += pos.tolist()
+        x = torch.arange(S + 1)[None]
+        assert zigzag.take(x, S, cp, r).tolist()[0] == pos.tolist()
+        assert zigzag.take(x, S, cp, r, shift=1).tolist()[0] == [p + 1 for p in pos.tolist()]
+    assert sorted(seen) == list(range(S))
+    # work per rank in units of half blocks: 2 for the diagonal + 1 per peer = balanced
+    work = [sum((1 if zigzag.block_plan(s, r, cp, 8, True, True)[1] - zigzag.block_plan(s, r, cp, 8, True, True)[0] == 4 else 2)
+                for s in range(cp)) for r in range(cp)]
+    assert len(set(work)) == 1
 
 
 # ------------------------------------------------------------------ DP (bucketed, overlapped) incl. grad accumulation

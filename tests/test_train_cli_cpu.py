@@ -40,7 +40,8 @@ def test_single_process_trains(tmp_path):
 
 @pytest.mark.parametrize("layout", [["--tensor_parallel_size", "2", "--sequence_parallel", "true"],
                                     ["--data_parallel_size", "2", "--gradient_accumulation_steps", "2"],
-                                    ["--pipeline_parallel_size", "2", "--gradient_accumulation_steps", "2"]])
+                                    ["--pipeline_parallel_size", "2", "--gradient_accumulation_steps", "2"],
+                                    ["--context_parallel_size", "2"]])
 def test_two_process_layouts(tmp_path, layout):
     out = _run(["--model_name_or_path", "tiny-qwen3", "--num_attention_heads", "4", "--num_key_value_heads", "2",
                 "--total_train_steps", "4", "--work_dir", str(tmp_path)] + layout, nproc=2)

@@ -186,7 +186,7 @@ def run_ours(args):
     from scaletorch_b200.trainer import GraphedTrainStep
 
     graphed = None
-    if args.cuda_graph and GraphedTrainStep.supported(cfg, optimizer):
+    if args.cuda_graph and GraphedTrainStep.supported(cfg, optimizer, model):
         graphed = GraphedTrainStep(model, optimizer, cfg, device, warmup=2)
     launches_per_graph = [0]
 
@@ -208,7 +208,7 @@ def run_ours(args):
     staged = DeviceBatches((args.steps + args.warmup) * args.grad_accum)
     for _ in range(args.warmup):
         step_with(staged)
-    while graphed is not None and graphed.graph is None:      # the capture itself never falls into the timed region
+    while graphed is not None and graphed.graph is None and not graphed.failed:   # the capture never falls into the timed region
         step_with(staged)
     sampler = ClockSampler(local_rank)
     if rank == 0:

@@ -10,8 +10,8 @@ zero-grad → GA × (forward, backward, bucket all-reduce) → clip → AdamW se
 
 The reference has no counterpart (eager PyTorch; ``tools/optimize_mfu.py`` tries ``torch.compile``).
 
-Not captured: pipeline-parallel schedules (NCCL p2p with data-dependent ordering across micro-batches) and the c10d
-fallback collectives; ``GraphedTrainStep.supported`` says whether a configuration qualifies.
+Not captured: pipeline-parallel schedules (NCCL p2p with data-dependent ordering across micro-batches), the c10d
+fallback collectives, and MoE models (capture of the routing ops invalidated the stream in the one attempt made); ``GraphedTrainStep.supported`` says whether a configuration qualifies.
 """
 from __future__ import annotations
 
@@ -48,14 +48,24 @@ class GraphedTrainStep:
         self.static_loss: torch.Tensor | None = None
         self._buffers: list[dict] | None = None
         self._steps_seen = 0
+        self.failed = False
         self.ga = config.gradient_accumulation_steps
 
     @staticmethod
-    def supported(config, optimizer) -> bool:
+    def supported(config, optimizer, model=None) -> bool:
         from .optimizer import FusedAdamW
 
         if not torch.cuda.is_available() or not isinstance(optimizer, FusedAdamW):
             return False
+        if pgm and pgm.ep_world_size > 1:
+            return False
+        if model is not None:
+            # MoE routing uses library sort / scatter ops whose capture invalidated the stream on this stack
+            # (cudaErrorStreamCaptureInvalidated, 2-GPU EP2 run): MoE models stay on the eager path for now
+            from ..models.model_qwen3_moe import MoELayer
+
+            if any(isinstance(m, MoELayer) for m in model.modules()):
+                return False
         if pgm and pgm.pp_world_size > 1:
             return False
         if pgm and pgm.world_size > 1 and not getattr(config, "fused_comm", True):
@@ -92,13 +102,24 @@ class GraphedTrainStep:
                 return self._eager(src)
             # capture; the captured work also *runs* once?  No: capture only records, so run the step for this batch by
             # replaying right after the capture.
+            if self.failed:
+                return self._eager(src)
             torch.cuda.synchronize()
             torch.cuda.empty_cache()          # the eager warm-up pool is not needed again: the graph owns its memory
-            self.graph = torch.cuda.CUDAGraph()
-            # thread_local: the loader's prefetch thread may pin memory while we capture; kernels launched into the
-            # capturing stream by the autograd thread are captured in either mode
-            with torch.cuda.graph(self.graph, capture_error_mode="thread_local"):
-                self.static_loss = self._eager(src)
+            graph = torch.cuda.CUDAGraph()
+            try:
+                # thread_local: the loader's prefetch thread may pin memory while we capture; kernels launched into the
+                # capturing stream by the autograd thread are captured in either mode
+                with torch.cuda.graph(graph, capture_error_mode="thread_local"):
+                    self.static_loss = self._eager(src)
+                self.graph = graph
+            except Exception as e:  # an op in this configuration cannot be captured: stay eager, loudly
+                import warnings
+
+                warnings.warn(f"CUDA-graph capture of the training step failed ({type(e).__name__}: {e}); running eagerly")
+                self.failed = True
+                torch.cuda.synchronize()
+                return self._eager(_StaticBatches(self._buffers, self.ga))
         self.optimizer.prepare_step()
         self.graph.replay()
         return self.static_loss

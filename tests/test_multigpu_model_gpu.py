@@ -66,7 +66,10 @@ def _worker(rank, world, port, mode, fused):
                     continue      # partial over heads / tokens: summed across TP by the trainer
                 ref = shard_tensor(n, fg[n], cfg, world, rank, 1, 0)
                 assert _rel(p.grad, ref) < 6e-2, (n, _rel(p.grad, ref))
-        elif mode == "cp":
+        elif mode in ("cp", "cp_zz"):
+            from scaletorch_b200.parallel.context_parallel import zigzag
+
+            zigzag.set_enabled(mode == "cp_zz")
             setup_process_group_manager(tp_size=1, cp_size=world, pp_size=1, dp_size=1)
             par = Qwen3(cfg, ParallelContext.from_pgm(fused_comm=fused)).to(torch.bfloat16).to(dev)
             par.load_state_dict(full.state_dict())
@@ -79,7 +82,11 @@ def _worker(rank, world, port, mode, fused):
             n = S2 // world
             for _ in range(2):
                 par.zero_grad()
-                lp = par.loss(x2[:, rank * n:(rank + 1) * n].contiguous(), y2[:, rank * n:(rank + 1) * n].contiguous())
+                if mode == "cp_zz":
+                    xs, ys = zigzag.take(x2, S2, world, rank).contiguous(), zigzag.take(y2, S2, world, rank).contiguous()
+                else:
+                    xs, ys = x2[:, rank * n:(rank + 1) * n].contiguous(), y2[:, rank * n:(rank + 1) * n].contiguous()
+                lp = par.loss(xs, ys)
                 lp.backward()
                 tot = lp.detach().float().clone()
                 dist.all_reduce(tot)
@@ -112,7 +119,7 @@ def _worker(rank, world, port, mode, fused):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("mode,fused", [("tp", False), ("tp", True), ("tp_sp", False), ("tp_sp", True), ("dp", False), ("dp", True), ("dp_tied", True), ("cp", False), ("cp", True)])
+@pytest.mark.parametrize("mode,fused", [("tp", False), ("tp", True), ("tp_sp", False), ("tp_sp", True), ("dp", False), ("dp", True), ("dp_tied", True), ("cp", False), ("cp", True), ("cp_zz", False), ("cp_zz", True)])
 def test_two_gpu_model_equality(mode, fused):
     if torch.cuda.device_count() < 2:
         pytest.skip("needs at least 2 GPUs")

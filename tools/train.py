@@ -117,7 +117,7 @@ def main(argv=None) -> None:
         prof = ProfilerWindow(config.profile_start_step, config.profile_end_step, config.trace_dir, global_rank)
         watchdog = StepWatchdog(config.step_timeout_s, config.work_dir or ".", global_rank).start()
         graphed = None
-        if config.use_cuda_graph and GraphedTrainStep.supported(config, optimizer):
+        if config.use_cuda_graph and GraphedTrainStep.supported(config, optimizer, model):
             graphed = GraphedTrainStep(model, optimizer, config, device)
             rank_print("whole-step CUDA graph replay enabled", is_print_rank=log_rank)
         monitor.start()

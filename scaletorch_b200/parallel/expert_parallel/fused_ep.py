@@ -82,6 +82,35 @@ def reset() -> None:
     _windows.clear()
 
 
+def ep_plan(table: torch.Tensor, flat: torch.Tensor, counts: torch.Tensor, rank: int, e_local: int, rows_cap: int):
+    """Destination of every ``(token, k)`` pair of rank ``rank`` -- pure tensor math, no communication.
+
+    ``table [ep, E]``: pairs every source rank sends to every global expert (identical on all ranks after the count
+    exchange); ``flat [P]``: this rank's expert ids in pair order; ``counts [E]`` = ``table[rank]``.  The receive region
+    of every rank is expert-major with each expert's segment padded to 128 rows, and inside a segment the rows are
+    ordered by source rank, then by the sender's stable order.  Returns ``(row [P] int32 (−1 = over capacity),
+    dest_rank [P] int32, dropped (scalar), offs_pad [e_local + 1] of *this* rank's experts (clamped to the capacity),
+    tokens_per_expert [e_local] of this rank's experts)``.
+    """
+    ep = table.shape[0]
+    P = flat.numel()
+    tot = table.sum(0)
+    pad = ((tot + 127) // 128 * 128).view(ep, e_local)
+    offs_pad_all = (torch.cumsum(pad, 1) - pad).reshape(-1)                  # start of every expert on its owner
+    prefix = (torch.cumsum(table, 0) - table)[rank]                          # rows of lower source ranks
+    offs_local = torch.cumsum(counts, 0) - counts
+    sort_idx = torch.argsort(flat, stable=True)
+    inv = torch.empty_like(sort_idx)
+    inv[sort_idx] = torch.arange(P, device=flat.device)
+    pos = offs_pad_all[flat] + prefix[flat] + inv - offs_local[flat]
+    over = pos >= rows_cap
+    row = torch.where(over, torch.full_like(pos, -1), pos).to(torch.int32).contiguous()
+    dest = torch.div(flat, e_local, rounding_mode="floor").to(torch.int32).contiguous()
+    zero = torch.zeros(1, dtype=torch.int64, device=flat.device)
+    offs_pad = torch.cat([zero, torch.cumsum(pad[rank], 0)]).clamp_(max=rows_cap)
+    return row, dest, over.sum(), offs_pad, tot.view(ep, e_local)[rank]
+
+
 class FusedEPState:
     """Routing plan of one MoE layer call (all tensors on the device)."""
 
@@ -96,27 +125,10 @@ class FusedEPState:
         table = torch.empty((ep, num_experts), dtype=torch.int32, device=idx.device)
         N.call("stb_ep_exchange_counts", win.bufs_dev, g.flag_pages_dev, win.off_table, counts.data_ptr(), num_experts,
                table.data_ptr(), rank, ep, SLOT_EP, g.take_epochs(SLOT_EP, 1), N.stream_ptr())
-        table = table.to(torch.int64)
-        tot = table.sum(0)
-        pad = ((tot + 127) // 128 * 128).view(ep, e_local)
-        offs_pad_all = (torch.cumsum(pad, 1) - pad).reshape(-1)                  # start of every expert on its owner
-        prefix = (torch.cumsum(table, 0) - table)[rank]                          # rows of lower source ranks
-        counts64 = counts.to(torch.int64)
-        offs_local = torch.cumsum(counts64, 0) - counts64
-        sort_idx = torch.argsort(flat, stable=True)
-        inv = torch.empty_like(sort_idx)
-        inv[sort_idx] = torch.arange(P, device=idx.device)
-        pos = offs_pad_all[flat] + prefix[flat] + inv - offs_local[flat]
-        over = pos >= win.rows_cap
-        self.dropped = over.sum()
-        self.row = torch.where(over, torch.full_like(pos, -1), pos).to(torch.int32).contiguous()
-        self.rank_of = torch.div(flat, e_local, rounding_mode="floor").to(torch.int32).contiguous()
+        plan = ep_plan(table.to(torch.int64), flat, counts.to(torch.int64), rank, e_local, win.rows_cap)
+        self.row, self.rank_of, self.dropped, offs_pad, self.tokens_per_expert = plan
         self.win, self.T, self.k, self.P = win, T, k, P
-        # receiver-side layout of my own experts
-        zero = torch.zeros(1, dtype=torch.int64, device=idx.device)
-        offs_pad = torch.cat([zero, torch.cumsum(pad[rank], 0)]).clamp_(max=win.rows_cap)
-        self.layout = GroupedLayout.from_padded_offsets(offs_pad, win.rows_cap, e_local)
-        self.tokens_per_expert = tot.view(ep, e_local)[rank]
+        self.layout = GroupedLayout.from_padded_offsets(offs_pad, win.rows_cap, e_local)   # my own experts' rows
 
     # -- raw kernels ---------------------------------------------------------------------------------------
     def push(self, src: torch.Tensor, scale: torch.Tensor | None) -> None:

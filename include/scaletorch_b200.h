@@ -198,6 +198,22 @@ int stb_ep_pull(const void* bufs_dev, const void* flag_pages_dev, long region_of
                 const int* src_rank, const int* src_row, const float* weights, long T, int k, int H, int rank,
                 int world, int slot, unsigned epoch, int sm_budget, cudaStream_t stream);    /* 2 epochs */
 
+/* ---- host runtime: native micro-batch producer, csrc/runtime/token_loader.cpp -----------------------------------
+ * Worker threads cut (input, target) windows out of a flat int32 token array, apply the context-parallel slice
+ * (contiguous or zig-zag) and fill a caller-owned ring of n_slots int64 [2][mbs][S / cp] host buffers (pin them).
+ * Sampling: sample w = tokens[w (S+1) : (w+1)(S+1)], per-epoch Fisher-Yates permutation from splitmix64(seed + epoch),
+ * data rank r takes perm[r], perm[r + world], ...  One consumer thread: next() blocks for the next batch in order and
+ * returns its slot, release() hands the slot back once its H2D copy has completed.
+ * Reference: torch DataLoader + DistributedSampler + Python collate, scaletorch/data/dataloader.py:107-292. */
+void* stb_loader_create(const int* tokens, long n_tokens, int seq_len, int mbs, int cp_rank, int cp_size, int zigzag,
+                        int data_rank, int data_world, int shuffle, unsigned long long seed, int n_slots,
+                        long long* ring, int n_threads);
+long stb_loader_batches_per_epoch(void* handle);
+long stb_loader_num_samples(void* handle);
+int stb_loader_next(void* handle, long* batch_out);
+int stb_loader_release(void* handle, int slot);
+void stb_loader_destroy(void* handle);
+
 #ifdef __cplusplus
 }
 #endif

@@ -49,6 +49,7 @@ _SIGS = {
     "stb_embedding_fwd": [_P, _P, _P, c_long, c_int, c_int, c_int, _P],
     "stb_embedding_bwd": [_P, _P, _P, c_long, c_int, c_int, c_int, _P],
 }
+_RESTYPES: dict = {}     # non-int return types of entry points registered by optional modules
 _LONG_RET = {
     "stb_rmsnorm_bwd_scratch_elems": [c_int, c_int],
     "stb_sumsq_scratch_bytes": [],
@@ -66,7 +67,7 @@ def _bind(lib: ctypes.CDLL) -> None:
     for name, sig in _SIGS.items():
         if hasattr(lib, name):
             fn = getattr(lib, name)
-            fn.restype = c_int
+            fn.restype = _RESTYPES.get(name, c_int)
             fn.argtypes = sig
     for name, sig in _LONG_RET.items():
         if hasattr(lib, name):
@@ -78,6 +79,7 @@ def _bind(lib: ctypes.CDLL) -> None:
 def register(name: str, argtypes: list, restype=c_int) -> None:
     """Registers the signature of an additional entry point (used by optional modules)."""
     _SIGS[name] = argtypes
+    _RESTYPES[name] = restype
     if _lib is not None and hasattr(_lib, name):
         fn = getattr(_lib, name)
         fn.restype = restype

@@ -49,6 +49,18 @@ def test_two_process_layouts(tmp_path, layout):
     assert len(ls) == 4 and all(0.0 < l < 12.0 for _, l in ls), out[-2000:]
 
 
+def test_native_loader_cli(tmp_path):
+    from scaletorch_b200.data import native_loader_available
+
+    if not native_loader_available():
+        pytest.skip("native library not built")
+    out = _run(["--model_name_or_path", "tiny-llama", "--total_train_steps", "4", "--work_dir", str(tmp_path),
+                "--native_loader", "true", "--num_samples", "64", "--data_parallel_size", "2",
+                "--gradient_accumulation_steps", "2"], nproc=2)
+    ls = _losses(out)
+    assert len(ls) == 4 and all(0.0 < l < 12.0 for _, l in ls), out[-2000:]
+
+
 def test_checkpoint_resume(tmp_path):
     common = ["--model_name_or_path", "tiny-llama", "--work_dir", str(tmp_path), "--save_model_checkpoint", "true",
               "--save_frequency", "3", "--log_lag", "0"]

@@ -50,7 +50,35 @@ except Exception:  # pragma: no cover
     wandb = None
 
 
+def build_native_loader(config, model_config):
+    """C++ micro-batch producer over a flat token array: a ``--token_file`` (int32 ``.npy`` or raw ``.bin``) or, with
+    ``--synthetic_data``, random ids.  Same batch dict and ``global_batch_size`` attribute as ``MicroBatchDataLoader``."""
+    import numpy as np
+
+    from scaletorch_b200.data import NativeTokenLoader
+    from scaletorch_b200.parallel.context_parallel import zigzag
+
+    S = config.sequence_length
+    if config.token_file:
+        arr = np.load(config.token_file) if config.token_file.endswith(".npy") else np.fromfile(config.token_file, dtype=np.int32)
+        tokens = torch.from_numpy(np.ascontiguousarray(arr, dtype=np.int32))
+    else:
+        g = torch.Generator().manual_seed(config.seed)
+        n = (config.num_samples or 4096) * (S + 1)
+        tokens = torch.randint(0, model_config.vocab_size, (n,), generator=g, dtype=torch.int32)
+    data_world = pgm.data_world_size if pgm else 1
+    loader = NativeTokenLoader(
+        tokens, S, config.micro_batch_size, cp_rank=pgm.cp_rank if pgm else 0, cp_size=pgm.cp_world_size if pgm else 1,
+        zigzag=zigzag.enabled(), data_rank=pgm.data_rank if pgm else 0, data_world=data_world, shuffle=True,
+        seed=config.seed, gradient_accumulation_steps=config.gradient_accumulation_steps)
+    loader.global_batch_size = config.micro_batch_size * config.gradient_accumulation_steps * data_world
+    loader.state_dict = lambda: {"batches_served": loader.batches_served}
+    return loader
+
+
 def build_data_loader(config, model_config, device):
+    if getattr(config, "native_loader", False):
+        return build_native_loader(config, model_config)
     return MicroBatchDataLoader(
         micro_batch_size=config.micro_batch_size, sequence_length=config.sequence_length,
         dataset_name=config.dataset_name, tokenizer_name_or_path=config.tokenizer_name_or_path

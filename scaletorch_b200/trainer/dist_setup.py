@@ -45,7 +45,11 @@ def initialize_distributed_training(config) -> tuple[int, int, int, torch.device
 
     cp = getattr(config, "context_parallel_size", 1)
     seq = getattr(config, "sequence_length", None) or 0
-    zigzag.set_enabled(bool(getattr(config, "cp_zigzag", False)) and cp > 1 and seq % (2 * cp) == 0)
+    want_zz = bool(getattr(config, "cp_zigzag", False)) and cp > 1
+    zigzag.set_enabled(want_zz and seq % (2 * cp) == 0)
+    if want_zz and not zigzag.enabled() and int(os.environ.get("RANK", 0)) == 0:
+        print(f"[scaletorch_b200] sequence_length {seq} is not divisible by 2*cp ({2 * cp}): contiguous context-parallel "
+              f"split instead of zig-zag", flush=True)
     if world_size == 1:
         return local_rank, global_rank, world_size, device
     backend = "gloo" if use_cpu else getattr(config, "backend", "nccl")

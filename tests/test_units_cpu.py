@@ -146,3 +146,39 @@ def test_bench_config_dict_names_the_layout():
     args.ep, args.tp, args.cp = 8, 1, 1
     dp, cfg = bench.build_config_dict(args, 8)
     assert dp == 1 and cfg["parallelism"] == "ep8dp1" and cfg["global_batch"] == 8     # EP ranks read distinct data
+
+
+def test_graphed_step_support_matrix(monkeypatch):
+    """Whole-step CUDA-graph replay is offered only for the layouts validated on hardware."""
+    import scaletorch_b200.trainer.graphed as G
+    from scaletorch_b200.trainer.optimizer import FusedAdamW
+
+    opt = FusedAdamW.__new__(FusedAdamW)
+    cfg = SimpleNamespace(fused_comm=True)
+    monkeypatch.setattr(torch.cuda, "is_available", lambda: True)
+
+    def pgm(**kw):
+        base = dict(pp_world_size=1, ep_world_size=1, tp_world_size=1, world_size=8)
+        base.update(kw)
+        m = SimpleNamespace(**base)
+        return m
+
+    monkeypatch.setattr(G, "pgm", pgm())
+    assert G.GraphedTrainStep.supported(cfg, opt)                                   # DP / CP
+    assert not G.GraphedTrainStep.supported(cfg, torch.optim.SGD([torch.nn.Parameter(torch.zeros(1))], lr=0.1))
+    for bad in (dict(pp_world_size=2), dict(ep_world_size=2), dict(tp_world_size=2)):
+        monkeypatch.setattr(G, "pgm", pgm(**bad))
+        assert not G.GraphedTrainStep.supported(cfg, opt), bad
+    monkeypatch.setattr(G, "pgm", pgm())
+    assert not G.GraphedTrainStep.supported(SimpleNamespace(fused_comm=False), opt)  # c10d collectives are not captured
+    from scaletorch_b200.models import Qwen3MoE
+    from scaletorch_b200.parallel.context import ParallelContext
+
+    moe_cfg = SimpleNamespace(model_type="qwen3_moe", num_experts=4, num_experts_per_tok=2, moe_intermediate_size=32,
+                              norm_topk_prob=True, decoder_sparse_step=1, mlp_only_layers=[], router_aux_loss_coef=0.0,
+                              vocab_size=64, hidden_size=32, num_attention_heads=2, num_key_value_heads=1, head_dim=16,
+                              max_position_embeddings=32, num_hidden_layers=1, intermediate_size=64, rms_norm_eps=1e-6,
+                              rope_theta=1e4, tie_word_embeddings=False)
+    assert not G.GraphedTrainStep.supported(cfg, opt, Qwen3MoE(moe_cfg, ParallelContext()))
+    monkeypatch.setattr(torch.cuda, "is_available", lambda: False)
+    assert not G.GraphedTrainStep.supported(cfg, opt)

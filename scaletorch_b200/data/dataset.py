@@ -97,3 +97,32 @@ class DatasetProcessor:
             lambda ex: fn(ex, self.tokenizer, sequence_length, text_column_name), batched=True,
             remove_columns=dataset.column_names, num_proc=num_proc if num_proc > 1 else None,
             desc=f"tokenize[{strategy}] S={sequence_length}")
+
+
+def export_flat_tokens(texts, tokenizer: Any, path: str, eos_token_id: int | None = None, batch_size: int = 1000) -> int:
+    """Tokenises ``texts`` (any iterable of strings) into ONE flat int32 array -- documents separated by ``eos_token_id``
+    when given -- and saves it as ``.npy``: the input format of the native loader (``data/native_loader.py``,
+    ``tools/train.py --native_loader true --token_file …``).  Same token stream as the ``concat_chunk`` strategy, without
+    materialising per-sample rows.  Returns the number of tokens written."""
+    parts: list[np.ndarray] = []
+    batch: list[str] = []
+
+    def flush():
+        if not batch:
+            return
+        enc = tokenizer(batch, add_special_tokens=False, return_attention_mask=False, return_token_type_ids=False)
+        for seq in enc["input_ids"]:
+            parts.append(np.asarray(seq, dtype=np.int32))
+            if eos_token_id is not None:
+                parts.append(np.asarray([eos_token_id], dtype=np.int32))
+        batch.clear()
+
+    for t in texts:
+        batch.append(str(t))
+        if len(batch) >= batch_size:
+            flush()
+    flush()
+    flat = np.concatenate(parts) if parts else np.zeros(0, dtype=np.int32)
+    os.makedirs(os.path.dirname(os.path.abspath(path)), exist_ok=True)
+    np.save(path, flat)
+    return int(flat.size)

@@ -63,3 +63,20 @@ def test_native_loader_rejects_bad_layouts():
         NativeTokenLoader(tokens, 30, 2, cp_size=4, zigzag=True)      # 30 % 8 != 0
     with pytest.raises(ValueError):
         NativeTokenLoader(tokens, 64, 64)                               # fewer samples than one batch
+
+
+def test_export_flat_tokens_roundtrip(tmp_path):
+    import numpy as np
+
+    from scaletorch_b200.data.dataset import export_flat_tokens
+
+    class FakeTok:
+        def __call__(self, texts, **kw):
+            return {"input_ids": [[ord(c) for c in t] for t in texts]}
+
+    path = str(tmp_path / "sub" / "tokens.npy")
+    n = export_flat_tokens(["ab", "c", "def"], FakeTok(), path, eos_token_id=0, batch_size=2)
+    arr = np.load(path)
+    assert n == 9 and arr.dtype == np.int32
+    assert arr.tolist() == [97, 98, 0, 99, 0, 100, 101, 102, 0]
+    assert export_flat_tokens([], FakeTok(), path) == 0

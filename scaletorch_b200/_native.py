@@ -26,6 +26,7 @@ launch_count = 0
 _P = c_void_p
 _SIGS = {
     "stb_gemm_bf16": [_P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, _P],
+    "stb_gemm_bf16_2cta": [_P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, _P],
     "stb_rmsnorm_fwd": [_P, _P, _P, _P, _P, _P, c_int, c_int, c_float, _P],
     "stb_rmsnorm_bwd": [_P, _P, _P, _P, _P, _P, _P, c_int, _P, c_int, c_int, _P],
     "stb_rmsnorm_bwd_noalloc": [_P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int, _P],

@@ -53,12 +53,35 @@ def gemm(
         return out
     assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16
     assert a.stride(1) == 1 and b.stride(1) == 1 and out.stride(1) == 1
+    if _USE_2CTA and _gemm_2cta(a, b, out, M, Nn, K, a_mn, b_mn, accumulate):
+        return out
     N.call(
         "stb_gemm_bf16", a.data_ptr(), b.data_ptr(), out.data_ptr(), M, Nn, K,
         a.stride(0), b.stride(0), out.stride(0), int(a_mn), int(b_mn),
         int(out.dtype == torch.float32), int(accumulate), force_bn, N.stream_ptr(),
     )
     return out
+
+
+# EXPERIMENTAL CTA-pair kernel (csrc/experimental/gemm_2cta.cu): opt-in, not yet validated on hardware
+import os as _os
+
+_USE_2CTA = _os.environ.get("SCALETORCH_B200_GEMM_2CTA", "0") == "1"
+
+
+def _gemm_2cta(a, b, out, M, Nn, K, a_mn, b_mn, accumulate, force: bool = False) -> bool:
+    """Runs the CTA-pair GEMM when the shape qualifies (large, TMA-storable C); returns False to fall back."""
+    lib = N.load()
+    if lib is None or not hasattr(lib, "stb_gemm_bf16_2cta"):
+        return False
+    esz = out.element_size()
+    if out.data_ptr() % 16 or (out.stride(0) * esz) % 16 or (accumulate and out.dtype != torch.float32):
+        return False
+    if not force and (M < 1024 or Nn < 1024):
+        return False
+    N.call("stb_gemm_bf16_2cta", a.data_ptr(), b.data_ptr(), out.data_ptr(), M, Nn, K, a.stride(0), b.stride(0),
+           out.stride(0), int(a_mn), int(b_mn), int(out.dtype == torch.float32), int(accumulate), N.stream_ptr())
+    return True
 
 
 def wgrad_into(param: torch.Tensor, dy2d: torch.Tensor, x2d: torch.Tensor) -> torch.Tensor | None:

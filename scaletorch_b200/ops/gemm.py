@@ -15,6 +15,8 @@ GEMM writes/accumulates straight into it from its epilogue and autograd sees
 """
 from __future__ import annotations
 
+import os
+
 import torch
 
 from .. import _native as N
@@ -64,9 +66,7 @@ def gemm(
 
 
 # EXPERIMENTAL CTA-pair kernel (csrc/experimental/gemm_2cta.cu): opt-in, not yet validated on hardware
-import os as _os
-
-_USE_2CTA = _os.environ.get("SCALETORCH_B200_GEMM_2CTA", "0") == "1"
+_USE_2CTA = os.environ.get("SCALETORCH_B200_GEMM_2CTA", "0") == "1"
 
 
 def _gemm_2cta(a, b, out, M, Nn, K, a_mn, b_mn, accumulate, force: bool = False) -> bool:

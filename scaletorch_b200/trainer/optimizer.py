@@ -17,6 +17,19 @@ from ..ops.optim import clip_coef_from_sumsq, fused_adamw_step, sum_of_squares
 from ..runtime.flat_params import FlatParamStore
 
 
+def _small_all_reduce(t: torch.Tensor, group) -> None:
+    """Sum of a small fp32 tensor over ``group``: c10d by default, the peer-memory kernel when opted in
+    (``runtime.fused_ops.SmallAllReduce``, experimental)."""
+    if t.is_cuda and t.dtype == torch.float32:
+        from ..runtime.fused_ops import SmallAllReduce
+        from ..runtime import symm
+
+        if SmallAllReduce.enabled() and symm.group_ready(group):
+            SmallAllReduce.for_group(group).all_reduce_(t)
+            return
+    dist.all_reduce(t, group=group)
+
+
 class FusedAdamW(torch.optim.Optimizer):
     def __init__(self, store: FlatParamStore, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8,
                  weight_decay: float = 0.01, max_grad_norm: float | None = None, norm_group=None,
@@ -41,7 +54,7 @@ class FusedAdamW(torch.optim.Optimizer):
         """Device scalars ``(coef, norm)`` of the global gradient norm over the model-parallel group."""
         ss = sum_of_squares(self.store.grad_flat)
         if self.norm_group is not None and dist.is_initialized() and dist.get_world_size(self.norm_group) > 1:
-            dist.all_reduce(ss, group=self.norm_group)
+            _small_all_reduce(ss, self.norm_group)
         coef, norm = clip_coef_from_sumsq(ss, self.max_grad_norm or 0.0)
         self.last_grad_norm = norm
         return coef, norm

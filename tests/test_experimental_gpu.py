@@ -34,3 +34,39 @@ def test_gemm_2cta(M, Nn, K, a_mn, b_mn):
     assert _gemm_2cta(a, b, acc, M, Nn, K, a_mn, b_mn, True, force=True)
     torch.cuda.synchronize()
     assert _rel(acc, ref + 1.0) < 5e-3
+
+
+def _small_ar_worker(rank, world, port):
+    import torch.distributed as dist
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        from scaletorch_b200.runtime.fused_ops import SmallAllReduce
+
+        ar = SmallAllReduce.for_group(dist.group.WORLD)
+        for n in (1, 3, 4, 1000, 4097):
+            for _ in range(2):
+                t = torch.randn(n, device="cuda")
+                ref = t.clone()
+                dist.all_reduce(ref)
+                ar.all_reduce_(t)
+                torch.cuda.synchronize()
+                assert torch.allclose(t, ref, atol=1e-5), (n, (t - ref).abs().max())
+        dist.barrier()
+    finally:
+        dist.destroy_process_group()
+
+
+def test_small_all_reduce_two_gpus():
+    import socket
+
+    import torch.multiprocessing as mp
+
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs at least 2 GPUs")
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    mp.spawn(_small_ar_worker, args=(2, port), nprocs=2, join=True)

@@ -35,6 +35,8 @@ def create_model(config, dtype: torch.dtype, device: torch.device):
     """Returns ``(model, model_config)``; ``model`` is wrapped for PP / DP as the layout requires."""
     t0 = time.time()
     model_config = resolve_model_config(config.model_name_or_path)
+    if getattr(config, "ep_capacity_factor", None) is not None:
+        model_config.ep_capacity_factor = float(config.ep_capacity_factor)
     for k in ("num_hidden_layers", "num_attention_heads", "num_key_value_heads"):
         v = getattr(config, k, None)
         if v is not None and v != getattr(model_config, k, None):

@@ -50,6 +50,24 @@ except Exception:  # pragma: no cover
     wandb = None
 
 
+def report_dropped_pairs(model, step: int) -> None:
+    """The peer-memory EP path has a static receive capacity (``--ep_capacity_factor`` / SCALETORCH_B200_EP_CAPACITY);
+    pairs beyond it are dropped on the sender.  Make that visible: every 50 steps each rank that dropped something says so
+    (one host read per MoE layer, off the critical path of the lagged logger) and the counters are reset."""
+    raw = model
+    while hasattr(raw, "module") and isinstance(raw.module, torch.nn.Module):
+        raw = raw.module
+    total = 0
+    for m in raw.modules():
+        d = getattr(m, "dropped_pairs", None)
+        if isinstance(d, torch.Tensor):
+            total += int(d.item())
+            m.dropped_pairs = None
+    if total > 0:
+        rank_print(f"[step {step}] expert-parallel capacity exceeded: {total} (token, expert) pairs dropped since the last "
+                   f"report; raise --ep_capacity_factor", is_print_rank=True)
+
+
 def build_native_loader(config, model_config):
     """C++ micro-batch producer over a flat token array: a ``--token_file`` (int32 ``.npy`` or raw ``.bin``) or, with
     ``--synthetic_data``, random ids.  Same batch dict and ``global_batch_size`` attribute as ``MicroBatchDataLoader``."""
@@ -161,6 +179,8 @@ def main(argv=None) -> None:
             gn = norm_reader.pop() if gn == "reader" else gn
             log_training_metrics(config, model_config, st, loss, lr_, gn, stats["iteration_time"], tokens_per_step, tokens_,
                                  num_params, world_size, logger=logger, wandb_run=run)
+            if st % 50 == 0:
+                report_dropped_pairs(model, st)
 
         while config.max_tokens is None or trained_tokens < config.max_tokens:
             prof.step(step)

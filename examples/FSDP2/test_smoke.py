@@ -28,7 +28,8 @@ def test_fsdp2_checkpoint_resume(tmp_path):
     assert "resumed from step 2" in out and "step   2 loss" in out
 
 
-@pytest.mark.parametrize("tp", [2])
-def test_fsdp2_tp(tp):
-    out = _run("fsdp2_tp_main.py", "--tp", str(tp), "--steps", "2", nproc=2)
+@pytest.mark.parametrize("nproc,tp", [(2, 2), (4, 2)])
+def test_fsdp2_tp(nproc, tp):
+    """(4, 2) is the 2-D case of the reference's test_smoke_mp.py: dp2 x tp2 on four CPU processes (gloo)."""
+    out = _run("fsdp2_tp_main.py", "--tp", str(tp), "--steps", "2", nproc=nproc)
     assert "step   1 loss" in out

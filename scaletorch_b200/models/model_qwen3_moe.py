@@ -109,9 +109,11 @@ class MoELayer(nn.Module):
         the reference (``tensor_parallel.py:132-138``)."""
         ctx = self.ctx
         if ctx.sp:
-            from ..parallel.tensor_parallel import tp_comms
-
-            x = tp_comms.gather_from_sequence_parallel_region(x, ctx.tp_group)
+            # every TP rank runs the whole MoE branch on all tokens (experts are not TP-sharded) and keeps its token shard
+            # of the result; because each rank therefore sees the *complete* output gradient, the gradient w.r.t. the
+            # gathered input is complete on every rank too: the backward of this gather is a slice, not the
+            # reduce-scatter of the Megatron-SP gather (which would count the branch tp times)
+            x = _GatherKeepGrad.apply(x, ctx.tp_group)
         weights, idx, aux = self.router(x)
         self._aux_loss = aux
         if self.ep_size > 1 and self.use_fused_ep and self._fused_ep_ok(x):
@@ -153,6 +155,30 @@ class MoELayer(nn.Module):
         w = weights.reshape(-1).index_select(0, sort_idx).to(ys.dtype)
         ys = ys * w.unsqueeze(-1)
         return torch.zeros((T, H), dtype=ys.dtype, device=ys.device).index_add(0, token_of, ys)
+
+
+class _GatherKeepGrad(torch.autograd.Function):
+    """All-gather the TP ranks' token shards along dim 0; the backward keeps this rank's slice of the (already
+    complete) gradient.  Counterpart of :class:`_SplitKeepGrad` around the TP-replicated MoE branch."""
+
+    @staticmethod
+    def forward(ctx, x, group):
+        import torch.distributed as dist
+
+        ctx.group = group
+        ws = dist.get_world_size(group)
+        x = x.contiguous()
+        out = torch.empty((ws * x.shape[0],) + tuple(x.shape[1:]), dtype=x.dtype, device=x.device)
+        dist.all_gather_into_tensor(out, x, group=group)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        import torch.distributed as dist
+
+        ws, r = dist.get_world_size(ctx.group), dist.get_rank(ctx.group)
+        n = g.shape[0] // ws
+        return g[r * n:(r + 1) * n].contiguous(), None
 
 
 class _SplitKeepGrad(torch.autograd.Function):

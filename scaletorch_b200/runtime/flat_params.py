@@ -41,6 +41,7 @@ class FlatParamStore:
     def __init__(self, module: nn.Module, grad_dtype: torch.dtype = torch.float32, grad_alloc=None):
         """``grad_alloc(numel) -> fp32 tensor`` lets the caller place the gradient buffer in symmetric memory
         (data-parallel buckets are then reduced in place over NVLink)."""
+        self.module = module
         named = []
         seen: set[int] = set()
         for name, p in module.named_parameters():

@@ -43,16 +43,74 @@ class FusedAdamW(torch.optim.Optimizer):
         self.max_grad_norm = max_grad_norm
         self.norm_group = norm_group
         self.last_grad_norm: torch.Tensor | None = None  # device scalar (read lazily for logging)
+        # Expert weights receive the token contributions of every EP rank, each differentiated from that rank's own
+        # (un-averaged) loss, so their raw gradient is ep x the gradient of the mean loss; dense gradients get their
+        # 1/ep from the mean all-reduce over the data replicas.  The factor is folded into the expert range's AdamW
+        # launch and norm contribution instead of a separate pass over the expert gradients.
+        from ..parallel.process_group import process_group_manager as _pgm
+
+        ep = _pgm.ep_world_size if _pgm else 1
+        self.expert_grad_scale = 1.0 / ep if (ep > 1 and store.expert_numel > 0 and norm_group is not None) else 1.0
         # step-dependent scalars {lr, 1-β1^t, 1-β2^t} live in device memory so the whole step can sit in a CUDA graph
         self._hyper_dev = self._hyper_host = None
         if store.device.type == "cuda":
             self._hyper_dev = torch.zeros(4, dtype=torch.float32, device=store.device)
             self._hyper_host = torch.zeros(4, dtype=torch.float32, pin_memory=True)
 
+    def _local_sumsq(self) -> torch.Tensor:
+        """This rank's share of the global Σg²: every parameter counted exactly once across the model-parallel group.
+
+        A parameter that is replicated on ``r`` ranks of the group (after gradient synchronisation its gradient is
+        identical on all of them) contributes ``Σg² / r`` here: dense tensor-parallel shards are replicated over EP
+        (r = ep), dense non-sharded parameters (norm weights, router) over TP × EP, experts over TP, and a tied
+        embedding / LM head split across the first and last pipeline stage once more.  (Summing the plain local
+        Σg² over the group, as a first version did, counted norm weights tp times; the reference clips with the
+        rank-local norm, SURVEY §2.7 #13.)"""
+        from ..parallel.process_group import process_group_manager as pgm
+
+        store = self.store
+        tp = pgm.tp_world_size if pgm else 1
+        ep = pgm.ep_world_size if pgm else 1
+        pp = pgm.pp_world_size if pgm else 1
+        if self.norm_group is None or (tp == 1 and ep == 1 and pp == 1):   # no model parallelism: nothing is replicated
+            return sum_of_squares(store.grad_flat[:store.total_numel])
+        g = store.grad_flat
+        ss_dense = sum_of_squares(g[:store.dense_numel])
+        ss_exp = sum_of_squares(g[store.dense_numel:store.total_numel]) if store.expert_numel > 0 else None
+        rep = getattr(self, "_norm_classes", None)
+        if rep is None:
+            from ..utils.misc import is_tp_sharded_name
+
+            tp_rep = [s for s in store.slots if s.segment == "dense" and tp > 1 and not is_tp_sharded_name(s.name)]
+            tied = []
+            if pp > 1:
+                root = getattr(store, "module", None)
+                if root is not None and getattr(root, "tie_word_embeddings", False):
+                    tied = [s for s in store.slots if s.name in ("embedding.weight", "final_proj.weight")]
+            rep = self._norm_classes = (tp_rep, tied)
+        tp_rep, tied = rep
+
+        def ss_of(slots):
+            if not slots:
+                return None
+            return torch.stack([s.param.main_grad.float().pow(2).sum() for s in slots]).sum().reshape(1)
+
+        total = ss_dense / ep
+        s_rep = ss_of(tp_rep)
+        if s_rep is not None:
+            total = total - s_rep * ((1.0 - 1.0 / tp) / ep)
+        s_tied = ss_of(tied)
+        if s_tied is not None:                      # the same matrix lives on the first and the last stage
+            r_t = ep * (tp if tp_rep and tied[0] in tp_rep else 1)
+            total = total - s_tied * (0.5 / r_t)
+        if ss_exp is not None:
+            total = total + ss_exp * (self.expert_grad_scale ** 2 / tp)
+        return total
+
     @torch.no_grad()
     def compute_clip(self):
         """Device scalars ``(coef, norm)`` of the global gradient norm over the model-parallel group."""
-        ss = sum_of_squares(self.store.grad_flat)
+        ss = self._local_sumsq()
         if self.norm_group is not None and dist.is_initialized() and dist.get_world_size(self.norm_group) > 1:
             _small_all_reduce(ss, self.norm_group)
         coef, norm = clip_coef_from_sumsq(ss, self.max_grad_norm or 0.0)
@@ -83,9 +141,15 @@ class FusedAdamW(torch.optim.Optimizer):
         coef = None
         if self.max_grad_norm is not None and self.max_grad_norm > 0:
             coef, _ = self.compute_clip()
-        fused_adamw_step(self.store.param_flat, self.store.grad_flat, self.exp_avg, self.exp_avg_sq,
-                         lr=g["lr"], betas=g["betas"], eps=g["eps"], weight_decay=g["weight_decay"],
-                         step=max(self.step_count, 1), clip_coef=coef, grad_scale=grad_scale, hyper=self._hyper_dev)
+        st = self.store
+        ranges = [(0, st.total_numel, grad_scale)]
+        if self.expert_grad_scale != 1.0:
+            ranges = [(0, st.dense_numel, grad_scale), (st.dense_numel, st.total_numel, grad_scale * self.expert_grad_scale)]
+        for lo, hi, gs in ranges:
+            if hi > lo:
+                fused_adamw_step(st.param_flat[lo:hi], st.grad_flat[lo:hi], self.exp_avg[lo:hi], self.exp_avg_sq[lo:hi],
+                                 lr=g["lr"], betas=g["betas"], eps=g["eps"], weight_decay=g["weight_decay"],
+                                 step=max(self.step_count, 1), clip_coef=coef, grad_scale=gs, hyper=self._hyper_dev)
         return loss
 
     def zero_grad(self, set_to_none: bool = True) -> None:

@@ -85,6 +85,11 @@ _TP_SHARDED_KEYS = ("q_proj", "k_proj", "v_proj", "qkv_proj", "out_proj", "o_pro
                     "gate_up_proj", "down_proj", "embedding", "final_proj")
 
 
+def is_tp_sharded_name(name: str) -> bool:
+    """True for parameters that tensor parallelism shards (by name, like the reference's ``get_num_params``)."""
+    return any(k in name for k in _TP_SHARDED_KEYS) and "norm" not in name and "router" not in name and ".experts." not in name
+
+
 def get_num_params(model: torch.nn.Module) -> int:
     """Global parameter count: TP-sharded tensors × tp, expert tensors × ep, summed over PP stages
     (reference ``misc.py:177-207``)."""

@@ -281,3 +281,65 @@ def _pp_worker(rank, world, engine, tie):
 @pytest.mark.parametrize("engine,tie", [("afab", False), ("1f1b", False), ("1f1b", True)])
 def test_pipeline_parallel_matches_single_process(engine, tie):
     run_distributed(_pp_worker, 2, engine, tie)
+
+
+# ------------------------------------------------------------------ mixed layouts through optimiser steps
+def _train_worker(rank, world, layout):
+    """Three clipped AdamW steps on a mixed layout must track single-process training: losses, the *global* gradient norm
+    (every parameter counted once across the model-parallel group) and the updated parameters."""
+    import torch.distributed as dist
+
+    from scaletorch_b200.parallel.context import ParallelContext
+    from scaletorch_b200.parallel.data_parallel.data_parallel import DataParallelBucket, get_store
+    from scaletorch_b200.parallel.process_group import process_group_manager as pgm
+    from scaletorch_b200.parallel.process_group import setup_process_group_manager
+    from scaletorch_b200.parallel.tensor_parallel.tensor_parallel import mark_tp_partial_params
+    from scaletorch_b200.trainer.optimizer import FusedAdamW
+    from scaletorch_b200.utils.sharding import load_from_unsharded, shard_tensor
+
+    tp, dp, ep = layout
+    setup_process_group_manager(tp_size=tp, cp_size=1, pp_size=1, dp_size=dp, ep_size=ep)
+    name = "qwen3_moe" if ep > 1 else "qwen3"
+    cfg = TinyCfg(model_type=name, tie_word_embeddings=(ep == 1), router_aux_loss_coef=0.0)
+    ctx = ParallelContext.from_pgm(sequence_parallel=tp > 1)
+    full, par = _models(cfg, name, ctx)
+    load_from_unsharded(par, dict(full.named_parameters()), cfg, tp=tp, tp_rank=pgm.tp_rank, ep=ep, ep_rank=pgm.ep_rank)
+    if tp > 1:
+        mark_tp_partial_params(par, pgm.tp_group, ctx.sp)
+    full_opt = FusedAdamW(get_store(full), lr=1e-2, weight_decay=0.0, max_grad_norm=0.05)
+    store = get_store(par, pgm.grad_sync_group if pgm.grad_sync_world_size > 1 else None)
+    if tp > 1:
+        store.tp_group = pgm.tp_group
+    model = DataParallelBucket(par, bucket_size=5000) if pgm.grad_sync_world_size > 1 else par
+    opt = FusedAdamW(store, lr=1e-2, weight_decay=0.0, max_grad_norm=0.05,
+                     norm_group=pgm.mp_group if len(pgm.mp_group_ids) > 1 else None)
+    replicas = pgm.data_world_size
+    torch.manual_seed(99)
+    for step in range(3):
+        ids = torch.randint(0, cfg.vocab_size, (2 * replicas, 17))
+        x, y = ids[:, :-1], ids[:, 1:]
+        full_opt.zero_grad()
+        lf = full.loss(x, y)
+        lf.backward()
+        full_opt.step()
+        opt.zero_grad()
+        if hasattr(model, "reset"):
+            model.reset()
+        r = pgm.data_rank
+        lp = (model.module if hasattr(model, "module") else model).loss(x[2 * r:2 * r + 2], y[2 * r:2 * r + 2])
+        lp.backward()
+        opt.step()
+        tot = lp.detach().clone()
+        dist.all_reduce(tot, group=pgm.grad_sync_group)
+        assert abs(tot.item() / pgm.grad_sync_world_size - lf.item()) < 2e-4, (step, tot.item(), lf.item())
+        assert abs(opt.grad_norm() - full_opt.grad_norm()) < 2e-3 * full_opt.grad_norm(), (
+            step, opt.grad_norm(), full_opt.grad_norm())
+    ref = dict(full.named_parameters())
+    for n, p in par.named_parameters():
+        want = shard_tensor(n, ref[n].detach(), cfg, tp, pgm.tp_rank, ep, pgm.ep_rank)
+        assert rel_err(p.detach(), want) < 2e-3, f"{n}: {rel_err(p.detach(), want)}"
+
+
+@pytest.mark.parametrize("layout", [(2, 2, 1), (2, 1, 2), (1, 2, 2)], ids=["tp2dp2", "tp2ep2", "dp2ep2"])
+def test_mixed_layout_training_tracks_single_process(layout):
+    run_distributed(_train_worker, 4, layout)

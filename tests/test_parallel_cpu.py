@@ -297,8 +297,9 @@ def _train_worker(rank, world, layout):
     from scaletorch_b200.trainer.optimizer import FusedAdamW
     from scaletorch_b200.utils.sharding import load_from_unsharded, shard_tensor
 
-    tp, dp, ep = layout
-    setup_process_group_manager(tp_size=tp, cp_size=1, pp_size=1, dp_size=dp, ep_size=ep)
+    tp, dp, ep = layout[:3]
+    cp = layout[3] if len(layout) > 3 else 1
+    setup_process_group_manager(tp_size=tp, cp_size=cp, pp_size=1, dp_size=dp, ep_size=ep)
     name = "qwen3_moe" if ep > 1 else "qwen3"
     cfg = TinyCfg(model_type=name, tie_word_embeddings=(ep == 1), router_aux_loss_coef=0.0)
     ctx = ParallelContext.from_pgm(sequence_parallel=tp > 1)
@@ -326,7 +327,11 @@ def _train_worker(rank, world, layout):
         if hasattr(model, "reset"):
             model.reset()
         r = pgm.data_rank
-        lp = (model.module if hasattr(model, "module") else model).loss(x[2 * r:2 * r + 2], y[2 * r:2 * r + 2])
+        xs, ys = x[2 * r:2 * r + 2], y[2 * r:2 * r + 2]
+        if cp > 1:
+            n = xs.shape[1] // cp
+            xs, ys = xs[:, pgm.cp_rank * n:(pgm.cp_rank + 1) * n].contiguous(), ys[:, pgm.cp_rank * n:(pgm.cp_rank + 1) * n].contiguous()
+        lp = (model.module if hasattr(model, "module") else model).loss(xs, ys)
         lp.backward()
         opt.step()
         tot = lp.detach().clone()
@@ -340,6 +345,78 @@ def _train_worker(rank, world, layout):
         assert rel_err(p.detach(), want) < 2e-3, f"{n}: {rel_err(p.detach(), want)}"
 
 
-@pytest.mark.parametrize("layout", [(2, 2, 1), (2, 1, 2), (1, 2, 2)], ids=["tp2dp2", "tp2ep2", "dp2ep2"])
+@pytest.mark.parametrize("layout", [(2, 2, 1), (2, 1, 2), (1, 2, 2), (1, 2, 1, 2), (2, 1, 1, 2)],
+                         ids=["tp2dp2", "tp2ep2", "dp2ep2", "cp2dp2", "tp2cp2"])
 def test_mixed_layout_training_tracks_single_process(layout):
     run_distributed(_train_worker, 4, layout)
+
+
+def _pp_train_worker(rank, world, tp, dp, tie):
+    """Pipeline stages (1F1B) combined with TP or DP, through clipped optimiser steps: the tied embedding / LM head lives on
+    both the first and the last stage and must be counted once in the global norm."""
+    import re
+
+    from scaletorch_b200.parallel.context import ParallelContext
+    from scaletorch_b200.parallel.data_parallel.data_parallel import DataParallelBucket, get_store
+    from scaletorch_b200.parallel.pipeline_parallel.pipeline_parallel import PipelineParallel, train_step_pipeline_1f1b
+    from scaletorch_b200.parallel.process_group import process_group_manager as pgm
+    from scaletorch_b200.parallel.process_group import setup_process_group_manager
+    from scaletorch_b200.parallel.tensor_parallel.tensor_parallel import mark_tp_partial_params
+    from scaletorch_b200.trainer.optimizer import FusedAdamW
+    from scaletorch_b200.utils.sharding import load_from_unsharded, shard_tensor
+
+    setup_process_group_manager(tp_size=tp, cp_size=1, pp_size=2, dp_size=dp)
+    cfg = TinyCfg(model_type="qwen3", num_hidden_layers=3, tie_word_embeddings=tie)
+    ctx = ParallelContext.from_pgm(sequence_parallel=tp > 1)
+    full, proto = _models(cfg, "qwen3", ctx)
+    par = PipelineParallel(proto, cfg)
+    load_from_unsharded(par, dict(full.named_parameters()), cfg, tp=tp, tp_rank=pgm.tp_rank, layer_ids=par.layer_ids)
+    if tp > 1:
+        mark_tp_partial_params(par, pgm.tp_group, ctx.sp)
+    full_opt = FusedAdamW(get_store(full), lr=1e-2, weight_decay=0.0, max_grad_norm=0.05)
+    store = get_store(par, pgm.grad_sync_group if pgm.grad_sync_world_size > 1 else None)
+    if tp > 1:
+        store.tp_group = pgm.tp_group
+    model = DataParallelBucket(par, bucket_size=5000) if pgm.grad_sync_world_size > 1 else par
+    opt = FusedAdamW(store, lr=1e-2, weight_decay=0.0, max_grad_norm=0.05, norm_group=pgm.mp_group)
+    ga, mbs, S = 2, 2, 16
+    torch.manual_seed(9)
+    for step in range(3):
+        ids = torch.randint(0, cfg.vocab_size, (dp * ga * mbs, S + 1))
+        full_opt.zero_grad()
+        full.loss(ids[:, :-1], ids[:, 1:]).backward()
+        full_opt.step()
+        mine = ids[pgm.dp_rank * ga * mbs:(pgm.dp_rank + 1) * ga * mbs]
+
+        class Loader:
+            gradient_accumulation_steps = ga
+
+            def __init__(self):
+                self.i = 0
+
+            def __next__(self):
+                b = mine[self.i * mbs:(self.i + 1) * mbs]
+                self.i += 1
+                return {"input_ids": b[:, :-1].contiguous(), "target_ids": b[:, 1:].contiguous()}
+
+        opt.zero_grad()
+        if hasattr(model, "reset"):
+            model.reset()
+        s_local = S // tp if ctx.sp else S
+        train_step_pipeline_1f1b(model, Loader(), (mbs, s_local, cfg.hidden_size), torch.device("cpu"), torch.float32)
+        opt.step()
+        assert abs(opt.grad_norm() - full_opt.grad_norm()) < 2e-3 * full_opt.grad_norm(), (
+            step, opt.grad_norm(), full_opt.grad_norm())
+    ref = dict(full.named_parameters())
+    for n, p in par.named_parameters():
+        m = re.match(r"decoder_layers\.(\d+)\.(.*)", n)
+        src = f"decoder_layers.{par.layer_ids[int(m.group(1))]}.{m.group(2)}" if m else n
+        if src == "final_proj.weight" and tie:
+            src = "embedding.weight"
+        want = shard_tensor(src, ref[src].detach(), cfg, tp, pgm.tp_rank, 1, 0)
+        assert rel_err(p.detach(), want) < 2e-3, f"{n}: {rel_err(p.detach(), want)}"
+
+
+@pytest.mark.parametrize("tp,dp,tie", [(1, 2, True), (2, 1, True), (2, 1, False)], ids=["pp2dp2-tied", "pp2tp2-tied", "pp2tp2"])
+def test_pipeline_mixed_layout_training_tracks_single_process(tp, dp, tie):
+    run_distributed(_pp_train_worker, 4, tp, dp, tie)

@@ -77,3 +77,17 @@ def test_watchdog_turns_a_hang_into_an_exit(tmp_path):
                 "--step_timeout_s", "3"], env={"SCALETORCH_B200_FAULT_INJECT": "0:3:hang"}, expect_rc=124, timeout=120)
     assert "[watchdog] rank 0 stuck after step 3" in out
     assert (tmp_path / "hang_rank0.txt").exists() and (tmp_path / "heartbeat_rank0.json").exists()
+
+
+def test_cli_loss_trajectories_agree_across_layouts(tmp_path):
+    """Same seed, same global batch: single process, DP2 and (zig-zag) CP2 must print the same losses step by step."""
+    common = ["--model_name_or_path", "tiny-qwen3", "--total_train_steps", "4", "--log_lag", "0", "--seed", "7",
+              "--num_samples", "64"]
+    single = _losses(_run(common + ["--micro_batch_size", "4", "--work_dir", str(tmp_path / "a")]))
+    dp2 = _losses(_run(common + ["--micro_batch_size", "2", "--data_parallel_size", "2", "--work_dir", str(tmp_path / "b")],
+                       nproc=2))
+    cp2 = _losses(_run(common + ["--micro_batch_size", "4", "--context_parallel_size", "2", "--work_dir", str(tmp_path / "c")],
+                       nproc=2))
+    assert len(single) == len(dp2) == len(cp2) == 4
+    for (s, a), (_, b), (_, c) in zip(single, dp2, cp2):
+        assert abs(a - b) < 2e-3 and abs(a - c) < 2e-3, (s, a, b, c)      # the metrics line prints 4 decimals

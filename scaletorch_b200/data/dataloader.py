@@ -122,3 +122,17 @@ class MicroBatchDataLoader(DataLoader):
 
     def state_dict(self) -> dict:
         return {"epoch": self._epoch, "batches_served": self.batches_served}
+
+    def load_state_dict(self, state: dict) -> None:
+        """Resume the sample stream where a checkpoint left it: same epoch (= same shuffle) and position, so a resumed run
+        sees exactly the batches the uninterrupted run would have seen (the reference restarts the sampler on resume,
+        SURVEY §5.4).  The skipped batches of the current epoch are drawn and discarded."""
+        served = int(state.get("batches_served", 0))
+        per_epoch = max(1, len(self.sampler_) // self.micro_batch_size)
+        self._epoch, skip = divmod(served, per_epoch)
+        self.sampler_.set_epoch(self._epoch)
+        self._iterator = super().__iter__()
+        self._prefetched = None
+        for _ in range(skip):
+            next(self._iterator)
+        self.batches_served = served

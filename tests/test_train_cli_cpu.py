@@ -62,14 +62,21 @@ def test_native_loader_cli(tmp_path):
 
 
 def test_checkpoint_resume(tmp_path):
+    const_lr = ["--lr_scheduler_type", "step", "--step_size", "1000"]     # the schedule must not depend on total steps
     common = ["--model_name_or_path", "tiny-llama", "--work_dir", str(tmp_path), "--save_model_checkpoint", "true",
-              "--save_frequency", "3", "--log_lag", "0"]
+              "--save_frequency", "3", "--log_lag", "0"] + const_lr
     out1 = _run(common + ["--total_train_steps", "3"])
     assert (tmp_path / "3").is_dir()
     out2 = _run(common + ["--total_train_steps", "5", "--resume_path", str(tmp_path / "3")])
     assert "Loaded checkpoint at step 3" in out2
     assert [s for s, _ in _losses(out2)] == [4, 5]
     assert all(0.0 < l < 12.0 for _, l in _losses(out1) + _losses(out2))
+    # a resumed run continues the uninterrupted trajectory: weights, optimiser state, LR schedule AND data position
+    out3 = _run(["--model_name_or_path", "tiny-llama", "--work_dir", str(tmp_path / "straight"), "--log_lag", "0",
+                 "--total_train_steps", "5"] + const_lr)
+    straight = dict(_losses(out3))
+    for s, l in _losses(out2):
+        assert abs(l - straight[s]) < 2e-3, (s, l, straight[s])
 
 
 def test_watchdog_turns_a_hang_into_an_exit(tmp_path):

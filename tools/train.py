@@ -149,6 +149,9 @@ def main(argv=None) -> None:
             sched_path = os.path.join(config.resume_path, "scheduler.pt")
             if os.path.exists(sched_path):
                 lr_scheduler.load_state_dict(torch.load(sched_path, weights_only=False))
+            dl_state = (getattr(ckpt, "last_extra", None) or {}).get("data_loader")
+            if dl_state and hasattr(data_loader, "load_state_dict"):
+                data_loader.load_state_dict(dl_state)
             rank_print(f"Loaded checkpoint at step {step}, trained_tokens={trained_tokens}", is_print_rank=log_rank)
         if world_size > 1:
             dist.barrier()

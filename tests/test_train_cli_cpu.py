@@ -98,3 +98,20 @@ def test_cli_loss_trajectories_agree_across_layouts(tmp_path):
     assert len(single) == len(dp2) == len(cp2) == 4
     for (s, a), (_, b), (_, c) in zip(single, dp2, cp2):
         assert abs(a - b) < 2e-3 and abs(a - c) < 2e-3, (s, a, b, c)      # the metrics line prints 4 decimals
+
+
+def test_checkpoint_resume_under_tensor_parallel(tmp_path):
+    """Per-(tp, pp, ep) checkpoint files: a TP2+SP run resumed from step 3 continues the uninterrupted trajectory."""
+    base = ["--model_name_or_path", "tiny-qwen3", "--num_attention_heads", "4", "--num_key_value_heads", "2",
+            "--tensor_parallel_size", "2", "--sequence_parallel", "true", "--log_lag", "0",
+            "--lr_scheduler_type", "step", "--step_size", "1000"]
+    saving = ["--save_model_checkpoint", "true", "--save_frequency", "3", "--work_dir", str(tmp_path / "run")]
+    _run(base + saving + ["--total_train_steps", "3"], nproc=2)
+    files = sorted(os.listdir(tmp_path / "run" / "3"))
+    assert any(f.startswith("weights_tp_rank_world_size=0_2") for f in files) and any(
+        f.startswith("weights_tp_rank_world_size=1_2") for f in files), files
+    resumed = _losses(_run(base + saving + ["--total_train_steps", "5", "--resume_path", str(tmp_path / "run" / "3")], nproc=2))
+    straight = dict(_losses(_run(base + ["--total_train_steps", "5", "--work_dir", str(tmp_path / "straight")], nproc=2)))
+    assert [s for s, _ in resumed] == [4, 5]
+    for s, l in resumed:
+        assert abs(l - straight[s]) < 2e-3, (s, l, straight[s])

@@ -24,6 +24,15 @@ def _run(args, nproc=1, env=None, timeout=600, expect_rc=0):
     return p.stdout + p.stderr
 
 
+def _run_many(jobs):
+    """Runs several independent CLI jobs ``(args, nproc)`` concurrently (process start-up dominates their cost)."""
+    from concurrent.futures import ThreadPoolExecutor
+
+    with ThreadPoolExecutor(max_workers=len(jobs)) as ex:
+        futs = [ex.submit(_run, a, n) for a, n in jobs]
+        return [f.result() for f in futs]
+
+
 def _losses(out):
     return [(int(s), float(l)) for s, l in LINE.findall(out)]
 
@@ -38,15 +47,16 @@ def test_single_process_trains(tmp_path):
     assert any(f.startswith("performance_logs_0_") for f in os.listdir(tmp_path))
 
 
-@pytest.mark.parametrize("layout", [["--tensor_parallel_size", "2", "--sequence_parallel", "true"],
-                                    ["--data_parallel_size", "2", "--gradient_accumulation_steps", "2"],
-                                    ["--pipeline_parallel_size", "2", "--gradient_accumulation_steps", "2"],
-                                    ["--context_parallel_size", "2"]])
-def test_two_process_layouts(tmp_path, layout):
-    out = _run(["--model_name_or_path", "tiny-qwen3", "--num_attention_heads", "4", "--num_key_value_heads", "2",
-                "--total_train_steps", "4", "--work_dir", str(tmp_path)] + layout, nproc=2)
-    ls = _losses(out)
-    assert len(ls) == 4 and all(0.0 < l < 12.0 for _, l in ls), out[-2000:]
+def test_two_process_layouts(tmp_path):
+    layouts = {"tp2sp": ["--tensor_parallel_size", "2", "--sequence_parallel", "true"],
+               "dp2ga2": ["--data_parallel_size", "2", "--gradient_accumulation_steps", "2"],
+               "pp2ga2": ["--pipeline_parallel_size", "2", "--gradient_accumulation_steps", "2"],
+               "cp2": ["--context_parallel_size", "2"]}
+    jobs = [(["--model_name_or_path", "tiny-qwen3", "--num_attention_heads", "4", "--num_key_value_heads", "2",
+              "--total_train_steps", "4", "--work_dir", str(tmp_path / k)] + v, 2) for k, v in layouts.items()]
+    for k, out in zip(layouts, _run_many(jobs)):
+        ls = _losses(out)
+        assert len(ls) == 4 and all(0.0 < l < 12.0 for _, l in ls), (k, out[-2000:])
 
 
 def test_native_loader_cli(tmp_path):
@@ -65,15 +75,15 @@ def test_checkpoint_resume(tmp_path):
     const_lr = ["--lr_scheduler_type", "step", "--step_size", "1000"]     # the schedule must not depend on total steps
     common = ["--model_name_or_path", "tiny-llama", "--work_dir", str(tmp_path), "--save_model_checkpoint", "true",
               "--save_frequency", "3", "--log_lag", "0"] + const_lr
-    out1 = _run(common + ["--total_train_steps", "3"])
+    out1, out3 = _run_many([(common + ["--total_train_steps", "3"], 1),
+                            (["--model_name_or_path", "tiny-llama", "--work_dir", str(tmp_path / "straight"), "--log_lag", "0",
+                              "--total_train_steps", "5"] + const_lr, 1)])
     assert (tmp_path / "3").is_dir()
     out2 = _run(common + ["--total_train_steps", "5", "--resume_path", str(tmp_path / "3")])
     assert "Loaded checkpoint at step 3" in out2
     assert [s for s, _ in _losses(out2)] == [4, 5]
     assert all(0.0 < l < 12.0 for _, l in _losses(out1) + _losses(out2))
     # a resumed run continues the uninterrupted trajectory: weights, optimiser state, LR schedule AND data position
-    out3 = _run(["--model_name_or_path", "tiny-llama", "--work_dir", str(tmp_path / "straight"), "--log_lag", "0",
-                 "--total_train_steps", "5"] + const_lr)
     straight = dict(_losses(out3))
     for s, l in _losses(out2):
         assert abs(l - straight[s]) < 2e-3, (s, l, straight[s])
@@ -90,11 +100,10 @@ def test_cli_loss_trajectories_agree_across_layouts(tmp_path):
     """Same seed, same global batch: single process, DP2 and (zig-zag) CP2 must print the same losses step by step."""
     common = ["--model_name_or_path", "tiny-qwen3", "--total_train_steps", "4", "--log_lag", "0", "--seed", "7",
               "--num_samples", "64"]
-    single = _losses(_run(common + ["--micro_batch_size", "4", "--work_dir", str(tmp_path / "a")]))
-    dp2 = _losses(_run(common + ["--micro_batch_size", "2", "--data_parallel_size", "2", "--work_dir", str(tmp_path / "b")],
-                       nproc=2))
-    cp2 = _losses(_run(common + ["--micro_batch_size", "4", "--context_parallel_size", "2", "--work_dir", str(tmp_path / "c")],
-                       nproc=2))
+    outs = _run_many([(common + ["--micro_batch_size", "4", "--work_dir", str(tmp_path / "a")], 1),
+                      (common + ["--micro_batch_size", "2", "--data_parallel_size", "2", "--work_dir", str(tmp_path / "b")], 2),
+                      (common + ["--micro_batch_size", "4", "--context_parallel_size", "2", "--work_dir", str(tmp_path / "c")], 2)])
+    single, dp2, cp2 = (_losses(o) for o in outs)
     assert len(single) == len(dp2) == len(cp2) == 4
     for (s, a), (_, b), (_, c) in zip(single, dp2, cp2):
         assert abs(a - b) < 2e-3 and abs(a - c) < 2e-3, (s, a, b, c)      # the metrics line prints 4 decimals
@@ -106,12 +115,13 @@ def test_checkpoint_resume_under_tensor_parallel(tmp_path):
             "--tensor_parallel_size", "2", "--sequence_parallel", "true", "--log_lag", "0",
             "--lr_scheduler_type", "step", "--step_size", "1000"]
     saving = ["--save_model_checkpoint", "true", "--save_frequency", "3", "--work_dir", str(tmp_path / "run")]
-    _run(base + saving + ["--total_train_steps", "3"], nproc=2)
+    _, straight_out = _run_many([(base + saving + ["--total_train_steps", "3"], 2),
+                                 (base + ["--total_train_steps", "5", "--work_dir", str(tmp_path / "straight")], 2)])
     files = sorted(os.listdir(tmp_path / "run" / "3"))
     assert any(f.startswith("weights_tp_rank_world_size=0_2") for f in files) and any(
         f.startswith("weights_tp_rank_world_size=1_2") for f in files), files
     resumed = _losses(_run(base + saving + ["--total_train_steps", "5", "--resume_path", str(tmp_path / "run" / "3")], nproc=2))
-    straight = dict(_losses(_run(base + ["--total_train_steps", "5", "--work_dir", str(tmp_path / "straight")], nproc=2)))
+    straight = dict(_losses(straight_out))
     assert [s for s, _ in resumed] == [4, 5]
     for s, l in resumed:
         assert abs(l - straight[s]) < 2e-3, (s, l, straight[s])

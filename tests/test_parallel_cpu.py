@@ -299,7 +299,8 @@ def _train_worker(rank, world, layout):
 
     tp, dp, ep = layout[:3]
     cp = layout[3] if len(layout) > 3 else 1
-    setup_process_group_manager(tp_size=tp, cp_size=cp, pp_size=1, dp_size=dp, ep_size=ep)
+    replicate = bool(layout[4]) if len(layout) > 4 else False      # reference semantics: EP ranks read identical tokens
+    setup_process_group_manager(tp_size=tp, cp_size=cp, pp_size=1, dp_size=dp, ep_size=ep, ep_replicate_data=replicate)
     name = "qwen3_moe" if ep > 1 else "qwen3"
     cfg = TinyCfg(model_type=name, tie_word_embeddings=(ep == 1), router_aux_loss_coef=0.0)
     ctx = ParallelContext.from_pgm(sequence_parallel=tp > 1)
@@ -345,8 +346,8 @@ def _train_worker(rank, world, layout):
         assert rel_err(p.detach(), want) < 2e-3, f"{n}: {rel_err(p.detach(), want)}"
 
 
-@pytest.mark.parametrize("layout", [(2, 2, 1), (2, 1, 2), (1, 2, 2), (1, 2, 1, 2), (2, 1, 1, 2)],
-                         ids=["tp2dp2", "tp2ep2", "dp2ep2", "cp2dp2", "tp2cp2"])
+@pytest.mark.parametrize("layout", [(2, 2, 1), (2, 1, 2), (1, 2, 2), (1, 2, 1, 2), (2, 1, 1, 2), (1, 2, 2, 1, 1)],
+                         ids=["tp2dp2", "tp2ep2", "dp2ep2", "cp2dp2", "tp2cp2", "dp2ep2-replicated"])
 def test_mixed_layout_training_tracks_single_process(layout):
     run_distributed(_train_worker, 4, layout)
 

@@ -352,6 +352,11 @@ def test_mixed_layout_training_tracks_single_process(layout):
     run_distributed(_train_worker, 4, layout)
 
 
+def test_3d_layout_tp2_cp2_dp2_tracks_single_process():
+    """The flagship 3-D layout (BASELINE: Qwen3-8B TP2-CP2-DP2 + SP) on eight CPU processes."""
+    run_distributed(_train_worker, 8, (2, 2, 1, 2))
+
+
 def _pp_train_worker(rank, world, tp, dp, tie):
     """Pipeline stages (1F1B) combined with TP or DP, through clipped optimiser steps: the tied embedding / LM head lives on
     both the first and the last stage and must be counted once in the global norm."""

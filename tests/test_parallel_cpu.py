@@ -300,6 +300,10 @@ def _train_worker(rank, world, layout):
     tp, dp, ep = layout[:3]
     cp = layout[3] if len(layout) > 3 else 1
     replicate = bool(layout[4]) if len(layout) > 4 else False      # reference semantics: EP ranks read identical tokens
+    zz = bool(layout[5]) if len(layout) > 5 else False
+    from scaletorch_b200.parallel.context_parallel import zigzag
+
+    zigzag.set_enabled(zz)
     setup_process_group_manager(tp_size=tp, cp_size=cp, pp_size=1, dp_size=dp, ep_size=ep, ep_replicate_data=replicate)
     name = "qwen3_moe" if ep > 1 else "qwen3"
     cfg = TinyCfg(model_type=name, tie_word_embeddings=(ep == 1), router_aux_loss_coef=0.0)
@@ -329,7 +333,10 @@ def _train_worker(rank, world, layout):
             model.reset()
         r = pgm.data_rank
         xs, ys = x[2 * r:2 * r + 2], y[2 * r:2 * r + 2]
-        if cp > 1:
+        if cp > 1 and zz:
+            S_ = xs.shape[1]
+            xs, ys = zigzag.take(xs, S_, cp, pgm.cp_rank).contiguous(), zigzag.take(ys, S_, cp, pgm.cp_rank).contiguous()
+        elif cp > 1:
             n = xs.shape[1] // cp
             xs, ys = xs[:, pgm.cp_rank * n:(pgm.cp_rank + 1) * n].contiguous(), ys[:, pgm.cp_rank * n:(pgm.cp_rank + 1) * n].contiguous()
         lp = (model.module if hasattr(model, "module") else model).loss(xs, ys)
@@ -346,8 +353,9 @@ def _train_worker(rank, world, layout):
         assert rel_err(p.detach(), want) < 2e-3, f"{n}: {rel_err(p.detach(), want)}"
 
 
-@pytest.mark.parametrize("layout", [(2, 2, 1), (2, 1, 2), (1, 2, 2), (1, 2, 1, 2), (2, 1, 1, 2), (1, 2, 2, 1, 1)],
-                         ids=["tp2dp2", "tp2ep2", "dp2ep2", "cp2dp2", "tp2cp2", "dp2ep2-replicated"])
+@pytest.mark.parametrize("layout", [(2, 2, 1), (2, 1, 2), (1, 2, 2), (1, 2, 1, 2), (2, 1, 1, 2), (1, 2, 2, 1, 1),
+                                    (2, 1, 1, 2, 0, 1)],
+                         ids=["tp2dp2", "tp2ep2", "dp2ep2", "cp2dp2", "tp2cp2", "dp2ep2-replicated", "tp2cp2-zigzag"])
 def test_mixed_layout_training_tracks_single_process(layout):
     run_distributed(_train_worker, 4, layout)
 

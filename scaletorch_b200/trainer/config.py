@@ -143,6 +143,7 @@ class TrainingArguments:
     max_tokens: int | None = field(default=None, metadata={"help": "Stop after this many trained tokens"})
     native_loader: bool = field(default=False, metadata={"help": "Produce micro-batches with the C++ worker threads (data/native_loader.py); synthetic or flat-token data"})
     token_file: str | None = field(default=None, metadata={"help": "Flat int32 token file (.npy / raw .bin) for --native_loader"})
+    zero_stage: int = field(default=0, metadata={"help": "1 = shard AdamW state and update over the gradient-sync group (trainer/zero.py)"})
     use_cuda_graph: bool = field(default=False, metadata={"help": "Replay the whole step from a CUDA graph (trainer/graphed.py)"})
     log_lag: int = field(default=1, metadata={"help": "Log step i after enqueueing step i+lag (0 = synchronous logging)"})
     total_train_steps: int | None = field(default=None, metadata={"help": "Stop after this many steps"})

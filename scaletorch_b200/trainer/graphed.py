@@ -59,6 +59,8 @@ class GraphedTrainStep:
 
         if not torch.cuda.is_available() or not isinstance(optimizer, FusedAdamW):
             return False
+        if hasattr(optimizer, "shards"):        # ZeRO-1 broadcasts parameters through c10d: not captured
+            return False
         if pgm and (pgm.ep_world_size > 1 or pgm.tp_world_size > 1):
             # validated on hardware: single GPU, DP (2/4/8 ranks) and CP.  TP2+SP hung inside / after capture in the one
             # run made (gpurun_out/tp2_graph.log, round 1) and EP invalidated the capture: both stay eager until debugged

@@ -96,8 +96,15 @@ def create_optimizer(model: torch.nn.Module, config, device: torch.device):
 
         store = get_store(raw)
         norm_group = pgm.mp_group if (pgm and len(pgm.mp_group_ids) > 1) else None
-        return FusedAdamW(store, lr=lr, betas=betas, weight_decay=wd,
-                          max_grad_norm=getattr(config, "max_grad_norm", None), norm_group=norm_group)
+        kw = dict(lr=lr, betas=betas, weight_decay=wd, max_grad_norm=getattr(config, "max_grad_norm", None),
+                  norm_group=norm_group)
+        if getattr(config, "zero_stage", 0) >= 1 and pgm and pgm.grad_sync_world_size > 1:
+            from .zero import ZeroFusedAdamW
+
+            return ZeroFusedAdamW(store, dense_group=pgm.grad_sync_group,
+                                  expert_group=pgm.expert_grad_sync_group if pgm.expert_grad_sync_world_size > 1 else None,
+                                  **kw)
+        return FusedAdamW(store, **kw)
     params = [p for p in raw.parameters() if p.requires_grad]
     if opt == "adamw":
         return torch.optim.AdamW(params, lr=lr, betas=betas, weight_decay=wd)

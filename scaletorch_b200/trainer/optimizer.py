@@ -33,12 +33,13 @@ def _small_all_reduce(t: torch.Tensor, group) -> None:
 class FusedAdamW(torch.optim.Optimizer):
     def __init__(self, store: FlatParamStore, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8,
                  weight_decay: float = 0.01, max_grad_norm: float | None = None, norm_group=None,
-                 norm_scale_tp_replicated: bool = True):
+                 norm_scale_tp_replicated: bool = True, _alloc_state: bool = True):
         self.store = store
         defaults = dict(lr=lr, betas=tuple(betas), eps=eps, weight_decay=weight_decay)
         super().__init__(store.parameters(), defaults)
-        self.exp_avg = torch.zeros(store.total_numel, dtype=torch.float32, device=store.device)
-        self.exp_avg_sq = torch.zeros(store.total_numel, dtype=torch.float32, device=store.device)
+        if _alloc_state:
+            self.exp_avg = torch.zeros(store.total_numel, dtype=torch.float32, device=store.device)
+            self.exp_avg_sq = torch.zeros(store.total_numel, dtype=torch.float32, device=store.device)
         self.step_count = 0
         self.max_grad_norm = max_grad_norm
         self.norm_group = norm_group
@@ -141,6 +142,11 @@ class FusedAdamW(torch.optim.Optimizer):
         coef = None
         if self.max_grad_norm is not None and self.max_grad_norm > 0:
             coef, _ = self.compute_clip()
+        self._apply_update(g, coef, grad_scale)
+        return loss
+
+    def _apply_update(self, g: dict, coef, grad_scale: float) -> None:
+        """AdamW over the flat buffers: one launch, or two when the expert range carries its own gradient scale."""
         st = self.store
         ranges = [(0, st.total_numel, grad_scale)]
         if self.expert_grad_scale != 1.0:
@@ -150,7 +156,6 @@ class FusedAdamW(torch.optim.Optimizer):
                 fused_adamw_step(st.param_flat[lo:hi], st.grad_flat[lo:hi], self.exp_avg[lo:hi], self.exp_avg_sq[lo:hi],
                                  lr=g["lr"], betas=g["betas"], eps=g["eps"], weight_decay=g["weight_decay"],
                                  step=max(self.step_count, 1), clip_coef=coef, grad_scale=gs, hyper=self._hyper_dev)
-        return loss
 
     def zero_grad(self, set_to_none: bool = True) -> None:
         self.store.zero_grad(set_to_zero=False)

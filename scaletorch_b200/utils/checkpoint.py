@@ -317,6 +317,9 @@ class CheckpointManager:
 
     def save_checkpoint(self, model: nn.Module, optimizer, trained_steps: int, trained_tokens: int, out_dir: str,
                         extra: dict | None = None) -> str | None:
+        # a sharded (ZeRO-1) optimiser assembles its state collectively: every rank must take part before the
+        # non-writing ranks leave
+        opt_state = optimizer.state_dict() if (optimizer is not None and hasattr(optimizer, "shards")) else None
         if not self.cp_dp_first:
             return None
         os.makedirs(out_dir, exist_ok=True)
@@ -324,7 +327,7 @@ class CheckpointManager:
         raw = self._unwrap(model)
         payload = {
             "model": {k: v.detach().cpu() for k, v in raw.state_dict().items()},
-            "optimizer": _to_cpu(optimizer.state_dict()) if optimizer is not None else None,
+            "optimizer": _to_cpu(opt_state if opt_state is not None else optimizer.state_dict()) if optimizer is not None else None,
             "trained_steps": int(trained_steps),
             "trained_tokens": int(trained_tokens),
             "rng": {"torch": torch.get_rng_state(),

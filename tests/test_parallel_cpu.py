@@ -495,3 +495,64 @@ def test_hf_checkpoint_loads_into_shards(tmp_path, name, layout):
     m1, mc = create_model(cfg, torch.float32, torch.device("cpu"))
     save_file(export_hf_state_dict(m1, mc), str(d / "model.safetensors"))
     run_distributed(_hf_load_worker, 4, str(d), layout, name)
+
+
+# ------------------------------------------------------------------ ZeRO-1 (sharded optimiser state)
+def _zero_worker(rank, world, layout):
+    """The sharded optimiser must produce exactly the parameters of the unsharded one, hold 1/N of the state, and
+    exchange checkpoints with it in both directions."""
+    import copy
+
+    from scaletorch_b200.parallel.context import ParallelContext
+    from scaletorch_b200.parallel.data_parallel.data_parallel import DataParallelBucket, get_store
+    from scaletorch_b200.parallel.process_group import process_group_manager as pgm
+    from scaletorch_b200.parallel.process_group import setup_process_group_manager
+    from scaletorch_b200.trainer.optimizer import FusedAdamW
+    from scaletorch_b200.trainer.zero import ZeroFusedAdamW
+    from scaletorch_b200.utils.sharding import load_from_unsharded
+
+    dp, ep = layout
+    setup_process_group_manager(tp_size=1, cp_size=1, pp_size=1, dp_size=dp, ep_size=ep)
+    name = "qwen3_moe" if ep > 1 else "qwen3"
+    cfg = TinyCfg(model_type=name, tie_word_embeddings=(ep == 1), router_aux_loss_coef=0.0)
+    ctx = ParallelContext.from_pgm()
+    full, a = _models(cfg, name, ctx)
+    _, b = _models(cfg, name, ctx)
+    for m in (a, b):
+        load_from_unsharded(m, dict(full.named_parameters()), cfg, ep=ep, ep_rank=pgm.ep_rank)
+    norm_group = pgm.mp_group if len(pgm.mp_group_ids) > 1 else None
+    kw = dict(lr=1e-2, weight_decay=0.01, max_grad_norm=0.05, norm_group=norm_group)
+    exp_group = pgm.expert_grad_sync_group if pgm.expert_grad_sync_world_size > 1 else None
+    sa, sb = get_store(a, pgm.grad_sync_group), get_store(b, pgm.grad_sync_group)
+    ma, mb = DataParallelBucket(a, bucket_size=5000), DataParallelBucket(b, bucket_size=5000)
+    oa = FusedAdamW(sa, **kw)
+    ob = ZeroFusedAdamW(sb, dense_group=pgm.grad_sync_group, expert_group=exp_group, **kw)
+    assert ob.state_bytes() < oa.exp_avg.numel() * 8 * 0.8
+    torch.manual_seed(17)
+    r = pgm.data_rank
+
+    def steps(n, models):
+        for _ in range(n):
+            ids = torch.randint(0, cfg.vocab_size, (2 * pgm.data_world_size, 17))
+            x, y = ids[2 * r:2 * r + 2, :-1], ids[2 * r:2 * r + 2, 1:]
+            for m, o in models:
+                o.zero_grad()
+                m.reset()
+                m.module.loss(x, y).backward()
+                o.step()
+
+    steps(3, [(ma, oa), (mb, ob)])
+    assert torch.equal(sa.param_flat, sb.param_flat)
+    # checkpoints are interchangeable: sharded -> full tensors == the unsharded optimiser's state, and back
+    sd_b, sd_a = ob.state_dict(), oa.state_dict()
+    assert sd_b["exp_avg"].shape == sd_a["exp_avg"].shape
+    assert torch.allclose(sd_b["exp_avg"], sd_a["exp_avg"].cpu()) and torch.allclose(sd_b["exp_avg_sq"], sd_a["exp_avg_sq"].cpu())
+    oc = ZeroFusedAdamW(sb, dense_group=pgm.grad_sync_group, expert_group=exp_group, **kw)
+    oc.load_state_dict(copy.deepcopy(sd_a))
+    steps(2, [(ma, oa), (mb, oc)])
+    assert torch.equal(sa.param_flat, sb.param_flat)
+
+
+@pytest.mark.parametrize("world,layout", [(2, (2, 1)), (4, (2, 2))], ids=["dp2", "dp2ep2"])
+def test_zero1_matches_unsharded_optimizer(world, layout):
+    run_distributed(_zero_worker, world, layout)

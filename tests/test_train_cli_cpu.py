@@ -51,7 +51,9 @@ def test_two_process_layouts(tmp_path):
     layouts = {"tp2sp": ["--tensor_parallel_size", "2", "--sequence_parallel", "true"],
                "dp2ga2": ["--data_parallel_size", "2", "--gradient_accumulation_steps", "2"],
                "pp2ga2": ["--pipeline_parallel_size", "2", "--gradient_accumulation_steps", "2"],
-               "cp2": ["--context_parallel_size", "2"]}
+               "cp2": ["--context_parallel_size", "2"],
+               "dp2zero1": ["--data_parallel_size", "2", "--zero_stage", "1", "--save_model_checkpoint", "true",
+                            "--save_frequency", "2"]}
     jobs = [(["--model_name_or_path", "tiny-qwen3", "--num_attention_heads", "4", "--num_key_value_heads", "2",
               "--total_train_steps", "4", "--work_dir", str(tmp_path / k)] + v, 2) for k, v in layouts.items()]
     for k, out in zip(layouts, _run_many(jobs)):

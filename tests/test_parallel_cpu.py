@@ -301,6 +301,7 @@ def _train_worker(rank, world, layout):
     cp = layout[3] if len(layout) > 3 else 1
     replicate = bool(layout[4]) if len(layout) > 4 else False      # reference semantics: EP ranks read identical tokens
     zz = bool(layout[5]) if len(layout) > 5 else False
+    gc = bool(layout[6]) if len(layout) > 6 else False             # per-layer activation recomputation
     from scaletorch_b200.parallel.context_parallel import zigzag
 
     zigzag.set_enabled(zz)
@@ -339,7 +340,7 @@ def _train_worker(rank, world, layout):
         elif cp > 1:
             n = xs.shape[1] // cp
             xs, ys = xs[:, pgm.cp_rank * n:(pgm.cp_rank + 1) * n].contiguous(), ys[:, pgm.cp_rank * n:(pgm.cp_rank + 1) * n].contiguous()
-        lp = (model.module if hasattr(model, "module") else model).loss(xs, ys)
+        lp = (model.module if hasattr(model, "module") else model).loss(xs, ys, gradient_checkpointing=gc)
         lp.backward()
         opt.step()
         tot = lp.detach().clone()
@@ -354,8 +355,9 @@ def _train_worker(rank, world, layout):
 
 
 @pytest.mark.parametrize("layout", [(2, 2, 1), (2, 1, 2), (1, 2, 2), (1, 2, 1, 2), (2, 1, 1, 2), (1, 2, 2, 1, 1),
-                                    (2, 1, 1, 2, 0, 1)],
-                         ids=["tp2dp2", "tp2ep2", "dp2ep2", "cp2dp2", "tp2cp2", "dp2ep2-replicated", "tp2cp2-zigzag"])
+                                    (2, 1, 1, 2, 0, 1), (2, 1, 2, 1, 0, 0, 1), (2, 1, 1, 2, 0, 1, 1)],
+                         ids=["tp2dp2", "tp2ep2", "dp2ep2", "cp2dp2", "tp2cp2", "dp2ep2-replicated", "tp2cp2-zigzag",
+                              "tp2ep2-recompute", "tp2cp2-zigzag-recompute"])
 def test_mixed_layout_training_tracks_single_process(layout):
     run_distributed(_train_worker, 4, layout)
 

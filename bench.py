@@ -314,10 +314,23 @@ def run_ours(args):
 # ------------------------------------------------------------------------------------ reference
 def run_reference(args):
     ref_dir = os.path.join(ROOT, "baseline", "_ref")
+    sys.path.insert(0, os.path.join(ROOT, "baseline"))  # run_reference.py, install_reference.py + the colorama stand-in
+    rank, local_rank, world = dist_env()
     if not os.path.isdir(os.path.join(ref_dir, "scaletorch")):
-        print(json.dumps({"impl": "reference", "unavailable": "baseline/_ref/scaletorch not installed (pip --target baseline/_ref /root/reference)"}))
+        # lazily install wherever /root/reference is visible (local rank 0 installs, the others wait for the files)
+        import install_reference
+
+        if local_rank == 0:
+            install_reference.ensure()
+        else:
+            for _ in range(600):
+                if install_reference.installed():
+                    break
+                time.sleep(0.5)
+    if not os.path.isdir(os.path.join(ref_dir, "scaletorch")):
+        if rank == 0:
+            print(json.dumps({"impl": "reference", "unavailable": "baseline/_ref/scaletorch not installed and /root/reference not visible"}))
         return
-    sys.path.insert(0, os.path.join(ROOT, "baseline"))  # run_reference.py + the colorama stand-in
     try:
         import run_reference
 

@@ -15,6 +15,53 @@ import os
 import sys
 
 
+def random_checkpoint(model_dir: str, local_rank: int, limit_gb: float = 2.6):
+    """A random-weight HF-layout ``model.safetensors`` next to a copy of ``config.json`` (under /tmp), for models with
+    tied embeddings only.  Why: without a checkpoint the reference materialises with ``to_empty`` + ``reset_parameters``
+    (`scaletorch/utils/checkpoint.py:90-97`), which unties the LM head and never initialises it (`model_qwen3.py:313-322`
+    skips ``final_proj`` when ``tie_word_embeddings``): 751.6 M instead of 596.0 M parameters for Qwen3-0.6B and a NaN
+    loss from the uninitialised matrix.  Its stock checkpoint path (`checkpoint.py:99-142`) ties the head
+    (``_handle_final_projection``) and then re-randomises everything with ``reset_parameters`` -- so a file of random
+    weights gives exactly "random-init weights of that architecture" through the reference's own loader.
+    Returns (dir to pass as ``model_name_or_path``, note)."""
+    import shutil
+
+    import torch
+
+    cfg = json.load(open(os.path.join(model_dir, "config.json")))
+    if not cfg.get("tie_word_embeddings", False) or cfg.get("model_type") not in ("qwen3", "llama", "qwen2"):
+        return model_dir, "no-checkpoint init (untied head: nothing to work around)"
+    H, L, V = cfg["hidden_size"], cfg["num_hidden_layers"], cfg["vocab_size"]
+    nh, nkv, I = cfg["num_attention_heads"], cfg["num_key_value_heads"], cfg["intermediate_size"]
+    hd = cfg.get("head_dim") or H // nh
+    per_layer = {"input_layernorm": (H,), "post_attention_layernorm": (H,), "mlp.gate_proj": (I, H), "mlp.up_proj": (I, H),
+                 "mlp.down_proj": (H, I), "self_attn.q_proj": (nh * hd, H), "self_attn.k_proj": (nkv * hd, H),
+                 "self_attn.v_proj": (nkv * hd, H), "self_attn.o_proj": (H, nh * hd)}
+    if cfg["model_type"] in ("qwen3", "qwen2"):
+        per_layer.update({"self_attn.q_norm": (hd,), "self_attn.k_norm": (hd,)})
+    n = V * H + H + L * sum(int(torch.Size(s).numel()) for s in per_layer.values())
+    if n * 2 / 1e9 > limit_gb:
+        return model_dir, f"no-checkpoint init (random checkpoint would be {n * 2 / 1e9:.1f} GB)"
+    out = os.path.join("/tmp", "stb_ref_ckpt", os.path.basename(model_dir.rstrip("/")))
+    done = os.path.join(out, ".done")
+    if local_rank == 0 and not os.path.exists(done):
+        from safetensors.torch import save_file
+
+        os.makedirs(out, exist_ok=True)
+        for f in os.listdir(model_dir):
+            if f.endswith(".json") or f.endswith(".txt"):
+                shutil.copy(os.path.join(model_dir, f), os.path.join(out, f))
+        g = torch.Generator().manual_seed(1234)
+        mk = lambda shape: (torch.ones(shape) if len(shape) == 1 else torch.randn(shape, generator=g) * 0.02).to(torch.bfloat16)  # noqa: E731
+        sd = {"model.embed_tokens.weight": mk((V, H)), "model.norm.weight": mk((H,))}
+        for i in range(L):
+            for k, shape in per_layer.items():
+                sd[f"model.layers.{i}.{k}.weight"] = mk(shape)
+        save_file(sd, os.path.join(out, "model.safetensors"))
+        open(done, "w").write("ok")
+    return out, "random-weight checkpoint through the reference's HF loader (keeps the LM head tied)"
+
+
 def main(args, root, ref_dir, ClockSampler, timed_region, build_config_dict, dist_env, baseline_table):
     sys.path.insert(0, ref_dir)
     os.environ.setdefault("FLASH_ATTEN", "1")
@@ -36,7 +83,7 @@ def main(args, root, ref_dir, ClockSampler, timed_region, build_config_dict, dis
     if world != args.gpus:
         raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
     dp, cfgd = build_config_dict(args, world)
-    model_dir = os.path.join(root, "configs", args.model)
+    model_dir, init_note = random_checkpoint(os.path.join(root, "configs", args.model), local_rank)
     cfg = ScaleTorchArguments(
         model_name_or_path=model_dir, micro_batch_size=args.micro_batch_size, sequence_length=args.seq_len,
         gradient_accumulation_steps=args.grad_accum, tensor_parallel_size=args.tp, context_parallel_size=args.cp,
@@ -46,6 +93,8 @@ def main(args, root, ref_dir, ClockSampler, timed_region, build_config_dict, dis
     _, _, _, _, device = initialize_distributed_training(cfg)
     if device.type == "cuda":
         torch.cuda.set_device(device)
+    if world > 1:
+        dist.barrier()  # local rank 0 has finished writing the checkpoint
     model, model_config = create_model(cfg, dtype, device)
     model.train()
     optimizer = create_optimizer(model, cfg, device)
@@ -117,6 +166,7 @@ def main(args, root, ref_dir, ClockSampler, timed_region, build_config_dict, dis
             "dtype": str(dtype).replace("torch.", ""), "data": "synthetic tokens, random-init weights",
             "impl": "reference", "config": cfgd, "tokens_per_s_per_gpu": value / world, "num_params": num_params,
             "clocks": clocks, "e2e": e2e, "gpu_launches": 0,
+            "init": init_note,
             "notes": "unmodified reference (PyTorch + cuBLAS + SDPA + NCCL); colorama replaced by a stand-in module",
         }), flush=True)
     if world > 1 and dist.is_initialized():

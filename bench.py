@@ -189,14 +189,16 @@ def run_ours(args):
     if args.cuda_graph and GraphedTrainStep.supported(cfg, optimizer, model):
         graphed = GraphedTrainStep(model, optimizer, cfg, device, warmup=2)
     launches_per_graph = [0]
+    per_kernel_graph: dict = {}
 
     def step_with(src):
         if graphed is not None:
             was_captured = graphed.graph is not None
-            c0 = _native.launch_count
+            c0, k0 = _native.launch_count, dict(_native.launch_counts)
             loss = graphed(src)
             if not was_captured and graphed.graph is not None:
                 launches_per_graph[0] = _native.launch_count - c0      # kernels recorded into the graph
+                per_kernel_graph.update({k: v - k0.get(k, 0) for k, v in _native.launch_counts.items() if v > k0.get(k, 0)})
             return loss
         optimizer.zero_grad()
         if hasattr(model, "reset"):
@@ -251,11 +253,22 @@ def run_ours(args):
             dist.barrier()
             dist.destroy_process_group()
         return
-    l0 = _native.launch_count
+    l0, k0 = _native.launch_count, dict(_native.launch_counts)
     ms = timed_region(torch, dist, world, lambda: step_with(staged), args.steps)
     launches = _native.launch_count - l0
+    per_kernel = {k: v - k0.get(k, 0) for k, v in _native.launch_counts.items() if v > k0.get(k, 0)}
     if graphed is not None and graphed.graph is not None:
         launches = launches_per_graph[0] * args.steps              # replayed from the graph: same kernels every step
+        per_kernel = {k: v * args.steps for k, v in per_kernel_graph.items()}
+    comm_kernels = ("stb_allreduce_f32", "stb_reduce_scatter_f32", "stb_adamw_shard_bcast", "stb_allreduce_tiny_f32",
+                    "stb_embedding_bwd_peers", "stb_ag_gemm_bf16", "stb_gemm_rs_bf16", "stb_allreduce_bf16",
+                    "stb_allreduce_oneshot_bf16", "stb_ep_push", "stb_ep_pull", "stb_ep_exchange_counts", "stb_symm_barrier")
+    # which transport the gradient synchronisation used: NVLS multimem / peer loads-stores / c10d-NCCL
+    store = getattr(model, "store", None) or getattr(model, "_stb_store", None)
+    gw = getattr(store, "grad_window", None)
+    dp_transport = None
+    if world > 1 and dp * args.cp * (args.ep if args.ep > 1 else 1) > 1:
+        dp_transport = "nccl" if gw is None else ("nvls" if gw.mc_ptr else "p2p")
     clocks = sampler.stop() if rank == 0 else {}
 
     # end-to-end: public API, per-step pinned H2D of the batch + D2H read of the loss
@@ -294,6 +307,8 @@ def run_ours(args):
             "tokens_per_s_per_gpu": value / world,
             "mfu_pct_of_nominal_2.25PF": get_mfu(value / world, num_params, model_config, 2.25e15, args.seq_len),
             "num_params": num_params, "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
+            "comm_kernel_launches": {k: per_kernel.get(k, 0) for k in comm_kernels if per_kernel.get(k, 0)},
+            "dp_transport": dp_transport, "optimizer": type(optimizer).__name__,
             "cuda_graph": bool(graphed is not None and graphed.graph is not None),
             "native_lib": str(_native.lib_path()),
         }

@@ -279,6 +279,164 @@ __global__ void __launch_bounds__(256)
   grid_finish_cross_gpu_barrier(flag_pages, rank, world, slot, epoch + 1, epoch_arg);   // staging areas may be reused
 }
 
+// ---- ZeRO-1 over peer memory: reduce-scatter of gradient buckets + sharded AdamW that broadcasts the new parameters ----
+// Every rank owns one contiguous shard [own_lo, own_hi) of the flat fp32 gradient / bf16 parameter buffers.  A bucket
+// [offset, offset + n) is reduced only on the rank(s) whose shard it intersects: that rank sums the range over all
+// ranks (multimem.ld_reduce through the switch, or peer loads), scales it and stores it into ITS buffer alone -- the
+// other ranks never need the reduced gradient, so the broadcast half of an all-reduce (n x 4 bytes of NVLink ingress
+// and HBM writes per rank) disappears, and AdamW touches 1/world of the elements.  What travels instead is the bf16
+// parameter shard after the update (2 bytes per parameter).
+// Reference counterpart: the bucket all-reduce of scaletorch/parallel/data_parallel/bucket.py:58-78 followed by a
+// replicated torch.optim.AdamW step (trainer/model_builder.py:119-134).
+template <bool MULTIMEM>
+__global__ void __launch_bounds__(512)
+    reduce_scatter_f32_kernel(float* const* bufs, const float* mc, uint32_t* const* flag_pages, long offset, long n,
+                              long own_lo, long own_hi, float scale, int rank, int world, int slot, uint32_t epoch_arg) {
+  const uint32_t epoch = symm_epoch_load(flag_pages, rank, slot, epoch_arg);
+  grid_cross_gpu_barrier(flag_pages, rank, world, slot, epoch);   // every rank's bucket is complete
+  const long lo = max(offset, own_lo), hi = min(offset + n, own_hi);       // multiples of 4 except possibly `hi`
+  if (lo < hi) {
+    float* mine = bufs[rank];
+    const long v0 = lo >> 2, v1 = hi >> 2;
+    constexpr int U = 8;
+    const long stride = long(gridDim.x) * blockDim.x;
+    for (long i0 = v0 + long(blockIdx.x) * blockDim.x + threadIdx.x; i0 < v1; i0 += stride * U) {
+      float4 acc[U];
+      if (MULTIMEM) {
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const long i = i0 + u * stride;
+          if (i < v1) acc[u] = multimem_ld_reduce_f4(mc + (i << 2));
+        }
+      } else {
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const long i = i0 + u * stride;
+          acc[u] = (i < v1) ? ld_peer_f4(mine + (i << 2)) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        for (int p = 1; p < world; ++p) {
+          const float* src = bufs[(rank + p) % world];
+          float4 v[U];
+#pragma unroll
+          for (int u = 0; u < U; ++u) {
+            const long i = i0 + u * stride;
+            v[u] = (i < v1) ? ld_peer_f4(src + (i << 2)) : make_float4(0.f, 0.f, 0.f, 0.f);
+          }
+#pragma unroll
+          for (int u = 0; u < U; ++u) {
+            acc[u].x += v[u].x; acc[u].y += v[u].y; acc[u].z += v[u].z; acc[u].w += v[u].w;
+          }
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long i = i0 + u * stride;
+        if (i < v1) {
+          acc[u].x *= scale; acc[u].y *= scale; acc[u].z *= scale; acc[u].w *= scale;
+          *reinterpret_cast<float4*>(mine + (i << 2)) = acc[u];
+        }
+      }
+    }
+    // scalar tail (hi not a multiple of 4): plain peer loads
+    for (long i = (v1 << 2) + long(blockIdx.x) * blockDim.x + threadIdx.x; i < hi; i += stride) {
+      float acc = 0.f;
+      for (int p = 0; p < world; ++p) acc += bufs[p][i];
+      mine[i] = acc * scale;
+    }
+  }
+  // peers may overwrite their gradient buffers (next backward) only after every owner has read them
+  grid_finish_cross_gpu_barrier(flag_pages, rank, world, slot, epoch + 1, epoch_arg);
+}
+
+STB_DEVICE void multimem_st_b128(void* mc, const uint4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc), "r"(v.x), "r"(v.y),
+               "r"(v.z), "r"(v.w)
+               : "memory");
+}
+STB_DEVICE void st_peer_b128(void* p, const uint4& v) {
+  asm volatile("st.global.relaxed.sys.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
+               : "memory");
+}
+
+// AdamW on this rank's shard: g / m / v are local fp32 arrays of `n` elements (n % 8 == 0), the bf16 parameters are
+// read from the local copy at element `p_off` of the symmetric parameter buffer and the updated values are written to
+// EVERY rank's copy (one multimem.st per 16 bytes through the switch, or one store per peer).  Opening barrier: no
+// rank may still be reading parameters (its backward has finished); closing barrier: when the kernel completes on a
+// rank, every rank's writes into that rank's copy have landed.  hyper = {lr, 1 - beta1^t, 1 - beta2^t} on the device.
+template <bool MULTIMEM>
+__global__ void __launch_bounds__(512)
+    adamw_shard_bcast_kernel(__nv_bfloat16* const* pbufs, __nv_bfloat16* pmc, uint32_t* const* flag_pages, long p_off,
+                             const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v, long n,
+                             float beta1, float beta2, float eps, float weight_decay,
+                             const float* __restrict__ clip_coef_ptr, float grad_scale, const float* __restrict__ hyper,
+                             int rank, int world, int slot, uint32_t epoch_arg) {
+  const uint32_t epoch = symm_epoch_load(flag_pages, rank, slot, epoch_arg);
+  grid_cross_gpu_barrier(flag_pages, rank, world, slot, epoch);
+  const float lr = hyper[0], inv_bc1 = 1.f / hyper[1], inv_sqrt_bc2 = rsqrtf(hyper[2]);
+  const float clip = (clip_coef_ptr ? *clip_coef_ptr : 1.f) * grad_scale;
+  const float decay = 1.f - lr * weight_decay;
+  const __nv_bfloat16* p_local = pbufs[rank] + p_off;
+  const long nvec = n >> 3;
+  for (long i = long(blockIdx.x) * blockDim.x + threadIdx.x; i < nvec; i += long(gridDim.x) * blockDim.x) {
+    const float4 g0 = reinterpret_cast<const float4*>(g)[2 * i], g1 = reinterpret_cast<const float4*>(g)[2 * i + 1];
+    const float4 m0 = reinterpret_cast<const float4*>(m)[2 * i], m1 = reinterpret_cast<const float4*>(m)[2 * i + 1];
+    const float4 v0 = reinterpret_cast<const float4*>(v)[2 * i], v1 = reinterpret_cast<const float4*>(v)[2 * i + 1];
+    const uint4 pr = reinterpret_cast<const uint4*>(p_local)[i];
+    float ga[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+    float ma[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
+    float va[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+    const uint32_t pu[4] = {pr.x, pr.y, pr.z, pr.w};
+    float pf[8];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float2 f = unpack_bf16x2(pu[j]);
+      pf[2 * j] = f.x; pf[2 * j + 1] = f.y;
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float gj = ga[j] * clip;
+      ma[j] = beta1 * ma[j] + (1.f - beta1) * gj;
+      va[j] = beta2 * va[j] + (1.f - beta2) * gj * gj;
+      pf[j] = pf[j] * decay - lr * (ma[j] * inv_bc1) / (sqrtf(va[j]) * inv_sqrt_bc2 + eps);
+    }
+    reinterpret_cast<float4*>(m)[2 * i] = make_float4(ma[0], ma[1], ma[2], ma[3]);
+    reinterpret_cast<float4*>(m)[2 * i + 1] = make_float4(ma[4], ma[5], ma[6], ma[7]);
+    reinterpret_cast<float4*>(v)[2 * i] = make_float4(va[0], va[1], va[2], va[3]);
+    reinterpret_cast<float4*>(v)[2 * i + 1] = make_float4(va[4], va[5], va[6], va[7]);
+    const uint4 out = make_uint4(pack_bf16x2(pf[0], pf[1]), pack_bf16x2(pf[2], pf[3]), pack_bf16x2(pf[4], pf[5]),
+                                 pack_bf16x2(pf[6], pf[7]));
+    if (MULTIMEM) {
+      multimem_st_b128(pmc + p_off + (i << 3), out);
+    } else {
+      for (int p = 0; p < world; ++p) st_peer_b128(pbufs[(rank + p) % world] + p_off + (i << 3), out);
+    }
+  }
+  grid_finish_cross_gpu_barrier(flag_pages, rank, world, slot, epoch + 1, epoch_arg);
+}
+
+// In-place sum of `n` (<= 32) fp32 values living at element `offset` of every rank's symmetric buffer: every rank
+// reads all copies and writes the total into its OWN copy.  Used for the squared-norm partials of the sharded
+// optimiser; one CTA, two device barriers, no library call in the step.
+__global__ void __launch_bounds__(32)
+    allreduce_tiny_f32_kernel(float* const* bufs, uint32_t* const* flag_pages, long offset, int n, int rank, int world,
+                              int slot, uint32_t epoch_arg) {
+  const uint32_t epoch = symm_epoch_load(flag_pages, rank, slot, epoch_arg);
+  cross_gpu_barrier(flag_pages, rank, world, slot, epoch);          // every rank's partials are written
+  __syncwarp();
+  float acc = 0.f;
+  if (int(threadIdx.x) < n)
+    for (int p = 0; p < world; ++p) {
+      float x;
+      asm volatile("ld.global.relaxed.sys.f32 %0, [%1];" : "=f"(x) : "l"(bufs[p] + offset + threadIdx.x) : "memory");
+      acc += x;
+    }
+  __syncwarp();
+  cross_gpu_barrier(flag_pages, rank, world, slot, epoch + 1);      // everybody has read everybody's partials
+  __syncwarp();
+  if (int(threadIdx.x) < n) bufs[rank][offset + threadIdx.x] = acc;
+  if (threadIdx.x == 0) symm_epoch_store(flag_pages, rank, slot, epoch_arg, epoch + 2);
+}
+
 static int comm_grid(int sm_budget) {
   const int sms = sm_count();
   if (sm_budget <= 0 || sm_budget > sms) sm_budget = sms;
@@ -375,6 +533,61 @@ extern "C" int stb_embedding_bwd_peers(const void* bufs_dev, const void* flag_pa
   embedding_bwd_peers_kernel<<<comm_grid(sm_budget), 256, 0, stream>>>(
       (const uint8_t* const*)bufs_dev, (uint32_t* const*)flag_pages_dev, ids_off, dout_off, dW, T, H, vocab_start,
       vocab_local, scale, rank, world, slot, epoch);
+  STB_CHECK_LAUNCH();
+  return 0;
+}
+
+// Consumes 2 epochs.  The reduced, scaled range [max(offset, own_lo), min(offset + n, own_hi)) lands in this rank's
+// buffer only; `multicast_ptr` is the NVLS address of the SAME symmetric buffer (element 0), or NULL for peer loads.
+extern "C" int stb_reduce_scatter_f32(const void* bufs_dev, const void* multicast_ptr, const void* flag_pages_dev,
+                                      long offset_elems, long n, long own_lo, long own_hi, float scale, int rank,
+                                      int world, int slot, unsigned epoch, int sm_budget, cudaStream_t stream) {
+  STB_REQUIRE(world <= kMaxWorld && slot < kMaxSlots, "reduce_scatter: world %d / slot %d out of range", world, slot);
+  STB_REQUIRE(offset_elems % 4 == 0 && own_lo % 4 == 0, "reduce_scatter_f32: offsets must be multiples of 4 elements");
+  if (n == 0) return 0;
+  const int grid = comm_grid(sm_budget);
+  if (multicast_ptr != nullptr)
+    reduce_scatter_f32_kernel<true><<<grid, 512, 0, stream>>>((float* const*)bufs_dev, (const float*)multicast_ptr,
+                                                              (uint32_t* const*)flag_pages_dev, offset_elems, n, own_lo,
+                                                              own_hi, scale, rank, world, slot, epoch);
+  else
+    reduce_scatter_f32_kernel<false><<<grid, 512, 0, stream>>>((float* const*)bufs_dev, nullptr,
+                                                               (uint32_t* const*)flag_pages_dev, offset_elems, n, own_lo,
+                                                               own_hi, scale, rank, world, slot, epoch);
+  STB_CHECK_LAUNCH();
+  return 0;
+}
+
+// Consumes 2 epochs.  See adamw_shard_bcast_kernel.
+extern "C" int stb_adamw_shard_bcast(const void* pbufs_dev, void* p_multicast_ptr, const void* flag_pages_dev,
+                                     long p_offset_elems, const float* g, float* m, float* v, long n, float beta1,
+                                     float beta2, float eps, float weight_decay, const float* clip_coef,
+                                     float grad_scale, const float* hyper, int rank, int world, int slot,
+                                     unsigned epoch, int sm_budget, cudaStream_t stream) {
+  STB_REQUIRE(world <= kMaxWorld && slot < kMaxSlots, "adamw_shard_bcast: world %d / slot %d out of range", world, slot);
+  STB_REQUIRE(p_offset_elems % 8 == 0 && n % 8 == 0, "adamw_shard_bcast: offset and n must be multiples of 8 elements");
+  STB_REQUIRE(hyper != nullptr, "adamw_shard_bcast: hyper must point at {lr, bc1, bc2} in device memory");
+  const int grid = comm_grid(sm_budget);
+  if (p_multicast_ptr != nullptr)
+    adamw_shard_bcast_kernel<true><<<grid, 512, 0, stream>>>(
+        (__nv_bfloat16* const*)pbufs_dev, (__nv_bfloat16*)p_multicast_ptr, (uint32_t* const*)flag_pages_dev,
+        p_offset_elems, g, m, v, n, beta1, beta2, eps, weight_decay, clip_coef, grad_scale, hyper, rank, world, slot,
+        epoch);
+  else
+    adamw_shard_bcast_kernel<false><<<grid, 512, 0, stream>>>(
+        (__nv_bfloat16* const*)pbufs_dev, nullptr, (uint32_t* const*)flag_pages_dev, p_offset_elems, g, m, v, n, beta1,
+        beta2, eps, weight_decay, clip_coef, grad_scale, hyper, rank, world, slot, epoch);
+  STB_CHECK_LAUNCH();
+  return 0;
+}
+
+// Consumes 2 epochs.  n <= 32 fp32 values at element `offset` of every rank's symmetric buffer, summed in place.
+extern "C" int stb_allreduce_tiny_f32(const void* bufs_dev, const void* flag_pages_dev, long offset_elems, int n,
+                                      int rank, int world, int slot, unsigned epoch, cudaStream_t stream) {
+  STB_REQUIRE(world <= kMaxWorld && slot < kMaxSlots, "allreduce_tiny: world %d / slot %d out of range", world, slot);
+  STB_REQUIRE(n >= 1 && n <= 32, "allreduce_tiny: n %d out of range (1..32)", n);
+  allreduce_tiny_f32_kernel<<<1, 32, 0, stream>>>((float* const*)bufs_dev, (uint32_t* const*)flag_pages_dev,
+                                                  offset_elems, n, rank, world, slot, epoch);
   STB_CHECK_LAUNCH();
   return 0;
 }

@@ -28,12 +28,14 @@ STB_DEVICE uint32_t mapa_shared(uint32_t smem_addr, uint32_t rank) {
   return r;
 }
 // Arrive on an mbarrier that lives in another (or this) CTA of the cluster.
+// (default .release.cta semantics: the .release.cluster form costs MEMBAR.ALL.GPU + ERRBAR per arrive; the data these
+// barriers order -- TMA bytes, tensor-memory reads -- is ordered by complete_tx / tcgen05 fences, not by this arrive)
 STB_DEVICE void mbar_arrive_cluster(uint32_t cluster_addr) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
 // arrive + expect_tx on an mbarrier given by its shared::cluster address
 STB_DEVICE void mbar_arrive_expect_tx_cluster(uint32_t cluster_addr, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.release.cluster.shared::cluster.b64 _, [%0], %1;" ::"r"(cluster_addr),
+  asm volatile("mbarrier.arrive.expect_tx.shared::cluster.b64 _, [%0], %1;" ::"r"(cluster_addr),
                "r"(bytes)
                : "memory");
 }

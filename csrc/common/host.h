@@ -26,6 +26,13 @@ int make_tmap_3d(CUtensorMap* out, const void* base, int elem_bytes, uint64_t di
 int make_tmap_bshd(CUtensorMap* out, const void* base, int B, int S, int H, int D, long sb, long ss,
                    long sh, uint32_t box_d, uint32_t box_s);
 
+// CTA-pair GEMM (csrc/gemm_pair.cu): entry, its work model, and the k-split it would choose.
+namespace pair {
+int run(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc, int a_mn, int b_mn,
+        int out_fp32, int accumulate, int bn, int splits, cudaStream_t stream);
+float pick_config(int M, int N, int K, int out_fp32, int n_pairs, int* bn_out, int* splits_out);
+}  // namespace pair
+
 #define STB_CHECK_CUDA(expr)                                                              \
   do {                                                                                    \
     cudaError_t _e = (expr);                                                              \

@@ -18,6 +18,8 @@
 //                               (TMA reduce-add when accumulating; direct stores if C is unaligned)
 // The accumulator is double-buffered in TMEM so the epilogue of tile i overlaps
 // the main loop of tile i+1.
+#include <stdlib.h>
+
 #include "common/host.h"
 #include "common/ptx.cuh"
 
@@ -603,6 +605,27 @@ static int pick_bn(int M, int N) {
   return (t128 <= sms) ? 128 : 256;
 }
 
+// Same time unit as pair::pair_cost (csrc/gemm_pair.cu): a 64-deep k-block of a 128 x 256 tile at full tensor rate.
+// The single-CTA main loop runs below that rate because it is L2->SMEM bound (x1.12 for the 256-wide tile, x1.3 for
+// the 128-wide one, from profiles/gemm_v3_vs_cublas.jsonl).
+static float single_cost(int M, int N, int K, int out_fp32, int bn) {
+  const long tiles = long((M + kBM - 1) / kBM) * ((N + bn - 1) / bn);
+  const long waves = (tiles + sm_count() - 1) / sm_count();
+  const int kb = (K + kBK - 1) / kBK;
+  const float per = bn == 256 ? 1.12f : 0.65f;
+  return float(waves) * float(kb) * per + (bn == 256 ? 5.0f : 2.5f) * (out_fp32 ? 1.5f : 1.0f);
+}
+
+// 0 = never, 1 = whenever the shape is legal, 2 (default) = when the work model says the pair kernel is faster
+static int pair_policy() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("SCALETORCH_B200_GEMM_PAIR");
+    v = e ? atoi(e) : 2;
+  }
+  return v;
+}
+
 }  // namespace stb
 
 // C ABI ---------------------------------------------------------------------
@@ -622,6 +645,15 @@ static int gemm_dispatch(const void* A, const void* B, void* C, int M, int N, in
   const int celt = out_fp32 ? 4 : 2;
   const void* c0 = fx.n_dest > 0 ? fx.c_dest[0] : C;
   const bool epi_tma = ((reinterpret_cast<uintptr_t>(c0) & 15) == 0) && ((size_t(ldc) * celt) % 16 == 0);
+  // plain GEMMs go to the CTA-pair kernel when it is faster (the fused-collective variants stay here)
+  const bool plain = fx.n_dest == 0 && fx.a_ready == nullptr && fx.n_copy == 0;
+  if (plain && epi_tma && force_bn == 0 && pair_policy() > 0 && (!accumulate || out_fp32)) {
+    const int n_pairs = sm_count() / 2;
+    int pbn = 256, ps = 1;
+    const float pc = pair::pick_config(M, N, K, out_fp32, n_pairs, &pbn, &ps);
+    if (pair_policy() == 1 || pc <= single_cost(M, N, K, out_fp32, bn))
+      return pair::run(A, B, C, M, N, K, lda, ldb, ldc, a_mn, b_mn, out_fp32, accumulate, pbn, ps, stream);
+  }
   STB_REQUIRE(epi_tma || fx.n_dest == 0, "gemm_rs: destination buffers must be 16-byte aligned");
 #define STB_GEMM_CASE(BN_, AMN_, BMN_)                                                             \
   return epi_tma ? launch_gemm<BN_, AMN_, BMN_, true>(A, B, C, M, N, K, lda, ldb, ldc, out_fp32,   \
@@ -677,6 +709,8 @@ extern "C" int stb_ag_gemm_bf16(void* A_full, const void* B, void* C, int M, int
   using namespace stb;
   STB_REQUIRE(M % world == 0 && (M / world) % kBM == 0, "ag_gemm: M / world must be a multiple of %d", kBM);
   STB_REQUIRE(flag_rows % kBM == 0 || kBM % flag_rows == 0, "ag_gemm: flag_rows must divide or be a multiple of %d", kBM);
+  // the copy CTAs number flags per source shard, the TMA producer by global row: both agree only if shards are whole flag blocks
+  STB_REQUIRE((M / world) % flag_rows == 0, "ag_gemm: M / world (%d) must be a multiple of flag_rows (%d)", M / world, flag_rows);
   STB_REQUIRE(n_copy >= 1 && n_copy < sm_count() / 2, "ag_gemm: n_copy %d out of range", n_copy);
   STB_REQUIRE((long(K) * 2) % 16 == 0 && shard_offset_bytes % 16 == 0, "ag_gemm: rows must be 16-byte multiples");
   GemmFused fx;

@@ -20,13 +20,14 @@ _lock = threading.Lock()
 _lib: ctypes.CDLL | None = None
 _load_error: str | None = None
 
-# Number of kernels launched through this binding (bench.py reports it as gpu_launches).
+# Number of kernels launched through this binding (bench.py reports it as gpu_launches), and the same per entry point.
 launch_count = 0
+launch_counts: dict[str, int] = {}
 
 _P = c_void_p
 _SIGS = {
     "stb_gemm_bf16": [_P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, _P],
-    "stb_gemm_bf16_2cta": [_P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, _P],
+    "stb_gemm_bf16_2cta": [_P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, _P],
     "stb_rmsnorm_fwd": [_P, _P, _P, _P, _P, _P, c_int, c_int, c_float, _P],
     "stb_rmsnorm_bwd": [_P, _P, _P, _P, _P, _P, _P, c_int, _P, c_int, c_int, _P],
     "stb_rmsnorm_bwd_noalloc": [_P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int, _P],
@@ -141,6 +142,7 @@ def call(name: str, *args) -> None:
         msg = lib.stb_last_error()
         raise RuntimeError(f"{name} failed ({rc}): {msg.decode() if msg else '?'}")
     launch_count += 1
+    launch_counts[name] = launch_counts.get(name, 0) + 1
 
 
 def call_long(name: str, *args) -> int:

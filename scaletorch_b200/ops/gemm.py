@@ -15,8 +15,6 @@ GEMM writes/accumulates straight into it from its epilogue and autograd sees
 """
 from __future__ import annotations
 
-import os
-
 import torch
 
 from .. import _native as N
@@ -55,8 +53,6 @@ def gemm(
         return out
     assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16
     assert a.stride(1) == 1 and b.stride(1) == 1 and out.stride(1) == 1
-    if _USE_2CTA and _gemm_2cta(a, b, out, M, Nn, K, a_mn, b_mn, accumulate):
-        return out
     N.call(
         "stb_gemm_bf16", a.data_ptr(), b.data_ptr(), out.data_ptr(), M, Nn, K,
         a.stride(0), b.stride(0), out.stride(0), int(a_mn), int(b_mn),
@@ -65,23 +61,15 @@ def gemm(
     return out
 
 
-# EXPERIMENTAL CTA-pair kernel (csrc/experimental/gemm_2cta.cu): opt-in, not yet validated on hardware
-_USE_2CTA = os.environ.get("SCALETORCH_B200_GEMM_2CTA", "0") == "1"
-
-
-def _gemm_2cta(a, b, out, M, Nn, K, a_mn, b_mn, accumulate, force: bool = False) -> bool:
-    """Runs the CTA-pair GEMM when the shape qualifies (large, TMA-storable C); returns False to fall back."""
-    lib = N.load()
-    if lib is None or not hasattr(lib, "stb_gemm_bf16_2cta"):
-        return False
-    esz = out.element_size()
-    if out.data_ptr() % 16 or (out.stride(0) * esz) % 16 or (accumulate and out.dtype != torch.float32):
-        return False
-    if not force and (M < 1024 or Nn < 1024):
-        return False
+def gemm_pair(a, b, out, *, a_mn: bool = False, b_mn: bool = False, accumulate: bool = False, bn: int = 0,
+              splits: int = 0):
+    """The CTA-pair (``cta_group::2``) kernel called directly, with an explicit tile width (128 / 256) and k-split (0 = let the library choose).
+    ``gemm`` reaches the same kernel through ``stb_gemm_bf16``'s own dispatch; this entry exists for tests and tuning."""
+    M, K = (a.shape[1], a.shape[0]) if a_mn else a.shape
+    Nn = b.shape[1] if b_mn else b.shape[0]
     N.call("stb_gemm_bf16_2cta", a.data_ptr(), b.data_ptr(), out.data_ptr(), M, Nn, K, a.stride(0), b.stride(0),
-           out.stride(0), int(a_mn), int(b_mn), int(out.dtype == torch.float32), int(accumulate), N.stream_ptr())
-    return True
+           out.stride(0), int(a_mn), int(b_mn), int(out.dtype == torch.float32), int(accumulate), bn, splits, N.stream_ptr())
+    return out
 
 
 def wgrad_into(param: torch.Tensor, dy2d: torch.Tensor, x2d: torch.Tensor) -> torch.Tensor | None:

@@ -37,6 +37,9 @@ class Bucket:
         self.grad_window = grad_window
         self.comm_stream = comm_stream
         self.sm_budget = sm_budget
+        # set by the sharded optimiser (trainer/zero.py::PeerShardedAdamW): this rank keeps only the reduced gradient
+        # of its own shard [own_lo, own_hi) of the flat buffer -> reduce-scatter instead of all-reduce
+        self.own_range: tuple[int, int] | None = None
 
     @property
     def numel(self) -> int:
@@ -60,7 +63,11 @@ class Bucket:
             ready.record(cur)
             self.comm_stream.wait_event(ready)
             with torch.cuda.stream(self.comm_stream):
-                self.grad_window.all_reduce_range_(self.start, self.numel, inv, self.sm_budget)
+                if self.own_range is not None:
+                    self.grad_window.reduce_scatter_range_(self.start, self.numel, inv, self.own_range[0],
+                                                           self.own_range[1], self.sm_budget)
+                else:
+                    self.grad_window.all_reduce_range_(self.start, self.numel, inv, self.sm_budget)
                 done = torch.cuda.Event()
                 done.record(self.comm_stream)
             self.handle = _EventHandle(done)

@@ -41,17 +41,31 @@ def get_store(module: nn.Module, grad_sync_group=None, fused_comm: bool = True) 
             if symm.group_ready(grad_sync_group) and symm.has_kernel("stb_allreduce_f32"):
                 from ...runtime.fused_ops import GradWindow
 
+                import os
+
+                from ...runtime.fused_ops import ParamWindow
+
                 holder = {}
 
                 def alloc(numel):
                     holder["w"] = GradWindow(grad_sync_group, numel)
                     return holder["w"].grad[:numel]
 
-                store = FlatParamStore(module, grad_alloc=alloc)
+                def palloc(numel, dtype):
+                    holder["p"] = ParamWindow(grad_sync_group, numel, dtype)
+                    return holder["p"].param[:numel]
+
+                # the sharded optimiser needs the parameters in symmetric memory too (bf16 models only)
+                sharded = (os.environ.get("SCALETORCH_B200_DP_SHARDED", "1") == "1" and p0.dtype == torch.bfloat16
+                           and symm.has_kernel("stb_adamw_shard_bcast") and not (pgm and pgm.pp_world_size > 1))
+                store = FlatParamStore(module, grad_alloc=alloc, param_alloc=palloc if sharded else None)
                 window = holder["w"]
+                store.param_window = holder.get("p")
         if store is None:
             store = FlatParamStore(module)
         store.grad_window = window
+        if not hasattr(store, "param_window"):
+            store.param_window = None
         module._stb_store = store
     return store
 

@@ -17,6 +17,7 @@ import torch
 import torch.distributed as dist
 import torch.nn as nn
 
+from ..process_group import get_process_group_manager
 from ..process_group import process_group_manager as pgm
 from .pp_comms import bidirectional_pipeline_communicate, pipeline_communicate, post_recv
 
@@ -57,6 +58,11 @@ class PipelineParallel(nn.Module):
         object.__setattr__(self, "_proto", model)
         self._pipeline_loss = None
         self.tied_across_stages = bool(self.tie_word_embeddings and self.pp_size > 1 and (self.is_first or self.is_last))
+        # dist.new_group is collective over the WORLD: the (first, last) pair groups are created here, by every rank
+        # (middle stages included), not lazily by the two stages that use them
+        if self.tie_word_embeddings and self.pp_size > 1 and pgm and dist.is_available() and dist.is_initialized() \
+                and pgm.pp_world_size == self.pp_size:
+            _first_last_group()
 
     # nn.Module bookkeeping: do not register the prototype model as a sub-module (its unused layers would
     # otherwise be materialised and counted)
@@ -164,11 +170,14 @@ def sync_tied_embedding_grads(model: PipelineParallel) -> None:
 
 
 _FL_GROUP = None
+_FL_OWNER = None
 
 
 def _first_last_group():
-    global _FL_GROUP
-    if _FL_GROUP is None:
+    """Group of this rank's (first stage, last stage) pair; ``None`` on middle stages.  Collective on first use."""
+    global _FL_GROUP, _FL_OWNER
+    if _FL_OWNER is not get_process_group_manager():
+        _FL_GROUP, _FL_OWNER = None, get_process_group_manager()
         # every rank must create every (first,last) pair group in the same order
         mine = None
         grid = pgm.grid
@@ -181,8 +190,8 @@ def _first_last_group():
                         g = dist.new_group(ranks=ranks)
                         if pgm.global_rank in ranks:
                             mine = g
-        _FL_GROUP = mine
-    return _FL_GROUP
+        _FL_GROUP = mine if mine is not None else False
+    return _FL_GROUP or None
 
 
 def _forward_step(model, data_loader, recv, device, dtype, ga: int, gradient_checkpointing: bool):

@@ -38,9 +38,10 @@ def is_expert_param(name: str) -> bool:
 
 
 class FlatParamStore:
-    def __init__(self, module: nn.Module, grad_dtype: torch.dtype = torch.float32, grad_alloc=None):
+    def __init__(self, module: nn.Module, grad_dtype: torch.dtype = torch.float32, grad_alloc=None, param_alloc=None):
         """``grad_alloc(numel) -> fp32 tensor`` lets the caller place the gradient buffer in symmetric memory
-        (data-parallel buckets are then reduced in place over NVLink)."""
+        (data-parallel buckets are then reduced in place over NVLink); ``param_alloc(numel, dtype)`` does the same
+        for the parameter buffer (the sharded optimiser writes updated parameters into every rank's copy)."""
         self.module = module
         named = []
         seen: set[int] = set()
@@ -69,7 +70,9 @@ class FlatParamStore:
                 self.dense_numel = off
         self.total_numel = off
         self.expert_numel = off - self.dense_numel
-        self.param_flat = torch.zeros(off, dtype=self.param_dtype, device=self.device)
+        self.param_flat = (param_alloc(off, self.param_dtype) if param_alloc is not None
+                           else torch.zeros(off, dtype=self.param_dtype, device=self.device))
+        assert self.param_flat.numel() >= off and self.param_flat.dtype == self.param_dtype
         self.grad_flat = grad_alloc(off) if grad_alloc is not None else torch.zeros(off, dtype=grad_dtype, device=self.device)
         assert self.grad_flat.numel() >= off and self.grad_flat.dtype == grad_dtype
         for s in self.slots:

@@ -31,6 +31,9 @@ N.register("stb_allreduce_bf16", [_P, _P, _P, _L, _L, _I, _I, _I, _U, _I, _P])
 N.register("stb_allreduce_oneshot_bf16", [_P, _P, _L, _P, _L, _I, _I, _I, _U, _I, _P])
 N.register("stb_allgather_pull", [_P, _P, _L, _P, _L, _L, _I, _P, _I, _I, _I, _U, _I, _P])
 N.register("stb_embedding_bwd_peers", [_P, _P, _L, _L, _P, _L, _I, _I, _I, _F, _I, _I, _I, _U, _I, _P])
+N.register("stb_reduce_scatter_f32", [_P, _P, _P, _L, _L, _L, _L, _F, _I, _I, _I, _U, _I, _P])
+N.register("stb_adamw_shard_bcast", [_P, _P, _P, _L, _P, _P, _P, _L, _F, _F, _F, _F, _P, _F, _P, _I, _I, _I, _U, _I, _P])
+N.register("stb_allreduce_tiny_f32", [_P, _P, _L, _I, _I, _I, _I, _U, _P])
 N.register("stb_gemm_rs_bf16", [_P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _I, _P])
 N.register("stb_ag_gemm_bf16", [_P, _P, _P, _I, _I, _I, _I, _I, _I, _P, _P, _L, _P, _U, _I, _I, _I, _I, _I, _P])
 
@@ -246,6 +249,47 @@ class GradWindow:
         epoch = g.take_epochs(SLOT_DP, 2)
         N.call("stb_allreduce_f32", self.bufs_dev, self.mc_ptr or None, g.flag_pages_dev, start, numel, float(scale),
                g.rank, g.world, SLOT_DP, epoch, sm_budget, N.stream_ptr())
+
+    def reduce_scatter_range_(self, start: int, numel: int, scale: float, own_lo: int, own_hi: int,
+                              sm_budget: int = 32) -> None:
+        """Mean of ``[start, start + numel)`` over the group, kept only where it intersects this rank's shard
+        ``[own_lo, own_hi)`` (``stb_reduce_scatter_f32``); every rank must call it (the kernel synchronises the group)."""
+        g = self.g
+        epoch = g.take_epochs(SLOT_DP, 2)
+        N.call("stb_reduce_scatter_f32", self.bufs_dev, self.mc_ptr or None, g.flag_pages_dev, start, numel, own_lo,
+               own_hi, float(scale), g.rank, g.world, SLOT_DP, epoch, sm_budget, N.stream_ptr())
+
+
+class ParamWindow:
+    """bf16 parameter buffer in symmetric memory: the sharded optimiser (``trainer/zero.py::PeerShardedAdamW``) updates
+    its shard and writes the new values into every rank's copy from inside the AdamW kernel
+    (``stb_adamw_shard_bcast``: ``multimem.st`` through the switch, or one store per peer).  Also holds 32 fp32 words per
+    rank for the squared-norm partials (``stb_allreduce_tiny_f32``)."""
+
+    def __init__(self, group, numel: int, dtype: torch.dtype):
+        import torch.distributed._symmetric_memory as sm
+
+        assert dtype == torch.bfloat16, "the peer-memory parameter window holds bf16 parameters"
+        self.g = get_group(group)
+        dev = self.g.device
+        nbytes = (numel * 2 + (1 << 21) - 1) // (1 << 21) * (1 << 21)
+        self.raw = sm.empty(nbytes + 4096, dtype=torch.uint8, device=dev)
+        self.raw.zero_()
+        self.h = sm.rendezvous(self.raw, group=group)
+        self.bufs_dev = int(self.h.buffer_ptrs_dev)
+        self.mc_ptr = 0 if _no_multimem() else _multicast_ptr(self.h)
+        self.param = self.raw[: numel * 2].view(torch.bfloat16)
+        self.scratch_off = nbytes // 4                        # fp32 element offset of the 32-word scratch
+        self.scratch = self.raw[nbytes: nbytes + 128].view(torch.float32)
+        torch.cuda.synchronize()
+        dist.barrier(group)
+
+    def all_reduce_scalars_(self, n: int) -> torch.Tensor:
+        """Sums ``self.scratch[:n]`` over the group in place (n <= 32) and returns the view."""
+        g = self.g
+        N.call("stb_allreduce_tiny_f32", self.bufs_dev, g.flag_pages_dev, self.scratch_off, n, g.rank, g.world, SLOT_AR,
+               g.take_epochs(SLOT_AR, 2), N.stream_ptr())
+        return self.scratch[:n]
 
 
 class EmbeddingGradExchange:

@@ -75,3 +75,7 @@ def cleanup_distributed() -> None:
         pgm._instance = None
     if dist.is_initialized():
         dist.destroy_process_group()
+
+
+# the reference's name (scaletorch/trainer/__init__.py:16, dist_setup.py)
+cleanup_distributed_training = cleanup_distributed

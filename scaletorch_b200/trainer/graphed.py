@@ -59,7 +59,7 @@ class GraphedTrainStep:
 
         if not torch.cuda.is_available() or not isinstance(optimizer, FusedAdamW):
             return False
-        if hasattr(optimizer, "shards"):        # ZeRO-1 broadcasts parameters through c10d: not captured
+        if hasattr(optimizer, "shards"):        # c10d ZeRO-1 broadcasts parameters through NCCL: not captured
             return False
         if pgm and (pgm.ep_world_size > 1 or pgm.tp_world_size > 1):
             # validated on hardware: single GPU, DP (2/4/8 ranks) and CP.  TP2+SP hung inside / after capture in the one

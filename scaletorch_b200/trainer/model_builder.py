@@ -57,6 +57,8 @@ def create_model(config, dtype: torch.dtype, device: torch.device):
         model, model_config, save_dir=config.model_name_or_path,
         load_weights=getattr(config, "load_pretrained_weights", False))
     model.to(dtype).to(device)
+    if pgm:
+        sync_replicated_parameters(model)
     if pgm and pgm.tp_world_size > 1:
         from ..parallel.tensor_parallel.tensor_parallel import mark_tp_partial_params
 
@@ -73,6 +75,48 @@ def create_model(config, dtype: torch.dtype, device: torch.device):
     rank_print(f"init model parallel time: {time.time() - t0:.2f}s",
                is_print_rank=(not pgm) or pgm.global_rank == 0)
     return model, model_config
+
+
+@torch.no_grad()
+def sync_replicated_parameters(model: torch.nn.Module) -> int:
+    """Makes every *replicated* parameter start bit-equal on the ranks that hold a copy of it.
+
+    The per-rank seed offset above exists so that *shards* differ; it must not leak into tensors that an axis only
+    replicates, because their gradients are summed/averaged over that axis on the assumption that the copies are one
+    tensor.  After materialising: tensors TP does not shard (norms, router, stacked experts) are broadcast from TP
+    rank 0; everything but the experts is broadcast from EP rank 0; with tied embeddings split over pipeline stages
+    the first stage's embedding is sent to the last stage's LM-head copy.  Returns the number of tensors broadcast.
+    """
+    import torch.distributed as dist
+
+    from ..utils.misc import is_tp_sharded_name
+
+    if not (dist.is_available() and dist.is_initialized()):
+        return 0
+    n = 0
+    named = [(k, p) for k, p in model.named_parameters()]
+    if pgm.tp_world_size > 1:
+        src = dist.get_global_rank(pgm.tp_group, 0)
+        for k, p in named:
+            if not is_tp_sharded_name(k):
+                dist.broadcast(p.data, src=src, group=pgm.tp_group)
+                n += 1
+    if pgm.ep_world_size > 1:
+        src = dist.get_global_rank(pgm.ep_group, 0)
+        for k, p in named:
+            if ".experts." not in k:
+                dist.broadcast(p.data, src=src, group=pgm.ep_group)
+                n += 1
+    raw = unwrap(model)
+    if getattr(raw, "tie_word_embeddings", False) and pgm.pp_world_size > 1:
+        from ..parallel.pipeline_parallel.pipeline_parallel import _first_last_group
+
+        group = _first_last_group()          # created by every rank in PipelineParallel.__init__
+        if group is not None and getattr(raw, "tied_across_stages", False):
+            w = raw.embedding.weight if raw.is_first else raw.final_proj.weight
+            dist.broadcast(w.data, src=dist.get_global_rank(group, 0), group=group)
+            n += 1
+    return n
 
 
 def unwrap(model):
@@ -98,6 +142,14 @@ def create_optimizer(model: torch.nn.Module, config, device: torch.device):
         norm_group = pgm.mp_group if (pgm and len(pgm.mp_group_ids) > 1) else None
         kw = dict(lr=lr, betas=betas, weight_decay=wd, max_grad_norm=getattr(config, "max_grad_norm", None),
                   norm_group=norm_group)
+        bm = getattr(model, "bucket_manager", None)
+        if (getattr(store, "param_window", None) is not None and bm is not None and pgm and pgm.pp_world_size == 1
+                and pgm.grad_sync_world_size > 1 and getattr(config, "zero_stage", 0) != -1):
+            # gradient buffer and parameters are in symmetric memory: ZeRO-1 on the peer-memory kernels (reduce-scatter
+            # during backward, sharded AdamW that writes the new parameters into every rank's copy)
+            from .zero import PeerShardedAdamW
+
+            return PeerShardedAdamW(store, bm, pgm.grad_sync_group, **kw)
         if getattr(config, "zero_stage", 0) >= 1 and pgm and pgm.grad_sync_world_size > 1:
             from .zero import ZeroFusedAdamW
 

@@ -57,6 +57,60 @@ def test_gemm_wgrad_layout(M, Nn, K):
     assert _rel_err(c, 2 * ref) < 5e-3
 
 
+@pytest.mark.parametrize("M,Nn,K", [(256, 256, 64), (512, 512, 256), (4096, 3072, 1024), (1000, 1544, 200)])
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, True)])
+@pytest.mark.parametrize("bn", [128, 256])
+def test_gemm_pair_kernel(M, Nn, K, a_mn, b_mn, bn):
+    """CTA-pair (cta_group::2) kernel called directly against an fp32 matmul: store, fp32 accumulate, ragged edges."""
+    from scaletorch_b200.ops.gemm import gemm_pair
+
+    torch.manual_seed(0)
+    a = torch.randn((K, M) if a_mn else (M, K), device="cuda").bfloat16()
+    b = torch.randn((K, Nn) if b_mn else (Nn, K), device="cuda").bfloat16()
+    ref = (a.float().t() if a_mn else a.float()) @ (b.float() if b_mn else b.float().t())
+    out = torch.full((M, Nn), float("nan"), device="cuda", dtype=torch.bfloat16)
+    gemm_pair(a, b, out, a_mn=a_mn, b_mn=b_mn, bn=bn, splits=1)
+    torch.cuda.synchronize()
+    assert _rel_err(out, ref) < 5e-3
+    acc = torch.ones((M, Nn), device="cuda", dtype=torch.float32)
+    gemm_pair(a, b, acc, a_mn=a_mn, b_mn=b_mn, accumulate=True, bn=bn, splits=1)
+    torch.cuda.synchronize()
+    assert _rel_err(acc, ref + 1.0) < 5e-3
+
+
+@pytest.mark.parametrize("splits", [0, 2, 3, 7])
+@pytest.mark.parametrize("accumulate", [False, True])
+@pytest.mark.parametrize("bn", [128, 256])
+def test_gemm_pair_split_k(splits, accumulate, bn):
+    """Weight-gradient shape (few tiles, long reduction): every k-split reduce-adds into the fp32 destination."""
+    from scaletorch_b200.ops.gemm import gemm_pair
+
+    torch.manual_seed(1)
+    M, Nn, K = 1024, 2048, 4096 + 64          # K not a multiple of the split
+    a = torch.randn(K, M, device="cuda").bfloat16()
+    b = torch.randn(K, Nn, device="cuda").bfloat16()
+    ref = a.float().t() @ b.float()
+    out = torch.full((M, Nn), 3.0 if accumulate else float("nan"), device="cuda", dtype=torch.float32)
+    gemm_pair(a, b, out, a_mn=True, b_mn=True, accumulate=accumulate, bn=bn, splits=splits)
+    torch.cuda.synchronize()
+    assert _rel_err(out, ref + (3.0 if accumulate else 0.0)) < 5e-3
+
+
+def test_gemm_default_dispatch_matches_single_cta():
+    """``ops.gemm`` (library-chosen kernel) and the single-CTA kernel (forced tile width) agree on model shapes."""
+    torch.manual_seed(2)
+    for (M, Nn, K) in [(4096, 4096, 1024), (4096, 1024, 3072), (384, 640, 512)]:
+        a = torch.randn(M, K, device="cuda").bfloat16()
+        b = torch.randn(Nn, K, device="cuda").bfloat16()
+        ref = a.float() @ b.float().t()
+        assert _rel_err(ops.gemm(a, b), ref) < 5e-3
+        assert _rel_err(ops.gemm(a, b, force_bn=256), ref) < 5e-3
+        w = torch.randn(M, Nn, device="cuda").bfloat16()          # wgrad: [K=M tokens] reduction, fp32 out
+        dw = torch.zeros(Nn, K, device="cuda")
+        ops.gemm(w, a, a_mn=True, b_mn=True, out=dw)
+        assert _rel_err(dw, w.float().t() @ a.float()) < 5e-3
+
+
 def test_gemm_strided_views():
     torch.manual_seed(3)
     big = _bf(512, 1024)

@@ -558,3 +558,62 @@ def _zero_worker(rank, world, layout):
 @pytest.mark.parametrize("world,layout", [(2, (2, 1)), (4, (2, 2))], ids=["dp2", "dp2ep2"])
 def test_zero1_matches_unsharded_optimizer(world, layout):
     run_distributed(_zero_worker, world, layout)
+
+
+# ------------------------------------------------------------------ replicated parameters start equal (create_model)
+def _replica_worker(rank, world, name, layout):
+    """Through ``create_model`` (random init): a tensor that an axis only replicates must be bit-equal on all ranks of
+    that axis, while the shards of an axis differ; with tied embeddings over pp=3 the middle stage joins the collective
+    group creation and the last stage's LM-head copy equals the first stage's embedding."""
+    import torch.distributed as dist
+
+    from scaletorch_b200.parallel.process_group import process_group_manager as pgm
+    from scaletorch_b200.trainer import ScaleTorchArguments, create_model, initialize_distributed_training
+    from scaletorch_b200.utils.misc import is_tp_sharded_name
+
+    tp, pp, ep = layout
+    cfg = ScaleTorchArguments(model_name_or_path=name, micro_batch_size=1, sequence_length=16, dtype="float32", use_cpu=True,
+                              tensor_parallel_size=tp, pipeline_parallel_size=pp, expert_parallel_size=ep,
+                              data_parallel_size=world // (tp * pp * ep), seed=5, num_hidden_layers=3,
+                              num_attention_heads=4, num_key_value_heads=2)
+    initialize_distributed_training(cfg)
+    model, mc = create_model(cfg, torch.float32, torch.device("cpu"))
+    raw = model.module if hasattr(model, "module") else model
+
+    def gathered(t, group):
+        out = [torch.empty_like(t) for _ in range(dist.get_world_size(group))]
+        dist.all_gather(out, t.detach().contiguous(), group=group)
+        return out
+
+    n_rep = n_shard = 0
+    for k, p in raw.named_parameters():
+        if tp > 1:
+            copies = gathered(p, pgm.tp_group)
+            if is_tp_sharded_name(k):
+                assert not torch.equal(copies[0], copies[1]), f"TP shards of {k} are identical"
+                n_shard += 1
+            else:
+                assert all(torch.equal(copies[0], c) for c in copies[1:]), f"{k} differs across TP ranks"
+                n_rep += 1
+        if ep > 1:
+            copies = gathered(p, pgm.ep_group)
+            if ".experts." in k:
+                assert not torch.equal(copies[0], copies[1]), f"EP shards of {k} are identical"
+                n_shard += 1
+            else:
+                assert all(torch.equal(copies[0], c) for c in copies[1:]), f"{k} differs across EP ranks"
+                n_rep += 1
+    if tp > 1 or ep > 1:
+        assert n_rep > 3 and n_shard > 1, (n_rep, n_shard)
+    if pp > 1 and mc.tie_word_embeddings:
+        H, V = mc.hidden_size, mc.vocab_size // tp
+        w = raw.embedding.weight if raw.is_first else (raw.final_proj.weight if raw.is_last else torch.zeros(V, H))
+        copies = gathered(w, pgm.pp_group)
+        assert torch.equal(copies[0], copies[-1]), "tied embedding / LM-head copies differ across pipeline stages"
+        assert copies[0].abs().sum() > 0
+
+
+@pytest.mark.parametrize("name,layout,world", [("tiny-qwen3-moe", (2, 1, 2), 4), ("tiny-qwen3", (1, 3, 1), 3)],
+                         ids=["moe-tp2ep2", "dense-pp3-tied"])
+def test_replicated_parameters_start_equal(name, layout, world):
+    run_distributed(_replica_worker, world, name, layout)

@@ -44,7 +44,18 @@ struct AttnBwdParams {
   int B, Sq, Sk, Hq, Hkv;
   float scale, scale_log2;
   int causal;
+  // blockwise (ring) attention: this call covers query rows [q_lo, q_lo + Sq) of tensors with S_tot rows per batch
+  // (lse / delta are [B,Hq,S_tot]); plain attention: q_lo = 0, S_tot = Sq
+  int q_lo, S_tot;
+  int dq_f32;        // dq is an fp32 buffer (element strides as given) ...
+  int dq_acc;        // ... and this call adds to it instead of overwriting
+  int dkv_f32_add;   // dk / dv are fp32 buffers, possibly in a peer GPU's memory: contributions are red.add-ed into them
 };
+
+STB_DEVICE void red_add_f32x4_sys(float* p, float a, float b, float c, float d) {
+  asm volatile("red.relaxed.sys.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d)
+               : "memory");
+}
 
 // --------------------------------------------------------------------------------------- delta
 __global__ void __launch_bounds__(256)
@@ -234,7 +245,7 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
       float stat = 0.f;
       if (tid < 128) {
         const int c = tid & 63, q = q0 + c;
-        const size_t idx = (size_t(b) * p.Hq + hq) * p.Sq + q;
+        const size_t idx = (size_t(b) * p.Hq + hq) * p.S_tot + p.q_lo + q;
         if (tid < 64) stat = (q < p.Sq) ? p.lse[idx] * kLog2e : CUDART_INF_F;
         else stat = (q < p.Sq) ? p.delta[idx] : 0.f;
       }
@@ -313,8 +324,17 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
 #pragma unroll
           for (int j = 0; j < 32; ++j) r[j] = 0;
         }
-        if (key_ok) {
-          const float osc = which == 0 ? 1.f : p.scale;     // dK = scale * dS^T Q (dS was accumulated unscaled)
+        const float osc = which == 0 ? 1.f : p.scale;     // dK = scale * dS^T Q (dS was accumulated unscaled)
+        if (key_ok && p.dkv_f32_add) {
+          // ring attention: add this rank's contribution to the block owner's fp32 accumulator (peer memory)
+          float* fdst = reinterpret_cast<float*>(base) + b * sb_ + long(key) * ss_ + hkv * sh_ + c * 32;
+          if (n_iter > 0) {
+#pragma unroll
+            for (int t = 0; t < 8; ++t)
+              red_add_f32x4_sys(fdst + 4 * t, __uint_as_float(r[4 * t + 0]) * osc, __uint_as_float(r[4 * t + 1]) * osc,
+                                __uint_as_float(r[4 * t + 2]) * osc, __uint_as_float(r[4 * t + 3]) * osc);
+          }
+        } else if (key_ok) {
 #pragma unroll
           for (int t = 0; t < 4; ++t)
             *reinterpret_cast<uint4*>(dst + c * 32 + 8 * t) = make_uint4(
@@ -470,7 +490,7 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
     const uint32_t lane_addr = uint32_t(quarter * 32) << 16;
     const int q = q0 + row;
     const bool q_ok = q < p.Sq;
-    const size_t sidx = (size_t(b) * p.Hq + hq) * p.Sq + (q_ok ? q : 0);
+    const size_t sidx = (size_t(b) * p.Hq + hq) * p.S_tot + p.q_lo + (q_ok ? q : 0);
     const float lse2 = q_ok ? p.lse[sidx] * kLog2e : CUDART_INF_F;
     const float dl = q_ok ? p.delta[sidx] : 0.f;
     const int q_pos = q + shift;
@@ -521,8 +541,22 @@ __global__ void __launch_bounds__(kBwdThreads, 1)
       uint32_t r[32];
       tmem_ld_32x32b_x32(tmem_base + lane_addr + 256 + c * 32, r);
       tmem_ld_wait();
-      if (q_ok) {
-        const float osc = p.scale;                           // dQ = scale * dS K
+      const float osc = p.scale;                           // dQ = scale * dS K
+      if (q_ok && p.dq_f32) {
+        // ring attention: dQ accumulates over the key blocks in fp32 (no per-block bf16 round trip, no eager add)
+        float4* fdst = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.dq) + b * p.dq_sb + long(q) * p.dq_ss +
+                                                 hq * p.dq_sh + c * 32);
+#pragma unroll
+        for (int t = 0; t < 8; ++t) {
+          float4 v = make_float4(__uint_as_float(r[4 * t + 0]) * osc, __uint_as_float(r[4 * t + 1]) * osc,
+                                 __uint_as_float(r[4 * t + 2]) * osc, __uint_as_float(r[4 * t + 3]) * osc);
+          if (p.dq_acc) {
+            const float4 o = fdst[t];
+            v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w;
+          }
+          fdst[t] = v;
+        }
+      } else if (q_ok) {
 #pragma unroll
         for (int t = 0; t < 4; ++t)
           *reinterpret_cast<uint4*>(dst + c * 32 + 8 * t) = make_uint4(
@@ -544,25 +578,27 @@ using namespace stb;
 
 // dout/out: contiguous [B,Sq,Hq,128]; q,k,v,dq,dk,dv: [B,S,H,128] views with element strides; lse: [B,Hq,Sq];
 // delta: [B,Hq,Sq] fp32 scratch written by this call.
-extern "C" int stb_flash_attn_bwd(const void* dout, const void* q, const void* k, const void* v, const void* out,
-                                  const float* lse, float* delta, void* dq, void* dk, void* dv, int B, int Sq,
-                                  int Sk, int Hq, int Hkv, int D, long q_sb, long q_ss, long q_sh, long k_sb,
-                                  long k_ss, long k_sh, long v_sb, long v_ss, long v_sh, long dq_sb, long dq_ss,
-                                  long dq_sh, long dk_sb, long dk_ss, long dk_sh, long dv_sb, long dv_ss, long dv_sh,
-                                  float scale, int causal, cudaStream_t stream) {
+static int flash_attn_bwd_impl(const void* dout, const void* q, const void* k, const void* v, const void* out,
+                               const float* lse, float* delta, void* dq, void* dk, void* dv, int B, int Sq,
+                               int Sk, int Hq, int Hkv, int D, long q_sb, long q_ss, long q_sh, long k_sb,
+                               long k_ss, long k_sh, long v_sb, long v_ss, long v_sh, long dq_sb, long dq_ss,
+                               long dq_sh, long dk_sb, long dk_ss, long dk_sh, long dv_sb, long dv_ss, long dv_sh,
+                               float scale, int causal, int q_lo, int S_tot, int compute_delta, int dq_f32, int dq_acc,
+                               int dkv_f32_add, cudaStream_t stream) {
   STB_REQUIRE(D == 128, "flash_attn_bwd: head_dim must be 128 (got %d)", D);
   STB_REQUIRE(Hq % Hkv == 0, "flash_attn_bwd: Hq=%d must be a multiple of Hkv=%d", Hq, Hkv);
   STB_REQUIRE(!causal || Sq <= Sk, "flash_attn_bwd: causal attention needs Sq <= Sk");
   STB_REQUIRE((dq_ss % 8) == 0 && (dk_ss % 8) == 0 && (dv_ss % 8) == 0 && (dq_sh % 8) == 0 && (dk_sh % 8) == 0 &&
                   (dv_sh % 8) == 0,
               "flash_attn_bwd: gradient strides must be multiples of 8 elements");
+  STB_REQUIRE(q_lo >= 0 && q_lo + Sq <= S_tot, "flash_attn_bwd: query window [%d, %d) outside %d rows", q_lo, q_lo + Sq, S_tot);
   if (B == 0 || Sq == 0 || Sk == 0) return 0;
-  {
-    const long rows = long(B) * Sq * Hq;
+  if (compute_delta) {   // over all S_tot rows of dout / out (once per backward, also for blockwise attention)
+    const long rows = long(B) * S_tot * Hq;
     long blocks = (rows + 7) / 8;
     const long cap = long(sm_count()) * 16;
     attn_bwd_delta_kernel<<<int(blocks < cap ? blocks : cap), 256, 0, stream>>>(
-        (const __nv_bfloat16*)dout, (const __nv_bfloat16*)out, delta, B, Sq, Hq);
+        (const __nv_bfloat16*)dout, (const __nv_bfloat16*)out, delta, B, S_tot, Hq);
     STB_CHECK_LAUNCH();
   }
   AttnBwdParams p;
@@ -572,7 +608,9 @@ extern "C" int stb_flash_attn_bwd(const void* dout, const void* q, const void* k
   p.dv = (__nv_bfloat16*)dv; p.dv_sb = dv_sb; p.dv_ss = dv_ss; p.dv_sh = dv_sh;
   p.B = B; p.Sq = Sq; p.Sk = Sk; p.Hq = Hq; p.Hkv = Hkv;
   p.scale = scale; p.scale_log2 = scale * kLog2e; p.causal = causal;
-  const long do_ss = long(Hq) * 128, do_sb = do_ss * Sq;
+  p.q_lo = q_lo; p.S_tot = S_tot; p.dq_f32 = dq_f32; p.dq_acc = dq_acc; p.dkv_f32_add = dkv_f32_add;
+  const long do_ss = long(Hq) * 128, do_sb = do_ss * S_tot;
+  dout = static_cast<const __nv_bfloat16*>(dout) + long(q_lo) * do_ss;     // first row of the query window
   static bool attr_set = false;
   if (!attr_set) {
     STB_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_dkdv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, DkvSmem::kBytes));
@@ -600,4 +638,32 @@ extern "C" int stb_flash_attn_bwd(const void* dout, const void* q, const void* k
     STB_CHECK_LAUNCH();
   }
   return 0;
+}
+
+extern "C" int stb_flash_attn_bwd(const void* dout, const void* q, const void* k, const void* v, const void* out,
+                                  const float* lse, float* delta, void* dq, void* dk, void* dv, int B, int Sq,
+                                  int Sk, int Hq, int Hkv, int D, long q_sb, long q_ss, long q_sh, long k_sb,
+                                  long k_ss, long k_sh, long v_sb, long v_ss, long v_sh, long dq_sb, long dq_ss,
+                                  long dq_sh, long dk_sb, long dk_ss, long dk_sh, long dv_sb, long dv_ss, long dv_sh,
+                                  float scale, int causal, cudaStream_t stream) {
+  return flash_attn_bwd_impl(dout, q, k, v, out, lse, delta, dq, dk, dv, B, Sq, Sk, Hq, Hkv, D, q_sb, q_ss, q_sh, k_sb,
+                             k_ss, k_sh, v_sb, v_ss, v_sh, dq_sb, dq_ss, dq_sh, dk_sb, dk_ss, dk_sh, dv_sb, dv_ss, dv_sh,
+                             scale, causal, 0, Sq, 1, 0, 0, 0, stream);
+}
+
+// One key block of the backward of a blockwise (ring) attention.  dout / out: contiguous [B,S_tot,Hq,128]; lse / delta:
+// [B,Hq,S_tot] (the GLOBAL log-sum-exp over all key blocks); the call covers query rows [q_lo, q_lo + Sq) -- q / dq point
+// at row q_lo -- against the Sk keys of this block.  delta is computed when compute_delta != 0 (first block of a
+// backward).  dq: fp32, overwritten (dq_acc = 0) or accumulated (dq_acc = 1).  dk / dv: fp32 accumulators that may live
+// in another GPU's memory; this rank's contributions are added with red.global.add (the owner zeroes them beforehand).
+extern "C" int stb_flash_attn_bwd_block(const void* dout, const void* q, const void* k, const void* v, const void* out,
+                                        const float* lse, float* delta, float* dq, float* dk, float* dv, int B, int Sq,
+                                        int Sk, int Hq, int Hkv, int D, long q_sb, long q_ss, long q_sh, long k_sb,
+                                        long k_ss, long k_sh, long v_sb, long v_ss, long v_sh, long dq_sb, long dq_ss,
+                                        long dq_sh, long dk_sb, long dk_ss, long dk_sh, long dv_sb, long dv_ss,
+                                        long dv_sh, float scale, int causal, int q_lo, int S_tot, int compute_delta,
+                                        int dq_acc, cudaStream_t stream) {
+  return flash_attn_bwd_impl(dout, q, k, v, out, lse, delta, dq, dk, dv, B, Sq, Sk, Hq, Hkv, D, q_sb, q_ss, q_sh, k_sb,
+                             k_ss, k_sh, v_sb, v_ss, v_sh, dq_sb, dq_ss, dq_sh, dk_sb, dk_ss, dk_sh, dv_sb, dv_ss, dv_sh,
+                             scale, causal, q_lo, S_tot, compute_delta, 1, dq_acc, 1, stream);
 }

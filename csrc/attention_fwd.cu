@@ -35,6 +35,9 @@ constexpr int kTileBytes = 2 * kHalfBytes;   // 32 KB
 struct AttnFwdParams {
   __nv_bfloat16* out;
   float* lse;
+  float* acc;     // optional fp32 [B,Sq,Hq,128] running output of a blockwise (ring) attention; nullptr = none
+  int merge;      // 1: (acc | out, lse) hold the result over earlier key blocks: fold this block in (log-sum-exp merge)
+  int q_lo, S_tot;  // the call covers query rows [q_lo, q_lo + Sq) of out / acc ([B,S_tot,Hq,128]) and lse ([B,Hq,S_tot])
   int B, Sq, Sk, Hq, Hkv;
   int n_qtiles;
   float scale_log2;
@@ -306,19 +309,67 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
     xsum[half * 128 + row] = l;
     named_bar_sync(1, 256);
     const float ltot = l + xsum[(half ^ 1) * 128 + row];
-    const float inv = (ltot > 0.f) ? 1.f / ltot : 0.f;
+    float inv = (ltot > 0.f) ? 1.f / ltot : 0.f;
     const int q = q0 + row;
     if (q < p.Sq) {
-      __nv_bfloat16* dst = p.out + ((size_t(b) * p.Sq + q) * p.Hq + hq) * kHeadDim + half * 64;
+      const size_t row_off = ((size_t(b) * p.S_tot + p.q_lo + q) * p.Hq + hq) * kHeadDim + half * 64;
+      const size_t lse_idx = (size_t(b) * p.Hq + hq) * p.S_tot + p.q_lo + q;
+      __nv_bfloat16* dst = p.out + row_off;
+      float lse_out = (ltot > 0.f) ? (m + log2f(ltot)) * 0.6931471805599453f : -CUDART_INF_F;
+      if (p.merge) {
+        // ring attention: (prev, lse_prev) cover the key blocks seen so far.  out = w_prev * prev + w_cur * o / ltot with
+        // w = exp(lse - logaddexp(lse_prev, lse_cur)); the merge costs one extra read of the row and no extra launch
+        // (reference: the eager update_out_and_lse of context_parallel.py:367-424)
+        const float lse_prev = p.lse[lse_idx];
+        const float mx = fmaxf(lse_prev, lse_out);
+        float w_prev = 0.f, w_cur = 0.f;
+        if (mx > -CUDART_INF_F) {
+          const float e_prev = __expf(lse_prev - mx), e_cur = __expf(lse_out - mx);
+          const float tot = e_prev + e_cur;
+          w_prev = e_prev / tot;
+          w_cur = e_cur / tot;
+          lse_out = mx + __logf(tot);
+        }
+        inv *= w_cur;
+        if (p.acc != nullptr) {
+          const float4* prev = reinterpret_cast<const float4*>(p.acc + row_off);
+#pragma unroll
+          for (int t = 0; t < 16; ++t) {
+            const float4 v = prev[t];
+            o[4 * t + 0] = o[4 * t + 0] * inv + w_prev * v.x; o[4 * t + 1] = o[4 * t + 1] * inv + w_prev * v.y;
+            o[4 * t + 2] = o[4 * t + 2] * inv + w_prev * v.z; o[4 * t + 3] = o[4 * t + 3] * inv + w_prev * v.w;
+          }
+        } else {
+          const uint4* prev = reinterpret_cast<const uint4*>(dst);
+#pragma unroll
+          for (int t = 0; t < 8; ++t) {
+            const uint4 v = prev[t];
+            const float2 a = unpack_bf16x2(v.x), c = unpack_bf16x2(v.y), d = unpack_bf16x2(v.z), e = unpack_bf16x2(v.w);
+            o[8 * t + 0] = o[8 * t + 0] * inv + w_prev * a.x; o[8 * t + 1] = o[8 * t + 1] * inv + w_prev * a.y;
+            o[8 * t + 2] = o[8 * t + 2] * inv + w_prev * c.x; o[8 * t + 3] = o[8 * t + 3] * inv + w_prev * c.y;
+            o[8 * t + 4] = o[8 * t + 4] * inv + w_prev * d.x; o[8 * t + 5] = o[8 * t + 5] * inv + w_prev * d.y;
+            o[8 * t + 6] = o[8 * t + 6] * inv + w_prev * e.x; o[8 * t + 7] = o[8 * t + 7] * inv + w_prev * e.y;
+          }
+        }
+        inv = 1.f;
+      }
+      if (p.acc != nullptr) {
+        float4* a4 = reinterpret_cast<float4*>(p.acc + row_off);
+#pragma unroll
+        for (int t = 0; t < 16; ++t)
+          a4[t] = make_float4(o[4 * t + 0] * inv, o[4 * t + 1] * inv, o[4 * t + 2] * inv, o[4 * t + 3] * inv);
+      }
 #pragma unroll
       for (int t = 0; t < 8; ++t) {
         *reinterpret_cast<uint4*>(dst + 8 * t) =
             make_uint4(pack_bf16x2(o[8 * t + 0] * inv, o[8 * t + 1] * inv), pack_bf16x2(o[8 * t + 2] * inv, o[8 * t + 3] * inv),
                        pack_bf16x2(o[8 * t + 4] * inv, o[8 * t + 5] * inv), pack_bf16x2(o[8 * t + 6] * inv, o[8 * t + 7] * inv));
       }
-      if (half == 0)
-        p.lse[(size_t(b) * p.Hq + hq) * p.Sq + q] =
-            (ltot > 0.f) ? (m + log2f(ltot)) * 0.6931471805599453f : -CUDART_INF_F;
+      // both halves of a row read lse_prev above: the row's partner must have read it before it is overwritten
+      if (p.merge) named_bar_sync(1, 256);
+      if (half == 0) p.lse[lse_idx] = lse_out;
+    } else if (p.merge) {
+      named_bar_sync(1, 256);
     }
   }
 
@@ -333,10 +384,10 @@ using namespace stb;
 
 // q: [B,Sq,Hq,128], k/v: [B,Sk,Hkv,128] bf16 with element strides (batch, token, head); out: contiguous
 // [B,Sq,Hq,128] bf16; lse: [B,Hq,Sq] fp32.  causal: query i attends keys <= i + (Sk - Sq).
-extern "C" int stb_flash_attn_fwd(const void* q, const void* k, const void* v, void* out, float* lse, int B,
-                                  int Sq, int Sk, int Hq, int Hkv, int D, long q_sb, long q_ss, long q_sh,
-                                  long k_sb, long k_ss, long k_sh, long v_sb, long v_ss, long v_sh, float scale,
-                                  int causal, cudaStream_t stream) {
+static int flash_attn_fwd_impl(const void* q, const void* k, const void* v, void* out, float* lse, float* acc, int merge,
+                               int q_lo, int S_tot, int B, int Sq, int Sk, int Hq, int Hkv, int D, long q_sb, long q_ss, long q_sh,
+                               long k_sb, long k_ss, long k_sh, long v_sb, long v_ss, long v_sh, float scale,
+                               int causal, cudaStream_t stream) {
   STB_REQUIRE(D == kHeadDim, "flash_attn: head_dim must be 128 (got %d)", D);
   STB_REQUIRE(Hq % Hkv == 0, "flash_attn: Hq=%d must be a multiple of Hkv=%d", Hq, Hkv);
   STB_REQUIRE(!causal || Sq <= Sk, "flash_attn: causal attention needs Sq <= Sk");
@@ -348,6 +399,10 @@ extern "C" int stb_flash_attn_fwd(const void* q, const void* k, const void* v, v
   AttnFwdParams p;
   p.out = (__nv_bfloat16*)out;
   p.lse = lse;
+  p.acc = acc;
+  p.merge = merge;
+  p.q_lo = q_lo;
+  p.S_tot = S_tot;
   p.B = B; p.Sq = Sq; p.Sk = Sk; p.Hq = Hq; p.Hkv = Hkv;
   p.n_qtiles = (Sq + kTile - 1) / kTile;
   p.scale_log2 = scale * 1.4426950408889634f;
@@ -362,4 +417,27 @@ extern "C" int stb_flash_attn_fwd(const void* q, const void* k, const void* v, v
   flash_attn_fwd_kernel<<<grid, kAttnThreads, AttnSmem::kBytes, stream>>>(tmQ, tmK, tmV, p);
   STB_CHECK_LAUNCH();
   return 0;
+}
+
+extern "C" int stb_flash_attn_fwd(const void* q, const void* k, const void* v, void* out, float* lse, int B,
+                                  int Sq, int Sk, int Hq, int Hkv, int D, long q_sb, long q_ss, long q_sh,
+                                  long k_sb, long k_ss, long k_sh, long v_sb, long v_ss, long v_sh, float scale,
+                                  int causal, cudaStream_t stream) {
+  return flash_attn_fwd_impl(q, k, v, out, lse, nullptr, 0, 0, Sq, B, Sq, Sk, Hq, Hkv, D, q_sb, q_ss, q_sh, k_sb, k_ss, k_sh,
+                             v_sb, v_ss, v_sh, scale, causal, stream);
+}
+
+// One key block of a blockwise (ring) attention over query rows [q_lo, q_lo + Sq) of out / acc / lse (S_tot rows per
+// batch; q points at row q_lo).  merge = 0: first block, (out, lse) are written; merge = 1: (out, lse)
+// -- and the fp32 running output `acc` when given -- hold the result over the blocks seen so far and this block is
+// folded into them in the kernel's epilogue.  `acc` (fp32 [B,Sq,Hq,128], optional) keeps the running output in full
+// precision between blocks; `out` always receives the bf16 value.
+extern "C" int stb_flash_attn_fwd_block(const void* q, const void* k, const void* v, void* out, float* lse, float* acc,
+                                        int merge, int q_lo, int S_tot, int B, int Sq, int Sk, int Hq, int Hkv, int D,
+                                        long q_sb, long q_ss, long q_sh, long k_sb, long k_ss, long k_sh, long v_sb,
+                                        long v_ss, long v_sh, float scale, int causal, cudaStream_t stream) {
+  STB_REQUIRE(q_lo >= 0 && q_lo + Sq <= S_tot, "flash_attn_fwd_block: query window [%d, %d) outside %d rows", q_lo,
+              q_lo + Sq, S_tot);
+  return flash_attn_fwd_impl(q, k, v, out, lse, acc, merge, q_lo, S_tot, B, Sq, Sk, Hq, Hkv, D, q_sb, q_ss, q_sh, k_sb, k_ss, k_sh,
+                             v_sb, v_ss, v_sh, scale, causal, stream);
 }

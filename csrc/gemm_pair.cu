@@ -261,7 +261,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 
 // Work model used to choose tile width and k-split, and to decide between this kernel and the single-CTA one.  Unit of
 // time: one 64-deep k-block of a 128 x 256 (per SM) tile at full tensor rate (512 clk ~ 0.27 us).  Constants fitted to
-// tools/gemm_sweep.py runs (profiles/gemm_sweep_r2.jsonl): the 128-wide tile moves 1.5x the operand bytes per flop;
+// tools/gemm_sweep.py runs (profiles/gemm_sweep_r2.jsonl): the 128-wide tile moves 1.5x the operand bytes per flop and
+// ran 4096^3 in 146 us where the 256-wide tile needs 99 us, so it only pays when it halves the number of waves;
 // a k-split costs the zero-fill launch plus read-modify-write epilogues (~6 us) and more per extra split.
 constexpr float kEpiUnits = 5.0f;        // exposed drain of a CTA's last 128 x 256 accumulator half (bf16 store)
 constexpr float kSplitUnits = 20.0f;     // zero-fill + reduce-add epilogue instead of a store
@@ -274,7 +275,7 @@ float pair_cost(int M, int N, int K, int out_fp32, int bn, int splits, int n_pai
   const int per = (kb + splits - 1) / splits;
   const long units = tiles * ((kb + per - 1) / per);
   const long waves = (units + n_pairs - 1) / n_pairs;
-  const float width = bn == 256 ? 1.0f : 0.54f;
+  const float width = bn == 256 ? 1.0f : 0.76f;   // the 128-wide pair tile is L2->SMEM bound like the single-CTA kernel
   float c = float(waves) * float(per) * width + kEpiUnits * width * (out_fp32 ? 1.5f : 1.0f);
   if (splits > 1) c += kSplitUnits + kPerSplitUnits * float(splits);
   return c;

@@ -46,7 +46,7 @@ __device__ __forceinline__ MaxSum block_ms_reduce(MaxSum v, MaxSum* red) {
 // stats[row] = {max, sumexp (relative to max), target logit or 0 when the target is not local}
 __global__ void __launch_bounds__(kCeThreads)
     ce_stats_kernel(const __nv_bfloat16* __restrict__ logits, const long* __restrict__ targets,
-                    float* __restrict__ stats, int rows, int V, long ld, int vocab_start) {
+                    float* __restrict__ stats, int rows, int V, long ld, int vocab_start, int merge) {
   __shared__ MaxSum red[kCeThreads / 32];
   for (int row = blockIdx.x; row < rows; row += gridDim.x) {
     const __nv_bfloat16* lr = logits + size_t(row) * ld;
@@ -82,7 +82,14 @@ __global__ void __launch_bounds__(kCeThreads)
     acc = block_ms_reduce(acc, red);
     if (threadIdx.x == 0) {
       const long t = targets[row] - vocab_start;
-      const float tl = (t >= 0 && t < V) ? __bfloat162float(lr[t]) : 0.f;
+      float tl = (t >= 0 && t < V) ? __bfloat162float(lr[t]) : 0.f;
+      if (merge) {   // vocabulary processed in column chunks: fold this chunk into the running (max, sum-exp, target)
+        MaxSum old;
+        old.m = stats[3 * row + 0];
+        old.s = stats[3 * row + 1];
+        acc = ms_merge(old, acc);
+        tl += stats[3 * row + 2];
+      }
       stats[3 * row + 0] = acc.m;
       stats[3 * row + 1] = acc.s;
       stats[3 * row + 2] = tl;
@@ -324,7 +331,20 @@ extern "C" int stb_ce_stats(const void* logits, const long* targets, float* stat
   if (rows == 0) return 0;
   const int cap = sm_count() * 4;
   ce_stats_kernel<<<rows < cap ? rows : cap, kCeThreads, 0, stream>>>(
-      (const __nv_bfloat16*)logits, targets, stats, rows, V, ld, vocab_start);
+      (const __nv_bfloat16*)logits, targets, stats, rows, V, ld, vocab_start, 0);
+  STB_CHECK_LAUNCH();
+  return 0;
+}
+
+// Statistics of one column chunk [rows, Vc] of the logits (first column = global vocabulary id `vocab_start`); with
+// merge != 0 the chunk is folded into the running statistics already in `stats` (online softmax over chunks).
+extern "C" int stb_ce_stats_chunk(const void* logits, const long* targets, float* stats, int rows, int Vc, long ld,
+                                  int vocab_start, int merge, cudaStream_t stream) {
+  STB_REQUIRE(ld % 8 == 0 && (reinterpret_cast<uintptr_t>(logits) & 15) == 0, "ce: chunk must be 16-byte aligned, ld %% 8");
+  if (rows == 0) return 0;
+  const int cap = sm_count() * 4;
+  ce_stats_kernel<<<rows < cap ? rows : cap, kCeThreads, 0, stream>>>(
+      (const __nv_bfloat16*)logits, targets, stats, rows, Vc, ld, vocab_start, merge);
   STB_CHECK_LAUNCH();
   return 0;
 }

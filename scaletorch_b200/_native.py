@@ -38,9 +38,16 @@ _SIGS = {
     "stb_flash_attn_bwd": [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int,
                            c_long, c_long, c_long, c_long, c_long, c_long, c_long, c_long, c_long,
                            c_long, c_long, c_long, c_long, c_long, c_long, c_long, c_long, c_long, c_float, c_int, _P],
+    "stb_flash_attn_fwd_block": [_P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
+                                 c_long, c_long, c_long, c_long, c_long, c_long, c_long, c_long, c_long, c_float, c_int, _P],
+    "stb_flash_attn_bwd_block": [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int,
+                                 c_long, c_long, c_long, c_long, c_long, c_long, c_long, c_long, c_long,
+                                 c_long, c_long, c_long, c_long, c_long, c_long, c_long, c_long, c_long, c_float, c_int,
+                                 c_int, c_int, c_int, c_int, _P],
     "stb_swiglu_fwd": [_P, _P, c_long, c_int, _P],
     "stb_swiglu_bwd": [_P, _P, _P, c_long, c_int, _P],
     "stb_ce_stats": [_P, _P, _P, c_int, c_int, c_long, c_int, _P],
+    "stb_ce_stats_chunk": [_P, _P, _P, c_int, c_int, c_long, c_int, c_int, _P],
     "stb_ce_finalize": [_P, _P, _P, _P, c_int, c_long, _P],
     "stb_ce_grad": [_P, _P, _P, c_int, c_int, c_long, c_int, c_float, _P, c_long, _P],
     "stb_adamw": [_P, c_int, _P, _P, _P, c_long, c_float, c_float, c_float, c_float, c_float, c_int, _P, c_float, _P],

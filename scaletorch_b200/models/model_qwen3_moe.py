@@ -43,18 +43,17 @@ class MoERouter(nn.Module):
             nn.init.normal_(self.gate.weight, std=0.02)
 
     def forward(self, x: torch.Tensor):
-        """x ``[T, H]`` → ``(weights [T,k] fp32, indices [T,k] int64, aux_loss scalar)``."""
-        logits = ops.linear(x, self.gate.weight).float()
-        topk_logits, topk_idx = torch.topk(logits, self.top_k, dim=-1)
-        weights = F.softmax(topk_logits, dim=-1)
-        if self.norm_topk_prob:
-            weights = weights / weights.sum(dim=-1, keepdim=True)
-        aux = logits.new_zeros(())
-        if self.training and self.aux_loss_coef > 0:
-            probs = F.softmax(logits, dim=-1)
-            f = expert_counts(topk_idx, self.num_experts).to(probs.dtype) / x.shape[0]
-            aux = self.aux_loss_coef * self.num_experts * (f * probs.mean(dim=0)).sum()
-        return weights, topk_idx, aux
+        """x ``[T, H]`` → ``(weights [T,k] fp32, indices [T,k], aux_loss scalar)``.
+
+        Gate GEMM, then ONE routing kernel (``ops.moe_routing``): top-k, softmax over the k selected logits (which already
+        sums to one, so ``norm_topk_prob`` changes nothing), per-expert counts, the position of every pair inside its
+        expert and the Switch aux loss.  Counts and positions are kept in ``self.plan`` for the expert-parallel dispatch."""
+        from ..ops.moe_routing import route
+
+        logits = ops.linear(x, self.gate.weight)
+        weights, idx, pos, counts, aux = route(logits, self.top_k, self.aux_loss_coef, self.training)
+        self.plan = (pos, counts)
+        return weights, idx, aux
 
 
 class MoEExperts(nn.Module):
@@ -120,9 +119,11 @@ class MoELayer(nn.Module):
             from ..parallel.expert_parallel import fused_ep
 
             out, st = fused_ep.fused_moe_ep(x, weights, idx, self.experts.gate_up_proj, self.experts.down_proj,
-                                            self.num_experts, ctx.ep_group, self.ep_capacity_factor)
+                                            self.num_experts, ctx.ep_group, self.ep_capacity_factor,
+                                            plan=self.router.plan)
             self.dropped_pairs = st.dropped if self.dropped_pairs is None else self.dropped_pairs + st.dropped
         elif self.ep_size > 1:
+            idx = idx.long()
             recv, tokens_per_expert, state = dispatch_tokens(x, idx, self.num_experts, self.ep_size, ctx.ep_group)
             y = self.experts(recv, tokens_per_expert)
             out = gather_tokens(y, weights, state, ctx.ep_group)
@@ -146,7 +147,7 @@ class MoELayer(nn.Module):
     def _forward_local(self, x, weights, idx):
         T, H = x.shape
         k = idx.shape[1]
-        flat = idx.reshape(-1)
+        flat = idx.reshape(-1).long()
         sort_idx = torch.argsort(flat, stable=True)
         token_of = torch.div(sort_idx, k, rounding_mode="floor")
         xs = x.index_select(0, token_of)

@@ -85,12 +85,31 @@ def _flash_bwd(do, q, k, v, out, lse, dq, dk, dv, causal, scale):
            dv.stride(0), dv.stride(1), dv.stride(2), float(scale), int(causal), N.stream_ptr())
 
 
+_warned_head_dim: set = set()
+
+
 def _sdpa(q, k, v, causal, scale):
-    """Library attention (PyTorch SDPA) -- used only while the native kernel is absent."""
+    """Library attention for head dims the native kernel does not cover (it is written for D = 128, the head dim of
+    every Qwen3 / Llama-2/3 size the reference benchmarks).  Returns ``(out, lse)`` like the native path -- ``lse`` comes
+    from the flash backend so ring attention keeps working -- and says so once per head dim instead of silently
+    changing kernels."""
+    D = q.shape[-1]
+    if D not in _warned_head_dim:
+        _warned_head_dim.add(D)
+        import warnings
+
+        warnings.warn(f"flash_attention: head_dim {D} runs on the PyTorch SDPA flash backend; the native tcgen05 kernel "
+                      f"covers head_dim 128 only")
     g = q.shape[2] // k.shape[2]
-    o = F.scaled_dot_product_attention(q.transpose(1, 2), k.transpose(1, 2), v.transpose(1, 2),
-                                       is_causal=causal, scale=scale, enable_gqa=g > 1)
-    return o.transpose(1, 2)
+    qt, kt, vt = q.transpose(1, 2), k.transpose(1, 2), v.transpose(1, 2)
+    if g > 1:
+        kt, vt = kt.repeat_interleave(g, dim=1), vt.repeat_interleave(g, dim=1)
+    try:
+        res = torch.ops.aten._scaled_dot_product_flash_attention(qt, kt, vt, 0.0, causal, False, scale=scale)
+        return res[0].transpose(1, 2), res[1].detach()
+    except Exception:  # backend refuses this head dim / dtype: plain SDPA, lse from the fp32 oracle only if asked for
+        o = F.scaled_dot_product_attention(qt, kt, vt, is_causal=causal, scale=scale)
+        return o.transpose(1, 2), None
 
 
 class _FlashAttention(torch.autograd.Function):
@@ -117,7 +136,7 @@ def flash_attention(q, k, v, causal: bool = True, scale: float | None = None):
     if N.use_native(q) and q.dtype == torch.bfloat16:
         if native_attention_available() and q.shape[-1] == 128:
             return _FlashAttention.apply(q, k, v, causal, scale)
-        return _sdpa(q, k, v, causal, scale), None
+        return _sdpa(q, k, v, causal, scale)
     return attention_ref(q, k, v, causal, scale)
 
 
@@ -234,6 +253,37 @@ def attention_block_bwd_ref(do, q, k, v, out, lse, causal, scale, q_offset: int 
     dk = torch.einsum("bhgqk,bhgqd->bhkd", ds, qf).permute(0, 2, 1, 3)
     dv = torch.einsum("bhgqk,bhgqd->bhkd", p, dof).permute(0, 2, 1, 3)
     return dq.to(q.dtype), dk.to(k.dtype), dv.to(v.dtype)
+
+
+def ring_block_fwd_(q, k, v, out, lse, acc, merge: bool, q_lo: int, causal: bool, scale: float) -> None:
+    """One key block of a blockwise attention, merged in the kernel's epilogue (``stb_flash_attn_fwd_block``).
+
+    ``q [B,Sq,Hq,D]`` are query rows ``[q_lo, q_lo + Sq)`` of ``out [B,S,Hq,D]`` (bf16), ``acc`` (fp32 running output,
+    optional) and ``lse [B,Hq,S]``; with ``merge`` the block is folded into the result over the blocks seen so far
+    (reference: the eager ``update_out_and_lse``, ``context_parallel.py:367-424``)."""
+    B, Sq, Hq, D = q.shape
+    Sk, Hkv = k.shape[1], k.shape[2]
+    N.call("stb_flash_attn_fwd_block", q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr(), lse.data_ptr(),
+           N.ptr(acc), int(merge), int(q_lo), out.shape[1], B, Sq, Sk, Hq, Hkv, D,
+           q.stride(0), q.stride(1), q.stride(2), k.stride(0), k.stride(1), k.stride(2),
+           v.stride(0), v.stride(1), v.stride(2), float(scale), int(causal), N.stream_ptr())
+
+
+def ring_block_bwd_(do, q, k, v, out, lse, delta, dq32, dk32_ptr: int, dv32_ptr: int, kv_strides, q_lo: int, causal: bool,
+                    scale: float, first: bool) -> None:
+    """One key block of the backward of a blockwise attention (``stb_flash_attn_bwd_block``): ``dq32`` (fp32, full
+    ``[B,S,Hq,D]``) is written on the ``first`` block and accumulated afterwards; this rank's (dK, dV) contributions are
+    ``red.add``-ed into the fp32 accumulators at ``dk32_ptr`` / ``dv32_ptr`` -- raw device addresses, usually in the memory
+    of the GPU that owns the block -- laid out with ``kv_strides`` (batch, token, head; in elements)."""
+    B, Sq, Hq, D = q.shape
+    Sk, Hkv = k.shape[1], k.shape[2]
+    dq = dq32[:, q_lo:]
+    N.call("stb_flash_attn_bwd_block", do.data_ptr(), q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr(),
+           lse.data_ptr(), delta.data_ptr(), dq.data_ptr(), dk32_ptr, dv32_ptr, B, Sq, Sk, Hq, Hkv, D,
+           q.stride(0), q.stride(1), q.stride(2), k.stride(0), k.stride(1), k.stride(2),
+           v.stride(0), v.stride(1), v.stride(2), dq.stride(0), dq.stride(1), dq.stride(2),
+           kv_strides[0], kv_strides[1], kv_strides[2], kv_strides[0], kv_strides[1], kv_strides[2],
+           float(scale), int(causal), int(q_lo), out.shape[1], int(first), int(not first), N.stream_ptr())
 
 
 def attention_block_fwd(q, k, v, causal, scale):

@@ -22,6 +22,21 @@ def cross_entropy_ref(logits: torch.Tensor, targets: torch.Tensor, ignore_index:
     return F.cross_entropy(logits.float().view(-1, logits.shape[-1]), targets.reshape(-1), ignore_index=ignore_index)
 
 
+def _chunks(T: int, V: int) -> list[tuple[int, int]]:
+    """Column chunks of the vocabulary such that one ``[T, Vc]`` bf16 chunk of logits (plus its weight rows) stays in the
+    126 MB L2 between the kernel that writes it and the kernels that read it: forward = GEMM → statistics, backward =
+    gradient-in-place → dgrad GEMM → wgrad GEMM.  The logits still exist in HBM once (the backward needs them), but the
+    statistics pass and both backward GEMMs read them from L2: ≈3 × T·V·2 bytes of HBM reads saved per step
+    (3.7 GB for 4096 tokens of a 151,936-word vocabulary)."""
+    import os
+
+    budget = int(os.environ.get("SCALETORCH_B200_CE_CHUNK_MB", "64")) << 20
+    if budget <= 0 or T * V * 2 <= 2 * budget:
+        return [(0, V)]
+    vc = max(1024, (budget // (T * 2)) // 256 * 256)
+    return [(c, min(V, c + vc)) for c in range(0, V, vc)]
+
+
 class _LinearCrossEntropy(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, weight, targets, loss_scale, ignore_index, tp_group, vocab_start):
@@ -30,10 +45,20 @@ class _LinearCrossEntropy(torch.autograd.Function):
         T = x2.shape[0]
         V = weight.shape[0]
         tgt = targets.reshape(-1).contiguous()
-        logits = gemm(x2, weight)  # [T, V_local] bf16
         stats = torch.empty((T, 3), dtype=torch.float32, device=x.device)
-        N.call("stb_ce_stats", logits.data_ptr(), tgt.data_ptr(), stats.data_ptr(), T, V, logits.stride(0),
-               vocab_start, N.stream_ptr())
+        chunks = _chunks(T, V) if (V % 8 == 0 and getattr(weight, "main_grad", None) is not None) else [(0, V)]
+        if len(chunks) == 1:
+            logits = gemm(x2, weight)  # [T, V_local] bf16
+            N.call("stb_ce_stats", logits.data_ptr(), tgt.data_ptr(), stats.data_ptr(), T, V, logits.stride(0),
+                   vocab_start, N.stream_ptr())
+        else:
+            logits = torch.empty((T, V), dtype=x2.dtype, device=x.device)
+            for i, (c0, c1) in enumerate(chunks):
+                lc = logits[:, c0:c1]
+                gemm(x2, weight[c0:c1], out=lc)
+                N.call("stb_ce_stats_chunk", lc.data_ptr(), tgt.data_ptr(), stats.data_ptr(), T, c1 - c0, V,
+                       vocab_start + c0, int(i > 0), N.stream_ptr())
+        ctx.chunks = chunks
         if tp_group is not None and dist.get_world_size(tp_group) > 1:
             gmax = stats[:, 0].clone()
             dist.all_reduce(gmax, op=dist.ReduceOp.MAX, group=tp_group)
@@ -57,11 +82,43 @@ class _LinearCrossEntropy(torch.autograd.Function):
         ignore_index, vocab_start, xshape = ctx.cfg
         T, V = logits.shape
         scale = (dloss.to(torch.float32) * inv).contiguous()
+        if len(ctx.chunks) > 1:
+            return _LinearCrossEntropy._backward_chunked(ctx, x2, weight, tgt, logits, lse, scale)
         N.call("stb_ce_grad", logits.data_ptr(), tgt.data_ptr(), lse.data_ptr(), T, V, logits.stride(0),
                vocab_start, 1.0, scale.data_ptr(), ignore_index, N.stream_ptr())
         dx = gemm(logits, weight, b_mn=True).view(xshape) if ctx.needs_input_grad[0] else None
         dw = wgrad_into(weight, logits, x2) if ctx.needs_input_grad[1] else None
         return dx, dw, None, None, None, None, None
+
+
+def _backward_chunked(ctx, x2, weight, tgt, logits, lse, scale):
+    """Per column chunk: gradient in place → dgrad (accumulated into an fp32 dX) → wgrad into the chunk's rows of the
+    flat fp32 gradient buffer; each chunk is consumed out of L2 right after it is produced."""
+    ignore_index, vocab_start, xshape = ctx.cfg
+    T, V = logits.shape
+    H = x2.shape[1]
+    need_dx, need_dw = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
+    dx32 = torch.empty((T, H), dtype=torch.float32, device=x2.device) if need_dx else None
+    mg = weight.main_grad.view(V, H)
+    acc_w = bool(getattr(weight, "grad_written", False))
+    for i, (c0, c1) in enumerate(ctx.chunks):
+        lc = logits[:, c0:c1]
+        N.call("stb_ce_grad", lc.data_ptr(), tgt.data_ptr(), lse.data_ptr(), T, c1 - c0, V, vocab_start + c0, 1.0,
+               scale.data_ptr(), ignore_index, N.stream_ptr())
+        if need_dx:
+            gemm(lc, weight[c0:c1], b_mn=True, out=dx32, accumulate=i > 0)
+        if need_dw:
+            gemm(lc, x2, a_mn=True, b_mn=True, out=mg[c0:c1], accumulate=acc_w)
+    if need_dw:
+        weight.grad_written = True
+        hook = getattr(weight, "grad_ready_hook", None)
+        if hook is not None:
+            hook()
+    dx = dx32.to(x2.dtype).view(xshape) if need_dx else None
+    return dx, None, None, None, None, None, None
+
+
+_LinearCrossEntropy._backward_chunked = staticmethod(_backward_chunked)
 
 
 def linear_cross_entropy(

@@ -51,6 +51,15 @@ class GroupedLayout:
         self.tile_expert = torch.where(tiles < offs_pad[-1], te, torch.full_like(te, -1)).to(torch.int32).contiguous()
         return self
 
+    @classmethod
+    def from_device_tables(cls, offs_pad: torch.Tensor, tile_expert: torch.Tensor, r_max: int, num_experts: int):
+        """Layout whose ``offs_pad [E+1]`` / ``tile_expert [r_max / 128]`` int32 tables were written by a kernel
+        (``stb_ep_plan``)."""
+        self = cls.__new__(cls)
+        self.offs_pad, self.tile_expert = offs_pad, tile_expert
+        self.r_max, self.E, self.num_rows = r_max, num_experts, None
+        return self
+
     def pad(self, x_sorted: torch.Tensor) -> torch.Tensor:
         out = torch.zeros((self.r_max, x_sorted.shape[1]), dtype=x_sorted.dtype, device=x_sorted.device)
         return out.index_copy(0, self.dest, x_sorted)

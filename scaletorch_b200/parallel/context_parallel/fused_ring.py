@@ -5,10 +5,13 @@ Forward: K/V are copied once into the CP group's window; after one on-device bar
 peer blocks into local staging buffers (one pass over NVLink per block -- measured: letting the attention kernel's
 TMA read the peer window directly re-reads each block once per query tile and makes the kernel NVLink-bound, 178 ms
 vs 121 ms per step on Qwen3-1.7B cp2), step 0 (own block, causal) runs meanwhile, then step ``s`` runs the tcgen05
-flash kernel on the staged block of rank ``(r - s) mod cp`` and the partial ``(out, lse)`` results are merged.  Backward: each rank computes the (dK, dV) contributions of the blocks
-it attended to into its own window (one slot per source block); after a barrier the owner of each block sums the
-contributions of the ranks that used it by reading their windows.  No send/recv, no forwarding hops, K/V travel
-un-expanded (``Hkv`` heads).
+flash kernel on the staged block of rank ``(r - s) mod cp`` and folds the partial result into ``(out, lse)`` in its
+epilogue (``stb_flash_attn_fwd_block``).  Backward: each rank runs the block backward kernel per block it attended to;
+dQ accumulates in fp32 inside the kernel and the (dK, dV) contributions are added straight into the fp32 accumulators
+in the window of the rank that owns the block (``red.global.add`` over NVLink), so after one barrier every owner holds
+its complete gradient.  No send/recv, no forwarding hops, no eager math between the attention launches, K/V travel
+un-expanded (``Hkv`` heads).  The staging copies run on the copy engines (peer ``cudaMemcpyAsync`` on a side stream):
+they take no SMs from the attention kernels they overlap with.
 
 Reference: ``RingAttentionFunc`` with batched isend/irecv and eager per-block attention
 (``scaletorch/parallel/context_parallel/context_parallel.py:111-263``, ``cp_comms.py:72-222``).
@@ -22,7 +25,6 @@ from ... import ops
 from ...runtime import fused_ops as F
 from ...runtime import symm
 from . import zigzag
-from .context_parallel import update_output_and_lse, update_rows
 
 SLOT_CP = 5
 _pull_streams: dict[int, torch.cuda.Stream] = {}
@@ -62,15 +64,19 @@ def _stage_peer_blocks(g, steps, shape, n):
 def available(q: torch.Tensor, k: torch.Tensor, group) -> bool:
     if not (q.is_cuda and q.dtype == torch.bfloat16 and q.shape[-1] == 128 and ops.native_attention_available()):
         return False
-    if not symm.group_ready(group):
+    if not symm.group_ready(group) or not symm.has_kernel("stb_flash_attn_bwd_block"):
         return False
     g = F.get_group(group)
     kv_bytes = k.numel() * 2
-    # window: [K | V] forward + cp x [dK | dV] fp32 backward slots must fit the spare + rs regions
-    return 2 * kv_bytes <= g.region_bytes and g.world * 2 * k.numel() * 4 <= 2 * g.region_bytes
+    # window: [K | V] bf16 in the spare region; fp32 [dK | dV] accumulators of the own block in the rs + ar regions
+    return 2 * kv_bytes <= g.region_bytes and 2 * k.numel() * 4 <= 2 * g.region_bytes
 
 
 class FusedRingAttention(torch.autograd.Function):
+    """No eager math between the attention launches: the (out, lse) merge happens in the forward kernel's epilogue
+    (fp32 running output), dQ accumulates in fp32 inside the backward kernel, and every rank adds its (dK, dV)
+    contributions straight into the block owner's fp32 accumulators over NVLink (``red.global.add``)."""
+
     @staticmethod
     def forward(ctx, q, k, v, sm_scale, is_causal, group):
         g = F.get_group(group)
@@ -88,16 +94,16 @@ class FusedRingAttention(torch.autograd.Function):
         plans = {s_: zigzag.block_plan(s_, r, cp, S, is_causal, zz) for s_ in range(1, cp)}
         steps = {s_: (r - s_) % cp for s_ in range(1, cp) if plans[s_] is not None}
         staged = _stage_peer_blocks(g, steps, (B, S, Hkv, D), n)
-        out, lse = ops.attention.attention_block_fwd(q, k, v, is_causal, sm_scale)
-        out, lse = update_output_and_lse(None, None, out, lse)
+        out = F._empty(q.shape, q.dtype, q.device)
+        lse = torch.empty((B, q.shape[2], S), dtype=torch.float32, device=q.device)
+        acc = torch.empty(q.shape, dtype=torch.float32, device=q.device) if steps else None
+        ops.attention.ring_block_fwd_(q, k, v, out, lse, acc, False, 0, is_causal, sm_scale)
         for step in steps:
             kb, vb, ev = staged[step]
             torch.cuda.current_stream().wait_event(ev)
             q_lo, k_hi, cf = plans[step]
-            b_out, b_lse = ops.attention.attention_block_fwd(q[:, q_lo:], kb[:, :k_hi], vb[:, :k_hi], cf, sm_scale)
-            out, lse = update_rows(out, lse, b_out, b_lse, q_lo)
+            ops.attention.ring_block_fwd_(q[:, q_lo:], kb[:, :k_hi], vb[:, :k_hi], out, lse, acc, True, q_lo, cf, sm_scale)
         g.barrier(SLOT_CP)                      # every pull has completed: windows may be overwritten
-        out = out.to(q.dtype)
         ctx.save_for_backward(q, k, v, out, lse)
         ctx.cfg = (sm_scale, is_causal, group, zz)
         return out
@@ -115,20 +121,19 @@ class FusedRingAttention(torch.autograd.Function):
         vw = g.view(g.off_spare + n * 2, (B, S, Hkv, D), torch.bfloat16)
         kw.copy_(k)
         vw.copy_(v)
-        # contribution slots: slot j holds this rank's (dK, dV) for block j, bf16, in the rs+ar regions
-        slot_bytes = 2 * n * 2
-        base = g.off_rs
-
-        def slot(j):
-            dk = g.view(base + j * slot_bytes, (B, S, Hkv, D), torch.bfloat16)
-            dv = g.view(base + j * slot_bytes + n * 2, (B, S, Hkv, D), torch.bfloat16)
-            return dk, dv
-
-        g.barrier(SLOT_CP)
+        # fp32 accumulators of the gradient of MY block, in my window: every rank that attended to the block adds into them
+        off_dk, off_dv = g.off_rs, g.off_rs + n * 4
+        dk32 = g.view(off_dk, (B, S, Hkv, D), torch.float32)
+        dv32 = g.view(off_dv, (B, S, Hkv, D), torch.float32)
+        g.view(off_dk, (2 * n,), torch.float32).zero_()
+        g.rs_dirty = True
+        g.barrier(SLOT_CP)                      # K/V published, accumulators zeroed
         plans = {s_: zigzag.block_plan(s_, r, cp, S, is_causal, zz) for s_ in range(1, cp)}
         steps = {s_: (r - s_) % cp for s_ in range(1, cp) if plans[s_] is not None}
         staged = _stage_peer_blocks(g, steps, (B, S, Hkv, D), n)
-        dq = torch.zeros(q.shape, dtype=torch.float32, device=q.device)
+        dq32 = torch.empty(q.shape, dtype=torch.float32, device=q.device)
+        delta = torch.empty((B, q.shape[2], S), dtype=torch.float32, device=q.device)
+        kv_strides = (S * Hkv * D, Hkv * D, D)
         for step in [0] + list(steps):
             src = (r - step) % cp
             if step == 0:
@@ -138,37 +143,11 @@ class FusedRingAttention(torch.autograd.Function):
                 kb, vb, ev = staged[step]
                 torch.cuda.current_stream().wait_event(ev)
                 q_lo, k_hi, cf = plans[step]
-            dkj, dvj = slot(src)
-            if q_lo == 0 and k_hi == S:
-                dqj = torch.empty_like(q)
-                ops.attention._flash_bwd(dout, q, kb, vb, out, lse, dqj, dkj, dvj, cf, sm_scale)
-                dq += dqj.float()
-            else:                       # zig-zag half block: queries [q_lo:] x keys [:k_hi]
-                qs = q[:, q_lo:]
-                dqj = torch.empty_like(qs)
-                if k_hi < S:            # the untouched half of the contribution slot must read as zero
-                    dkj[:, k_hi:].zero_()
-                    dvj[:, k_hi:].zero_()
-                ops.attention._flash_bwd(dout[:, q_lo:].contiguous(), qs, kb[:, :k_hi], vb[:, :k_hi],
-                                         out[:, q_lo:].contiguous(), lse[:, :, q_lo:].contiguous(), dqj,
-                                         dkj[:, :k_hi], dvj[:, :k_hi], cf, sm_scale)
-                dq[:, q_lo:] += dqj.float()
-        g.barrier(SLOT_CP)                      # all contributions are written
-        # block r was used by ranks r, r+1, ..., cp-1 (causal) or by everyone
-        dk = torch.zeros(k.shape, dtype=torch.float32, device=k.device)
-        dv = torch.zeros(v.shape, dtype=torch.float32, device=v.device)
-        users = range(cp) if (zz or not is_causal) else range(r, cp)
-        for u in users:
-            off = base + r * slot_bytes
-            if u == r:
-                dku, dvu = slot(r)
-            else:
-                dku = g.window_h.get_buffer(u, (B, S, Hkv, D), torch.bfloat16, off // 2)
-                dvu = g.window_h.get_buffer(u, (B, S, Hkv, D), torch.bfloat16, (off + n * 2) // 2)
-            dk += dku.float()
-            dv += dvu.float()
-        g.barrier(SLOT_CP)                      # contribution slots may be reused
-        return dq.to(q.dtype), dk.to(k.dtype), dv.to(v.dtype), None, None, None
+            ops.attention.ring_block_bwd_(dout, q[:, q_lo:], kb[:, :k_hi], vb[:, :k_hi], out, lse, delta, dq32,
+                                          g.peer_ptrs[src] + off_dk, g.peer_ptrs[src] + off_dv, kv_strides, q_lo, cf,
+                                          sm_scale, first=(step == 0))
+        g.barrier(SLOT_CP)                      # every rank's contributions have landed in the owners' accumulators
+        return dq32.to(q.dtype), dk32.to(k.dtype), dv32.to(v.dtype), None, None, None
 
 
 def fused_ring_attention(q, k, v, sm_scale: float, is_causal: bool, group) -> torch.Tensor:

@@ -37,13 +37,20 @@ _P, _I, _L, _U = ctypes.c_void_p, ctypes.c_int, ctypes.c_long, ctypes.c_uint
 N.register("stb_ep_exchange_counts", [_P, _P, _L, _P, _I, _P, _I, _I, _I, _U, _P])
 N.register("stb_ep_push", [_P, _P, _L, _P, _P, _P, _P, _L, _I, _I, _I, _I, _I, _U, _I, _P])
 N.register("stb_ep_pull", [_P, _P, _L, _P, _P, _P, _P, _P, _L, _I, _I, _I, _I, _I, _U, _I, _P])
+N.register("stb_ep_plan", [_P, _P, _P, _L, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P, _I, _P])
+N.register("stb_ep_zero_padding", [_P, _P, _P, _I, _I, _I, _P])
+N.register("stb_copy_rows_dyn", [_P, _P, _P, _L, _I, _P])
 
 SLOT_EP = 6
 _windows: dict = {}
 
 
-def default_capacity_factor() -> float:
-    return float(os.environ.get("SCALETORCH_B200_EP_CAPACITY", "2.0"))
+def default_capacity_factor() -> float | None:
+    """``None`` = dropless (receive regions sized for the worst case ``ep × T·k`` rows).  A smaller factor bounds the
+    regions and every row-padded activation at ``factor × T·k`` rows and DROPS the pairs that do not fit -- an explicit
+    opt-in (``--ep_capacity_factor`` / ``SCALETORCH_B200_EP_CAPACITY``), never the default."""
+    v = os.environ.get("SCALETORCH_B200_EP_CAPACITY")
+    return float(v) if v else None
 
 
 class EPWindow:
@@ -83,7 +90,9 @@ def reset() -> None:
 
 
 def ep_plan(table: torch.Tensor, flat: torch.Tensor, counts: torch.Tensor, rank: int, e_local: int, rows_cap: int):
-    """Destination of every ``(token, k)`` pair of rank ``rank`` -- pure tensor math, no communication.
+    """Destination of every ``(token, k)`` pair of rank ``rank`` -- pure tensor math, no communication.  The GPU path
+    computes the same plan with ONE kernel (``stb_ep_plan``, ``csrc/moe_router.cu``); this function is its oracle
+    (``tests/test_ep_plan_cpu.py``, ``tests/test_kernels_gpu.py``) with positions in the sender's stable order.
 
     ``table [ep, E]``: pairs every source rank sends to every global expert (identical on all ranks after the count
     exchange); ``flat [P]``: this rank's expert ids in pair order; ``counts [E]`` = ``table[rank]``.  The receive region
@@ -112,29 +121,51 @@ def ep_plan(table: torch.Tensor, flat: torch.Tensor, counts: torch.Tensor, rank:
 
 
 class FusedEPState:
-    """Routing plan of one MoE layer call (all tensors on the device)."""
+    """Routing plan of one MoE layer call (all tensors on the device, built by two kernels: the count exchange and
+    ``stb_ep_plan``)."""
 
-    def __init__(self, win: EPWindow, idx: torch.Tensor, num_experts: int):
+    def __init__(self, win: EPWindow, idx: torch.Tensor, num_experts: int, plan=None):
         g = win.g
         ep, rank = g.world, g.rank
         T, k = idx.shape
         e_local = num_experts // ep
         P = T * k
-        flat = idx.reshape(-1)
-        counts = expert_counts(flat, num_experts).to(torch.int32)
-        table = torch.empty((ep, num_experts), dtype=torch.int32, device=idx.device)
+        dev = idx.device
+        if plan is not None and plan[0].dtype == torch.int32 and idx.dtype == torch.int32:
+            pos, counts = plan                               # from the routing kernel (ops/moe_routing.py)
+            flat = idx.reshape(-1)
+        else:                                                # ids from elsewhere: positions by a stable sort
+            flat64 = idx.reshape(-1).long()
+            c64 = expert_counts(flat64, num_experts)
+            order = torch.argsort(flat64, stable=True)
+            inv = torch.empty_like(order)
+            inv[order] = torch.arange(P, device=dev)
+            pos = (inv - (torch.cumsum(c64, 0) - c64)[flat64]).to(torch.int32)
+            counts, flat = c64.to(torch.int32), flat64.to(torch.int32)
+        table = torch.empty((ep, num_experts), dtype=torch.int32, device=dev)
         N.call("stb_ep_exchange_counts", win.bufs_dev, g.flag_pages_dev, win.off_table, counts.data_ptr(), num_experts,
                table.data_ptr(), rank, ep, SLOT_EP, g.take_epochs(SLOT_EP, 1), N.stream_ptr())
-        plan = ep_plan(table.to(torch.int64), flat, counts.to(torch.int64), rank, e_local, win.rows_cap)
-        self.row, self.rank_of, self.dropped, offs_pad, self.tokens_per_expert = plan
-        self.win, self.T, self.k, self.P = win, T, k, P
-        self.layout = GroupedLayout.from_padded_offsets(offs_pad, win.rows_cap, e_local)   # my own experts' rows
+        n_tiles = win.rows_cap // 128
+        meta = torch.zeros(1 + (e_local + 1) + e_local + n_tiles, dtype=torch.int32, device=dev)
+        self.dropped = meta[0:1]
+        offs_pad = meta[1:e_local + 2]
+        self.tokens_per_expert = meta[e_local + 2:2 * e_local + 2]
+        tile_expert = meta[2 * e_local + 2:]
+        self.row = torch.empty(P, dtype=torch.int32, device=dev)
+        self.rank_of = torch.empty(P, dtype=torch.int32, device=dev)
+        N.call("stb_ep_plan", table.data_ptr(), flat.data_ptr(), pos.data_ptr(), P, num_experts, ep, rank, win.rows_cap,
+               self.row.data_ptr(), self.rank_of.data_ptr(), self.dropped.data_ptr(), offs_pad.data_ptr(),
+               self.tokens_per_expert.data_ptr(), tile_expert.data_ptr(), n_tiles, N.stream_ptr())
+        self.win, self.T, self.k, self.P, self.e_local = win, T, k, P, e_local
+        self.offs_pad = offs_pad
+        self.layout = GroupedLayout.from_device_tables(offs_pad, tile_expert, win.rows_cap, e_local)
 
     # -- raw kernels ---------------------------------------------------------------------------------------
     def push(self, src: torch.Tensor, scale: torch.Tensor | None) -> None:
-        """rows of ``src [T, H]`` → peers' X regions (zeroed first so the padding rows are exact zeros)."""
+        """rows of ``src [T, H]`` → peers' X regions; only the (< 128 per expert) padding rows are zeroed first."""
         win, g = self.win, self.win.g
-        win.x.zero_()
+        N.call("stb_ep_zero_padding", win.x.data_ptr(), self.offs_pad.data_ptr(), self.tokens_per_expert.data_ptr(),
+               self.e_local, win.hidden, win.rows_cap, N.stream_ptr())
         N.call("stb_ep_push", win.bufs_dev, g.flag_pages_dev, win.off_x, src.data_ptr(), self.rank_of.data_ptr(),
                self.row.data_ptr(), scale.data_ptr() if scale is not None else None, self.P, self.k, win.hidden,
                g.rank, g.world, SLOT_EP, g.take_epochs(SLOT_EP, 2), 0, N.stream_ptr())
@@ -158,7 +189,11 @@ class _Dispatch(torch.autograd.Function):
     def forward(ctx, x, st: FusedEPState):
         ctx.st = st
         st.push(x.contiguous(), None)
-        return st.win.x.clone()
+        # private copy of the rows in use (saved for the expert wgrad; the window is recycled by the next layer)
+        xp = torch.empty_like(st.win.x)
+        N.call("stb_copy_rows_dyn", st.win.x.data_ptr(), xp.data_ptr(), st.offs_pad[st.e_local:].data_ptr(),
+               st.win.hidden * 2, st.win.rows_cap, N.stream_ptr())
+        return xp
 
     @staticmethod
     def backward(ctx, d_xpad):
@@ -195,16 +230,17 @@ class _Combine(torch.autograd.Function):
 
 
 def fused_moe_ep(x: torch.Tensor, weights: torch.Tensor, idx: torch.Tensor, gate_up_proj: torch.Tensor,
-                 down_proj: torch.Tensor, num_experts: int, group, capacity_factor: float | None = None):
-    """Full EP MoE branch: returns ``(out [T, H], FusedEPState)``."""
+                 down_proj: torch.Tensor, num_experts: int, group, capacity_factor: float | None = None, plan=None):
+    """Full EP MoE branch: returns ``(out [T, H], FusedEPState)``.  ``plan``: ``(pos, counts)`` of the routing kernel."""
     T, H = x.shape
     k = idx.shape[1]
     ep = dist.get_world_size(group)
     e_local = num_experts // ep
-    cf = min(default_capacity_factor() if capacity_factor is None else capacity_factor, float(ep))
+    cf = default_capacity_factor() if capacity_factor is None else capacity_factor
+    cf = float(ep) if cf is None else min(float(cf), float(ep))      # dropless unless a capacity was asked for
     rows_cap = (int(cf * T * k) + e_local * 127 + 127) // 128 * 128
     win = get_window(group, rows_cap, H, num_experts)
-    st = FusedEPState(win, idx, num_experts)
+    st = FusedEPState(win, idx, num_experts, plan)
     xp = _Dispatch.apply(x, st)
     gu = _GroupedLinearPadded.apply(xp, gate_up_proj, st.layout, {"dx": win.y})
     y = _GroupedLinearPadded.apply(swiglu(gu), down_proj, st.layout, {"out": win.y})

@@ -106,6 +106,11 @@ class SymmGroup:
         self.off_ag, self.off_rs, self.off_ar, self.off_spare = 0, q, 2 * q, 3 * q
         self.region_bytes = q
         self.ready_flags = torch.zeros(1 << 16, dtype=torch.int32, device=dev)   # AG->GEMM row-block flags (local)
+        # GEMM->reduce-scatter destinations are double-buffered halves of the RS region; both start out zeroed and each
+        # call re-zeroes the half the NEXT call will add into (see gemm_reduce_scatter)
+        self.window[self.off_rs:self.off_rs + q].zero_()
+        self.rs_parity = 0
+        self.rs_dirty = False          # set by other users of the RS region (ring attention accumulators)
         torch.cuda.synchronize()
         dist.barrier(group)            # flag pages are zero everywhere before the first device barrier
 
@@ -169,15 +174,26 @@ def gemm_reduce_scatter(x: torch.Tensor, weight: torch.Tensor, group, b_mn: bool
     T, K = x.shape
     Nn = weight.shape[1] if b_mn else weight.shape[0]
     rows = T // g.world
-    assert rows * Nn * 2 <= g.region_bytes, "reduce-scatter destination does not fit the symmetric window region"
-    dest = g.view(g.off_rs, (rows, Nn), torch.bfloat16)
-    dest.zero_()
-    g.barrier(SLOT_RS)                                   # every destination is zeroed
-    ptrs = g.peer_ptr_array(g.off_rs)
+    half = g.region_bytes // 2
+    assert rows * Nn * 2 <= half, "reduce-scatter destination does not fit half of the symmetric window region"
+    # Two destination buffers alternate.  The one this call adds into was zeroed on every rank during the previous call,
+    # before that call's closing barrier; this call zeroes the other one for its successor.  One device barrier per call
+    # (it makes the adds visible AND orders the zero-fill before the next call's adds) instead of zero + barrier + GEMM +
+    # barrier.
+    if g.rs_dirty:                                       # somebody else wrote into the region: restore the invariant
+        g.window[g.off_rs:g.off_rs + g.region_bytes].zero_()
+        g.barrier(SLOT_RS)
+        g.rs_dirty = False
+    off = g.off_rs + g.rs_parity * half
+    other = g.off_rs + (1 - g.rs_parity) * half
+    g.rs_parity ^= 1
+    dest = g.view(off, (rows, Nn), torch.bfloat16)
+    g.window[other:other + half].zero_()
+    ptrs = g.peer_ptr_array(off)
     N.call("stb_gemm_rs_bf16", x.data_ptr(), weight.data_ptr(), ptrs, T, Nn, K, x.stride(0), weight.stride(0), Nn,
            int(b_mn), g.rank, g.world, N.stream_ptr())
-    g.barrier(SLOT_RS)                                   # every rank's adds have landed
-    return dest.clone()
+    g.barrier(SLOT_RS)                                   # every rank's adds have landed; the other half is zero everywhere
+    return dest.clone()                                  # the buffer is recycled two calls from now
 
 
 def gemm_all_reduce(x: torch.Tensor, weight: torch.Tensor, group, b_mn: bool = False) -> torch.Tensor:

@@ -246,6 +246,36 @@ def test_linear_cross_entropy(V):
     assert _rel_err(w.grad, wr.grad) < 3e-2
 
 
+def test_linear_cross_entropy_chunked(monkeypatch):
+    """Vocabulary processed in column chunks (online statistics, per-chunk gradient / dgrad / wgrad into main_grad)."""
+    monkeypatch.setenv("SCALETORCH_B200_CE_CHUNK_MB", "1")
+    torch.manual_seed(9)
+    T, H, V = 384, 256, 20000                      # 1 MB budget -> chunks of 1280 columns, ragged last chunk
+    x = _bf(T, H).requires_grad_()
+    w = torch.nn.Parameter(_bf(V, H, scale=0.05))
+    w.main_grad = torch.full((V * H,), float("nan"), device="cuda")
+    w.grad_written = False
+    tgt = torch.randint(0, V, (T,), device="cuda")
+    tgt[::13] = -100
+    from scaletorch_b200.ops.cross_entropy import _chunks
+
+    assert len(_chunks(T, V)) > 8
+    loss = ops.linear_cross_entropy(x, w, tgt, loss_scale=0.5)
+    (loss * 2.0).backward()
+    xr = x.detach().float().requires_grad_()
+    wr = w.detach().float().requires_grad_()
+    lr = torch.nn.functional.cross_entropy(xr @ wr.t(), tgt, ignore_index=-100) * 0.5
+    (lr * 2.0).backward()
+    assert abs(loss.item() - lr.item()) < 2e-2 * abs(lr.item())
+    assert _rel_err(x.grad, xr.grad) < 3e-2
+    assert w.grad is None and w.grad_written
+    assert _rel_err(w.main_grad.view(V, H), wr.grad) < 3e-2
+    # second backward accumulates into main_grad
+    loss2 = ops.linear_cross_entropy(x, w, tgt, loss_scale=0.5)
+    (loss2 * 2.0).backward()
+    assert _rel_err(w.main_grad.view(V, H), 2 * wr.grad) < 3e-2
+
+
 def test_embedding():
     torch.manual_seed(10)
     V, H = 1000, 256
@@ -353,3 +383,69 @@ def test_moe_layer_native_matches_oracle():
     assert _rel_err(xg, x.grad) < 5e-2
     for n, p in layer.named_parameters():
         assert _rel_err(grads[n], p.grad) < 6e-2, n
+
+
+@pytest.mark.parametrize("T,E,k", [(777, 128, 8), (64, 8, 2), (1000, 60, 4), (33, 256, 16)])
+@pytest.mark.parametrize("coef", [0.0, 0.01])
+def test_moe_router_kernels(T, E, k, coef):
+    """Routing kernel (top-k, gate weights, counts, positions, aux loss) and its backward vs the PyTorch oracle."""
+    from scaletorch_b200.ops.moe_routing import route, route_ref
+
+    torch.manual_seed(3)
+    # distinct bf16 logits per row so that top-k has no ties to break differently
+    base = torch.stack([torch.randperm(E, device="cuda").float() for _ in range(T)]) / 8.0 - E / 16.0
+    logits = base.bfloat16().requires_grad_()
+    w, idx, pos, counts, aux = route(logits, k, coef, True)
+    assert idx.dtype == torch.int32 and pos.dtype == torch.int32
+    lr = logits.detach().clone().requires_grad_()
+    w_r, idx_r, pos_r, counts_r, aux_r = route_ref(lr, k, coef, True)
+    assert torch.equal(idx.long(), idx_r)
+    assert torch.equal(counts.long(), counts_r)
+    assert _rel_err(w, w_r) < 1e-5
+    assert abs(float(aux) - float(aux_r)) <= 2e-3 * max(1e-3, abs(float(aux_r))), (float(aux), float(aux_r))
+    # positions: a bijection onto [0, count) inside every expert
+    flat, p = idx.reshape(-1).long(), pos.reshape(-1).long()
+    key = flat * (T * k) + p
+    assert key.unique().numel() == T * k
+    assert bool((p < counts.long()[flat]).all()) and bool((p >= 0).all())
+    gw = torch.randn(T, k, device="cuda")
+    (w * gw).sum().add(aux * 3.0).backward()
+    (w_r * gw).sum().add(aux_r * 3.0).backward()
+    assert _rel_err(logits.grad, lr.grad) < 2e-2, _rel_err(logits.grad, lr.grad)
+
+
+@pytest.mark.parametrize("ep,E,cap_factor", [(4, 32, 4.0), (2, 8, 1.1), (8, 128, 8.0)])
+def test_ep_plan_kernel_matches_tensor_plan(ep, E, cap_factor):
+    """``stb_ep_plan`` against the pure-tensor plan: same segments, same owner ranks, rows a bijection per expert."""
+    from scaletorch_b200.parallel.expert_parallel import fused_ep  # registers the kernel signatures
+
+    torch.manual_seed(11)
+    T, k = 500, 2
+    e_local = E // ep
+    idx = [torch.stack([torch.randperm(E, device="cuda")[:k] for _ in range(T)]) for _ in range(ep)]
+    table = torch.stack([torch.bincount(i.reshape(-1), minlength=E) for i in idx]).to(torch.int32)
+    rows_cap = (int(cap_factor * T * k) + e_local * 127 + 127) // 128 * 128
+    for r in range(ep):
+        flat = idx[r].reshape(-1)
+        row_t, dest_t, drop_t, offs_t, tpe_t = fused_ep.ep_plan(table.long(), flat, table[r].long(), r, e_local, rows_cap)
+        order = torch.argsort(flat, stable=True)
+        inv = torch.empty_like(order)
+        inv[order] = torch.arange(flat.numel(), device="cuda")
+        c = table[r].long()
+        pos = (inv - (torch.cumsum(c, 0) - c)[flat]).to(torch.int32)
+        n_tiles = rows_cap // 128
+        row = torch.empty(T * k, dtype=torch.int32, device="cuda")
+        dest = torch.empty_like(row)
+        dropped = torch.zeros(1, dtype=torch.int32, device="cuda")
+        offs = torch.empty(e_local + 1, dtype=torch.int32, device="cuda")
+        tpe = torch.empty(e_local, dtype=torch.int32, device="cuda")
+        tile_e = torch.empty(n_tiles, dtype=torch.int32, device="cuda")
+        N.call("stb_ep_plan", table.data_ptr(), flat.to(torch.int32).data_ptr(), pos.data_ptr(), T * k, E, ep, r, rows_cap,
+               row.data_ptr(), dest.data_ptr(), dropped.data_ptr(), offs.data_ptr(), tpe.data_ptr(), tile_e.data_ptr(),
+               n_tiles, N.stream_ptr())
+        torch.cuda.synchronize()
+        assert torch.equal(row, row_t) and torch.equal(dest, dest_t)
+        assert int(dropped) == int(drop_t)
+        assert torch.equal(offs.long(), offs_t.long()) and torch.equal(tpe.long(), tpe_t.long())
+        lay = fused_ep.GroupedLayout.from_padded_offsets(offs_t, rows_cap, e_local)
+        assert torch.equal(tile_e, lay.tile_expert)

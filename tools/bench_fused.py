@@ -3,12 +3,11 @@
     torchrun --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 tools/bench_fused.py [--tokens 8192] [--hidden 4096] [--ffn 12288]
 
 For every op it prints (rank 0, max over ranks, CUDA events, 10 timed iterations after 3 warm-ups):
-  fused ms | unfused ms | speed-up | roofline ms = max(FLOPs / measured bf16 peak, NVLink bytes per GPU / 900 GB/s) | fraction
+  fused ms | unfused ms | speed-up | roofline ms = max(FLOPs / measured bf16 peak, NVLink bytes per GPU / 770 GB/s measured) | fraction
 Ops: all-gather→GEMM (column-parallel fwd with SP), GEMM→reduce-scatter (row-parallel fwd with SP), GEMM→all-reduce
 (row-parallel fwd without SP), fp32 gradient all-reduce (DP bucket, NVLS vs peer loads vs NCCL).
 JSON lines are appended to gpurun_out/fused.jsonl (copy the ones to keep into profiles/).
 
-Written at the end of round 1 after the GPU budget was spent: not yet run on hardware.
 """
 from __future__ import annotations
 
@@ -26,7 +25,7 @@ from scaletorch_b200.runtime import fused_ops as F  # noqa: E402
 from scaletorch_b200.runtime import symm  # noqa: E402
 from scaletorch_b200.utils.device import get_measured_peaks  # noqa: E402
 
-NVLINK_GBS = 900.0
+NVLINK_GBS = 770.0      # measured peer-copy bandwidth per direction on this pool (B200_PROFILING.md); nominal 900
 
 
 def timeit(fn, iters: int = 10, warmup: int = 3) -> float:

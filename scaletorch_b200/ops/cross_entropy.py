@@ -30,7 +30,10 @@ def _chunks(T: int, V: int) -> list[tuple[int, int]]:
     (3.7 GB for 4096 tokens of a 151,936-word vocabulary)."""
     import os
 
-    budget = int(os.environ.get("SCALETORCH_B200_CE_CHUNK_MB", "64")) << 20
+    # Off by default: measured on B200 (Qwen3-0.6B, 4096 tokens, V = 151,936; profiles/ce_chunking_r2.md) the 19 chunks
+    # cost more in launches, GEMM prologue/epilogue tails and the fp32 dX accumulation than the L2 hits save
+    # (27.09 ms/step chunked vs 26.75 ms unchunked).  SCALETORCH_B200_CE_CHUNK_MB=64 turns it on.
+    budget = int(os.environ.get("SCALETORCH_B200_CE_CHUNK_MB", "0")) << 20
     if budget <= 0 or T * V * 2 <= 2 * budget:
         return [(0, V)]
     vc = max(1024, (budget // (T * 2)) // 256 * 256)

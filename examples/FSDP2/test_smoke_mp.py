@@ -31,10 +31,10 @@ def _batch(step: int, vocab: int, batch: int, seq: int):
     return tok[:, :-1], tok[:, 1:]
 
 
-def _train(model, opt, steps, rank, world, vocab, start=0):
+def _train(model, opt, steps, rank, world, vocab, start=0, global_batch=8):
     losses = []
     for step in range(start, steps):
-        x, y = _batch(step, vocab, 4 * world, 32)
+        x, y = _batch(step, vocab, global_batch, 32)
         x, y = x[rank::world], y[rank::world]                  # disjoint shares of one global batch
         loss = F.cross_entropy(model(x).float().flatten(0, 1), y.flatten())
         loss.backward()

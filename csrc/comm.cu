@@ -200,7 +200,7 @@ __global__ void __launch_bounds__(512)
   for (long i = long(blockIdx.x) * blockDim.x + threadIdx.x; i < nvec; i += long(gridDim.x) * blockDim.x) {
     float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     for (int p = 0; p < world; ++p) {
-      const uint4 v = ld_nc_v4(bufs[(rank + p) % world] + offset + (i << 3));
+      const uint4 v = ld_peer_v4(bufs[(rank + p) % world] + offset + (i << 3));
       const uint32_t u[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
@@ -234,7 +234,7 @@ __global__ void __launch_bounds__(512)
     const uint4* s = reinterpret_cast<const uint4*>(bufs[src] + offset_bytes + r0 * row_bytes);
     uint4* d = reinterpret_cast<uint4*>(dst + (long(src) * rows_per_rank + r0) * row_bytes);
     const long nv = (r1 - r0) * vec_per_row;
-    for (long i = threadIdx.x; i < nv; i += blockDim.x) d[i] = ld_nc_v4(s + i);
+    for (long i = threadIdx.x; i < nv; i += blockDim.x) d[i] = ld_peer_v4(s + i);
     __threadfence();
     __syncthreads();
     if (threadIdx.x == 0) st_release_gpu(ready + long(src) * blocks_per_rank + rb, epoch);
@@ -266,7 +266,7 @@ __global__ void __launch_bounds__(256)
     const int c = int(r % vec_per_row) * 8;
     const long id = reinterpret_cast<const long*>(bufs[src] + ids_off)[t] - vocab_start;
     if (id < 0 || id >= vocab_local) continue;
-    const uint4 d = ld_nc_v4(reinterpret_cast<const __nv_bfloat16*>(bufs[src] + dout_off) + t * H + c);
+    const uint4 d = ld_peer_v4(reinterpret_cast<const __nv_bfloat16*>(bufs[src] + dout_off) + t * H + c);
     const uint32_t du[4] = {d.x, d.y, d.z, d.w};
     float* dst = dW + id * H + c;
 #pragma unroll

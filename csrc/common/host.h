@@ -27,10 +27,12 @@ int make_tmap_bshd(CUtensorMap* out, const void* base, int B, int S, int H, int 
                    long sh, uint32_t box_d, uint32_t box_s);
 
 // CTA-pair GEMM (csrc/gemm_pair.cu): entry, its work model, and the k-split it would choose.
+struct GemmFused;   // csrc/common/gemm_fused.cuh
 namespace pair {
 int run(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc, int a_mn, int b_mn,
-        int out_fp32, int accumulate, int bn, int splits, cudaStream_t stream);
+        int out_fp32, int accumulate, int bn, int splits, cudaStream_t stream, const GemmFused* fx);
 float pick_config(int M, int N, int K, int out_fp32, int n_pairs, int* bn_out, int* splits_out);
+float pair_cost(int M, int N, int K, int out_fp32, int bn, int splits, int n_pairs);
 }  // namespace pair
 
 #define STB_CHECK_CUDA(expr)                                                              \

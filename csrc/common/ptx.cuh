@@ -271,6 +271,16 @@ STB_DEVICE uint4 ld_nc_v4(const void* p) {
                : "l"(p));
   return r;
 }
+// Data in symmetric / peer memory that another GPU (re)writes while this kernel is resident -- read after an acquire on a
+// flag -- must not go through the non-coherent path: PTX requires .nc data to be read-only for the kernel's lifetime.
+STB_DEVICE uint4 ld_peer_v4(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.relaxed.sys.v4.u32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p)
+               : "memory");
+  return r;
+}
 STB_DEVICE void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
   asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d)
                : "memory");

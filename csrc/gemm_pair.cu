@@ -22,6 +22,7 @@
 // 16-byte aligned with a 16-byte-multiple row pitch (stb_gemm_bf16 falls back to the single-CTA kernel otherwise).
 // All TMA loads here read this GPU's memory; the fused-collective GEMMs stay on the single-CTA kernel.
 #include "common/cluster.cuh"
+#include "common/gemm_fused.cuh"
 #include "common/host.h"
 #include "common/ptx.cuh"
 
@@ -50,6 +51,19 @@ struct Params {
   int tiles_m, tiles_n, num_tiles, k_blocks;
   int splits, kb_per_split, num_units;   // unit u = (split u / num_tiles, tile u % num_tiles)
   int out_fp32, accumulate;
+  // ---- fused collectives (0 / nullptr = plain GEMM); same meaning as in the single-CTA kernel (gemm_tcgen05.cu)
+  int m_rotate;                 // rotation of the 256-row tile index: other ranks' rows first / local rows first
+  int rows_per_dest;            // GEMM->reduce-scatter: rows [d * rows_per_dest, ...) are added into tensor map d
+  const uint32_t* a_ready;      // all-gather->GEMM: one flag per a_flag_rows rows of A, ready when >= a_epoch
+  uint32_t a_epoch;
+  int a_flag_rows;
+  int n_copy;                   // leading CTAs (whole pairs) of the grid that run the copy role
+  const uint8_t* const* ag_bufs;
+  uint32_t* const* ag_flag_pages;
+  long ag_offset_bytes;
+  uint8_t* ag_dst;
+  uint32_t* ag_ready;
+  int ag_rank, ag_world, ag_slot;
 };
 
 // Grouped tile order: kGroup consecutive M tiles share each sweep over N, so the tiles in flight at any time
@@ -63,7 +77,7 @@ STB_DEVICE void unit_coords(const Params& p, int unit, int& tm, int& tn, int& kb
   const int first_m = g * kGroup;
   const int gm = min(p.tiles_m - first_m, kGroup);
   const int r = tile - g * group_size;
-  tm = first_m + r % gm;
+  tm = (first_m + r % gm + p.m_rotate) % p.tiles_m;
   tn = r / gm;
   kb0 = split * p.kb_per_split;
   kb1 = min(p.k_blocks, kb0 + p.kb_per_split);
@@ -72,7 +86,19 @@ STB_DEVICE void unit_coords(const Params& p, int unit, int& tm, int& tn, int& kb
 template <int kBN, bool A_MN, bool B_MN>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
     gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                     const __grid_constant__ CUtensorMap tmC, const Params p) {
+                     const __grid_constant__ CMaps tmCs, const Params p) {
+  // all-gather->GEMM with device-driven epochs (see gemm_tcgen05.cu): every CTA reads the slot's counter and checks in
+  uint32_t a_epoch = p.a_epoch;
+  if (p.a_ready != nullptr && p.a_epoch == 0) {
+    uint32_t* page = p.ag_flag_pages[p.ag_rank];
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(a_epoch) : "l"(page + 8 * 16 + 16 + p.ag_slot) : "memory");
+    __syncthreads();
+    if (threadIdx.x == 0) atomicAdd(page + 8 * 16 + 24 + p.ag_slot, 1u);
+  }
+  if (int(blockIdx.x) < p.n_copy) {   // communication CTAs (whole pairs): no TMEM, no pipeline, no cluster barrier
+    ag_copy_role(p, a_epoch);
+    return;
+  }
   constexpr int kBNc = Cfg<kBN>::kBNc, kBBytes = Cfg<kBN>::kBBytes, kStageBytes = Cfg<kBN>::kStageBytes;
   constexpr int kStages = Cfg<kBN>::kStages, kTmemCols = Cfg<kBN>::kTmemCols;
   extern __shared__ uint8_t smem_raw[];
@@ -90,12 +116,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = cluster_ctarank();
   const bool leader = rank == 0;
-  const int pair_id = int(blockIdx.x) >> 1, n_pairs = int(gridDim.x) >> 1;
+  const int pair_id = (int(blockIdx.x) - p.n_copy) >> 1, n_pairs = (int(gridDim.x) - p.n_copy) >> 1;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
-    tma_prefetch_desc(&tmC);
+    tma_prefetch_desc(&tmCs.m[0]);
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < kStages; ++i) {
@@ -127,6 +153,18 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
         unit_coords(p, unit, tm, tn, kb0, kb1);
         const int m0 = tm * 2 * kBMc + int(rank) * kBMc;      // my 128 rows of A
         const int n0 = tn * kBN + int(rank) * kBNc;           // my 128 rows of B
+        if (p.a_ready != nullptr) {
+          // all-gather->GEMM: my 128 rows of A are being pulled from a peer by the copy CTAs of this grid
+          const int last_row = min(m0 + kBMc, p.M) - 1;
+          for (int fb = m0 / p.a_flag_rows; fb <= last_row / p.a_flag_rows; ++fb) {
+            const uint32_t* f = p.a_ready + fb;
+            uint32_t v;
+            do {
+              asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
+            } while (int32_t(v - a_epoch) < 0);
+          }
+          asm volatile("fence.proxy.async.global;" ::: "memory");  // generic-proxy writes -> TMA (async proxy) reads
+        }
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
           const uint32_t bar = mapa_shared(smem_u32(&full_bar[stage]), 0);   // the leader's barrier
@@ -206,7 +244,15 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
       const uint32_t acc_phase = (it >> 1) & 1;
       mbar_wait(&tmem_full[acc], acc_phase);
       tc_fence_after();
-      const int row0 = tm * 2 * kBMc + int(rank) * kBMc + ew * 32;
+      int row0 = tm * 2 * kBMc + int(rank) * kBMc + ew * 32;
+      // GEMM->reduce-scatter: this CTA's 128 rows belong to rank `dest`, whose output buffer (peer memory) tensor map
+      // `dest` addresses: the TMA reduce-add below travels over NVLink
+      const CUtensorMap* tmC = &tmCs.m[0];
+      if (p.rows_per_dest > 0) {
+        const int dest = row0 / p.rows_per_dest;
+        tmC = &tmCs.m[dest];
+        row0 -= dest * p.rows_per_dest;
+      }
       const uint32_t taddr = tmem_base + (uint32_t(ew * 32) << 16) + acc * kBN;
       const uint32_t empty_addr = mapa_shared(smem_u32(&tmem_empty[acc]), 0);
       const int step = p.out_fp32 ? 32 : 64;            // columns per 128-byte staging row
@@ -245,8 +291,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
         fence_proxy_async_smem();
         __syncwarp();
         if (lane == 0) {
-          if (add) tma_reduce_add_2d(&tmC, slots + slot * 4096, tn * kBN + c, row0);
-          else tma_store_2d(&tmC, slots + slot * 4096, tn * kBN + c, row0);
+          if (add) tma_reduce_add_2d(tmC, slots + slot * 4096, tn * kBN + c, row0);
+          else tma_store_2d(tmC, slots + slot * 4096, tn * kBN + c, row0);
           tma_store_commit();
         }
         slot ^= 1;
@@ -300,7 +346,7 @@ float pick_config(int M, int N, int K, int out_fp32, int n_pairs, int* bn_out, i
 }
 
 template <int BN, bool A_MN, bool B_MN>
-static int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const Params& p,
+static int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CMaps& tmC, const Params& p,
                   cudaStream_t stream) {
   auto kern = gemm_pair_kernel<BN, A_MN, B_MN>;
   static bool attr_set[64] = {false};
@@ -310,9 +356,10 @@ static int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensor
     STB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::kSmemBytes));
     attr_set[dev] = true;
   }
-  int grid = sm_count() & ~1;                       // whole pairs only
+  int grid = (sm_count() - p.n_copy) & ~1;          // whole pairs only, all co-resident with the copy CTAs
   const int need = 2 * p.num_units;
   if (need < grid) grid = need;
+  grid += p.n_copy;
   kern<<<grid, kThreads, Cfg<BN>::kSmemBytes, stream>>>(tmA, tmB, tmC, p);
   STB_CHECK_LAUNCH();
   return 0;
@@ -320,12 +367,21 @@ static int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensor
 
 // bn: 0 = choose, 128 / 256 = forced tile width.  splits: 0 = choose, 1 = none, n > 1 = forced (fp32 destination only).
 int run(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc, int a_mn, int b_mn,
-        int out_fp32, int accumulate, int bn, int splits, cudaStream_t stream) {
+        int out_fp32, int accumulate, int bn, int splits, cudaStream_t stream, const GemmFused* fxp) {
+  static const GemmFused no_fusion;
+  const GemmFused& fx = fxp != nullptr ? *fxp : no_fusion;
+  const bool fused = fx.n_dest > 0 || fx.a_ready != nullptr;
+  if (fused) {
+    bn = 256;
+    splits = 1;
+  }
+  if (fx.n_dest > 0) C = fx.c_dest[0];
   STB_REQUIRE(M > 0 && N > 0 && K > 0, "gemm_pair: empty problem");
   const int esz = out_fp32 ? 4 : 2;
   STB_REQUIRE((reinterpret_cast<uintptr_t>(C) & 15) == 0 && (long(ldc) * esz) % 16 == 0,
               "gemm_pair: C must be 16-byte aligned with a 16-byte-multiple row pitch");
-  STB_REQUIRE(!accumulate || out_fp32, "gemm_pair: accumulation needs an fp32 destination");
+  STB_REQUIRE(!accumulate || out_fp32 || fx.n_dest > 0, "gemm_pair: accumulation needs an fp32 destination");
+  STB_REQUIRE(fx.n_copy % 2 == 0, "gemm_pair: the copy role takes whole CTA pairs (n_copy %d)", fx.n_copy);
   STB_REQUIRE(!(a_mn && !b_mn), "gemm_pair: (A MN-major, B K-major) is not instantiated");
   STB_REQUIRE(bn == 0 || bn == 128 || bn == 256, "gemm_pair: tile width %d", bn);
   const int n_pairs = sm_count() / 2;
@@ -337,7 +393,8 @@ int run(const void* A, const void* B, void* C, int M, int N, int K, int lda, int
     else splits = 1;
   }
   if (!out_fp32) splits = 1;
-  CUtensorMap tmA, tmB, tmC;
+  CUtensorMap tmA, tmB;
+  CMaps tmC;
   int rc;
   // operand boxes: K-major -> [64 k] x [rows per CTA]; MN-major -> [64 rows] x [64 k] atoms (as in the single-CTA kernel)
   if (!a_mn) rc = make_tmap_2d(&tmA, A, 2, K, M, uint64_t(lda) * 2, kBK, kBMc, 1);
@@ -346,9 +403,18 @@ int run(const void* A, const void* B, void* C, int M, int N, int K, int lda, int
   if (!b_mn) rc = make_tmap_2d(&tmB, B, 2, K, N, uint64_t(ldb) * 2, kBK, bn / 2, 1);
   else rc = make_tmap_2d(&tmB, B, 2, N, K, uint64_t(ldb) * 2, 64, kBK, 1);
   if (rc) return rc;
-  if (out_fp32) rc = make_tmap_2d(&tmC, C, 4, N, M, uint64_t(ldc) * 4, 32, 32, 1);
-  else rc = make_tmap_2d(&tmC, C, 2, N, M, uint64_t(ldc) * 2, 64, 32, 1);
-  if (rc) return rc;
+  const int nd = fx.n_dest > 0 ? fx.n_dest : 1;
+  const int c_rows = fx.n_dest > 0 ? M / fx.n_dest : M;
+  for (int d = 0; d < kMaxDest; ++d) {
+    if (d < nd) {
+      void* base = fx.n_dest > 0 ? fx.c_dest[d] : C;
+      if (out_fp32) rc = make_tmap_2d(&tmC.m[d], base, 4, N, c_rows, uint64_t(ldc) * 4, 32, 32, 1);
+      else rc = make_tmap_2d(&tmC.m[d], base, 2, N, c_rows, uint64_t(ldc) * 2, 64, 32, 1);
+      if (rc) return rc;
+    } else {
+      tmC.m[d] = tmC.m[0];
+    }
+  }
   Params p;
   p.M = M; p.N = N; p.K = K;
   p.tiles_m = (M + 2 * kBMc - 1) / (2 * kBMc);
@@ -360,6 +426,12 @@ int run(const void* A, const void* B, void* C, int M, int N, int K, int lda, int
   p.splits = (p.k_blocks + p.kb_per_split - 1) / p.kb_per_split;     // no empty range
   p.num_units = p.num_tiles * p.splits;
   p.out_fp32 = out_fp32; p.accumulate = accumulate;
+  p.m_rotate = fx.m_rotate % p.tiles_m;
+  p.rows_per_dest = fx.n_dest > 0 ? M / fx.n_dest : 0;
+  p.a_ready = fx.a_ready; p.a_epoch = fx.a_epoch; p.a_flag_rows = fx.a_flag_rows; p.n_copy = fx.n_copy;
+  p.ag_bufs = fx.ag_bufs; p.ag_flag_pages = fx.ag_flag_pages; p.ag_offset_bytes = fx.ag_offset_bytes;
+  p.ag_dst = fx.ag_dst; p.ag_ready = const_cast<uint32_t*>(fx.a_ready);
+  p.ag_rank = fx.ag_rank; p.ag_world = fx.ag_world; p.ag_slot = fx.ag_slot;
   if (p.splits > 1 && !accumulate)   // every split adds: start from zero
     STB_CHECK_CUDA(cudaMemset2DAsync(C, size_t(ldc) * 4, 0, size_t(N) * 4, size_t(M), stream));
 #define STB_PAIR_CASE(BN_)                                                    \
@@ -381,5 +453,5 @@ int run(const void* A, const void* B, void* C, int M, int N, int K, int lda, int
 extern "C" int stb_gemm_bf16_2cta(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc,
                                   int a_mn, int b_mn, int out_fp32, int accumulate, int bn, int splits,
                                   cudaStream_t stream) {
-  return stb::pair::run(A, B, C, M, N, K, lda, ldb, ldc, a_mn, b_mn, out_fp32, accumulate, bn, splits, stream);
+  return stb::pair::run(A, B, C, M, N, K, lda, ldb, ldc, a_mn, b_mn, out_fp32, accumulate, bn, splits, stream, nullptr);
 }

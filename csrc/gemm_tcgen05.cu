@@ -20,6 +20,7 @@
 // the main loop of tile i+1.
 #include <stdlib.h>
 
+#include "common/gemm_fused.cuh"
 #include "common/host.h"
 #include "common/ptx.cuh"
 
@@ -53,11 +54,6 @@ struct GemmParams {
   int ag_rank, ag_world, ag_slot;
 };
 
-constexpr int kMaxDest = 8;
-struct CMaps {
-  CUtensorMap m[kMaxDest];
-};
-
 template <int BN>
 struct GemmCfg {
   static constexpr int kABytes = kBM * kBK * 2;
@@ -79,98 +75,6 @@ STB_DEVICE void tile_coords(int tile, int tiles_m, int tiles_n, int& m, int& n) 
   const int r = tile - g * group_size;
   m = first_m + r % gm;
   n = r / gm;
-}
-
-// ---- copy role of the all-gather->GEMM kernel --------------------------------------------------------
-// Flag-page layout and barrier protocol are shared with csrc/comm.cu (kMaxWorld = 16, kMaxSlots = 8).
-STB_DEVICE void ag_cross_gpu_barrier(uint32_t* const* pages, int rank, int world, int slot, uint32_t epoch) {
-  const int t = threadIdx.x;
-  if (t < world) {
-    __threadfence_system();
-    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(pages[t] + slot * 16 + rank), "r"(epoch) : "memory");
-    const uint32_t* mine = pages[rank] + slot * 16 + t;
-    uint32_t v;
-    do {
-      asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(mine) : "memory");
-    } while (int32_t(v - epoch) < 0);
-  }
-}
-
-STB_DEVICE void ag_copy_role(const GemmParams& p, const uint32_t a_epoch) {
-  uint32_t* go = p.ag_flag_pages[p.ag_rank] + 8 * 16 + p.ag_slot;
-  uint32_t* done = p.ag_flag_pages[p.ag_rank] + 8 * 16 + 8 + p.ag_slot;
-  // 1. every rank has written its shard (cross-GPU barrier by copy CTA 0, released locally to the others)
-  if (blockIdx.x == 0) {
-    if (threadIdx.x < 32) ag_cross_gpu_barrier(p.ag_flag_pages, p.ag_rank, p.ag_world, p.ag_slot, a_epoch);
-    __syncthreads();
-    if (threadIdx.x == 0) asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(go), "r"(a_epoch) : "memory");
-  } else {
-    if (threadIdx.x == 0) {
-      uint32_t v;
-      do {
-        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(go) : "memory");
-      } while (int32_t(v - a_epoch) < 0);
-    }
-    __syncthreads();
-  }
-  // 2. pull row blocks: own shard first, then the peers in ring order (the order the compute CTAs consume)
-  const long rows_per_rank = p.M / p.ag_world;
-  const long row_bytes = long(p.K) * 2;
-  const long blocks_per_rank = (rows_per_rank + p.a_flag_rows - 1) / p.a_flag_rows;
-  const long total = blocks_per_rank * p.ag_world;
-  const long vec_per_row = row_bytes >> 4;
-  for (long blk = blockIdx.x; blk < total; blk += p.n_copy) {
-    const int src = int((p.ag_rank + blk / blocks_per_rank) % p.ag_world);
-    const long rb = blk % blocks_per_rank;
-    const long r0 = rb * p.a_flag_rows, r1 = min(rows_per_rank, r0 + long(p.a_flag_rows));
-    const uint4* s = reinterpret_cast<const uint4*>(p.ag_bufs[src] + p.ag_offset_bytes + r0 * row_bytes);
-    uint4* d = reinterpret_cast<uint4*>(p.ag_dst + (long(src) * rows_per_rank + r0) * row_bytes);
-    const long nv = (r1 - r0) * vec_per_row;
-    long i = threadIdx.x;
-    for (; i + 7 * kGemmThreads < nv; i += 8 * kGemmThreads) {   // 8 x 16 B in flight per thread
-      uint4 v[8];
-#pragma unroll
-      for (int u = 0; u < 8; ++u) v[u] = ld_nc_v4(s + i + u * kGemmThreads);
-#pragma unroll
-      for (int u = 0; u < 8; ++u) d[i + u * kGemmThreads] = v[u];
-    }
-    for (; i < nv; i += kGemmThreads) d[i] = ld_nc_v4(s + i);
-    __threadfence();
-    __syncthreads();
-    if (threadIdx.x == 0)
-      asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p.ag_ready + long(src) * blocks_per_rank + rb),
-                   "r"(a_epoch)
-                   : "memory");
-  }
-  // 3. tell the peers their shard buffers may be reused: all copy CTAs done -> cross-GPU barrier
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    __threadfence_system();
-    atomicAdd(done, 1u);
-  }
-  if (blockIdx.x == 0) {
-    if (threadIdx.x == 0) {
-      uint32_t v;
-      do {
-        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(done) : "memory");
-      } while (v < uint32_t(p.n_copy));
-      *done = 0;
-    }
-    __syncthreads();
-    if (threadIdx.x < 32) ag_cross_gpu_barrier(p.ag_flag_pages, p.ag_rank, p.ag_world, p.ag_slot, a_epoch + 1);
-    if (p.a_epoch == 0 && threadIdx.x == 0) {
-      // device-driven epochs: advance the slot counter once every CTA of the grid has read it
-      uint32_t* checkin = p.ag_flag_pages[p.ag_rank] + 8 * 16 + 24 + p.ag_slot;
-      uint32_t v;
-      do {
-        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(checkin) : "memory");
-      } while (v < gridDim.x);
-      *checkin = 0;
-      asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p.ag_flag_pages[p.ag_rank] + 8 * 16 + 16 + p.ag_slot),
-                   "r"(a_epoch + 2)
-                   : "memory");
-    }
-  }
 }
 
 template <int BN, bool A_MN, bool B_MN, bool EPI_TMA>
@@ -508,21 +412,6 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
   if (warp == 2) tmem_dealloc(tmem_base, Cfg::kTmemCols);
 }
 
-struct GemmFused {
-  int m_rotate = 0;
-  int n_dest = 0;                 // > 0: GEMM->reduce-scatter into c_dest[d] (each [M / n_dest, N], ld = ldc)
-  void* c_dest[kMaxDest] = {nullptr};
-  const uint32_t* a_ready = nullptr;
-  uint32_t a_epoch = 0;
-  int a_flag_rows = 0;
-  int n_copy = 0;
-  const uint8_t* const* ag_bufs = nullptr;
-  uint32_t* const* ag_flag_pages = nullptr;
-  long ag_offset_bytes = 0;
-  uint8_t* ag_dst = nullptr;
-  int ag_rank = 0, ag_world = 1, ag_slot = 0;
-};
-
 template <int BN, bool A_MN, bool B_MN, bool EPI_TMA>
 static int launch_gemm(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb,
                        int ldc, int out_fp32, int accumulate, cudaStream_t stream, const GemmFused& fx) {
@@ -645,14 +534,22 @@ static int gemm_dispatch(const void* A, const void* B, void* C, int M, int N, in
   const int celt = out_fp32 ? 4 : 2;
   const void* c0 = fx.n_dest > 0 ? fx.c_dest[0] : C;
   const bool epi_tma = ((reinterpret_cast<uintptr_t>(c0) & 15) == 0) && ((size_t(ldc) * celt) % 16 == 0);
-  // plain GEMMs go to the CTA-pair kernel when it is faster (the fused-collective variants stay here)
+  // the CTA-pair kernel takes the GEMM when it is faster; fused-collective variants too, when their row blocks are
+  // whole 256-row pair tiles and the copy CTAs come in pairs
   const bool plain = fx.n_dest == 0 && fx.a_ready == nullptr && fx.n_copy == 0;
-  if (plain && epi_tma && force_bn == 0 && pair_policy() > 0 && (!accumulate || out_fp32)) {
-    const int n_pairs = sm_count() / 2;
+  const bool fused_ok = !plain && (fx.n_dest == 0 || (M / fx.n_dest) % 256 == 0) &&
+                        (fx.a_ready == nullptr || ((M / fx.ag_world) % 256 == 0 && fx.n_copy % 2 == 0)) && M % 256 == 0;
+  if ((plain || fused_ok) && epi_tma && force_bn == 0 && pair_policy() > 0 && (!accumulate || out_fp32 || fx.n_dest > 0)) {
+    const int n_pairs = (sm_count() - fx.n_copy) / 2;
     int pbn = 256, ps = 1;
-    const float pc = pair::pick_config(M, N, K, out_fp32, n_pairs, &pbn, &ps);
-    if (pair_policy() == 1 || pc <= single_cost(M, N, K, out_fp32, bn))
-      return pair::run(A, B, C, M, N, K, lda, ldb, ldc, a_mn, b_mn, out_fp32, accumulate, pbn, ps, stream);
+    float pc = pair::pick_config(M, N, K, out_fp32, n_pairs, &pbn, &ps);
+    if (!plain) pc = pair::pair_cost(M, N, K, out_fp32, 256, 1, n_pairs);
+    if (pair_policy() == 1 || pc <= single_cost(M, N, K, out_fp32, bn)) {
+      GemmFused f2 = fx;
+      f2.m_rotate = fx.m_rotate / 2;                       // 128-row tiles -> 256-row pair tiles
+      return pair::run(A, B, C, M, N, K, lda, ldb, ldc, a_mn, b_mn, out_fp32, accumulate, pbn, ps, stream,
+                       plain ? nullptr : &f2);
+    }
   }
   STB_REQUIRE(epi_tma || fx.n_dest == 0, "gemm_rs: destination buffers must be 16-byte aligned");
 #define STB_GEMM_CASE(BN_, AMN_, BMN_)                                                             \

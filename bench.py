@@ -260,7 +260,7 @@ def run_ours(args):
     if graphed is not None and graphed.graph is not None:
         launches = launches_per_graph[0] * args.steps              # replayed from the graph: same kernels every step
         per_kernel = {k: v * args.steps for k, v in per_kernel_graph.items()}
-    comm_kernels = ("stb_allreduce_f32", "stb_reduce_scatter_f32", "stb_adamw_shard_bcast", "stb_allreduce_tiny_f32",
+    comm_kernels = ("stb_allreduce_f32", "stb_reduce_scatter_f32", "stb_adamw_shard_bcast", "stb_param_bcast", "stb_allreduce_tiny_f32",
                     "stb_embedding_bwd_peers", "stb_ag_gemm_bf16", "stb_gemm_rs_bf16", "stb_allreduce_bf16",
                     "stb_allreduce_oneshot_bf16", "stb_ep_push", "stb_ep_pull", "stb_ep_exchange_counts", "stb_symm_barrier")
     # which transport the gradient synchronisation used: NVLS multimem / peer loads-stores / c10d-NCCL

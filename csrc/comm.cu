@@ -164,13 +164,26 @@ __global__ void __launch_bounds__(512)
   const long nvec = n >> 3;
   const long per = (nvec + world - 1) / world;
   const long lo = per * rank, hi = min(nvec, lo + per);
-  for (long i = lo + long(blockIdx.x) * blockDim.x + threadIdx.x; i < hi; i += long(gridDim.x) * blockDim.x) {
-    const long e = offset + (i << 3);
-    uint4 out;
-    if (MULTIMEM) {
-      out = multimem_ld_reduce_bf16x8(mc + e);
-      multimem_st_u4(mc + e, out);
-    } else {
+  if (MULTIMEM) {
+    // NVLS: 8 independent 16-byte ld_reduce in flight per thread, then 8 broadcast stores (as in the fp32 kernel)
+    constexpr int U = 8;
+    const long stride = long(gridDim.x) * blockDim.x;
+    for (long i0 = lo + long(blockIdx.x) * blockDim.x + threadIdx.x; i0 < hi; i0 += stride * U) {
+      uint4 acc[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long i = i0 + u * stride;
+        if (i < hi) acc[u] = multimem_ld_reduce_bf16x8(mc + offset + (i << 3));
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long i = i0 + u * stride;
+        if (i < hi) multimem_st_u4(mc + offset + (i << 3), acc[u]);
+      }
+    }
+  } else {
+    for (long i = lo + long(blockIdx.x) * blockDim.x + threadIdx.x; i < hi; i += long(gridDim.x) * blockDim.x) {
+      const long e = offset + (i << 3);
       float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
       for (int p = 0; p < world; ++p) {
         const float4 vf = ld_peer_f4(reinterpret_cast<const float*>(bufs[(rank + p) % world] + e));
@@ -182,8 +195,8 @@ __global__ void __launch_bounds__(512)
           acc[2 * j] += f.x; acc[2 * j + 1] += f.y;
         }
       }
-      out = make_uint4(pack_bf16x2(acc[0], acc[1]), pack_bf16x2(acc[2], acc[3]), pack_bf16x2(acc[4], acc[5]),
-                       pack_bf16x2(acc[6], acc[7]));
+      const uint4 out = make_uint4(pack_bf16x2(acc[0], acc[1]), pack_bf16x2(acc[2], acc[3]), pack_bf16x2(acc[4], acc[5]),
+                                   pack_bf16x2(acc[6], acc[7]));
       for (int p = 0; p < world; ++p) *reinterpret_cast<uint4*>(bufs[(rank + p) % world] + e) = out;
     }
   }
@@ -414,6 +427,46 @@ __global__ void __launch_bounds__(512)
   grid_finish_cross_gpu_barrier(flag_pages, rank, world, slot, epoch + 1, epoch_arg);
 }
 
+// Broadcast of one owner's parameter shard: elements [p_off, p_off + n) of the symmetric bf16 parameter buffer are
+// copied from rank `owner`'s copy into every rank's copy (multimem.st through the switch: the owner sends each byte
+// once, or one store per peer).  Every rank launches the kernel (opening barrier: nobody still reads the old values;
+// closing barrier: the values have landed everywhere); only the owner moves data.  Used by the sharded optimiser to
+// all-gather the updated parameters one owner after the other at the START of the next step, on the communication
+// stream, so the forward pass begins as soon as the first shards are in and the rest of the gather hides behind it.
+template <bool MULTIMEM>
+__global__ void __launch_bounds__(512)
+    param_bcast_kernel(__nv_bfloat16* const* pbufs, __nv_bfloat16* pmc, uint32_t* const* flag_pages, long p_off, long n,
+                       int owner, int rank, int world, int slot, uint32_t epoch_arg) {
+  const uint32_t epoch = symm_epoch_load(flag_pages, rank, slot, epoch_arg);
+  grid_cross_gpu_barrier(flag_pages, rank, world, slot, epoch);
+  if (rank == owner) {
+    const uint4* src = reinterpret_cast<const uint4*>(pbufs[rank] + p_off);
+    const long nvec = n >> 3;
+    constexpr int U = 4;
+    const long stride = long(gridDim.x) * blockDim.x;
+    for (long i0 = long(blockIdx.x) * blockDim.x + threadIdx.x; i0 < nvec; i0 += stride * U) {
+      uint4 v[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long i = i0 + u * stride;
+        if (i < nvec) v[u] = src[i];
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long i = i0 + u * stride;
+        if (i < nvec) {
+          if (MULTIMEM) {
+            multimem_st_b128(pmc + p_off + (i << 3), v[u]);
+          } else {
+            for (int p = 1; p < world; ++p) st_peer_b128(pbufs[(rank + p) % world] + p_off + (i << 3), v[u]);
+          }
+        }
+      }
+    }
+  }
+  grid_finish_cross_gpu_barrier(flag_pages, rank, world, slot, epoch + 1, epoch_arg);
+}
+
 // In-place sum of `n` (<= 32) fp32 values living at element `offset` of every rank's symmetric buffer: every rank
 // reads all copies and writes the total into its OWN copy.  Used for the squared-norm partials of the sharded
 // optimiser; one CTA, two device barriers, no library call in the step.
@@ -588,6 +641,26 @@ extern "C" int stb_allreduce_tiny_f32(const void* bufs_dev, const void* flag_pag
   STB_REQUIRE(n >= 1 && n <= 32, "allreduce_tiny: n %d out of range (1..32)", n);
   allreduce_tiny_f32_kernel<<<1, 32, 0, stream>>>((float* const*)bufs_dev, (uint32_t* const*)flag_pages_dev,
                                                   offset_elems, n, rank, world, slot, epoch);
+  STB_CHECK_LAUNCH();
+  return 0;
+}
+
+// Consumes 2 epochs.  See param_bcast_kernel.
+extern "C" int stb_param_bcast(const void* pbufs_dev, void* p_multicast_ptr, const void* flag_pages_dev,
+                               long p_offset_elems, long n, int owner, int rank, int world, int slot, unsigned epoch,
+                               int sm_budget, cudaStream_t stream) {
+  STB_REQUIRE(world <= kMaxWorld && slot < kMaxSlots, "param_bcast: world %d / slot %d out of range", world, slot);
+  STB_REQUIRE(p_offset_elems % 8 == 0 && n % 8 == 0, "param_bcast: offset and n must be multiples of 8 elements");
+  STB_REQUIRE(owner >= 0 && owner < world, "param_bcast: owner %d", owner);
+  const int grid = rank == owner ? comm_grid(sm_budget) : 1;
+  if (p_multicast_ptr != nullptr)
+    param_bcast_kernel<true><<<grid, 512, 0, stream>>>((__nv_bfloat16* const*)pbufs_dev, (__nv_bfloat16*)p_multicast_ptr,
+                                                       (uint32_t* const*)flag_pages_dev, p_offset_elems, n, owner, rank,
+                                                       world, slot, epoch);
+  else
+    param_bcast_kernel<false><<<grid, 512, 0, stream>>>((__nv_bfloat16* const*)pbufs_dev, nullptr,
+                                                        (uint32_t* const*)flag_pages_dev, p_offset_elems, n, owner,
+                                                        rank, world, slot, epoch);
   STB_CHECK_LAUNCH();
   return 0;
 }

@@ -17,6 +17,7 @@ Ops (all stream-ordered on the current stream, no host synchronisation):
 from __future__ import annotations
 
 import ctypes
+import os
 
 import torch
 import torch.distributed as dist
@@ -33,6 +34,7 @@ N.register("stb_allgather_pull", [_P, _P, _L, _P, _L, _L, _I, _P, _I, _I, _I, _U
 N.register("stb_embedding_bwd_peers", [_P, _P, _L, _L, _P, _L, _I, _I, _I, _F, _I, _I, _I, _U, _I, _P])
 N.register("stb_reduce_scatter_f32", [_P, _P, _P, _L, _L, _L, _L, _F, _I, _I, _I, _U, _I, _P])
 N.register("stb_adamw_shard_bcast", [_P, _P, _P, _L, _P, _P, _P, _L, _F, _F, _F, _F, _P, _F, _P, _I, _I, _I, _U, _I, _P])
+N.register("stb_param_bcast", [_P, _P, _P, _L, _L, _I, _I, _I, _I, _U, _I, _P])
 N.register("stb_allreduce_tiny_f32", [_P, _P, _L, _I, _I, _I, _I, _U, _P])
 N.register("stb_gemm_rs_bf16", [_P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _I, _P])
 N.register("stb_ag_gemm_bf16", [_P, _P, _P, _I, _I, _I, _I, _I, _I, _P, _P, _L, _P, _U, _I, _I, _I, _I, _I, _P])
@@ -149,10 +151,14 @@ def reset() -> None:
 
 
 # ------------------------------------------------------------------------------------------ ops
-def all_gather_gemm(x_shard: torch.Tensor, weight: torch.Tensor, group, b_mn: bool = False, n_copy: int = 16,
+def all_gather_gemm(x_shard: torch.Tensor, weight: torch.Tensor, group, b_mn: bool = False, n_copy: int = 0,
                     flag_rows: int = 128):
     """``(y [T, N], x_full [T, K])`` with ``T = world · T_shard``; weight ``[N, K]`` (or ``[K, N]`` if ``b_mn``)."""
     g = get_group(group)
+    if n_copy <= 0:
+        # copy CTAs drive TMA bulk copies (~100 KB in flight each): two pairs hide a TP2 gather behind the GEMM, wider
+        # groups move (world - 1) / world of the activation and get four
+        n_copy = int(os.environ.get("SCALETORCH_B200_AG_COPY_CTAS", 4 if g.world <= 2 else 8))
     Ts, K = x_shard.shape
     T = Ts * g.world
     Nn = weight.shape[1] if b_mn else weight.shape[0]

@@ -80,6 +80,10 @@ class GraphedTrainStep:
 
     # ------------------------------------------------------------------------------------------------------
     def _eager(self, src) -> torch.Tensor:
+        if hasattr(self.optimizer, "gather_params"):
+            # sharded optimiser with a deferred parameter gather: inside a captured step the gather of the PREVIOUS
+            # update sits at the beginning (communication stream, layer-wise waits), overlapping the forward pass
+            self.optimizer.gather_params(force=torch.cuda.is_current_stream_capturing())
         self.optimizer.zero_grad()
         if hasattr(self.model, "reset"):
             self.model.reset()

@@ -123,6 +123,7 @@ class PeerShardedAdamW(FusedAdamW):
     """
 
     SLOT = 3          # flag slot of the dense group's pages used on the main stream (fused_ops.SLOT_AR)
+    SLOT_COMM = 4     # flag slot used on the communication stream (shared with the bucket reduce-scatters: SLOT_DP)
 
     def __init__(self, store: FlatParamStore, bucket_manager, dense_group, sm_budget: int = 0, **kw):
         super().__init__(store, _alloc_state=False, **kw)
@@ -146,6 +147,82 @@ class PeerShardedAdamW(FusedAdamW):
         for b in bucket_manager.buckets:
             if b.grad_window is not None:
                 b.own_range = self.own
+        # Deferred parameter gather: the update writes only the local shard; the shards are broadcast one owner after
+        # the other on the communication stream (stb_param_bcast) and every decoder layer waits only for the owners of
+        # ITS parameters, so the forward pass starts once the first shards are in and the rest of the gather (2 bytes
+        # per parameter of NVLink ingress) hides behind it.  Falls back to broadcasting from inside the AdamW kernel
+        # when the model has no layer list to gate.
+        import os
+
+        self.comm_stream = bucket_manager.comm_stream
+        self._events: list = [None] * self.world
+        self._stale = False
+        self.deferred = (os.environ.get("SCALETORCH_B200_DP_DEFER_GATHER", "1") == "1" and self.comm_stream is not None
+                         and self._install_param_gates(store.module))
+
+    # ------------------------------------------------------------------------------------------ deferred gather
+    def _owner_of(self, elem: int) -> int:
+        return min(self.world - 1, elem // self.chunk)
+
+    def _install_param_gates(self, root) -> bool:
+        """Forward pre-hooks that make the current stream wait for the shards a module's parameters live in.  Gated
+        units: the root's direct children, with module lists expanded (decoder layers).  The last element of the last
+        module list waits for every shard, because what follows it (final norm, LM head) may read weights without
+        going through ``Module.__call__``."""
+        units, last_list = [], None
+        for child in root.children():
+            if isinstance(child, torch.nn.ModuleList):
+                elems = [m for m in child]
+                units.extend(elems)
+                if elems:
+                    last_list = elems[-1]
+            else:
+                units.append(child)
+        if last_list is None:
+            return False
+        dense_hi = self.store.dense_numel
+        for m in units:
+            offs = [p._stb_slot.offset + p._stb_slot.numel - 1 for p in m.parameters()
+                    if hasattr(p, "_stb_slot") and p._stb_slot.offset < dense_hi]
+            if not offs:
+                continue
+            k = self.world - 1 if m is last_list else self._owner_of(max(offs))
+            m.register_forward_pre_hook(lambda mod, args, k=k: self.wait_shard(k))
+        return True
+
+    def wait_shard(self, k: int) -> None:
+        """Orders the current stream after the broadcast of shards ``0..k`` of the pending gather (no host blocking)."""
+        ev = self._events[k]
+        if ev is not None:
+            torch.cuda.current_stream().wait_event(ev)
+
+    def gather_params(self, force: bool = False) -> None:
+        """Launches the all-gather of the updated parameter shards on the communication stream (asynchronous)."""
+        if not self.deferred or not (self._stale or force):
+            return
+        from .. import _native as N
+
+        sg = self.pw.g
+        main = torch.cuda.current_stream()
+        fork = torch.cuda.Event()
+        fork.record(main)
+        self.comm_stream.wait_event(fork)
+        with torch.cuda.stream(self.comm_stream):
+            for r in range(self.world):
+                a, b = self.bounds(r)
+                if b > a:
+                    N.call("stb_param_bcast", self.pw.bufs_dev, self.pw.mc_ptr or None, sg.flag_pages_dev, a, b - a, r,
+                           self.rank, self.world, self.SLOT_COMM, sg.take_epochs(self.SLOT_COMM, 2), 32, N.stream_ptr())
+                ev = torch.cuda.Event()
+                ev.record(self.comm_stream)
+                self._events[r] = ev
+        self._stale = False
+
+    def sync_params(self) -> None:
+        """Every rank's parameter copy is complete when the current stream reaches this point (call before reading
+        parameters outside a forward pass: checkpoints, evaluation with foreign code)."""
+        self.gather_params()
+        self.wait_shard(self.world - 1)
 
     def bounds(self, r: int) -> tuple[int, int]:
         n = self.store.dense_numel
@@ -200,16 +277,37 @@ class PeerShardedAdamW(FusedAdamW):
         sg = self.pw.g
         b1, b2 = g["betas"]
         grad = st.grad_flat[lo:hi]
-        N.call("stb_adamw_shard_bcast", self.pw.bufs_dev, self.pw.mc_ptr or None, sg.flag_pages_dev, lo,
-               grad.data_ptr() if hi > lo else None, self.exp_avg.data_ptr() if hi > lo else None,
-               self.exp_avg_sq.data_ptr() if hi > lo else None, max(0, hi - lo), float(b1), float(b2), float(g["eps"]),
-               float(g["weight_decay"]), N.ptr(coef), float(grad_scale), self._hyper_dev.data_ptr(), self.rank, self.world,
-               self.SLOT, sg.take_epochs(self.SLOT, 2), self.sm_budget, N.stream_ptr())
+        if self.deferred:
+            # nobody may still be reading the parameters I am about to overwrite locally: only my own forward/backward
+            # read my copy, and they precede this launch in stream order
+            if hi > lo:
+                fused_adamw_step(st.param_flat[lo:hi], grad, self.exp_avg, self.exp_avg_sq, lr=g["lr"], betas=g["betas"],
+                                 eps=g["eps"], weight_decay=g["weight_decay"], step=max(self.step_count, 1),
+                                 clip_coef=coef, grad_scale=grad_scale, hyper=self._hyper_dev)
+            self._stale = True
+            if not torch.cuda.is_current_stream_capturing():
+                self.gather_params()      # eager: start the gather now; a captured step gathers at its beginning
+        else:
+            self._bcast_update(g, coef, grad_scale)
         if st.expert_numel > 0:
             a, b = st.dense_numel, st.total_numel
             fused_adamw_step(st.param_flat[a:b], st.grad_flat[a:b], self.exp_avg_e, self.exp_avg_sq_e, lr=g["lr"],
                              betas=g["betas"], eps=g["eps"], weight_decay=g["weight_decay"], step=max(self.step_count, 1),
                              clip_coef=coef, grad_scale=grad_scale * self.expert_grad_scale, hyper=self._hyper_dev)
+
+    def _bcast_update(self, g: dict, coef, grad_scale: float) -> None:
+        from .. import _native as N
+
+        st = self.store
+        lo, hi = self.own
+        sg = self.pw.g
+        b1, b2 = g["betas"]
+        grad = st.grad_flat[lo:hi]
+        N.call("stb_adamw_shard_bcast", self.pw.bufs_dev, self.pw.mc_ptr or None, sg.flag_pages_dev, lo,
+               grad.data_ptr() if hi > lo else None, self.exp_avg.data_ptr() if hi > lo else None,
+               self.exp_avg_sq.data_ptr() if hi > lo else None, max(0, hi - lo), float(b1), float(b2), float(g["eps"]),
+               float(g["weight_decay"]), N.ptr(coef), float(grad_scale), self._hyper_dev.data_ptr(), self.rank, self.world,
+               self.SLOT, sg.take_epochs(self.SLOT, 2), self.sm_budget, N.stream_ptr())
 
     # ------------------------------------------------------------------------------------------ state
     def _gather(self, mine: torch.Tensor, mine_e) -> torch.Tensor:
@@ -226,6 +324,7 @@ class PeerShardedAdamW(FusedAdamW):
         return full
 
     def state_dict(self):
+        self.sync_params()          # checkpoints read the model right after this: every copy must be complete
         return {"step": self.step_count, "exp_avg": self._gather(self.exp_avg, self.exp_avg_e),
                 "exp_avg_sq": self._gather(self.exp_avg_sq, self.exp_avg_sq_e),
                 "param_groups": [{k: v for k, v in g.items() if k != "params"} for g in self.param_groups]}

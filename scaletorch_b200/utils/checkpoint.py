@@ -319,7 +319,8 @@ class CheckpointManager:
                         extra: dict | None = None) -> str | None:
         # a sharded (ZeRO-1) optimiser assembles its state collectively: every rank must take part before the
         # non-writing ranks leave
-        opt_state = optimizer.state_dict() if (optimizer is not None and hasattr(optimizer, "shards")) else None
+        sharded = optimizer is not None and (hasattr(optimizer, "shards") or hasattr(optimizer, "sync_params"))
+        opt_state = optimizer.state_dict() if sharded else None      # (also completes a deferred parameter gather)
         if not self.cp_dp_first:
             return None
         os.makedirs(out_dir, exist_ok=True)

@@ -157,7 +157,9 @@ class PeerShardedAdamW(FusedAdamW):
         self.comm_stream = bucket_manager.comm_stream
         self._events: list = [None] * self.world
         self._stale = False
-        self.deferred = (os.environ.get("SCALETORCH_B200_DP_DEFER_GATHER", "1") == "1" and self.comm_stream is not None
+        # Off by default: measured (profiles/dp_sharded_r2.md) the owner-by-owner gather is slower than broadcasting from
+        # inside the AdamW kernel, where all owners send at once (N=2: 29.02 vs 27.96 ms/step, N=8: 29.26 vs 28.80).
+        self.deferred = (os.environ.get("SCALETORCH_B200_DP_DEFER_GATHER", "0") == "1" and self.comm_stream is not None
                          and self._install_param_gates(store.module))
 
     # ------------------------------------------------------------------------------------------ deferred gather

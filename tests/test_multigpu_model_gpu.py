@@ -96,8 +96,8 @@ def _worker(rank, world, port, mode, fused):
                     gsum = p.grad.float().clone()
                     dist.all_reduce(gsum)
                     assert _rel(gsum / world, fg[nm]) < 8e-2, (nm, _rel(gsum / world, fg[nm]))
-        elif mode in ("dp_sharded", "dp_sharded_tied", "dp_sharded_nodefer"):
-            os.environ["SCALETORCH_B200_DP_DEFER_GATHER"] = "0" if mode == "dp_sharded_nodefer" else "1"
+        elif mode in ("dp_sharded", "dp_sharded_tied", "dp_sharded_defer"):
+            os.environ["SCALETORCH_B200_DP_DEFER_GATHER"] = "1" if mode == "dp_sharded_defer" else "0"
             # ZeRO-1 on the peer-memory kernels (reduce-scatter buckets, sharded AdamW that writes every rank's parameter
             # copy) against the single-GPU fused optimiser on the global batch: parameters after 3 clipped steps
             from scaletorch_b200.trainer.optimizer import FusedAdamW
@@ -116,7 +116,7 @@ def _worker(rank, world, port, mode, fused):
             kw = dict(lr=1e-3, betas=(0.9, 0.95), weight_decay=0.1, max_grad_norm=1.0)
             opt_full = FusedAdamW(st_full, **kw)
             opt = PeerShardedAdamW(st_par, dp.bucket_manager, pgm.grad_sync_group, **kw)
-            assert opt.deferred == (mode != "dp_sharded_nodefer")
+            assert opt.deferred == (mode == "dp_sharded_defer")
             assert opt.state_bytes() < opt_full.exp_avg.numel() * 8 * 0.75
             for step in range(3):
                 torch.manual_seed(100 + step)
@@ -171,7 +171,7 @@ def test_two_gpu_model_equality(mode, fused):
 
 
 @pytest.mark.parametrize("world", [2, 4, 8])
-@pytest.mark.parametrize("mode", ["dp_sharded", "dp_sharded_tied", "dp_sharded_nodefer", "dp", "dp_tied"])
+@pytest.mark.parametrize("mode", ["dp_sharded", "dp_sharded_tied", "dp_sharded_defer", "dp", "dp_tied"])
 def test_data_parallel_peer_kernels_at_every_width(mode, world):
     """The data-parallel peer-memory paths (bucket all-reduce, embedding row exchange, reduce-scatter + sharded AdamW) at
     2, 4 and 8 ranks -- whatever the box has."""

@@ -667,3 +667,16 @@ extern "C" int stb_flash_attn_bwd_block(const void* dout, const void* q, const v
                              k_ss, k_sh, v_sb, v_ss, v_sh, dq_sb, dq_ss, dq_sh, dk_sb, dk_ss, dk_sh, dv_sb, dv_ss, dv_sh,
                              scale, causal, q_lo, S_tot, compute_delta, 1, dq_acc, 1, stream);
 }
+
+// delta[b,h,q] = rowsum(dO * O) for contiguous [B,Sq,Hq,128] dout / out (the fused backward takes it as an input).
+extern "C" int stb_attn_bwd_delta(const void* dout, const void* out, float* delta, int B, int Sq, int Hq,
+                                  cudaStream_t stream) {
+  const long rows = long(B) * Sq * Hq;
+  if (rows == 0) return 0;
+  long blocks = (rows + 7) / 8;
+  const long cap = long(sm_count()) * 16;
+  attn_bwd_delta_kernel<<<int(blocks < cap ? blocks : cap), 256, 0, stream>>>(
+      (const __nv_bfloat16*)dout, (const __nv_bfloat16*)out, delta, B, Sq, Hq);
+  STB_CHECK_LAUNCH();
+  return 0;
+}

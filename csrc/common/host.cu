@@ -136,6 +136,23 @@ int make_tmap_bshd(CUtensorMap* out, const void* base, int B, int S, int H, int 
   return 0;
 }
 
+int make_tmap_bshd_f32(CUtensorMap* out, const void* base, int B, int S, int H, int D, long sb, long ss, long sh,
+                       uint32_t box_d, uint32_t box_s) {
+  ensure_context();
+  EncodeTiledFn enc = get_encode();
+  STB_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled entry point unavailable");
+  cuuint64_t dims[4] = {(cuuint64_t)D, (cuuint64_t)H, (cuuint64_t)S, (cuuint64_t)B};
+  cuuint64_t strides[3] = {(cuuint64_t)sh * 4, (cuuint64_t)ss * 4, (cuuint64_t)sb * 4};
+  cuuint32_t box[4] = {box_d, 1, box_s, 1};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<void*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  STB_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(bshd f32) failed: %d (B=%d S=%d H=%d D=%d strides=%ld,%ld,%ld)",
+              (int)r, B, S, H, D, sb, ss, sh);
+  return 0;
+}
+
 }  // namespace stb
 
 extern "C" const char* stb_last_error() { return stb::g_err; }

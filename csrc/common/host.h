@@ -26,6 +26,10 @@ int make_tmap_3d(CUtensorMap* out, const void* base, int elem_bytes, uint64_t di
 int make_tmap_bshd(CUtensorMap* out, const void* base, int B, int S, int H, int D, long sb, long ss,
                    long sh, uint32_t box_d, uint32_t box_s);
 
+// same for an fp32 tensor, not swizzled (shared-memory tile is dense [box_s][box_d]); used for TMA reduce-add tiles
+int make_tmap_bshd_f32(CUtensorMap* out, const void* base, int B, int S, int H, int D, long sb, long ss, long sh,
+                       uint32_t box_d, uint32_t box_s);
+
 // CTA-pair GEMM (csrc/gemm_pair.cu): entry, its work model, and the k-split it would choose.
 struct GemmFused;   // csrc/common/gemm_fused.cuh
 namespace pair {

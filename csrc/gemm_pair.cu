@@ -311,7 +311,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 // ran 4096^3 in 146 us where the 256-wide tile needs 99 us, so it only pays when it halves the number of waves;
 // a k-split costs the zero-fill launch plus read-modify-write epilogues (~6 us) and more per extra split.
 constexpr float kEpiUnits = 5.0f;        // exposed drain of a CTA's last 128 x 256 accumulator half (bf16 store)
-constexpr float kSplitUnits = 20.0f;     // zero-fill + reduce-add epilogue instead of a store
+constexpr float kSplitUnits = 40.0f;     // zero-fill launch (5.7 us measured in-step) + reduce-add epilogue instead of a store
 constexpr float kPerSplitUnits = 2.0f;
 constexpr int kMinKbPerSplit = 8;
 

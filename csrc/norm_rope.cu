@@ -11,6 +11,25 @@
 
 namespace stb {
 
+STB_DEVICE float half_warp_sum(float v) {
+#pragma unroll
+  for (int o = 8; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+STB_DEVICE void unpack8(const uint4& r, float (&f)[8]) {
+  const float2 a = unpack_bf16x2(r.x), b = unpack_bf16x2(r.y), c = unpack_bf16x2(r.z), d = unpack_bf16x2(r.w);
+  f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y; f[4] = c.x; f[5] = c.y; f[6] = d.x; f[7] = d.y;
+}
+STB_DEVICE uint4 pack8(const float (&f)[8]) {
+  return make_uint4(pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]), pack_bf16x2(f[4], f[5]), pack_bf16x2(f[6], f[7]));
+}
+STB_DEVICE void load8f(const float* p, float (&f)[8]) {
+  const float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
+  f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
+}
+
+
+
 // ----------------------------------------------------------------- RMSNorm
 template <int THREADS>
 __device__ __forceinline__ float block_sum(float v, float* red) {
@@ -203,8 +222,9 @@ rmsnorm_dw_reduce_kernel(const float* __restrict__ partial, float* __restrict__ 
 }
 
 // ------------------------------------------------------- QK-norm + RoPE
-// One warp per (token, head); head_dim == 128 -> 4 consecutive elements per lane;
-// rotate-half pairs element j with j+64, i.e. lane l with lane l^16.
+// head_dim == 128.  A head is handled by HALF a warp: 16 lanes x 8 consecutive bf16 (one 16-byte load / store per lane),
+// so a warp works on two heads of a token at a time and four head pairs are in flight per warp.  rotate-half pairs element
+// j with j + 64, i.e. lane l with lane l ^ 8 of the same half-warp; the norm reductions stay inside the 16 lanes.
 // in : qkv [T, (Hq + 2*Hkv) * 128]   (q heads, then k heads, then v heads)
 // out: qk  [T, (Hq + Hkv) * 128]     rotated q and k (v is consumed in place by attention)
 template <bool NORM>
@@ -214,50 +234,61 @@ __global__ void __launch_bounds__(128)
                            const float* __restrict__ sin_t, const int* __restrict__ pos,
                            __nv_bfloat16* __restrict__ out, float* __restrict__ rstd_out, int T, int S,
                            int Hq, int Hkv, int pos_offset, float eps) {
-  // one warp per token, looping over its q and k heads: the cos/sin row (2 x 512 B, 4x the bytes of one head) and
-  // the norm weights are loaded once per token instead of once per head
-  const int lane = threadIdx.x & 31;
+  const int lane = threadIdx.x & 31, l16 = lane & 15, grp = lane >> 4;
   const int nheads = Hq + Hkv;
   const int in_ld = (Hq + 2 * Hkv) * 128, out_ld = nheads * 128;
-  float wqf[4] = {1.f, 1.f, 1.f, 1.f}, wkf[4] = {1.f, 1.f, 1.f, 1.f};
+  float wqf[8], wkf[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) wqf[j] = wkf[j] = 1.f;
   if (NORM) {
-    const uint2 a = *reinterpret_cast<const uint2*>(wq + lane * 4), b = *reinterpret_cast<const uint2*>(wk + lane * 4);
-    const float2 a0 = unpack_bf16x2(a.x), a1 = unpack_bf16x2(a.y), b0 = unpack_bf16x2(b.x), b1 = unpack_bf16x2(b.y);
-    wqf[0] = a0.x, wqf[1] = a0.y, wqf[2] = a1.x, wqf[3] = a1.y;
-    wkf[0] = b0.x, wkf[1] = b0.y, wkf[2] = b1.x, wkf[3] = b1.y;
+    unpack8(*reinterpret_cast<const uint4*>(wq + l16 * 8), wqf);
+    unpack8(*reinterpret_cast<const uint4*>(wk + l16 * 8), wkf);
   }
+  const float sign = (l16 < 8) ? -1.f : 1.f;      // rotate-half: first half takes -x[j + 64], second half +x[j - 64]
   for (int t = blockIdx.x * 4 + (threadIdx.x >> 5); t < T; t += gridDim.x * 4) {
     const int p = pos ? pos[t] : (t % S) + pos_offset;
-    const float4 c = *reinterpret_cast<const float4*>(cos_t + size_t(p) * 128 + lane * 4);
-    const float4 s = *reinterpret_cast<const float4*>(sin_t + size_t(p) * 128 + lane * 4);
-    const float cf[4] = {c.x, c.y, c.z, c.w}, sf[4] = {s.x, s.y, s.z, s.w};
-    const __nv_bfloat16* src = qkv + size_t(t) * in_ld + lane * 4;
-    __nv_bfloat16* dst = out + size_t(t) * out_ld + lane * 4;
-#pragma unroll 4
-    for (int hd = 0; hd < nheads; ++hd) {
-      const uint2 raw = *reinterpret_cast<const uint2*>(src + hd * 128);
-      const float2 a = unpack_bf16x2(raw.x), b = unpack_bf16x2(raw.y);
-      float v[4] = {a.x, a.y, b.x, b.y};
-      if (NORM) {
-        float ss = v[0] * v[0] + v[1] * v[1] + v[2] * v[2] + v[3] * v[3];
-        ss = warp_sum(ss);
-        const float rstd = rsqrtf(ss * (1.f / 128.f) + eps);
-        if (lane == 0 && rstd_out) rstd_out[long(t) * nheads + hd] = rstd;
-        const bool is_q = hd < Hq;
+    float cf[8], sf[8];
+    load8f(cos_t + size_t(p) * 128 + l16 * 8, cf);
+    load8f(sin_t + size_t(p) * 128 + l16 * 8, sf);
+    const __nv_bfloat16* src = qkv + size_t(t) * in_ld + l16 * 8;
+    __nv_bfloat16* dst = out + size_t(t) * out_ld + l16 * 8;
+    constexpr int kB = 6;                          // head pairs whose loads are issued before any of them is consumed
+    for (int hb = 0; hb < nheads; hb += 2 * kB) {
+      uint4 raw[kB];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const float xn = __bfloat162float(__float2bfloat16(v[j] * rstd));
-          v[j] = __bfloat162float(__float2bfloat16(xn * (is_q ? wqf[j] : wkf[j])));
+      for (int i = 0; i < kB; ++i) {
+        const int hd = hb + 2 * i + grp;
+        raw[i] = hd < nheads ? *reinterpret_cast<const uint4*>(src + hd * 128) : make_uint4(0, 0, 0, 0);
+      }
+#pragma unroll
+      for (int i = 0; i < kB; ++i) {
+        const int hd = hb + 2 * i + grp;
+        const bool live = hd < nheads;
+        if (hb + 2 * i >= nheads) break;           // warp-uniform
+        float v[8];
+        unpack8(raw[i], v);
+        if (NORM) {
+          float ss = 0.f;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) ss += v[j] * v[j];
+          ss = half_warp_sum(ss);
+          const float rstd = rsqrtf(ss * (1.f / 128.f) + eps);
+          if (l16 == 0 && live && rstd_out) rstd_out[long(t) * nheads + hd] = rstd;
+          const bool is_q = hd < Hq;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float xn = __bfloat162float(__float2bfloat16(v[j] * rstd));
+            v[j] = __bfloat162float(__float2bfloat16(xn * (is_q ? wqf[j] : wkf[j])));
+          }
         }
-      }
-      float o[4];
+        float o[8];
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const float other = __shfl_xor_sync(0xffffffffu, v[j], 16);
-        const float rot = (lane < 16) ? -other : other;
-        o[j] = v[j] * cf[j] + rot * sf[j];
+        for (int j = 0; j < 8; ++j) {
+          const float other = __shfl_xor_sync(0xffffffffu, v[j], 8);
+          o[j] = v[j] * cf[j] + sign * other * sf[j];
+        }
+        if (live) *reinterpret_cast<uint4*>(dst + hd * 128) = pack8(o);
       }
-      *reinterpret_cast<uint2*>(dst + hd * 128) = make_uint2(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]));
     }
   }
 }
@@ -266,81 +297,117 @@ __global__ void __launch_bounds__(128)
 // (row stride (Hq+2Hkv)*128) and accumulates dwq/dwk[128] (fp32) with atomics, one per CTA.
 template <bool NORM>
 __global__ void __launch_bounds__(128)
-    qknorm_rope_bwd_kernel(const __nv_bfloat16* __restrict__ dqk, const __nv_bfloat16* __restrict__ qkv,
+    qknorm_rope_bwd_kernel(const __nv_bfloat16* __restrict__ dqk, const float* __restrict__ dq32,
+                           const __nv_bfloat16* __restrict__ qkv,
                            const __nv_bfloat16* __restrict__ wq, const __nv_bfloat16* __restrict__ wk,
                            const float* __restrict__ cos_t, const float* __restrict__ sin_t,
                            const int* __restrict__ pos, const float* __restrict__ rstd_in,
                            __nv_bfloat16* __restrict__ dqkv, float* __restrict__ dwq,
                            float* __restrict__ dwk, int T, int S, int Hq, int Hkv, int pos_offset) {
   __shared__ float sdw[2][128];
-  const int lane = threadIdx.x & 31;
+  const int lane = threadIdx.x & 31, l16 = lane & 15, grp = lane >> 4;
   if (NORM) {
     for (int i = threadIdx.x; i < 256; i += blockDim.x) (&sdw[0][0])[i] = 0.f;
     __syncthreads();
   }
   const int nheads = Hq + Hkv;
   const int in_ld = (Hq + 2 * Hkv) * 128, g_ld = nheads * 128;
-  float dwl[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
-  float wqf[4] = {1.f, 1.f, 1.f, 1.f}, wkf[4] = {1.f, 1.f, 1.f, 1.f};
-  if (NORM) {
-    const uint2 a = *reinterpret_cast<const uint2*>(wq + lane * 4), b = *reinterpret_cast<const uint2*>(wk + lane * 4);
-    const float2 a0 = unpack_bf16x2(a.x), a1 = unpack_bf16x2(a.y), b0 = unpack_bf16x2(b.x), b1 = unpack_bf16x2(b.y);
-    wqf[0] = a0.x, wqf[1] = a0.y, wqf[2] = a1.x, wqf[3] = a1.y;
-    wkf[0] = b0.x, wkf[1] = b0.y, wkf[2] = b1.x, wkf[3] = b1.y;
+  float dwl[2][8];
+  float wqf[8], wkf[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    dwl[0][j] = dwl[1][j] = 0.f;
+    wqf[j] = wkf[j] = 1.f;
   }
-  // one warp per token, looping over its heads (cos/sin row and weights loaded once per token)
+  if (NORM) {
+    unpack8(*reinterpret_cast<const uint4*>(wq + l16 * 8), wqf);
+    unpack8(*reinterpret_cast<const uint4*>(wk + l16 * 8), wkf);
+  }
+  // transpose of rotate-half: dv[j] = g[j] cos[j] + (j < 64 ? +1 : -1) * (g sin)[j ^ 64]
+  const float sign = (l16 < 8) ? 1.f : -1.f;
   for (int t = blockIdx.x * 4 + (threadIdx.x >> 5); t < T; t += gridDim.x * 4) {
     const int p = pos ? pos[t] : (t % S) + pos_offset;
-    const float4 c = *reinterpret_cast<const float4*>(cos_t + size_t(p) * 128 + lane * 4);
-    const float4 s = *reinterpret_cast<const float4*>(sin_t + size_t(p) * 128 + lane * 4);
-    const float cf[4] = {c.x, c.y, c.z, c.w}, sf[4] = {s.x, s.y, s.z, s.w};
-#pragma unroll 4
-    for (int hd = 0; hd < nheads; ++hd) {
-    const long idx = long(t) * nheads + hd;
-    const uint2 graw = *reinterpret_cast<const uint2*>(dqk + size_t(t) * g_ld + hd * 128 + lane * 4);
-    const float2 g0 = unpack_bf16x2(graw.x), g1 = unpack_bf16x2(graw.y);
-    const float go[4] = {g0.x, g0.y, g1.x, g1.y};
-    float dv[4];
+    float cf[8], sf[8];
+    load8f(cos_t + size_t(p) * 128 + l16 * 8, cf);
+    load8f(sin_t + size_t(p) * 128 + l16 * 8, sf);
+    constexpr int kB = 4;                          // head pairs whose loads are issued before any of them is consumed
+    for (int hb = 0; hb < nheads; hb += 2 * kB) {
+      uint4 graw[kB], xraw[kB];
+      float4 gq0[kB], gq1[kB];                     // q-head gradients when they arrive as fp32 (fused attention backward)
+      float rs[kB];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      // out[j] = v[j]cos[j] - v[j+64]sin[j];  out[j+64] = v[j+64]cos[j+64] + v[j]sin[j+64]
-      const float gs = go[j] * sf[j];
-      const float other = __shfl_xor_sync(0xffffffffu, gs, 16);
-      dv[j] = go[j] * cf[j] + ((lane < 16) ? other : -other);
-    }
-    float o[4];
-    if (NORM) {
-      const uint2 raw = *reinterpret_cast<const uint2*>(qkv + size_t(t) * in_ld + hd * 128 + lane * 4);
-      const float2 a = unpack_bf16x2(raw.x), b = unpack_bf16x2(raw.y);
-      const float x[4] = {a.x, a.y, b.x, b.y};
-      const float rstd = rstd_in[idx];
-      const bool is_q = hd < Hq;
-      float xn[4], g[4], dot = 0.f;
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        xn[j] = x[j] * rstd;
-        g[j] = dv[j] * (is_q ? wqf[j] : wkf[j]);
-        dot += g[j] * xn[j];
-        const float contrib = dv[j] * xn[j];
-        dwl[0][j] += is_q ? contrib : 0.f;
-        dwl[1][j] += is_q ? 0.f : contrib;
+      for (int i = 0; i < kB; ++i) {
+        const int hd = hb + 2 * i + grp;
+        const bool live = hd < nheads;
+        if (dq32 != nullptr && live && hd < Hq) {
+          const float* gp = dq32 + (size_t(t) * Hq + hd) * 128 + l16 * 8;
+          gq0[i] = *reinterpret_cast<const float4*>(gp);
+          gq1[i] = *reinterpret_cast<const float4*>(gp + 4);
+          graw[i] = make_uint4(0, 0, 0, 0);
+        } else {
+          graw[i] = live ? *reinterpret_cast<const uint4*>(dqk + size_t(t) * g_ld + hd * 128 + l16 * 8) : make_uint4(0, 0, 0, 0);
+        }
+        if (NORM) {
+          xraw[i] = live ? *reinterpret_cast<const uint4*>(qkv + size_t(t) * in_ld + hd * 128 + l16 * 8) : make_uint4(0, 0, 0, 0);
+          rs[i] = live ? rstd_in[long(t) * nheads + hd] : 0.f;
+        }
       }
-      dot = warp_sum(dot) * (1.f / 128.f);
 #pragma unroll
-      for (int j = 0; j < 4; ++j) o[j] = rstd * (g[j] - xn[j] * dot);
-    } else {
+      for (int i = 0; i < kB; ++i) {
+        const int hd = hb + 2 * i + grp;
+        const bool live = hd < nheads;
+        if (hb + 2 * i >= nheads) break;           // warp-uniform
+        float go[8], dv[8];
+        if (dq32 != nullptr && live && hd < Hq) {
+          go[0] = gq0[i].x; go[1] = gq0[i].y; go[2] = gq0[i].z; go[3] = gq0[i].w;
+          go[4] = gq1[i].x; go[5] = gq1[i].y; go[6] = gq1[i].z; go[7] = gq1[i].w;
+        } else {
+          unpack8(graw[i], go);
+        }
 #pragma unroll
-      for (int j = 0; j < 4; ++j) o[j] = dv[j];
-    }
-    *reinterpret_cast<uint2*>(dqkv + size_t(t) * in_ld + hd * 128 + lane * 4) =
-        make_uint2(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]));
+        for (int j = 0; j < 8; ++j) {
+          const float other = __shfl_xor_sync(0xffffffffu, go[j] * sf[j], 8);
+          dv[j] = go[j] * cf[j] + sign * other;
+        }
+        float o[8];
+        if (NORM) {
+          float x[8];
+          unpack8(xraw[i], x);
+          const float rstd = rs[i];
+          const bool is_q = hd < Hq;
+          float xn[8], g[8], dot = 0.f;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            xn[j] = x[j] * rstd;
+            g[j] = dv[j] * (is_q ? wqf[j] : wkf[j]);
+            dot += g[j] * xn[j];
+            const float contrib = dv[j] * xn[j];
+            dwl[0][j] += is_q ? contrib : 0.f;
+            dwl[1][j] += is_q ? 0.f : contrib;
+          }
+          dot = half_warp_sum(dot) * (1.f / 128.f);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) o[j] = rstd * (g[j] - xn[j] * dot);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) o[j] = dv[j];
+        }
+        if (live) *reinterpret_cast<uint4*>(dqkv + size_t(t) * in_ld + hd * 128 + l16 * 8) = pack8(o);
+      }
     }
   }
   if (NORM) {
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      atomicAdd(&sdw[0][lane * 4 + j], dwl[0][j]);
-      atomicAdd(&sdw[1][lane * 4 + j], dwl[1][j]);
+    for (int j = 0; j < 8; ++j) {   // the two half-warps hold the same element positions: fold them first
+      dwl[0][j] += __shfl_xor_sync(0xffffffffu, dwl[0][j], 16);
+      dwl[1][j] += __shfl_xor_sync(0xffffffffu, dwl[1][j], 16);
+    }
+    if (grp == 0) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        atomicAdd(&sdw[0][l16 * 8 + j], dwl[0][j]);
+        atomicAdd(&sdw[1][l16 * 8 + j], dwl[1][j]);
+      }
     }
     __syncthreads();
     atomicAdd(dwq + threadIdx.x, sdw[0][threadIdx.x]);
@@ -549,27 +616,48 @@ extern "C" int stb_qknorm_rope_fwd(const void* qkv, const void* wq, const void* 
   return 0;
 }
 
+static int qknorm_rope_bwd_impl(const void* dqk, const float* dq32, const void* qkv, const void* wq, const void* wk,
+                                const float* cos_t, const float* sin_t, const int* pos,
+                                const float* rstd, void* dqkv, float* dwq, float* dwk, int T, int S,
+                                int Hq, int Hkv, int head_dim, int pos_offset, int use_norm,
+                                cudaStream_t stream) {
+  STB_REQUIRE(head_dim == 128, "qknorm_rope: head_dim must be 128 (got %d)", head_dim);
+  if (T == 0) return 0;
+  long blocks = (long(T) + 3) / 4;
+  // every CTA ends with 256 global atomics on the same 256 weight-gradient words: few persistent CTAs (the atomics of
+  // 1024 short-lived CTAs serialised in L2 and cost more than the kernel's memory traffic)
+  const long cap = long(sm_count()) * 3;
+  const int grid = int(blocks < cap ? blocks : cap);
+  if (use_norm)
+    qknorm_rope_bwd_kernel<true><<<grid, 128, 0, stream>>>(
+        (const __nv_bfloat16*)dqk, dq32, (const __nv_bfloat16*)qkv, (const __nv_bfloat16*)wq,
+        (const __nv_bfloat16*)wk, cos_t, sin_t, pos, rstd, (__nv_bfloat16*)dqkv, dwq, dwk, T, S, Hq, Hkv,
+        pos_offset);
+  else
+    qknorm_rope_bwd_kernel<false><<<grid, 128, 0, stream>>>(
+        (const __nv_bfloat16*)dqk, dq32, nullptr, nullptr, nullptr, cos_t, sin_t, pos, nullptr,
+        (__nv_bfloat16*)dqkv, nullptr, nullptr, T, S, Hq, Hkv, pos_offset);
+  STB_CHECK_LAUNCH();
+  return 0;
+}
+
 extern "C" int stb_qknorm_rope_bwd(const void* dqk, const void* qkv, const void* wq, const void* wk,
                                    const float* cos_t, const float* sin_t, const int* pos,
                                    const float* rstd, void* dqkv, float* dwq, float* dwk, int T, int S,
                                    int Hq, int Hkv, int head_dim, int pos_offset, int use_norm,
                                    cudaStream_t stream) {
-  STB_REQUIRE(head_dim == 128, "qknorm_rope: head_dim must be 128 (got %d)", head_dim);
-  if (T == 0) return 0;
-  long blocks = (long(T) + 3) / 4;
-  const long cap = long(sm_count()) * 8;
-  const int grid = int(blocks < cap ? blocks : cap);
-  if (use_norm)
-    qknorm_rope_bwd_kernel<true><<<grid, 128, 0, stream>>>(
-        (const __nv_bfloat16*)dqk, (const __nv_bfloat16*)qkv, (const __nv_bfloat16*)wq,
-        (const __nv_bfloat16*)wk, cos_t, sin_t, pos, rstd, (__nv_bfloat16*)dqkv, dwq, dwk, T, S, Hq, Hkv,
-        pos_offset);
-  else
-    qknorm_rope_bwd_kernel<false><<<grid, 128, 0, stream>>>(
-        (const __nv_bfloat16*)dqk, nullptr, nullptr, nullptr, cos_t, sin_t, pos, nullptr,
-        (__nv_bfloat16*)dqkv, nullptr, nullptr, T, S, Hq, Hkv, pos_offset);
-  STB_CHECK_LAUNCH();
-  return 0;
+  return qknorm_rope_bwd_impl(dqk, nullptr, qkv, wq, wk, cos_t, sin_t, pos, rstd, dqkv, dwq, dwk, T, S, Hq, Hkv, head_dim,
+                              pos_offset, use_norm, stream);
+}
+
+// Same, with the gradient of the rotated QUERY heads given as a contiguous fp32 [T, Hq, 128] tensor (what the fused
+// attention backward accumulates); `dqk` then only supplies the key heads (columns [Hq*128, (Hq+Hkv)*128) of its rows).
+extern "C" int stb_qknorm_rope_bwd_f32q(const void* dqk, const float* dq32, const void* qkv, const void* wq,
+                                        const void* wk, const float* cos_t, const float* sin_t, const int* pos,
+                                        const float* rstd, void* dqkv, float* dwq, float* dwk, int T, int S, int Hq,
+                                        int Hkv, int head_dim, int pos_offset, int use_norm, cudaStream_t stream) {
+  return qknorm_rope_bwd_impl(dqk, dq32, qkv, wq, wk, cos_t, sin_t, pos, rstd, dqkv, dwq, dwk, T, S, Hq, Hkv, head_dim,
+                              pos_offset, use_norm, stream);
 }
 
 extern "C" int stb_swiglu_fwd(const void* gu, void* act, long T, int I, cudaStream_t stream) {

@@ -44,6 +44,12 @@ _SIGS = {
                                  c_long, c_long, c_long, c_long, c_long, c_long, c_long, c_long, c_long,
                                  c_long, c_long, c_long, c_long, c_long, c_long, c_long, c_long, c_long, c_float, c_int,
                                  c_int, c_int, c_int, c_int, _P],
+    "stb_attn_bwd_delta": [_P, _P, _P, c_int, c_int, c_int, _P],
+    "stb_flash_attn_bwd_fused": [_P, _P, _P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int,
+                                 c_long, c_long, c_long, c_long, c_long, c_long, c_long, c_long, c_long,
+                                 c_long, c_long, c_long, c_long, c_long, c_long, c_long, c_long, c_long, c_float, c_int, _P],
+    "stb_qknorm_rope_bwd_f32q": [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int,
+                                 c_int, _P],
     "stb_swiglu_fwd": [_P, _P, c_long, c_int, _P],
     "stb_swiglu_bwd": [_P, _P, _P, c_long, c_int, _P],
     "stb_ce_stats": [_P, _P, _P, c_int, c_int, c_long, c_int, _P],

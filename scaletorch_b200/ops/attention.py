@@ -88,6 +88,30 @@ def _flash_bwd(do, q, k, v, out, lse, dq, dk, dv, causal, scale):
 _warned_head_dim: set = set()
 
 
+def fused_bwd_available() -> bool:
+    """One-kernel backward (``csrc/attention_bwd_fused.cu``): S / dP and the elementwise pass run once, dQ is reduce-added
+    into an fp32 buffer.  ``SCALETORCH_B200_ATTN_BWD_FUSED=0`` selects the two-kernel backward."""
+    import os
+
+    lib = N.load()
+    return (lib is not None and hasattr(lib, "stb_flash_attn_bwd_fused")
+            and os.environ.get("SCALETORCH_B200_ATTN_BWD_FUSED", "1") == "1")
+
+
+def _flash_bwd_fused(do, q, k, v, out, lse, dq32, dk, dv, causal, scale):
+    """``dq32``: zero-initialised fp32 ``[B,Sq,Hq,D]`` (strided view allowed), accumulated into; ``dk`` / ``dv`` bf16."""
+    B, Sq, Hq, D = q.shape
+    Sk, Hkv = k.shape[1], k.shape[2]
+    delta = torch.empty((B, Hq, Sq), dtype=torch.float32, device=q.device)
+    N.call("stb_attn_bwd_delta", do.data_ptr(), out.data_ptr(), delta.data_ptr(), B, Sq, Hq, N.stream_ptr())
+    N.call("stb_flash_attn_bwd_fused", do.data_ptr(), q.data_ptr(), k.data_ptr(), v.data_ptr(), lse.data_ptr(),
+           delta.data_ptr(), dq32.data_ptr(), dk.data_ptr(), dv.data_ptr(), B, Sq, Sk, Hq, Hkv, D,
+           q.stride(0), q.stride(1), q.stride(2), k.stride(0), k.stride(1), k.stride(2),
+           v.stride(0), v.stride(1), v.stride(2),
+           dq32.stride(0), dq32.stride(1), dq32.stride(2), dk.stride(0), dk.stride(1), dk.stride(2),
+           dv.stride(0), dv.stride(1), dv.stride(2), float(scale), int(causal), N.stream_ptr())
+
+
 def _sdpa(q, k, v, causal, scale):
     """Library attention for head dims the native kernel does not cover (it is written for D = 128, the head dim of
     every Qwen3 / Llama-2/3 size the reference benchmarks).  Returns ``(out, lse)`` like the native path -- ``lse`` comes
@@ -125,7 +149,12 @@ class _FlashAttention(torch.autograd.Function):
     def backward(ctx, do, _dlse):
         q, k, v, out, lse = ctx.saved_tensors
         causal, scale = ctx.cfg
-        dq, dk, dv = torch.empty_like(q), torch.empty_like(k), torch.empty_like(v)
+        dk, dv = torch.empty_like(k), torch.empty_like(v)
+        if fused_bwd_available():
+            dq32 = torch.zeros(q.shape, dtype=torch.float32, device=q.device)
+            _flash_bwd_fused(do.contiguous(), q, k, v, out, lse, dq32, dk, dv, causal, scale)
+            return dq32.to(q.dtype), dk, dv, None, None
+        dq = torch.empty_like(q)
         _flash_bwd(do.contiguous(), q, k, v, out, lse, dq, dk, dv, causal, scale)
         return dq, dk, dv, None, None
 
@@ -183,7 +212,14 @@ class _QKVAttention(torch.autograd.Function):
         do4 = do.reshape(B, S, n_q, D)
         if not do4.is_contiguous():
             do4 = do4.contiguous()
-        _flash_bwd(do4, q, k, v, out, lse, dqk4[:, :, :n_q], dqk4[:, :, n_q:], d4[:, :, nqk:], causal, scale)
+        dq32 = None
+        if fused_bwd_available():
+            # dQ accumulates in fp32 (TMA reduce-add from the fused kernel) and is consumed as fp32 by the norm / RoPE
+            # backward below: no conversion pass, no bf16 round trip
+            dq32 = torch.zeros((B, S, n_q, D), dtype=torch.float32, device=qkv.device)
+            _flash_bwd_fused(do4, q, k, v, out, lse, dq32, dqk4[:, :, n_q:], d4[:, :, nqk:], causal, scale)
+        else:
+            _flash_bwd(do4, q, k, v, out, lse, dqk4[:, :, :n_q], dqk4[:, :, n_q:], d4[:, :, nqk:], causal, scale)
         dwq = dwk = None
         if use_norm:
             dq_dst, _, q_main = _norm._param_grad_out(wq)
@@ -192,10 +228,16 @@ class _QKVAttention(torch.autograd.Function):
                 dq_dst.zero_()
             if not (k_main and getattr(wk, "grad_written", False)):
                 dk_dst.zero_()
-        N.call("stb_qknorm_rope_bwd", dqk.data_ptr(), qkv.data_ptr(), N.ptr(wq), N.ptr(wk), cos.data_ptr(),
-               sin.data_ptr(), None, N.ptr(rstd), dqkv.data_ptr(),
-               dq_dst.data_ptr() if use_norm else None, dk_dst.data_ptr() if use_norm else None,
-               T, S, n_q, n_kv, D, pos_offset, int(use_norm), N.stream_ptr())
+        if dq32 is not None:
+            N.call("stb_qknorm_rope_bwd_f32q", dqk.data_ptr(), dq32.data_ptr(), qkv.data_ptr(), N.ptr(wq), N.ptr(wk),
+                   cos.data_ptr(), sin.data_ptr(), None, N.ptr(rstd), dqkv.data_ptr(),
+                   dq_dst.data_ptr() if use_norm else None, dk_dst.data_ptr() if use_norm else None,
+                   T, S, n_q, n_kv, D, pos_offset, int(use_norm), N.stream_ptr())
+        else:
+            N.call("stb_qknorm_rope_bwd", dqk.data_ptr(), qkv.data_ptr(), N.ptr(wq), N.ptr(wk), cos.data_ptr(),
+                   sin.data_ptr(), None, N.ptr(rstd), dqkv.data_ptr(),
+                   dq_dst.data_ptr() if use_norm else None, dk_dst.data_ptr() if use_norm else None,
+                   T, S, n_q, n_kv, D, pos_offset, int(use_norm), N.stream_ptr())
         if use_norm:
             dwq = _norm._finish_param_grad(wq, dq_dst, q_main)
             dwk = _norm._finish_param_grad(wk, dk_dst, k_main)

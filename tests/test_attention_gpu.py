@@ -49,11 +49,14 @@ def test_flash_fwd_reads_packed_qkv_views():
     assert (lse - ref_lse).abs().max().item() < 2e-2
 
 
+@pytest.mark.parametrize("fused", ["1", "0"], ids=["one-kernel", "two-kernel"])
 @pytest.mark.parametrize("B,S,Hq,Hkv,causal", [(1, 128, 1, 1, True), (2, 256, 4, 2, True), (1, 384, 4, 1, False),
-                                               (1, 200, 2, 2, True), (1, 1024, 4, 2, True)])
-def test_flash_bwd_matches_oracle(B, S, Hq, Hkv, causal):
+                                               (1, 200, 2, 2, True), (1, 1024, 4, 2, True), (2, 2048, 8, 2, True)])
+def test_flash_bwd_matches_oracle(B, S, Hq, Hkv, causal, fused, monkeypatch):
     if not A.native_attention_available():
         pytest.skip("native attention backward not built")
+    monkeypatch.setenv("SCALETORCH_B200_ATTN_BWD_FUSED", fused)
+    assert A.fused_bwd_available() == (fused == "1")
     torch.manual_seed(2)
     q, k, v = _bf(B, S, Hq, 128).requires_grad_(), _bf(B, S, Hkv, 128).requires_grad_(), _bf(B, S, Hkv, 128).requires_grad_()
     scale = 1.0 / math.sqrt(128)
@@ -69,9 +72,11 @@ def test_flash_bwd_matches_oracle(B, S, Hq, Hkv, causal):
     assert _rel(v.grad, vr.grad) < 3e-2
 
 
-def test_qkv_attention_block_matches_unfused():
+@pytest.mark.parametrize("fused", ["1", "0"], ids=["one-kernel", "two-kernel"])
+def test_qkv_attention_block_matches_unfused(fused, monkeypatch):
     if not A.native_attention_available():
         pytest.skip("native attention backward not built")
+    monkeypatch.setenv("SCALETORCH_B200_ATTN_BWD_FUSED", fused)
     torch.manual_seed(3)
     B, S, Hq, Hkv, D = 2, 256, 4, 2, 128
     qkv = _bf(B * S, (Hq + 2 * Hkv) * D).requires_grad_()

@@ -151,7 +151,7 @@ def test_linear_main_grad_accumulation():
     assert _rel_err(w.main_grad.view(192, 128), ref) < 5e-3
 
 
-@pytest.mark.parametrize("H", [128, 1024, 2048, 4096, 5120])
+@pytest.mark.parametrize("H", [128, 256, 768, 1024, 2048, 4096, 5120])
 @pytest.mark.parametrize("with_res", [False, True])
 def test_rmsnorm(H, with_res):
     torch.manual_seed(6)

@@ -92,6 +92,35 @@ def bench_mem(out):
           "frac_of_measured_hbm": round(4 * T * H * 2 / t / 1e6 / bw, 3)}, out)
     t = timeit(lambda: torch.nn.functional.rms_norm(x + r, (H,), w.float(), 1e-6))
     emit({"kernel": "torch add+rms_norm", "T": T, "H": H, "ms": round(t, 4)}, out)
+    # Qwen3-0.6B shapes: RMSNorm backward at H = 1024 and fused QK-norm + RoPE forward / backward (16 q + 8 kv heads)
+    T2, H2 = 4096, 1024
+    x2 = torch.randn(T2, H2, device="cuda").bfloat16().requires_grad_()
+    r2 = torch.randn(T2, H2, device="cuda").bfloat16().requires_grad_()
+    w2 = torch.ones(H2, device="cuda").bfloat16().requires_grad_()
+    hh, yy = ops.add_rmsnorm(x2, r2, w2, 1e-6)
+    gy, gh = torch.randn_like(yy), torch.randn_like(hh)
+    t = timeit(lambda: torch.autograd.grad((yy, hh), (x2, r2, w2), (gy, gh), retain_graph=True))
+    emit({"kernel": "add_rmsnorm_bwd (+dw reduce)", "T": T2, "H": H2, "ms": round(t, 4), "GBps": round(4 * T2 * H2 * 2 / t / 1e6, 1),
+          "frac_of_measured_hbm": round(4 * T2 * H2 * 2 / t / 1e6 / bw, 3)}, out)
+    from scaletorch_b200.ops import attention as A
+    nq, nkv, D = 16, 8, 128
+    qkv = torch.randn(T2, (nq + 2 * nkv) * D, device="cuda").bfloat16()
+    wq = torch.ones(D, device="cuda").bfloat16(); wk = torch.ones(D, device="cuda").bfloat16()
+    cos, sin = ops.get_cos_sin(4096, D, 1e6, device="cuda")
+    qk = torch.empty(T2, (nq + nkv) * D, device="cuda", dtype=torch.bfloat16)
+    rstd = torch.empty(T2 * (nq + nkv), device="cuda")
+    from scaletorch_b200 import _native as N
+    f = lambda: N.call("stb_qknorm_rope_fwd", qkv.data_ptr(), wq.data_ptr(), wk.data_ptr(), cos.data_ptr(), sin.data_ptr(), None,
+                       qk.data_ptr(), rstd.data_ptr(), T2, 2048, nq, nkv, D, 0, 1, 1e-6, N.stream_ptr())
+    t = timeit(f)
+    nb = 2 * T2 * (nq + nkv) * D * 2
+    emit({"kernel": "qknorm_rope_fwd", "T": T2, "heads": nq + nkv, "ms": round(t, 4), "GBps": round(nb / t / 1e6, 1), "frac_of_measured_hbm": round(nb / t / 1e6 / bw, 3)}, out)
+    dqk = torch.randn_like(qk); dqkv = torch.empty_like(qkv); dwq = torch.zeros(D, device="cuda"); dwk = torch.zeros(D, device="cuda")
+    b = lambda: N.call("stb_qknorm_rope_bwd", dqk.data_ptr(), qkv.data_ptr(), wq.data_ptr(), wk.data_ptr(), cos.data_ptr(), sin.data_ptr(),
+                       None, rstd.data_ptr(), dqkv.data_ptr(), dwq.data_ptr(), dwk.data_ptr(), T2, 2048, nq, nkv, D, 0, 1, N.stream_ptr())
+    t = timeit(b)
+    nb = 3 * T2 * (nq + nkv) * D * 2
+    emit({"kernel": "qknorm_rope_bwd", "T": T2, "heads": nq + nkv, "ms": round(t, 4), "GBps": round(nb / t / 1e6, 1), "frac_of_measured_hbm": round(nb / t / 1e6 / bw, 3)}, out)
     gu = torch.randn(T, 2 * I, device="cuda").bfloat16()
     t = timeit(lambda: ops.swiglu(gu))
     emit({"kernel": "swiglu_fwd", "T": T, "I": I, "ms": round(t, 4), "GBps": round(3 * T * I * 2 / t / 1e6, 1),

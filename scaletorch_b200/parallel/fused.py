@@ -22,21 +22,42 @@ def _world(group) -> int:
     return dist.get_world_size(group)
 
 
+def _policy(op: str, world: int) -> bool:
+    """Measured choice between the fused kernel and GEMM + c10d (profiles/fused_collectives_r2.md, B200, NVLink 5).
+
+    The fused kernels pay with SMs (copy CTAs), a staging copy or a device barrier; NCCL pays with a separate launch
+    and un-overlapped link time.  On a 2-GPU group the link time is 5-10 % of the GEMM and GEMM + NCCL wins in the model
+    (Qwen3-8B TP2+SP S4096: 133.7 ms c10d, 135.5 ms with only GEMM->reduce-scatter fused, 150.1 ms with everything fused);
+    from 4 ranks on the transfers are a third of the GEMM and GEMM->reduce-scatter / GEMM->all-reduce win (1.13x / 1.24x at
+    8 ranks), all-gather->GEMM ties.  ``SCALETORCH_B200_FUSED_TP=all|none|auto`` overrides."""
+    import os
+
+    mode = os.environ.get("SCALETORCH_B200_FUSED_TP", "auto")
+    if mode == "all":
+        return True
+    if mode == "none":
+        return False
+    return world >= 4
+
+
 def ag_gemm_available(x_shard: torch.Tensor, group) -> bool:
     """x_shard ``[T/world, K]``: every rank's row block must be a multiple of the 128-row tile."""
     return (_ok(x_shard, group) and symm.has_kernel("stb_ag_gemm_bf16") and x_shard.shape[0] % 128 == 0
-            and x_shard.numel() * 2 <= symm.region_bytes(group) and _world(group) <= 8)
+            and x_shard.numel() * 2 <= symm.region_bytes(group) and _world(group) <= 8
+            and _policy("ag_gemm", _world(group)))
 
 
 def gemm_rs_available(x_full: torch.Tensor, group) -> bool:
     """x_full ``[T, K]`` with ``T / world`` a multiple of 128."""
     w = _world(group)
-    return (_ok(x_full, group) and symm.has_kernel("stb_gemm_rs_bf16") and x_full.shape[0] % (128 * w) == 0 and w <= 8)
+    return (_ok(x_full, group) and symm.has_kernel("stb_gemm_rs_bf16") and x_full.shape[0] % (128 * w) == 0 and w <= 8
+            and _policy("gemm_rs", w))
 
 
 def gemm_ar_available(x: torch.Tensor, n_out: int, group) -> bool:
     return (_ok(x, group) and symm.has_kernel("stb_allreduce_oneshot_bf16")
-            and x.shape[0] * n_out * 2 <= symm.region_bytes(group) and (x.shape[0] * n_out) % 8 == 0)
+            and x.shape[0] * n_out * 2 <= symm.region_bytes(group) and (x.shape[0] * n_out) % 8 == 0
+            and _policy("gemm_ar", _world(group)))
 
 
 def allreduce_available(t: torch.Tensor, group) -> bool:

@@ -98,10 +98,20 @@ class FlatParamStore:
     # are folded into main_grad here, exactly like the reference's AccumulateGrad hook
     # (``data_parallel.py:254-295``): main_grad (+)= grad; grad = None.
     def _install_fallback_hooks(self) -> None:
+        import os
+
+        verbose = os.environ.get("SCALETORCH_B200_VERBOSE", "0") == "1"
+        seen: set[str] = set()
+
         def make(p: nn.Parameter):
             def hook(param):
                 if param.grad is None:
                     return
+                if verbose:
+                    name = getattr(getattr(param, "_stb_slot", None), "name", "?")
+                    if name not in seen:
+                        seen.add(name)
+                        print(f"[flat_params] gradient of {name} arrived through autograd (.grad), not a kernel epilogue", flush=True)
                 g = param.grad.detach().reshape(-1)
                 if param.grad_written:
                     param.main_grad.add_(g.to(param.main_grad.dtype))

@@ -61,7 +61,10 @@ class GraphedTrainStep:
             return False
         if hasattr(optimizer, "shards"):        # c10d ZeRO-1 broadcasts parameters through NCCL: not captured
             return False
-        if pgm and (pgm.ep_world_size > 1 or pgm.tp_world_size > 1):
+        import os
+
+        allow = os.environ.get("SCALETORCH_B200_GRAPH_MP", "")      # "tp", "ep" or "tp,ep": opt in to capturing these layouts
+        if pgm and ((pgm.ep_world_size > 1 and "ep" not in allow) or (pgm.tp_world_size > 1 and "tp" not in allow)):
             # validated on hardware: single GPU, DP (2/4/8 ranks) and CP.  TP2+SP hung inside / after capture in the one
             # run made (gpurun_out/tp2_graph.log, round 1) and EP invalidated the capture: both stay eager until debugged
             return False
@@ -70,7 +73,7 @@ class GraphedTrainStep:
             # (cudaErrorStreamCaptureInvalidated, 2-GPU EP2 run): MoE models stay on the eager path for now
             from ..models.model_qwen3_moe import MoELayer
 
-            if any(isinstance(m, MoELayer) for m in model.modules()):
+            if any(isinstance(m, MoELayer) for m in model.modules()) and "ep" not in allow:
                 return False
         if pgm and pgm.pp_world_size > 1:
             return False
@@ -124,9 +127,12 @@ class GraphedTrainStep:
                     self.static_loss = self._eager(src)
                 self.graph = graph
             except Exception as e:  # an op in this configuration cannot be captured: stay eager, loudly
+                import traceback
                 import warnings
 
-                warnings.warn(f"CUDA-graph capture of the training step failed ({type(e).__name__}: {e}); running eagerly")
+                where = "".join(traceback.format_exc().splitlines(keepends=True)[-14:])
+                warnings.warn(f"CUDA-graph capture of the training step failed ({type(e).__name__}: "
+                              f"{str(e).splitlines()[0] if str(e) else e}); running eagerly.  Raised at:\n{where}")
                 self.failed = True
                 torch.cuda.synchronize()
                 return self._eager(_StaticBatches(self._buffers, self.ga))

@@ -30,7 +30,8 @@ class Cfg:
 
 def _worker(rank, world, port, mode, fused):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
-                      LOCAL_RANK=str(rank), SCALETORCH_B200_FUSED_COMM="1" if fused else "0")
+                      LOCAL_RANK=str(rank), SCALETORCH_B200_FUSED_COMM="1" if fused else "0",
+                      SCALETORCH_B200_FUSED_TP="all")
     torch.cuda.set_device(rank)
     dev = torch.device("cuda", rank)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
@@ -178,3 +179,54 @@ def test_data_parallel_peer_kernels_at_every_width(mode, world):
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
     mp.spawn(_worker, args=(world, _free_port(), mode, True), nprocs=world, join=True)
+
+
+def _trainer_worker(rank, world, port, sharded, out_path):
+    """Three optimiser steps of tiny-qwen3 on a TP2 x DP2 grid through create_model / create_optimizer."""
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
+                      LOCAL_RANK=str(rank), SCALETORCH_B200_DP_SHARDED="1" if sharded else "0")
+    torch.cuda.set_device(rank)
+    try:
+        from scaletorch_b200.data import MicroBatchDataLoader
+        from scaletorch_b200.trainer import (ScaleTorchArguments, create_model, create_optimizer,
+                                             initialize_distributed_training, training_step)
+
+        cfg = ScaleTorchArguments(model_name_or_path="tiny-qwen3", micro_batch_size=2, sequence_length=256, synthetic_data=True,
+                                  dtype="bfloat16", learning_rate=1e-3, max_grad_norm=0.5, tensor_parallel_size=2,
+                                  data_parallel_size=world // 2, sequence_parallel=True, seed=3)
+        _, _, _, device = initialize_distributed_training(cfg)
+        model, mc = create_model(cfg, torch.bfloat16, device)
+        opt = create_optimizer(model, cfg, device)
+        assert type(opt).__name__ == ("PeerShardedAdamW" if sharded else "FusedAdamW"), type(opt).__name__
+        from scaletorch_b200.parallel.process_group import process_group_manager as pgm
+
+        loader = MicroBatchDataLoader(2, 256, synthetic=True, vocab_size=mc.vocab_size, seed=11 + pgm.dp_rank, num_samples=64)
+        rec = []
+        for _ in range(3):
+            opt.zero_grad()
+            if hasattr(model, "reset"):
+                model.reset()
+            loss = training_step(model, loader, device, torch.bfloat16, cfg)
+            opt.step()
+            rec.append((float(loss.item()), opt.grad_norm()))
+        if rank == 0:
+            torch.save(rec, out_path)
+        dist.barrier()
+    finally:
+        if dist.is_initialized():
+            dist.destroy_process_group()
+
+
+def test_sharded_optimizer_under_tensor_parallelism(tmp_path):
+    """TP2 x DP2: the sharded optimiser's global gradient norm (shards summed over the DP group, tensor-parallel
+    replicas counted once) and the loss trajectory must match the all-reduce + replicated AdamW path."""
+    if torch.cuda.device_count() < 4:
+        pytest.skip("needs 4 GPUs")
+    recs = []
+    for sharded in (True, False):
+        out = str(tmp_path / f"rec_{int(sharded)}.pt")
+        mp.spawn(_trainer_worker, args=(4, _free_port(), sharded, out), nprocs=4, join=True)
+        recs.append(torch.load(out))
+    for (l1, n1), (l0, n0) in zip(*recs):
+        assert abs(n1 - n0) < 2e-2 * max(n0, 1e-6), (recs[0], recs[1])
+        assert abs(l1 - l0) < 2e-2 * abs(l0), (recs[0], recs[1])

@@ -295,6 +295,17 @@ def run_ours(args):
         e2e = {"value": tokens * args.steps / (ms_e2e / 1e3), "unit": "tokens/s", "ms_per_step": ms_e2e / args.steps,
                "h2d_bytes_per_step": per_rank_tokens * 8 * 3, "d2h_bytes_per_step": 4, "last_loss": losses[-1]}
 
+    # expert parallelism: (token, expert) pairs dropped because a receive region was full, summed over layers and ranks
+    # (0 by construction unless a capacity factor below the EP size was asked for)
+    ep_dropped = None
+    if args.ep > 1:
+        tot = torch.zeros(1, dtype=torch.float64, device=device)
+        for m in model.modules():
+            d = getattr(m, "dropped_pairs", None)
+            if d is not None:
+                tot += d.double().sum()
+        dist.all_reduce(tot)
+        ep_dropped = int(tot.item())
     if rank == 0:
         tokens = cfgd["global_batch"] * args.seq_len
         value = tokens * args.steps / (ms / 1e3)
@@ -308,7 +319,8 @@ def run_ours(args):
             "mfu_pct_of_nominal_2.25PF": get_mfu(value / world, num_params, model_config, 2.25e15, args.seq_len),
             "num_params": num_params, "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
             "comm_kernel_launches": {k: per_kernel.get(k, 0) for k in comm_kernels if per_kernel.get(k, 0)},
-            "dp_transport": dp_transport, "optimizer": type(optimizer).__name__,
+            "dp_transport": dp_transport, "optimizer": type(optimizer).__name__, "ep_dropped_pairs": ep_dropped,
+            "ep_capacity_factor": os.environ.get("SCALETORCH_B200_EP_CAPACITY", "dropless") if args.ep > 1 else None,
             "cuda_graph": bool(graphed is not None and graphed.graph is not None),
             "native_lib": str(_native.lib_path()),
         }

@@ -193,7 +193,8 @@ def _trainer_worker(rank, world, port, sharded, out_path):
 
         cfg = ScaleTorchArguments(model_name_or_path="tiny-qwen3", micro_batch_size=2, sequence_length=256, synthetic_data=True,
                                   dtype="bfloat16", learning_rate=1e-3, max_grad_norm=0.5, tensor_parallel_size=2,
-                                  data_parallel_size=world // 2, sequence_parallel=True, seed=3)
+                                  data_parallel_size=world // 2, sequence_parallel=True, seed=3, num_attention_heads=4,
+                                  num_key_value_heads=2)
         _, _, _, device = initialize_distributed_training(cfg)
         model, mc = create_model(cfg, torch.bfloat16, device)
         opt = create_optimizer(model, cfg, device)

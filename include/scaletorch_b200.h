@@ -198,6 +198,95 @@ int stb_ep_pull(const void* bufs_dev, const void* flag_pages_dev, long region_of
                 const int* src_rank, const int* src_row, const float* weights, long T, int k, int H, int rank,
                 int world, int slot, unsigned epoch, int sm_budget, cudaStream_t stream);    /* 2 epochs */
 
+/* ---- round-2 entry points ---------------------------------------------------------------------------------------- */
+
+/* CTA-pair GEMM (csrc/gemm_pair.cu): cluster (2,1,1), tcgen05.mma.cta_group::2 with a 256-row UMMA tile, each CTA
+ * TMA-loads half of B, accumulators in both CTAs' TMEM, split-K by TMA reduce-add.  bn = 128 / 256 / 0 (cost model),
+ * splits = 0 (cost model) or the number of K partitions.  stb_gemm_bf16 dispatches here when its cost model says so
+ * (SCALETORCH_B200_GEMM_PAIR=0/1/2: never / cost model / always). */
+int stb_gemm_bf16_2cta(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc, int a_mn,
+                       int b_mn, int out_fp32, int accumulate, int bn, int splits, cudaStream_t stream);
+
+/* Attention on a (query block, key block) pair of a longer sequence -- the building block of ring attention
+ * (csrc/attention_fwd.cu, csrc/attention_bwd.cu).  q_lo / S_tot place the query rows inside the full sequence for the
+ * causal mask.  Forward: merge = 0 writes (out, lse, acc); merge = 1 folds this block into the running fp32 `acc` and
+ * `lse` (log-sum-exp merge in the epilogue) and rewrites `out`.  Backward: dq / dk / dv are fp32 accumulators; dq_acc = 1
+ * adds into dq; dk / dv are always added with red.global.add.v4.f32 at system scope, so they may live in a peer's window.
+ * Reference: scaletorch/parallel/context_parallel/context_parallel.py:40-244 (Python LSE merge, P2P per step). */
+int stb_flash_attn_fwd_block(const void* q, const void* k, const void* v, void* out, float* lse, float* acc, int merge,
+                             int q_lo, int S_tot, int B, int Sq, int Sk, int Hq, int Hkv, int D, long q_sb, long q_ss,
+                             long q_sh, long k_sb, long k_ss, long k_sh, long v_sb, long v_ss, long v_sh, float scale,
+                             int causal, cudaStream_t stream);
+int stb_flash_attn_bwd_block(const void* dout, const void* q, const void* k, const void* v, const void* out,
+                             const float* lse, float* delta, float* dq, float* dk, float* dv, int B, int Sq, int Sk,
+                             int Hq, int Hkv, int D, long q_sb, long q_ss, long q_sh, long k_sb, long k_ss, long k_sh,
+                             long v_sb, long v_ss, long v_sh, long dq_sb, long dq_ss, long dq_sh, long dk_sb, long dk_ss,
+                             long dk_sh, long dv_sb, long dv_ss, long dv_sh, float scale, int causal, int q_lo,
+                             int S_tot, int compute_delta, int dq_acc, cudaStream_t stream);
+/* delta[b, h, q] = rowsum(dO * O), contiguous [B, Sq, Hq, 128] operands. */
+int stb_attn_bwd_delta(const void* dout, const void* out, float* delta, int B, int Sq, int Hq, cudaStream_t stream);
+/* One-kernel backward (csrc/attention_bwd_fused.cu): S / dP and the exp pass are computed once per tile pair and feed
+ * dV, dK and dQ; dQ tiles are TMA reduce-added into the fp32 `dq`, which the caller zeroes beforehand. */
+int stb_flash_attn_bwd_fused(const void* dout, const void* q, const void* k, const void* v, const float* lse,
+                             const float* delta, float* dq, void* dk, void* dv, int B, int Sq, int Sk, int Hq, int Hkv,
+                             int D, long q_sb, long q_ss, long q_sh, long k_sb, long k_ss, long k_sh, long v_sb,
+                             long v_ss, long v_sh, long dq_sb, long dq_ss, long dq_sh, long dk_sb, long dk_ss,
+                             long dk_sh, long dv_sb, long dv_ss, long dv_sh, float scale, int causal,
+                             cudaStream_t stream);
+/* QK-norm + RoPE backward that takes dQ as the fp32 tensor written by stb_flash_attn_bwd_fused (no conversion pass). */
+int stb_qknorm_rope_bwd_f32q(const void* dqk, const float* dq32, const void* qkv, const void* wq, const void* wk,
+                             const float* cos_t, const float* sin_t, const int* pos, const float* rstd, void* dqkv,
+                             float* dwq, float* dwk, int T, int S, int Hq, int Hkv, int head_dim, int pos_offset,
+                             int use_norm, cudaStream_t stream);
+
+/* Vocabulary-chunked cross-entropy statistics: merge = 0 starts, merge = 1 folds chunk [vocab_start, vocab_start + Vc)
+ * into the running (max, sum-exp, target logit) rows (csrc/loss_optim.cu). */
+int stb_ce_stats_chunk(const void* logits, const long* targets, float* stats, int rows, int Vc, long ld,
+                       int vocab_start, int merge, cudaStream_t stream);
+
+/* ZeRO-1 over symmetric memory (csrc/comm.cu).  Reference: torch DDP all-reduce + replicated AdamW,
+ * scaletorch/parallel/data_parallel/*.py, scaletorch/trainer/*.py.
+ *   stb_reduce_scatter_f32   each rank reduces the [own_lo, own_hi) slice of bucket [offset, offset + n) from all
+ *                            peers' fp32 gradient windows (multimem.ld_reduce when multicast_ptr != NULL, peer loads
+ *                            otherwise) into its own window, scaled.                                   2 epochs
+ *   stb_allreduce_tiny_f32   <= 32 floats (sum of squares partials), one warp.                       1 epoch
+ *   stb_adamw_shard_bcast    AdamW on the owned fp32 shard (g, m, v local) and broadcast of the new bf16 parameters
+ *                            into every rank's parameter window (multimem.st or peer stores); clip_coef / hyper =
+ *                            {lr, bias-correction 1, bias-correction 2} are read from device memory.   2 epochs
+ *   stb_param_bcast          owner -> all broadcast of a parameter range (deferred gather).            2 epochs */
+int stb_reduce_scatter_f32(const void* bufs_dev, const void* multicast_ptr, const void* flag_pages_dev,
+                           long offset_elems, long n, long own_lo, long own_hi, float scale, int rank, int world,
+                           int slot, unsigned epoch, int sm_budget, cudaStream_t stream);
+int stb_allreduce_tiny_f32(const void* bufs_dev, const void* flag_pages_dev, long offset_elems, int n, int rank,
+                           int world, int slot, unsigned epoch, cudaStream_t stream);
+int stb_adamw_shard_bcast(const void* pbufs_dev, void* p_multicast_ptr, const void* flag_pages_dev, long p_offset_elems,
+                          const float* g, float* m, float* v, long n, float beta1, float beta2, float eps,
+                          float weight_decay, const float* clip_coef, float grad_scale, const float* hyper, int rank,
+                          int world, int slot, unsigned epoch, int sm_budget, cudaStream_t stream);
+int stb_param_bcast(const void* pbufs_dev, void* p_multicast_ptr, const void* flag_pages_dev, long p_offset_elems,
+                    long n, int owner, int rank, int world, int slot, unsigned epoch, int sm_budget,
+                    cudaStream_t stream);
+
+/* MoE routing and the expert-parallel plan on the device (csrc/moe_router.cu): no library sort / scan, no host sync.
+ * Reference: scaletorch/models/model_qwen3_moe.py:30-171, scaletorch/parallel/expert_parallel/ep_comms.py:96-102.
+ *   router_fwd   logits [T, E] bf16 -> top-k ids, softmax(top-k) weights, per-expert counts, position of each pair in
+ *                its expert's segment, per-expert sum of full-softmax probabilities (aux loss).  E <= 256, k <= 16.
+ *   router_bwd   d(weights), d(aux) -> d(logits).
+ *   ep_plan      [ep, E] count table -> destination (rank, row) of every pair in the receivers' 128-row-padded regions,
+ *                this rank's padded offsets / tile->expert table, number of pairs beyond rows_cap (dropped).
+ *   ep_zero_padding   zeroes only the padding rows of a receive region;  copy_rows_dyn  copies *n_rows rows. */
+int stb_moe_router_fwd(const void* logits, long T, int E, int k, float* weights, int* idx, int* pos, int* counts,
+                       float* psum, cudaStream_t stream);
+int stb_moe_router_bwd(const void* logits, const float* weights, const int* idx, const float* dweights,
+                       const int* counts, const float* g_aux, float aux_scale, long T, int E, int k, void* dlogits,
+                       cudaStream_t stream);
+int stb_ep_plan(const int* table, const int* flat, const int* pos, long P, int E, int ep, int rank, int rows_cap,
+                int* dst_row, int* dst_rank, int* dropped, int* offs_pad, int* tokens_per_expert, int* tile_expert,
+                int n_tiles, cudaStream_t stream);
+int stb_ep_zero_padding(void* region, const int* offs_pad, const int* tokens_per_expert, int e_local, int H,
+                        int rows_cap, cudaStream_t stream);
+int stb_copy_rows_dyn(const void* src, void* dst, const int* n_rows, long row_bytes, int max_rows, cudaStream_t stream);
+
 /* ---- host runtime: native micro-batch producer, csrc/runtime/token_loader.cpp -----------------------------------
  * Worker threads cut (input, target) windows out of a flat int32 token array, apply the context-parallel slice
  * (contiguous or zig-zag) and fill a caller-owned ring of n_slots int64 [2][mbs][S / cp] host buffers (pin them).

@@ -333,6 +333,8 @@ def run_ours(args):
             out["mfu_pct_of_measured_sustained"] = get_mfu(value / world, num_params, model_config,
                                                            peaks["bf16_tflops_sustained"] * 1e12, args.seq_len)
         print(json.dumps(out), flush=True)
+    if graphed is not None:
+        graphed.release()                           # graphs with collective nodes go before the communicator does
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

@@ -67,6 +67,9 @@ def initialize_distributed_training(config) -> tuple[int, int, int, torch.device
 
 
 def cleanup_distributed() -> None:
+    from .graphed import release_all
+
+    release_all()                                   # captured steps first: see graphed.release_all
     if pgm:
         try:
             pgm.cleanup()

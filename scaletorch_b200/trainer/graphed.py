@@ -10,17 +10,33 @@ zero-grad → GA × (forward, backward, bucket all-reduce) → clip → AdamW se
 
 The reference has no counterpart (eager PyTorch; ``tools/optimize_mfu.py`` tries ``torch.compile``).
 
-Captured and validated on hardware: single GPU, data parallelism (2 / 4 / 8 ranks) and context parallelism.  Not
-captured: pipeline-parallel schedules (NCCL p2p with data-dependent ordering across micro-batches), the c10d fallback
-collectives, tensor parallelism (the one TP2+SP attempt hung) and MoE models (capture of the routing ops invalidated the
-stream in the one attempt made); ``GraphedTrainStep.supported`` says whether a configuration qualifies.
+Captured and validated on hardware: single GPU, data parallelism (2 / 4 / 8 ranks, all-reduce and the sharded
+reduce-scatter / AdamW / broadcast path) and context parallelism.  Opt-in (``SCALETORCH_B200_GRAPH_MP=tp``): tensor
+parallelism -- the Qwen3-8B TP2 + SP step captures and replays (132.1 ms vs 133.7 ms eager, profiles/multigpu_r2_n2.jsonl);
+the one run made stalled while tearing the process group down with the graph alive, hence ``release_all`` below, and the
+layout stays opt-in until that teardown has been re-run on hardware.  Not captured: pipeline-parallel schedules (NCCL
+p2p with data-dependent ordering across micro-batches), the c10d ZeRO-1 fallback, and expert-parallel MoE steps
+(``cudaErrorStreamCaptureInvalidated`` at ``capture_end`` with no failing call before it; ``=ep`` opts in for debugging,
+``tools/debug_capture_moe*.py`` bisect it).  ``GraphedTrainStep.supported`` says whether a configuration qualifies.
 """
 from __future__ import annotations
+
+import weakref
 
 import torch
 
 from ..parallel.process_group import process_group_manager as pgm
 from .train_step import training_step
+
+_live: "weakref.WeakSet[GraphedTrainStep]" = weakref.WeakSet()
+
+
+def release_all() -> None:
+    """Drops every captured step graph.  ``cleanup_distributed`` calls it before ``destroy_process_group``: a graph that
+    holds NCCL kernel nodes keeps the communicator busy, and tearing the communicator down under it stalled the one
+    TP2 run that exited with the graph alive."""
+    for g in list(_live):
+        g.release()
 
 
 class _StaticBatches:
@@ -52,6 +68,15 @@ class GraphedTrainStep:
         self._steps_seen = 0
         self.failed = False
         self.ga = config.gradient_accumulation_steps
+        _live.add(self)
+
+    def release(self) -> None:
+        """Waits for the device, then frees the graph and the memory pool it owns (the step falls back to eager)."""
+        if self.graph is not None:
+            torch.cuda.synchronize()
+            self.graph.reset()
+            self.graph, self.static_loss = None, None
+            self.failed = True                       # do not re-capture after a release
 
     @staticmethod
     def supported(config, optimizer, model=None) -> bool:
@@ -65,12 +90,10 @@ class GraphedTrainStep:
 
         allow = os.environ.get("SCALETORCH_B200_GRAPH_MP", "")      # "tp", "ep" or "tp,ep": opt in to capturing these layouts
         if pgm and ((pgm.ep_world_size > 1 and "ep" not in allow) or (pgm.tp_world_size > 1 and "tp" not in allow)):
-            # validated on hardware: single GPU, DP (2/4/8 ranks) and CP.  TP2+SP hung inside / after capture in the one
-            # run made (gpurun_out/tp2_graph.log, round 1) and EP invalidated the capture: both stay eager until debugged
+            # validated on hardware: single GPU, DP (2/4/8 ranks) and CP; TP and EP are opt-in (module docstring)
             return False
         if model is not None:
-            # MoE routing uses library sort / scatter ops whose capture invalidated the stream on this stack
-            # (cudaErrorStreamCaptureInvalidated, 2-GPU EP2 run): MoE models stay on the eager path for now
+            # the EP2 MoE step invalidated its capture (module docstring): MoE models stay eager unless opted in
             from ..models.model_qwen3_moe import MoELayer
 
             if any(isinstance(m, MoELayer) for m in model.modules()) and "ep" not in allow:

@@ -44,7 +44,6 @@ struct Params {
   int B, Sq, Sk, Hq, Hkv;
   float scale, scale_log2;
   int causal;
-  int dbg;      // tuning experiments only (STB_FBWD_DBG): 1 = no TMA reduce, 2 = no staging stores, 4 = no dQ MMA
 };
 
 struct Smem {
@@ -211,7 +210,6 @@ __global__ void __launch_bounds__(kThreads, 1)
         for (int ks = 0; ks < 4; ++ks)   // dK += dS^T Q
           umma_f16_ss(tmem_base + kColDK, umma_smem_desc_sw128(dst_addr + ks * 32, 16, 1024),
                       umma_smem_desc_sw128(q_addr + ks * 2048, kSmallHalf, 1024), idesc_g, (i | ks) != 0);
-        if (!(p.dbg & 4))
 #pragma unroll
         for (int ks = 0; ks < 8; ++ks)   // dQ^T = K^T dS^T  (K = 128 keys, 16 per step; both operands MN-major)
           umma_f16_ss(tmem_base + kColDQ + db * kST, umma_smem_desc_sw128(k_addr + ks * 2048, kBigHalf, 1024),
@@ -355,7 +353,6 @@ __global__ void __launch_bounds__(kThreads, 1)
       mbar_arrive(&dq_free[db]);
       if (leader) tma_store_wait_read<0>();       // the previous reduce-add has finished reading the staging tile
       named_bar_sync(3, 128);
-      if (!(p.dbg & 2))
 #pragma unroll
       for (int j = 0; j < 32; ++j) {
         sDQ[j * 128 + d] = __uint_as_float(r0[j]) * p.scale;
@@ -363,7 +360,7 @@ __global__ void __launch_bounds__(kThreads, 1)
       }
       fence_proxy_async_smem();
       named_bar_sync(3, 128);
-      if (leader && !(p.dbg & 1)) {
+      if (leader) {
         tma_reduce_add_4d(&tmDQ, sDQ, 0, hq, q0, b);
         tma_store_commit();
       }
@@ -403,10 +400,6 @@ extern "C" int stb_flash_attn_bwd_fused(const void* dout, const void* q, const v
   p.dv = (__nv_bfloat16*)dv; p.dv_sb = dv_sb; p.dv_ss = dv_ss; p.dv_sh = dv_sh;
   p.B = B; p.Sq = Sq; p.Sk = Sk; p.Hq = Hq; p.Hkv = Hkv;
   p.scale = scale; p.scale_log2 = scale * kLog2e; p.causal = causal;
-  {
-    const char* e = getenv("STB_FBWD_DBG");
-    p.dbg = e ? atoi(e) : 0;
-  }
   const long do_ss = long(Hq) * 128, do_sb = do_ss * Sq;
   CUtensorMap tmQ, tmK, tmV, tmDO, tmDQ;
   if (int rc = make_tmap_bshd(&tmQ, q, B, Sq, Hq, D, q_sb, q_ss, q_sh, 64, kST)) return rc;

@@ -78,7 +78,7 @@ def bench_gemm(out):
             emit({"kernel": "gemm", "shape": name, "mode": mode, "M": M, "N": N, "K": K,
                   "ours_ms": round(t_o, 4), "cublas_ms": round(t_l, 4),
                   "ours_tflops": round(flops / t_o / 1e9, 1), "cublas_tflops": round(flops / t_l / 1e9, 1),
-                  "frac_of_measured_peak": round(flops / t_o / 1e9 / peak, 3)}, out)
+                  "frac_of_measured_peak": round(flops / t_o / 1e9 / peak, 3), "vs_cublas": round(t_l / t_o, 3)}, out)
             del a, b
 
 

@@ -22,4 +22,4 @@ dq32 = torch.zeros(q.shape, device="cuda", dtype=torch.float32)
 flops = 2.5 * 4.0 * B * Hq * S * S * D / 2
 t2 = timeit(lambda: A._flash_bwd(do, q, k, v, out, lse, dq, dk, dv, True, scale), iters=20)
 tf = timeit(lambda: A._flash_bwd_fused(do, q, k, v, out, lse, dq32, dk, dv, True, scale), iters=20)
-print(f"dbg={os.environ.get('STB_FBWD_DBG', '0')} two-kernel {t2 * 1e3:.1f} us ({flops / t2 / 1e9:.0f} TFLOP/s)   fused(+delta) {tf * 1e3:.1f} us ({flops / tf / 1e9:.0f} TFLOP/s)")
+print(f"two-kernel {t2 * 1e3:.1f} us ({flops / t2 / 1e9:.0f} TFLOP/s)   fused(+delta) {tf * 1e3:.1f} us ({flops / tf / 1e9:.0f} TFLOP/s)")

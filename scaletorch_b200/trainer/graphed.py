@@ -68,6 +68,13 @@ class GraphedTrainStep:
         self._steps_seen = 0
         self.failed = False
         self.ga = config.gradient_accumulation_steps
+        import os
+
+        # Warm-up and capture on ONE side stream (the documented recipe).  Autograd nodes that outlive an iteration --
+        # the AccumulateGrad node of a parameter whose gradient arrives through plain autograd -- remember the stream
+        # they were created on; if that is the default stream, the capture makes the default stream wait on a captured
+        # event, which invalidates the capture (cudaErrorStreamCaptureInvalidated at capture_end).
+        self._stream = torch.cuda.Stream() if os.environ.get("SCALETORCH_B200_GRAPH_SIDE_STREAM", "0") == "1" else None
         _live.add(self)
 
     def release(self) -> None:
@@ -135,7 +142,14 @@ class GraphedTrainStep:
         if self.graph is None:
             if self._steps_seen < self.warmup:
                 self._steps_seen += 1
-                return self._eager(src)
+                if self._stream is None:
+                    return self._eager(src)
+                cur = torch.cuda.current_stream()
+                self._stream.wait_stream(cur)
+                with torch.cuda.stream(self._stream):
+                    loss = self._eager(src)
+                cur.wait_stream(self._stream)
+                return loss
             # capture; the captured work also *runs* once?  No: capture only records, so run the step for this batch by
             # replaying right after the capture.
             if self.failed:
@@ -146,7 +160,7 @@ class GraphedTrainStep:
             try:
                 # thread_local: the loader's prefetch thread may pin memory while we capture; kernels launched into the
                 # capturing stream by the autograd thread are captured in either mode
-                with torch.cuda.graph(graph, capture_error_mode="thread_local"):
+                with torch.cuda.graph(graph, stream=self._stream, capture_error_mode="thread_local"):
                     self.static_loss = self._eager(src)
                 self.graph = graph
             except Exception as e:  # an op in this configuration cannot be captured: stay eager, loudly

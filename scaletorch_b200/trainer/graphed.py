@@ -11,13 +11,18 @@ zero-grad → GA × (forward, backward, bucket all-reduce) → clip → AdamW se
 The reference has no counterpart (eager PyTorch; ``tools/optimize_mfu.py`` tries ``torch.compile``).
 
 Captured and validated on hardware: single GPU, data parallelism (2 / 4 / 8 ranks, all-reduce and the sharded
-reduce-scatter / AdamW / broadcast path) and context parallelism.  Opt-in (``SCALETORCH_B200_GRAPH_MP=tp``): tensor
-parallelism -- the Qwen3-8B TP2 + SP step captures and replays (132.1 ms vs 133.7 ms eager, profiles/multigpu_r2_n2.jsonl);
-the one run made stalled while tearing the process group down with the graph alive, hence ``release_all`` below, and the
-layout stays opt-in until that teardown has been re-run on hardware.  Not captured: pipeline-parallel schedules (NCCL
-p2p with data-dependent ordering across micro-batches), the c10d ZeRO-1 fallback, and expert-parallel MoE steps
-(``cudaErrorStreamCaptureInvalidated`` at ``capture_end`` with no failing call before it; ``=ep`` opts in for debugging,
-``tools/debug_capture_moe*.py`` bisect it).  ``GraphedTrainStep.supported`` says whether a configuration qualifies.
+reduce-scatter / AdamW / broadcast path), context parallelism, and -- since warm-up and capture share one side stream --
+tensor parallelism (Qwen3-8B TP2 + SP: 131.8 ms replayed vs 133.7 ms eager) and expert-parallel MoE (Qwen3-30B-A3B
+shapes, 8 layers, EP2: 56.1 vs 57.9 ms), 2 ranks each (gpurun_out/n2c_*.log -> profiles/multigpu_r2_n2.jsonl).
+``SCALETORCH_B200_GRAPH_MP`` lists the model-parallel layouts that may be captured (default ``tp,ep``; ``none`` keeps
+them eager).  Not captured: pipeline-parallel schedules (NCCL p2p with data-dependent ordering across micro-batches) and
+the c10d ZeRO-1 fallback.  ``GraphedTrainStep.supported`` says whether a configuration qualifies.
+
+Two things that were needed beyond "no host sync": (1) the eager warm-up steps run on the SAME side stream the capture
+uses -- AccumulateGrad nodes remember the stream they were created on, and with warm-up on the default stream the
+captured backward made the default stream wait on a captured event, which invalidated MoE captures at ``capture_end``
+(``cudaErrorStreamCaptureInvalidated``) with no failing call before it; (2) graphs are released before the process
+group is destroyed (``release_all``) -- a graph holding NCCL kernel nodes stalled the communicator teardown.
 """
 from __future__ import annotations
 
@@ -74,7 +79,7 @@ class GraphedTrainStep:
         # the AccumulateGrad node of a parameter whose gradient arrives through plain autograd -- remember the stream
         # they were created on; if that is the default stream, the capture makes the default stream wait on a captured
         # event, which invalidates the capture (cudaErrorStreamCaptureInvalidated at capture_end).
-        self._stream = torch.cuda.Stream() if os.environ.get("SCALETORCH_B200_GRAPH_SIDE_STREAM", "0") == "1" else None
+        self._stream = torch.cuda.Stream() if os.environ.get("SCALETORCH_B200_GRAPH_SIDE_STREAM", "1") == "1" else None
         _live.add(self)
 
     def release(self) -> None:
@@ -95,12 +100,11 @@ class GraphedTrainStep:
             return False
         import os
 
-        allow = os.environ.get("SCALETORCH_B200_GRAPH_MP", "")      # "tp", "ep" or "tp,ep": opt in to capturing these layouts
+        allow = os.environ.get("SCALETORCH_B200_GRAPH_MP", "tp,ep")  # model-parallel layouts that may be captured
         if pgm and ((pgm.ep_world_size > 1 and "ep" not in allow) or (pgm.tp_world_size > 1 and "tp" not in allow)):
-            # validated on hardware: single GPU, DP (2/4/8 ranks) and CP; TP and EP are opt-in (module docstring)
+            # SCALETORCH_B200_GRAPH_MP=none (or a list without the layout) keeps these eager
             return False
         if model is not None:
-            # the EP2 MoE step invalidated its capture (module docstring): MoE models stay eager unless opted in
             from ..models.model_qwen3_moe import MoELayer
 
             if any(isinstance(m, MoELayer) for m in model.modules()) and "ep" not in allow:

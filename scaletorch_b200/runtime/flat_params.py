@@ -168,16 +168,7 @@ class FlatParamStore:
         import torch.distributed as dist
 
         flat = torch.cat([s.param.main_grad.reshape(-1) for s in slots])
-        done = False
-        if flat.is_cuda and flat.dtype == torch.float32:
-            from . import symm
-            from .fused_ops import SmallAllReduce
-
-            if SmallAllReduce.enabled() and symm.group_ready(group) and flat.numel() <= (1 << 20):
-                SmallAllReduce.for_group(group).all_reduce_(flat)
-                done = True
-        if not done:
-            dist.all_reduce(flat, group=group)
+        dist.all_reduce(flat, group=group)
         off = 0
         for s in slots:
             n = s.param.main_grad.numel()

@@ -343,55 +343,3 @@ class EmbeddingGradExchange:
         N.call("stb_embedding_bwd_peers", g.bufs_dev, g.flag_pages_dev, ids_off, dout_off, dst.data_ptr(), T, H,
                int(vocab_start), int(vocab_local), self.scale, g.rank, g.world, SLOT_EMB, g.take_epochs(SLOT_EMB, 2), 32,
                N.stream_ptr())
-
-
-class SmallAllReduce:
-    """fp32 sum all-reduce of small tensors (gradient-norm scalar, TP-partial norm-weight gradients) through a private
-    symmetric buffer and ``stb_allreduce_f32`` -- no c10d call, so the step stays free of NCCL kernels (a precondition
-    for capturing tensor-/expert-parallel steps in a CUDA graph, ``docs/roadmap.md`` §3).
-
-    EXPERIMENTAL: opt in with ``SCALETORCH_B200_PEER_SMALL_AR=1``; not yet run on hardware."""
-
-    _cache: dict = {}
-
-    def __init__(self, group, capacity: int = 1 << 20):
-        import torch.distributed._symmetric_memory as sm
-
-        self.g = get_group(group)
-        self.capacity = capacity
-        self.raw = sm.empty(capacity * 4, dtype=torch.uint8, device=self.g.device)
-        self.raw.zero_()
-        self.h = sm.rendezvous(self.raw, group=group)
-        self.bufs_dev = int(self.h.buffer_ptrs_dev)
-        self.buf = self.raw.view(torch.float32)
-        torch.cuda.synchronize()
-        dist.barrier(group)
-
-    @classmethod
-    def enabled(cls) -> bool:
-        import os
-
-        return os.environ.get("SCALETORCH_B200_PEER_SMALL_AR", "0") == "1"
-
-    @classmethod
-    def for_group(cls, group) -> "SmallAllReduce":
-        key = id(group)
-        if key not in cls._cache:
-            cls._cache[key] = cls(group)
-        return cls._cache[key]
-
-    def all_reduce_(self, t: torch.Tensor) -> torch.Tensor:
-        """In-place sum of the fp32 tensor ``t`` (numel <= capacity) over the group."""
-        n = t.numel()
-        if n > self.capacity or t.dtype != torch.float32:
-            raise ValueError(f"SmallAllReduce takes fp32 tensors of at most {self.capacity} elements")
-        padded = (n + 3) // 4 * 4
-        stage = self.buf[:padded]
-        if padded != n:
-            stage[n:].zero_()
-        stage[:n].copy_(t.reshape(-1))
-        g = self.g
-        N.call("stb_allreduce_f32", self.bufs_dev, None, g.flag_pages_dev, 0, padded, 1.0, g.rank, g.world, SLOT_AR,
-               g.take_epochs(SLOT_AR, 2), 8, N.stream_ptr())
-        t.copy_(stage[:n].view_as(t))
-        return t

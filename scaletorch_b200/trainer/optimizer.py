@@ -18,15 +18,8 @@ from ..runtime.flat_params import FlatParamStore
 
 
 def _small_all_reduce(t: torch.Tensor, group) -> None:
-    """Sum of a small fp32 tensor over ``group``: c10d by default, the peer-memory kernel when opted in
-    (``runtime.fused_ops.SmallAllReduce``, experimental)."""
-    if t.is_cuda and t.dtype == torch.float32:
-        from ..runtime.fused_ops import SmallAllReduce
-        from ..runtime import symm
-
-        if SmallAllReduce.enabled() and symm.group_ready(group):
-            SmallAllReduce.for_group(group).all_reduce_(t)
-            return
+    """Sum of a small fp32 tensor over ``group`` (c10d; it captures into the step graph).  The sharded optimiser uses the
+    peer-memory ``stb_allreduce_tiny_f32`` for its own partial sums (``trainer/zero.py``)."""
     dist.all_reduce(t, group=group)
 
 

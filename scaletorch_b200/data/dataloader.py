@@ -38,6 +38,15 @@ class MicroBatchDataLoader(DataLoader):
                  subset_name: str | None = None, pin_memory: bool = True, shuffle: bool = False, seed: int = 0,
                  synthetic: bool = False, vocab_size: int | None = None, dataset=None, tokenizer=None,
                  text_column_name: str = "text", strategy: str = "concat_chunk"):
+        # argument checks of the reference loader (``dataloader.py:60-105``): fail at construction, not in a worker
+        for name, v in (("micro_batch_size", micro_batch_size), ("sequence_length", sequence_length),
+                        ("gradient_accumulation_steps", gradient_accumulation_steps)):
+            if not isinstance(v, int) or isinstance(v, bool) or v < 1:
+                raise ValueError(f"{name} must be a positive integer, got {v!r}")
+        if num_samples is not None and (not isinstance(num_samples, int) or num_samples < 1):
+            raise ValueError(f"num_samples must be a positive integer or None, got {num_samples!r}")
+        if not isinstance(num_workers, int) or num_workers < 0:
+            raise ValueError(f"num_workers must be a non-negative integer, got {num_workers!r}")
         self.micro_batch_size = micro_batch_size
         self.sequence_length = sequence_length
         self.gradient_accumulation_steps = gradient_accumulation_steps
@@ -76,7 +85,12 @@ class MicroBatchDataLoader(DataLoader):
 
     def collate_batch(self, batch: list[dict[str, Any]]) -> dict[str, Any]:
         """Stack → CP-slice ``[cp_rank·S/cp, +S/cp)`` → shifted targets and absolute positions."""
+        if not batch:
+            raise ValueError("collate_batch got an empty batch")
         ids = torch.stack([torch.as_tensor(b["input_ids"], dtype=torch.long) for b in batch])  # [mbs, S+1]
+        if ids.shape[1] < self.sequence_length + 1:
+            raise ValueError(f"samples hold {ids.shape[1]} tokens; the loader needs sequence_length + 1 = "
+                             f"{self.sequence_length + 1} (targets are the inputs shifted by one)")
         if self.cp_world_size > 1:
             from ..parallel.context_parallel import zigzag
 

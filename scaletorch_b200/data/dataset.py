@@ -37,6 +37,10 @@ def get_tokenize_strategy(name: str) -> TokenizeFn:
 @register_tokenize_strategy("concat_chunk")
 def tokenizer_group_text(examples: dict[str, list], tokenizer: Any, sequence_length: int, text_column: str = "text"):
     """Concatenates the batch's tokens and emits chunks of ``sequence_length + 1`` ids."""
+    if not isinstance(sequence_length, int) or sequence_length < 1:
+        raise ValueError("sequence_length must be a positive integer")
+    if not examples or text_column not in examples:
+        raise ValueError(f"examples must hold a '{text_column}' column")
     enc = tokenizer(examples[text_column], add_special_tokens=False, return_attention_mask=False,
                     return_token_type_ids=False)
     ids = np.fromiter((t for seq in enc["input_ids"] for t in seq), dtype=np.int64)
@@ -59,6 +63,8 @@ class DatasetProcessor:
     def __init__(self, tokenizer_name_or_path: str | None = None, tokenizer: Any = None, device=None):
         if tokenizer is None and tokenizer_name_or_path is None:
             raise ValueError("either tokenizer or tokenizer_name_or_path must be given")
+        if tokenizer is None and (not isinstance(tokenizer_name_or_path, str) or not tokenizer_name_or_path.strip()):
+            raise ValueError(f"tokenizer_name_or_path must be a non-empty string, got {tokenizer_name_or_path!r}")
         self.tokenizer = tokenizer if tokenizer is not None else self.create_tokenizer(tokenizer_name_or_path)
 
     @staticmethod
@@ -88,8 +94,10 @@ class DatasetProcessor:
 
     def tokenize_dataset(self, dataset, text_column_name: str = "text", sequence_length: int = 1024, num_proc: int = 1,
                          strategy: str = "concat_chunk"):
-        if sequence_length < 1:
-            raise ValueError("sequence_length must be positive")
+        if not isinstance(sequence_length, int) or sequence_length < 1:
+            raise ValueError("sequence_length must be a positive integer")
+        if not isinstance(num_proc, int) or num_proc < 1:
+            raise ValueError("num_proc must be a positive integer")
         if text_column_name not in dataset.column_names:
             raise ValueError(f"column '{text_column_name}' not found in dataset columns {dataset.column_names}")
         fn = get_tokenize_strategy(strategy)

@@ -33,6 +33,10 @@ def rank_print(*args: Any, is_print_rank: bool = True, **kwargs: Any) -> None:
 def set_all_seed(seed: int, deterministic: bool = False, rank_offset: int = 0) -> None:
     """Seeds python / numpy / torch.  ``rank_offset`` lets model-parallel shards initialise
     differently (the reference seeds every rank identically, SURVEY §2.7 #14)."""
+    if isinstance(seed, bool) or not isinstance(seed, (int, np.integer)):
+        raise TypeError(f"seed must be an integer, got {type(seed).__name__}")
+    if seed < 0:
+        raise ValueError(f"seed must be non-negative, got {seed}")
     seed = int(seed) + int(rank_offset)
     random.seed(seed)
     np.random.seed(seed % (2**32))
@@ -43,6 +47,11 @@ def set_all_seed(seed: int, deterministic: bool = False, rank_offset: int = 0) -
 
 
 def to_readable_format(num: int | float, precision: int = 2) -> str:
+    """``1234567 -> '1.23M'`` (K / M / B / T; the sign is kept)."""
+    if isinstance(num, bool) or not isinstance(num, (int, float, np.integer, np.floating)):
+        raise TypeError(f"num must be a number, got {type(num).__name__}")
+    if not isinstance(precision, int) or precision < 0:
+        raise ValueError(f"precision must be a non-negative integer, got {precision!r}")
     n = float(num)
     for unit, div in (("T", 1e12), ("B", 1e9), ("M", 1e6), ("K", 1e3)):
         if abs(n) >= div:
@@ -58,6 +67,10 @@ def flops_per_token(num_params: float, num_layers: int, num_heads: int, head_dim
 def get_mfu(tokens_per_second: float, num_params: float, model_config: Any, theoretical_flops: float | None = None,
             seq_len: int | None = None) -> float:
     """Model FLOPs utilisation in percent for *one device's* tokens/s (reference ``misc.py:136-174``)."""
+    if tokens_per_second is None or tokens_per_second <= 0 or num_params is None or num_params <= 0:
+        return 0.0
+    if theoretical_flops is not None and theoretical_flops <= 0:
+        return 0.0
     L = model_config.num_hidden_layers
     heads = model_config.num_attention_heads
     hd = getattr(model_config, "head_dim", None) or model_config.hidden_size // heads
@@ -130,6 +143,8 @@ def average_loss_across_dp_cp_ranks(loss: float | torch.Tensor | None, device: t
     ``as_tensor=True`` returns the device scalar without synchronising (for lagged logging)."""
     from ..parallel.process_group import process_group_manager as pgm
 
+    if loss is not None and not isinstance(loss, (int, float, torch.Tensor, np.integer, np.floating)):
+        raise TypeError(f"loss must be a number, a tensor or None, got {type(loss).__name__}")
     if isinstance(loss, torch.Tensor):
         t = loss.detach().to(device=device, dtype=torch.float32).reshape(1).clone()
     else:

@@ -149,7 +149,7 @@ def test_bench_config_dict_names_the_layout():
 
 
 def test_graphed_step_support_matrix(monkeypatch):
-    """Whole-step CUDA-graph replay is offered only for the layouts validated on hardware."""
+    """Whole-step CUDA-graph replay is offered for the layouts validated on hardware; TP / EP can be opted out."""
     import scaletorch_b200.trainer.graphed as G
     from scaletorch_b200.trainer.optimizer import FusedAdamW
 
@@ -166,9 +166,17 @@ def test_graphed_step_support_matrix(monkeypatch):
     monkeypatch.setattr(G, "pgm", pgm())
     assert G.GraphedTrainStep.supported(cfg, opt)                                   # DP / CP
     assert not G.GraphedTrainStep.supported(cfg, torch.optim.SGD([torch.nn.Parameter(torch.zeros(1))], lr=0.1))
-    for bad in (dict(pp_world_size=2), dict(ep_world_size=2), dict(tp_world_size=2)):
-        monkeypatch.setattr(G, "pgm", pgm(**bad))
-        assert not G.GraphedTrainStep.supported(cfg, opt), bad
+    monkeypatch.delenv("SCALETORCH_B200_GRAPH_MP", raising=False)
+    monkeypatch.setattr(G, "pgm", pgm(pp_world_size=2))
+    assert not G.GraphedTrainStep.supported(cfg, opt)                               # pipeline schedules stay eager
+    for mp in (dict(ep_world_size=2), dict(tp_world_size=2)):                       # TP / EP: captured by default ...
+        monkeypatch.setattr(G, "pgm", pgm(**mp))
+        assert G.GraphedTrainStep.supported(cfg, opt), mp
+        monkeypatch.setenv("SCALETORCH_B200_GRAPH_MP", "none")                      # ... unless switched off
+        assert not G.GraphedTrainStep.supported(cfg, opt), mp
+        monkeypatch.setenv("SCALETORCH_B200_GRAPH_MP", "tp" if "ep_world_size" in mp else "ep")
+        assert not G.GraphedTrainStep.supported(cfg, opt), mp                       # only the other layout allowed
+        monkeypatch.delenv("SCALETORCH_B200_GRAPH_MP")
     monkeypatch.setattr(G, "pgm", pgm())
     assert not G.GraphedTrainStep.supported(SimpleNamespace(fused_comm=False), opt)  # c10d collectives are not captured
     from scaletorch_b200.models import Qwen3MoE
@@ -179,6 +187,10 @@ def test_graphed_step_support_matrix(monkeypatch):
                               vocab_size=64, hidden_size=32, num_attention_heads=2, num_key_value_heads=1, head_dim=16,
                               max_position_embeddings=32, num_hidden_layers=1, intermediate_size=64, rms_norm_eps=1e-6,
                               rope_theta=1e4, tie_word_embeddings=False)
-    assert not G.GraphedTrainStep.supported(cfg, opt, Qwen3MoE(moe_cfg, ParallelContext()))
+    moe = Qwen3MoE(moe_cfg, ParallelContext())
+    assert G.GraphedTrainStep.supported(cfg, opt, moe)                              # MoE steps capture (side-stream warm-up)
+    monkeypatch.setenv("SCALETORCH_B200_GRAPH_MP", "tp")
+    assert not G.GraphedTrainStep.supported(cfg, opt, moe)
+    monkeypatch.delenv("SCALETORCH_B200_GRAPH_MP")
     monkeypatch.setattr(torch.cuda, "is_available", lambda: False)
     assert not G.GraphedTrainStep.supported(cfg, opt)

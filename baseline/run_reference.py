@@ -59,6 +59,12 @@ def random_checkpoint(model_dir: str, local_rank: int, limit_gb: float = 2.6):
                 sd[f"model.layers.{i}.{k}.weight"] = mk(shape)
         save_file(sd, os.path.join(out, "model.safetensors"))
         open(done, "w").write("ok")
+    elif local_rank != 0:
+        import time
+
+        t0 = time.time()                      # the other ranks of the node wait for local rank 0's files
+        while not os.path.exists(done) and time.time() - t0 < 300:
+            time.sleep(0.2)
     return out, "random-weight checkpoint through the reference's HF loader (keeps the LM head tied)"
 
 

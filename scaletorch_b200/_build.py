@@ -89,7 +89,8 @@ def build(force: bool = False, verbose: bool = False) -> Path:
                 logs.append(log)
     newest = max((o.stat().st_mtime for o in objs), default=0)
     if force or not LIB_PATH.exists() or LIB_PATH.stat().st_mtime < newest:
-        cmd = [_nvcc(), "-shared", "-o", str(LIB_PATH), *map(str, objs)]
+        # -arch at link time too: without it nvcc adds an (empty) device-link stub for its default arch (sm_52)
+        cmd = [_nvcc(), "-shared", "-arch=sm_100a", "-o", str(LIB_PATH), *map(str, objs)]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")

@@ -46,6 +46,12 @@ def main() -> int:
             funcs[name] = []
         elif name is not None:
             funcs[name].append(line)
+    res: dict[str, dict[str, int]] = {}
+    usage = subprocess.run(["cuobjdump", "-res-usage", str(LIB)], capture_output=True, text=True).stdout.splitlines()
+    for i, line in enumerate(usage):
+        m = re.match(r"\s*Function (\S+):", line)
+        if m and i + 1 < len(usage):
+            res[m.group(1)] = {k: int(v) for k, v in re.findall(r"(REG|STACK|SHARED|LOCAL):(\d+)", usage[i + 1])}
     demangle = subprocess.run(["c++filt"], input="\n".join(funcs), capture_output=True, text=True).stdout.splitlines()
     pretty = dict(zip(funcs, demangle))
     OUT.mkdir(parents=True, exist_ok=True)
@@ -76,7 +82,7 @@ def main() -> int:
                 fh.write(f"Function : {pretty.get(f, f)}\n  mangled : {f}\n  instructions : {n}\n")
                 fh.write("  census : " + ", ".join(f"{k}={v}" for k, v in sorted(census.items())) + "\n")
                 fh.write("\n".join(kept) + "\n\n")
-                index.append((fam, pretty.get(f, f)[:110], n, dict(census)))
+                index.append((fam, pretty.get(f, f)[:110], n, dict(census), res.get(f, {})))
     with open(OUT / "INDEX.md", "w") as fh:
         fh.write("# SASS census per kernel (sm_100a, `tools/dump_sass.py`)\n\n")
         fh.write("`multimem.ld_reduce` has its own opcode (`LDGMC...ADD`); `multimem.st` lowers to an ordinary "
@@ -84,11 +90,13 @@ def main() -> int:
                  "(`adamw_shard_bcast_kernel<true>`, `param_bcast_kernel<true>`) show no multimem opcode here.  "
                  "`UTC*MMA` = tcgen05.mma, `LDTM` = tcgen05.ld, `UTMALDG/UTMASTG/UTMAREDG` = TMA tensor load / store / "
                  "reduce, `UBLKCP` = cp.async.bulk, `LDL+STL` = local-memory (spill) instructions.\n\n")
-        fh.write("| family | instantiation | instrs | UTC*MMA | LDTM | UTMALDG | UTMASTG | UTMAREDG | UBLKCP | multimem (LDGMC/STGMC/REDGMC) | "
-                 "LDL+STL |\n|---|---|---|---|---|---|---|---|---|---|---|\n")
-        for fam, nm, n, c in index:
+        fh.write("`regs` / `stack B` / `static smem B` are from `cuobjdump -res-usage` (dynamic shared memory is set at launch).\n\n")
+        fh.write("| family | instantiation | instrs | regs | stack B | static smem B | UTC*MMA | LDTM | UTMALDG | UTMASTG | UTMAREDG | "
+                 "UBLKCP | multimem (LDGMC/STGMC/REDGMC) | LDL+STL |\n|---|---|---|---|---|---|---|---|---|---|---|---|---|---|\n")
+        for fam, nm, n, c, r in index:
             mma = sum(v for k, v in c.items() if k.startswith("UTC") and k.endswith("MMA"))
-            fh.write(f"| {fam} | `{nm}` | {n} | {mma} | {c.get('LDTM', 0)} | {c.get('UTMALDG', 0)} | "
+            fh.write(f"| {fam} | `{nm}` | {n} | {r.get('REG', '-')} | {r.get('STACK', '-')} | {r.get('SHARED', '-')} | "
+                     f"{mma} | {c.get('LDTM', 0)} | {c.get('UTMALDG', 0)} | "
                      f"{c.get('UTMASTG', 0)} | {c.get('UTMAREDG', 0)} | {c.get('UBLKCP', 0)} | "
                      f"{c.get('LDGMC', 0) + c.get('STGMC', 0) + c.get('REDGMC', 0) + c.get('MULTIMEM', 0)} | "
                      f"{c.get('LDL', 0) + c.get('STL', 0)} |\n")

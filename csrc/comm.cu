@@ -144,7 +144,7 @@ __global__ void __launch_bounds__(512)
       }
     }
   }
-  if (rank == 0) {  // scalar tail (n % 4) handled by rank 0
+  if (rank == 0) {  // scalar tail (n % 4): rank 0 alone sums and stores it with plain accesses while the others run ahead -- correct only because every rank waits in the closing barrier below before anyone reads the result
     for (long i = (nvec << 2) + long(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += long(gridDim.x) * blockDim.x) {
       float acc = 0.f;
       for (int p = 0; p < world; ++p) acc += bufs[p][offset + i];

@@ -135,13 +135,22 @@ class MicroBatchDataLoader(DataLoader):
         return out
 
     def state_dict(self) -> dict:
-        return {"epoch": self._epoch, "batches_served": self.batches_served}
+        """Position of the sample stream.  ``samples_consumed`` (over all data ranks) is layout-independent: a checkpoint
+        converted to another layout (``tools/convert_checkpoint.py``) resumes at the same place in the data."""
+        return {"epoch": self._epoch, "batches_served": self.batches_served, "micro_batch_size": self.micro_batch_size,
+                "data_world_size": self.data_world_size,
+                "samples_consumed": self.batches_served * self.micro_batch_size * self.data_world_size}
 
     def load_state_dict(self, state: dict) -> None:
         """Resume the sample stream where a checkpoint left it: same epoch (= same shuffle) and position, so a resumed run
         sees exactly the batches the uninterrupted run would have seen (the reference restarts the sampler on resume,
         SURVEY §5.4).  The skipped batches of the current epoch are drawn and discarded."""
         served = int(state.get("batches_served", 0))
+        same_layout = (state.get("micro_batch_size", self.micro_batch_size) == self.micro_batch_size
+                       and state.get("data_world_size", self.data_world_size) == self.data_world_size)
+        if not same_layout and "samples_consumed" in state:
+            # saved under another micro-batch size / number of data ranks: continue after the same number of samples
+            served = int(state["samples_consumed"]) // (self.micro_batch_size * self.data_world_size)
         per_epoch = max(1, len(self.sampler_) // self.micro_batch_size)
         self._epoch, skip = divmod(served, per_epoch)
         self.sampler_.set_epoch(self._epoch)

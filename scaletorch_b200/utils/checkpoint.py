@@ -261,16 +261,30 @@ class InitializationManager:
         return state
 
 
-def export_hf_state_dict(model: nn.Module, model_config: Any) -> dict[str, torch.Tensor]:
-    """Splits the fused parameters of an *unsharded* (tp = ep = 1) model back into HF tensor names."""
-    if pgm and (pgm.tp_world_size > 1 or pgm.ep_world_size > 1):
-        raise RuntimeError("export_hf_state_dict needs an unsharded model (tp = ep = 1)")
-    mgr = InitializationManager(model, model_config)
+def hf_state_from_unsharded(state: dict[str, torch.Tensor], model_config: Any) -> dict[str, torch.Tensor]:
+    """Splits the fused tensors of an unsharded (tp = pp = ep = 1) state dict of this framework into HF tensor names --
+    the inverse of :meth:`InitializationManager.assemble`.  Works on plain state dicts, so merged training checkpoints
+    (``utils/sharding.py::merge_shards``, ``tools/convert_checkpoint.py``) can be exported without building a model."""
+    from types import SimpleNamespace
+
+    mgr = InitializationManager.__new__(InitializationManager)
+    mgr.model, mgr.cfg = SimpleNamespace(), model_config
+    mgr.tp = mgr.ep = 1
+    mgr.tp_rank = mgr.ep_rank = 0
+    mgr.model_type = getattr(model_config, "model_type", "llama")
+    mgr.head_dim = getattr(model_config, "head_dim", None) or model_config.hidden_size // model_config.num_attention_heads
+    mgr.layer_ids = list(range(model_config.num_hidden_layers))
     out: dict[str, torch.Tensor] = {}
     hd = mgr.head_dim
     nq, nkv = model_config.num_attention_heads, model_config.num_key_value_heads
-    for name, p in model.named_parameters():
-        names = mgr.hf_names_for_local(name)
+    tied = getattr(model_config, "tie_word_embeddings", False)
+    for name, p in state.items():
+        if tied and name == "final_proj.weight":
+            continue
+        try:
+            names = mgr.hf_names_for_local(name)
+        except KeyError:
+            continue                                                          # buffers (RoPE tables) have no HF counterpart
         t = p.detach().cpu()
         if name.endswith(("qkv_proj.weight", "qkv_proj.bias")):
             parts = torch.split(t, [nq * hd, nkv * hd, nkv * hd], dim=0)
@@ -284,9 +298,17 @@ def export_hf_state_dict(model: nn.Module, model_config: Any) -> dict[str, torch
             parts = [t]
         for n, part in zip(names, parts):
             out[n] = part.contiguous()
-    if getattr(model_config, "tie_word_embeddings", False):
+    if tied:
         out.pop("lm_head.weight", None)
     return out
+
+
+def export_hf_state_dict(model: nn.Module, model_config: Any) -> dict[str, torch.Tensor]:
+    """Splits the fused parameters of an *unsharded* (tp = ep = 1) model back into HF tensor names."""
+    if pgm and (pgm.tp_world_size > 1 or pgm.ep_world_size > 1):
+        raise RuntimeError("export_hf_state_dict needs an unsharded model (tp = ep = 1); merge sharded checkpoints "
+                           "with tools/convert_checkpoint.py")
+    return hf_state_from_unsharded(dict(model.named_parameters()), model_config)
 
 
 # ------------------------------------------------------------------ training checkpoints

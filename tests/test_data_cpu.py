@@ -234,3 +234,20 @@ def test_pretrain_dataset_pads_and_masks():
     assert s["target_ids"].tolist()[2:] == [-100] * 5
     full = ds[1]
     assert full["loss_mask"].sum().item() == 7 and (full["target_ids"] != -100).all()
+
+
+def test_loader_position_carries_over_to_another_micro_batch_size():
+    ds = SyntheticTokens(97, 8, num_samples=64, seed=3)
+    a = MicroBatchDataLoader(4, 8, dataset=ds)
+    for _ in range(5):
+        next(a)
+    state = a.state_dict()
+    assert state["samples_consumed"] == 20 and state["micro_batch_size"] == 4 and state["data_world_size"] == 1
+    b = MicroBatchDataLoader(2, 8, dataset=ds)                  # resumed with half the micro-batch: 20 samples = 10 batches in
+    b.load_state_dict(state)
+    assert b.batches_served == 10
+    nxt = next(b)["input_ids"]
+    assert torch.equal(nxt[0], ds[20]["input_ids"][:8]) and torch.equal(nxt[1], ds[21]["input_ids"][:8])
+    c = MicroBatchDataLoader(4, 8, dataset=ds)                  # same layout: the batch counter is used as before
+    c.load_state_dict({"epoch": 0, "batches_served": 5})
+    assert torch.equal(next(c)["input_ids"][0], ds[20]["input_ids"][:8])

@@ -1,0 +1,112 @@
+"""Merge the per-(tp, pp, ep) training checkpoints of one step into ONE model and export it.
+
+    python tools/convert_checkpoint.py --ckpt_dir work_dir/300 --model Qwen3-8B --to hf --out export/qwen3-8b-step300
+    python tools/convert_checkpoint.py --ckpt_dir work_dir/300 --model Qwen3-8B --to unsharded --out work_dir/300_merged
+
+``CheckpointManager`` writes one ``weights_tp_rank_world_size=…_pp_rank_world_size=…[_ep_rank_world_size=…].pth`` per
+coordinate and resumes only under the same layout (as the reference does, ``scaletorch/utils/checkpoint.py:467-560``).
+This tool is the way out of a layout: it reads every shard of a step, undoes the tensor-parallel slicing, the pipeline
+stage numbering and the expert sharding (``utils/sharding.py::merge_shards``), and writes either
+
+* ``--to hf``: ``model.safetensors`` (+ ``config.json``) in the HuggingFace layout -- loadable by ``transformers``, by
+  this framework under ANY layout (``--load_pretrained_weights true``), and by serving stacks;
+* ``--to unsharded``: a training checkpoint for tp = pp = ep = 1 (model weights, step and token counters; optimiser
+  state is NOT converted -- it restarts, as after any fine-tuning hand-over; the position in the data stream IS carried
+  over, in samples, so the continued run does not see the same batches again).
+
+Pure CPU; needs no process group and no GPU.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import re
+import shutil
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+from scaletorch_b200.trainer.config import resolve_model_config  # noqa: E402
+from scaletorch_b200.utils.checkpoint import hf_state_from_unsharded  # noqa: E402
+from scaletorch_b200.utils.sharding import merge_shards  # noqa: E402
+
+_NAME = re.compile(r"weights_tp_rank_world_size=(\d+)_(\d+)_pp_rank_world_size=(\d+)_(\d+)(?:_ep_rank_world_size=(\d+)_(\d+))?\.pth$")
+
+
+def find_shards(ckpt_dir: str) -> tuple[dict[tuple[int, int, int], str], tuple[int, int, int]]:
+    """``{(tp_rank, pp_rank, ep_rank): path}`` and the layout ``(tp, pp, ep)`` found in ``ckpt_dir``."""
+    found: dict[tuple[int, int, int], str] = {}
+    layout = None
+    for f in sorted(os.listdir(ckpt_dir)):
+        m = _NAME.match(f)
+        if not m:
+            continue
+        tr, tp, pr, pp = (int(m.group(i)) for i in range(1, 5))
+        er, ep = (int(m.group(5)), int(m.group(6))) if m.group(5) is not None else (0, 1)
+        if layout is None:
+            layout = (tp, pp, ep)
+        elif layout != (tp, pp, ep):
+            raise ValueError(f"{ckpt_dir} mixes layouts {layout} and {(tp, pp, ep)}")
+        found[(tr, pr, er)] = os.path.join(ckpt_dir, f)
+    if layout is None:
+        raise FileNotFoundError(f"no weights_tp_rank_world_size=*.pth files in {ckpt_dir}")
+    return found, layout
+
+
+def merge_checkpoint(ckpt_dir: str, model_config) -> tuple[dict[str, torch.Tensor], dict]:
+    """Returns ``(unsharded model state dict, meta)``; ``meta`` carries the step / token counters and the source layout."""
+    paths, (tp, pp, ep) = find_shards(ckpt_dir)
+    states, meta = {}, {}
+    for coord, path in paths.items():
+        blob = torch.load(path, map_location="cpu", weights_only=False)
+        states[coord] = blob["model"]
+        meta = {"trained_steps": int(blob.get("trained_steps", 0)), "trained_tokens": int(blob.get("trained_tokens", 0))}
+        dl = (blob.get("extra") or {}).get("data_loader")
+        if dl:
+            meta["data_loader"] = dl                    # position of the sample stream (layout-independent form inside)
+    full = merge_shards(states, model_config, tp, pp, ep)
+    meta["source_layout"] = {"tp": tp, "pp": pp, "ep": ep}
+    return full, meta
+
+
+def main(argv=None) -> int:
+    ap = argparse.ArgumentParser(description=__doc__.split("\n\n")[0])
+    ap.add_argument("--ckpt_dir", required=True, help="directory of ONE step: work_dir/<step>")
+    ap.add_argument("--model", required=True, help="model name or directory (config.json), as given to --model_name_or_path")
+    ap.add_argument("--to", choices=["hf", "unsharded"], default="hf")
+    ap.add_argument("--out", required=True)
+    ap.add_argument("--dtype", default=None, choices=[None, "bfloat16", "float32", "float16"], help="cast weights on export")
+    a = ap.parse_args(argv)
+    cfg = resolve_model_config(a.model)
+    full, meta = merge_checkpoint(a.ckpt_dir, cfg)
+    if a.dtype:
+        dt = getattr(torch, a.dtype)
+        full = {k: (v.to(dt) if v.is_floating_point() else v) for k, v in full.items()}
+    os.makedirs(a.out, exist_ok=True)
+    n = sum(v.numel() for k, v in full.items() if not (k == "final_proj.weight" and getattr(cfg, "tie_word_embeddings", False)))
+    if a.to == "hf":
+        from safetensors.torch import save_file
+
+        sd = hf_state_from_unsharded(full, cfg)
+        save_file(sd, os.path.join(a.out, "model.safetensors"), metadata={"format": "pt", **{k: json.dumps(v) for k, v in meta.items()}})  # (strings only)
+        src_cfg = next((os.path.join(d, "config.json") for d in (a.model, os.path.join(os.path.dirname(os.path.dirname(
+            os.path.abspath(__file__))), "configs", a.model)) if os.path.isfile(os.path.join(d, "config.json"))), None)
+        if src_cfg:
+            shutil.copy(src_cfg, os.path.join(a.out, "config.json"))
+        print(f"wrote {len(sd)} tensors ({n / 1e6:.1f} M parameters) from layout {meta['source_layout']} to {a.out}/model.safetensors")
+    else:
+        payload = {"model": full, "optimizer": None, "trained_steps": meta["trained_steps"],
+                   "trained_tokens": meta["trained_tokens"], "rng": None, "layout": {"tp": 1, "pp": 1, "ep": 1},
+                   "extra": {"converted_from": meta["source_layout"],
+                             **({"data_loader": meta["data_loader"]} if "data_loader" in meta else {})}}
+        path = os.path.join(a.out, "weights_tp_rank_world_size=0_1_pp_rank_world_size=0_1.pth")
+        torch.save(payload, path)
+        print(f"wrote {path} ({n / 1e6:.1f} M parameters, step {meta['trained_steps']})")
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -284,3 +284,35 @@ class DecoderLM(nn.Module):
 
     def get_aux_loss(self) -> torch.Tensor | None:
         return None
+
+    @torch.no_grad()
+    def generate(self, input_ids: torch.Tensor, max_new_tokens: int, temperature: float = 0.0, top_k: int | None = None,
+                 eos_token_id: int | None = None, generator: torch.Generator | None = None) -> torch.Tensor:
+        """Autoregressive continuation of ``input_ids [B, S]`` (sanity checks, evaluation samples, parity tests against
+        ``transformers.generate``).  ``temperature == 0`` is greedy.  No KV cache: every step re-runs the prompt through
+        the training kernels, which is the point -- it exercises exactly the forward the trainer uses; the context is
+        clipped to ``max_position_embeddings``.  Unsharded or tensor-parallel models (every TP rank returns the same
+        tokens); not for pipeline stages."""
+        was_training = self.training
+        self.eval()
+        max_ctx = int(getattr(self.config, "max_position_embeddings", 1 << 30))
+        done = torch.zeros(input_ids.shape[0], dtype=torch.bool, device=input_ids.device)
+        out = input_ids
+        for _ in range(max_new_tokens):
+            logits = self(out[:, -max_ctx:])[:, -1, :].float()
+            if temperature and temperature > 0:
+                logits = logits / temperature
+                if top_k is not None:
+                    kth = torch.topk(logits, min(top_k, logits.shape[-1]))[0][:, -1:]
+                    logits = logits.masked_fill(logits < kth, float("-inf"))
+                nxt = torch.multinomial(torch.softmax(logits, dim=-1), 1, generator=generator)
+            else:
+                nxt = logits.argmax(dim=-1, keepdim=True)
+            if eos_token_id is not None:
+                nxt = torch.where(done.unsqueeze(1), torch.full_like(nxt, eos_token_id), nxt)
+                done |= nxt.squeeze(1) == eos_token_id
+            out = torch.cat([out, nxt], dim=1)
+            if eos_token_id is not None and bool(done.all()):
+                break
+        self.train(was_training)
+        return out

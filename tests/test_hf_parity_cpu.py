@@ -98,3 +98,27 @@ def test_gradients_agree_with_transformers(tmp_path):
     assert rel_err(g_ours[:nq], g_hf) < 1e-4
     g_norm = grad_of(dict(ours.named_parameters())["decoder_layers.0.attention.q_norm.weight"])
     assert rel_err(g_norm, dict(hf.named_parameters())["model.layers.0.self_attn.q_norm.weight"].grad) < 1e-4
+
+
+@pytest.mark.parametrize("name", ["tiny-qwen3", "tiny-qwen3-moe"])
+def test_greedy_generation_matches_transformers(tmp_path, name):
+    from safetensors.torch import save_file
+
+    d = tmp_path / name
+    shutil.copytree(os.path.join(ROOT, "configs", name), d)
+    ours, mc = _ours(d)
+    save_file(export_hf_state_dict(ours, mc), str(d / "model.safetensors"), metadata={"format": "pt"})
+    hf = _hf(d)
+    prompt = torch.randint(0, mc.vocab_size, (2, 7))
+    mine = ours.generate(prompt, max_new_tokens=12)
+    theirs = hf.generate(prompt, max_new_tokens=12, do_sample=False, use_cache=True, pad_token_id=0, eos_token_id=None)
+    assert mine.shape == (2, 19) and torch.equal(mine, theirs)
+    assert not ours.training                                   # eval() models stay in eval mode
+    # sampling: reproducible with a generator, stops at eos and pads with it
+    g = torch.Generator().manual_seed(5)
+    a = ours.generate(prompt, 6, temperature=0.8, top_k=20, generator=g)
+    g = torch.Generator().manual_seed(5)
+    assert torch.equal(a, ours.generate(prompt, 6, temperature=0.8, top_k=20, generator=g))
+    eos = int(mine[0, 7])                                      # the first greedy token of row 0 acts as EOS
+    stopped = ours.generate(prompt, 12, eos_token_id=eos)
+    assert (stopped[0, 7:] == eos).all()

@@ -34,9 +34,24 @@ def _worker(rank, world, port, fn, args):
         dist.destroy_process_group()
 
 
+_START_METHOD = os.environ.get("STB_TEST_START_METHOD", "forkserver")
+if _START_METHOD == "forkserver":
+    # Children are forked from a clean, single-threaded server process that has already imported the heavy modules, so
+    # a rank starts in milliseconds instead of re-importing torch + transformers (several seconds per rank, ~250 ranks
+    # per suite run).  The server is started lazily by the first test and lives as long as the pytest process.
+    import multiprocessing as _pymp
+
+    try:
+        _pymp.set_forkserver_preload(["torch", "torch.distributed", "numpy", "transformers", "scaletorch_b200",
+                                      "scaletorch_b200.trainer", "scaletorch_b200.models"])
+    except Exception:  # pragma: no cover - platform without forkserver
+        _START_METHOD = "spawn"
+
+
 def run_distributed(fn, world_size: int, *args) -> None:
     """Runs ``fn(rank, world_size, *args)`` on ``world_size`` CPU processes with a gloo process group."""
-    mp.spawn(_worker, args=(world_size, _free_port(), fn, args), nprocs=world_size, join=True)
+    mp.start_processes(_worker, args=(world_size, _free_port(), fn, args), nprocs=world_size, join=True,
+                       start_method=_START_METHOD)
 
 
 class TinyCfg:

@@ -6,8 +6,6 @@ import pickle
 import shutil
 import tempfile
 
-import torch
-
 from .object_ops import all_gather_object, broadcast_object_list
 from .utils import barrier, get_rank, get_world_size
 

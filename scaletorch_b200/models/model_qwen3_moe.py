@@ -19,7 +19,6 @@ from typing import Any
 
 import torch
 import torch.nn as nn
-import torch.nn.functional as F
 
 from .. import ops
 from ..ops.grouped import expert_counts, grouped_mlp
@@ -131,8 +130,6 @@ class MoELayer(nn.Module):
             out = self._forward_local(x, weights, idx)
         out = out.to(x.dtype)
         if ctx.sp:
-            from ..parallel.tensor_parallel import tp_comms
-
             # every TP rank holds the full, identical output: keep the local token shard
             out = _SplitKeepGrad.apply(out, ctx.tp_group)
         return out

@@ -1,6 +1,4 @@
 """Whole-step CUDA-graph replay must reproduce the eager training trajectory (same kernels, same order)."""
-import copy
-
 import pytest
 import torch
 

@@ -1,5 +1,4 @@
 """Config dataclasses, LR schedulers, metrics line, optimizer / flat store, data loader, monitor (CPU)."""
-import math
 import re
 
 import pytest

@@ -50,8 +50,16 @@ if _START_METHOD == "forkserver":
 
 def run_distributed(fn, world_size: int, *args) -> None:
     """Runs ``fn(rank, world_size, *args)`` on ``world_size`` CPU processes with a gloo process group."""
-    mp.start_processes(_worker, args=(world_size, _free_port(), fn, args), nprocs=world_size, join=True,
-                       start_method=_START_METHOD)
+    global _START_METHOD
+    try:
+        mp.start_processes(_worker, args=(world_size, _free_port(), fn, args), nprocs=world_size, join=True,
+                           start_method=_START_METHOD)
+    except (OSError, ValueError, ImportError):
+        if _START_METHOD == "spawn":
+            raise
+        _START_METHOD = "spawn"               # the fork server could not be started here: plain spawn from now on
+        mp.start_processes(_worker, args=(world_size, _free_port(), fn, args), nprocs=world_size, join=True,
+                           start_method="spawn")
 
 
 class TinyCfg:

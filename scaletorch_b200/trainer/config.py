@@ -58,7 +58,7 @@ class ParallelArguments:
     backend: str = field(default="nccl", metadata={"help": "Distributed backend: nccl | gloo"})
     sequence_parallel: bool = field(default=False, metadata={"help": "Megatron sequence parallelism over the TP group (also enabled by env SEQUENCE_PARALLEL=1)"})
     ep_capacity_factor: float | None = field(default=None, metadata={"help": "Receive capacity of the peer-memory EP path as a multiple of tokens*top_k. Default (None, and env SCALETORCH_B200_EP_CAPACITY unset) is dropless (= ep size); a smaller value bounds memory and DROPS the pairs that do not fit (counted in ep_dropped_pairs)"})
-    cp_zigzag: bool = field(default=True, metadata={"help": "Load-balanced (zig-zag) causal context parallelism: rank r owns chunks r and 2cp-1-r (needs S % 2cp == 0; falls back to the contiguous split otherwise)"})
+    cp_zigzag: bool = field(default=True, metadata={"help": "Load-balanced (zig-zag) causal context parallelism: rank r owns chunks r and 2cp-1-r (needs S divisible by 2cp; falls back to the contiguous split otherwise)"})
     ep_replicate_data: bool = field(default=False, metadata={"help": "Reference semantics: every EP rank of a dp_rank reads the same samples"})
     fused_comm: bool = field(default=True, metadata={"help": "Use the fused compute+collective kernels over NVLink peer memory when available"})
     grad_wire_dtype: str = field(default="float32", metadata={"help": "dtype of DP gradient buckets on the wire: float32 | bfloat16"})

@@ -228,3 +228,11 @@ def test_total_steps_falls_back_to_config_then_default():
         opt.step()
         sched.step()
     assert opt.param_groups[0]["lr"] == 0.0
+
+
+def test_help_renders():
+    """argparse %-expands help strings: a stray '%' in one of them breaks ``--help`` for every flag."""
+    from transformers import HfArgumentParser
+
+    text = HfArgumentParser(K.ScaleTorchArguments).format_help()
+    assert "--tensor_parallel_size" in text and "--cp_zigzag" in text

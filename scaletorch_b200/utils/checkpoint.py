@@ -315,7 +315,13 @@ def export_hf_state_dict(model: nn.Module, model_config: Any) -> dict[str, torch
 class CheckpointManager:
     """Per-(tp, pp, ep) ``torch.save`` checkpoints under ``work_dir/<step>/`` (reference ``checkpoint.py:467-560``)."""
 
-    def __init__(self) -> None:
+    def __init__(self, async_save: bool = False) -> None:
+        """``async_save``: the step returns as soon as the state has been copied to host memory; serialisation and the
+        atomic publish run on a background thread (one save in flight: the next save -- or :meth:`wait` -- joins it).
+        The reference writes synchronously from the training loop (``checkpoint.py:467-520``)."""
+        self.async_save = bool(async_save)
+        self._writer = None              # background thread of the save in flight
+        self._writer_error: BaseException | None = None
         self.tp_rank = pgm.tp_rank if pgm else 0
         self.tp_size = pgm.tp_world_size if pgm else 1
         self.pp_rank = pgm.pp_rank if pgm else 0
@@ -349,8 +355,10 @@ class CheckpointManager:
         path = os.path.join(out_dir, self._filename())
         raw = self._unwrap(model)
         payload = {
-            "model": {k: v.detach().cpu() for k, v in raw.state_dict().items()},
-            "optimizer": _to_cpu(opt_state if opt_state is not None else optimizer.state_dict()) if optimizer is not None else None,
+            # a host SNAPSHOT: with async_save the writer thread must not see later updates (CPU tensors are cloned)
+            "model": _to_cpu(dict(raw.state_dict()), copy=self.async_save),
+            "optimizer": (_to_cpu(opt_state if opt_state is not None else optimizer.state_dict(), copy=self.async_save)
+                          if optimizer is not None else None),
             "trained_steps": int(trained_steps),
             "trained_tokens": int(trained_tokens),
             "rng": {"torch": torch.get_rng_state(),
@@ -359,10 +367,36 @@ class CheckpointManager:
         }
         if extra:
             payload["extra"] = extra
-        tmp = path + ".tmp"
-        torch.save(payload, tmp)
-        os.replace(tmp, path)  # atomic publish: a crash never leaves a truncated checkpoint behind
+        self.wait()                                   # at most one save in flight (and surface an earlier failure)
+        if self.async_save:
+            import threading
+
+            self._writer = threading.Thread(target=self._write, args=(payload, path), name="stb-checkpoint-writer", daemon=False)
+            self._writer.start()
+        else:
+            self._write(payload, path)
+            self._raise_writer_error()
         return path
+
+    def _write(self, payload: dict, path: str) -> None:
+        try:
+            tmp = path + ".tmp"
+            torch.save(payload, tmp)
+            os.replace(tmp, path)  # atomic publish: a crash never leaves a truncated checkpoint behind
+        except BaseException as e:  # reported by the next save / wait(), never lost
+            self._writer_error = e
+
+    def _raise_writer_error(self) -> None:
+        if self._writer_error is not None:
+            e, self._writer_error = self._writer_error, None
+            raise RuntimeError(f"checkpoint write failed: {type(e).__name__}: {e}") from e
+
+    def wait(self) -> None:
+        """Blocks until the save in flight (if any) has been published; raises if it failed."""
+        if self._writer is not None:
+            self._writer.join()
+            self._writer = None
+        self._raise_writer_error()
 
     def load_checkpoint(self, model: nn.Module, optimizer, load_dir: str, restore_rng: bool = True) -> tuple[int, int]:
         path = os.path.join(load_dir, self._filename())
@@ -388,11 +422,13 @@ class CheckpointManager:
         return int(ckpt["trained_steps"]), int(ckpt["trained_tokens"])
 
 
-def _to_cpu(obj):
+def _to_cpu(obj, copy: bool = False):
+    """Tensors of a nested structure on the host; ``copy`` also clones tensors that already live there."""
     if isinstance(obj, torch.Tensor):
-        return obj.detach().cpu()
+        t = obj.detach()
+        return t.clone() if (copy and t.device.type == "cpu") else t.cpu()
     if isinstance(obj, dict):
-        return {k: _to_cpu(v) for k, v in obj.items()}
+        return {k: _to_cpu(v, copy) for k, v in obj.items()}
     if isinstance(obj, (list, tuple)):
-        return type(obj)(_to_cpu(v) for v in obj)
+        return type(obj)(_to_cpu(v, copy) for v in obj)
     return obj

@@ -356,3 +356,43 @@ def test_to_cpu_walks_containers():
     out = C._to_cpu(obj)
     assert isinstance(out["b"], list) and isinstance(out["b"][1], tuple) and out["b"][1][1] == 3 and out["c"] == "s"
     assert out["a"].device.type == "cpu" and not out["a"].requires_grad
+
+
+def test_async_save_snapshots_the_state_and_publishes_atomically(tmp_path):
+    torch.manual_seed(0)
+    m = nn.Linear(64, 64)
+    opt = torch.optim.AdamW(m.parameters(), lr=1e-2)
+    m(torch.randn(2, 64)).sum().backward()
+    opt.step()
+    want = {k: v.detach().clone() for k, v in m.state_dict().items()}
+    want_m = opt.state_dict()["state"][0]["exp_avg"].clone()
+    ck = C.CheckpointManager(async_save=True)
+    path = ck.save_checkpoint(m, opt, 3, 300, str(tmp_path / "3"))
+    with torch.no_grad():                                         # training goes on while the writer thread works
+        for p in m.parameters():
+            p.add_(100.0)
+    opt.state_dict()["state"][0]["exp_avg"].add_(100.0)
+    ck.wait()
+    assert os.path.isfile(path) and not os.path.exists(path + ".tmp")
+    blob = torch.load(path, weights_only=False)
+    for k in want:
+        assert torch.equal(blob["model"][k], want[k]), k              # the snapshot, not the later values
+    assert torch.equal(blob["optimizer"]["state"][0]["exp_avg"], want_m)
+    # a second save joins the first one; wait() is idempotent
+    ck.save_checkpoint(m, opt, 4, 400, str(tmp_path / "4"))
+    ck.wait()
+    ck.wait()
+    assert torch.load(os.path.join(tmp_path, "4", ck._filename()), weights_only=False)["trained_steps"] == 4
+
+
+def test_async_save_reports_write_errors(tmp_path, monkeypatch):
+    ck = C.CheckpointManager(async_save=True)
+
+    def boom(*a, **k):
+        raise OSError("disk full")
+
+    monkeypatch.setattr(torch, "save", boom)
+    ck.save_checkpoint(nn.Linear(2, 2), None, 1, 1, str(tmp_path / "1"))
+    with pytest.raises(RuntimeError, match="disk full"):
+        ck.wait()
+    ck.wait()                                                     # reported once

@@ -127,3 +127,17 @@ def test_checkpoint_resume_under_tensor_parallel(tmp_path):
     assert [s for s, _ in resumed] == [4, 5]
     for s, l in resumed:
         assert abs(l - straight[s]) < 2e-3, (s, l, straight[s])
+
+
+def test_async_checkpoint_cli(tmp_path):
+    """--async_checkpoint true: every checkpoint is published (no temporary file left) by the time the job exits, and a
+    run resumed from the last one continues."""
+    common = ["--model_name_or_path", "tiny-llama", "--work_dir", str(tmp_path), "--save_model_checkpoint", "true",
+              "--save_frequency", "2", "--async_checkpoint", "true", "--log_lag", "0", "--lr_scheduler_type", "step", "--step_size", "1000"]
+    out = _run(common + ["--total_train_steps", "4"])
+    assert len(_losses(out)) == 4
+    for step in ("2", "4"):
+        files = os.listdir(tmp_path / step)
+        assert any(f.startswith("weights_") and f.endswith(".pth") for f in files) and not any(f.endswith(".tmp") for f in files)
+    out2 = _run(common + ["--total_train_steps", "5", "--resume_path", str(tmp_path / "4")])
+    assert [s for s, _ in _losses(out2)] == [5]

@@ -141,7 +141,7 @@ def main(argv=None) -> None:
         if total_steps is None and config.max_tokens is not None and tokens_per_step > 0:
             total_steps = config.max_tokens // tokens_per_step
         lr_scheduler = create_lr_scheduler(optimizer, config, total_steps)
-        ckpt = CheckpointManager()
+        ckpt = CheckpointManager(async_save=getattr(config, "async_checkpoint", False))
         monitor = PerformanceMonitor(config=config, log_dir=config.work_dir)
         trained_tokens, step = 0, 0
         if config.resume_path:
@@ -229,6 +229,7 @@ def main(argv=None) -> None:
                 break
         while pending:
             flush_one()
+        ckpt.wait()                      # an asynchronous save in flight is published before the job reports success
         prof.close()
         watchdog.stop()
     except Exception:

@@ -3,4 +3,4 @@ capabilities of jianzhnie/ScaleTorch: ``ProcessGroupManager`` over the ``[DP, PP
 ``HfArgumentParser`` training dataclasses, Llama / Qwen3 / Qwen3-MoE, HF-compatible checkpoints --
 on hand-written tcgen05 / TMA kernels and fused compute+collective kernels over NVLink peer memory.
 """
-__version__ = "0.1.0"
+__version__ = "0.2.0"

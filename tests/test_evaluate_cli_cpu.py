@@ -78,3 +78,22 @@ def test_max_batches_and_synthetic_data(token_file, model_dir):
     assert r["batches"] == 3 and r["tokens"] == 3 * 4 * 64
     r = _eval(["--model_name_or_path", "tiny-llama", "--synthetic_data", "true", "--num_samples", "16", "--max_batches", "2"])
     assert r["tokens"] == 2 * 4 * 64
+
+
+def test_generate_cli_is_deterministic_and_layout_independent(model_dir):
+    """tools/generate.py: greedy continuation of the saved model, identical in one process and under TP2."""
+    def gen(extra, nproc=1):
+        base = [sys.executable]
+        if nproc > 1:
+            base += ["-m", "torch.distributed.run", "--standalone", "--local-addr", "127.0.0.1", "--nproc-per-node", str(nproc)]
+        cmd = base + [os.path.join(ROOT, "tools", "generate.py"), "--model_name_or_path", model_dir, "--load_pretrained_weights", "true",
+                      "--use_cpu", "true", "--dtype", "float32", "--prompt_ids", "5,17,42,7", "--max_new_tokens", "6"] + extra
+        p = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT,
+                           env=dict(os.environ, CUDA_VISIBLE_DEVICES="", OMP_NUM_THREADS="2"))
+        assert p.returncode == 0, p.stdout[-1500:] + p.stderr[-3000:]
+        return json.loads([l for l in p.stdout.splitlines() if l.startswith("{")][-1])
+
+    a = gen([])
+    assert a["prompt_ids"] == [5, 17, 42, 7] and len(a["new_ids"]) == 6
+    assert gen([]) == a
+    assert gen(["--tensor_parallel_size", "2"], nproc=2)["new_ids"] == a["new_ids"]

@@ -49,8 +49,10 @@ def ag_gemm_available(x_shard: torch.Tensor, group) -> bool:
 
 def gemm_rs_available(x_full: torch.Tensor, group) -> bool:
     """x_full ``[T, K]`` with ``T / world`` a multiple of 128."""
+    if not _ok(x_full, group):
+        return False
     w = _world(group)
-    return (_ok(x_full, group) and symm.has_kernel("stb_gemm_rs_bf16") and x_full.shape[0] % (128 * w) == 0 and w <= 8
+    return (symm.has_kernel("stb_gemm_rs_bf16") and x_full.shape[0] % (128 * w) == 0 and w <= 8
             and _policy("gemm_rs", w))
 
 

@@ -194,3 +194,30 @@ def test_graphed_step_support_matrix(monkeypatch):
     monkeypatch.delenv("SCALETORCH_B200_GRAPH_MP")
     monkeypatch.setattr(torch.cuda, "is_available", lambda: False)
     assert not G.GraphedTrainStep.supported(cfg, opt)
+
+
+def test_fused_tp_policy_and_cpu_predicates(monkeypatch):
+    """The measured policy: fused TP kernels from 4 ranks up, overridable; CPU tensors never take the fused path."""
+    from scaletorch_b200.parallel import fused as Fz
+
+    monkeypatch.delenv("SCALETORCH_B200_FUSED_TP", raising=False)
+    assert [Fz._policy("gemm_rs", w) for w in (1, 2, 3, 4, 8)] == [False, False, False, True, True]
+    monkeypatch.setenv("SCALETORCH_B200_FUSED_TP", "all")
+    assert Fz._policy("ag_gemm", 2)
+    monkeypatch.setenv("SCALETORCH_B200_FUSED_TP", "none")
+    assert not Fz._policy("gemm_ar", 8)
+    monkeypatch.setenv("SCALETORCH_B200_FUSED_TP", "auto")
+    assert not Fz._policy("gemm_ar", 2) and Fz._policy("gemm_ar", 4)
+    x = torch.zeros(256, 64, dtype=torch.bfloat16)
+    for pred in (Fz.ag_gemm_available, Fz.gemm_rs_available, Fz.allreduce_available):
+        assert not pred(x, None)                                  # not CUDA: the c10d path serves it
+    assert not Fz.gemm_ar_available(x, 128, None)
+
+
+def test_ep_default_capacity_is_dropless(monkeypatch):
+    from scaletorch_b200.parallel.expert_parallel import fused_ep
+
+    monkeypatch.delenv("SCALETORCH_B200_EP_CAPACITY", raising=False)
+    assert fused_ep.default_capacity_factor() is None              # None = dropless (worst-case regions)
+    monkeypatch.setenv("SCALETORCH_B200_EP_CAPACITY", "1.5")
+    assert fused_ep.default_capacity_factor() == 1.5

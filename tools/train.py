@@ -68,6 +68,39 @@ def report_dropped_pairs(model, step: int) -> None:
                    f"report; raise --ep_capacity_factor", is_print_rank=True)
 
 
+class StopOnSignal:
+    """Graceful preemption (``--save_on_signal true``): SIGTERM / SIGUSR1 only set a flag; every
+    ``--signal_check_interval`` steps the ranks take the maximum of their flags over a small gloo group (signals reach
+    ranks at different times, and all of them have to stop after the SAME step because the step is full of collectives);
+    when the maximum is set, the caller writes a checkpoint and leaves the loop.  The reference has no signal handling
+    (SURVEY §5.3)."""
+
+    def __init__(self, enabled: bool, interval: int, world_size: int):
+        self.enabled, self.interval = bool(enabled), max(1, int(interval))
+        self.requested = False
+        self.group = None
+        if not self.enabled:
+            return
+        import signal
+
+        for sig in (signal.SIGTERM, signal.SIGUSR1):
+            signal.signal(sig, self._on_signal)
+        if world_size > 1:
+            self.group = dist.new_group(backend="gloo")          # every rank; host-side, independent of the NCCL stream
+
+    def _on_signal(self, signum, frame) -> None:
+        self.requested = True
+
+    def should_stop(self, step: int) -> bool:
+        if not self.enabled or (self.group is not None and step % self.interval != 0):
+            return False
+        if self.group is None:
+            return self.requested
+        flag = torch.tensor([int(self.requested)], dtype=torch.int64)
+        dist.all_reduce(flag, op=dist.ReduceOp.MAX, group=self.group)
+        return bool(flag.item())
+
+
 def build_native_loader(config, model_config):
     """C++ micro-batch producer over a flat token array: a ``--token_file`` (int32 ``.npy`` or raw ``.bin``) or, with
     ``--synthetic_data``, random ids.  Same batch dict and ``global_batch_size`` attribute as ``MicroBatchDataLoader``."""
@@ -169,6 +202,7 @@ def main(argv=None) -> None:
         if config.use_cuda_graph and GraphedTrainStep.supported(config, optimizer, model):
             graphed = GraphedTrainStep(model, optimizer, config, device)
             rank_print("whole-step CUDA graph replay enabled", is_print_rank=log_rank)
+        stopper = StopOnSignal(getattr(config, "save_on_signal", False), getattr(config, "signal_check_interval", 10), world_size)
         monitor.start()
         max_steps = config.total_train_steps or float("inf")
         log_lag = max(0, int(getattr(config, "log_lag", 1)))
@@ -226,6 +260,15 @@ def main(argv=None) -> None:
                 if log_rank:
                     torch.save(lr_scheduler.state_dict(), out_dir / "scheduler.pt")
             if step >= max_steps:
+                break
+            if stopper.should_stop(step):
+                out_dir = Path(config.work_dir) / f"{step}"
+                if not (config.save_model_checkpoint and config.save_frequency > 0 and step % config.save_frequency == 0):
+                    ckpt.save_checkpoint(model, optimizer, step, trained_tokens, str(out_dir),
+                                         extra={"data_loader": data_loader.state_dict()})
+                    if log_rank:
+                        torch.save(lr_scheduler.state_dict(), out_dir / "scheduler.pt")
+                rank_print(f"stop requested by signal: checkpoint written at step {step}, exiting", is_print_rank=log_rank)
                 break
         while pending:
             flush_one()

@@ -23,8 +23,15 @@ def _start(args, nproc=1):
 
 def _wait_for_step(proc, n, timeout=300):
     """Reads the child's output until ``Step: n`` has been logged; returns what was read."""
+    import select
+
     buf, t0 = "", time.time()
     while time.time() - t0 < timeout:
+        ready, _, _ = select.select([proc.stdout], [], [], 1.0)   # never block for good on a silent child
+        if not ready:
+            if proc.poll() is not None:
+                break
+            continue
         line = proc.stdout.readline()
         if not line:
             if proc.poll() is not None:

@@ -18,11 +18,12 @@ def main():
     ap.add_argument("--batch_sizes", default="1,2,4,8")
     ap.add_argument("--seq_lens", default="2048,4096,8192")
     ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--cpu", action="store_true", help="host dry run of the sweep (fp32, wall clock)")
     a = ap.parse_args()
     rows = []
     for bs, sl, gc_ in itertools.product(map(int, a.batch_sizes.split(",")), map(int, a.seq_lens.split(",")), (False, True)):
         try:
-            ms, mem, tps = benchmark(a.model, bs, sl, a.steps, gradient_checkpointing=gc_)
+            ms, mem, tps = benchmark(a.model, bs, sl, a.steps, gradient_checkpointing=gc_, cpu=a.cpu)
             rows.append((bs, sl, gc_, ms, tps, mem))
         except torch.cuda.OutOfMemoryError:
             rows.append((bs, sl, gc_, None, None, None))

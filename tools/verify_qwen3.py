@@ -35,7 +35,7 @@ def verify(path: str, device: torch.device, dtype: torch.dtype) -> bool:
     store = getattr(model, "_stb_store", None)
     g = store.grad_flat if store is not None else torch.cat([p.grad.reshape(-1).float() for p in model.parameters() if p.grad is not None])
     gfin = bool(torch.isfinite(g).all()) and float(g.abs().sum()) > 0
-    print(f"  loss {float(loss):.4f}  gradients finite and non-zero: {gfin}")
+    print(f"  loss {float(loss.detach()):.4f}  gradients finite and non-zero: {gfin}")
     return ok and gfin
 
 

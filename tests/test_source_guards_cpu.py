@@ -70,3 +70,15 @@ def test_peer_reads_after_a_flag_acquire_are_coherent():
     assert "ld_peer_v4" in comm and "ld_nc_v4" not in comm
     fused = (ROOT / "csrc" / "common" / "gemm_fused.cuh").read_text()
     assert "ld_nc_v4" not in fused
+
+
+def test_every_environment_switch_is_documented():
+    """A switch read anywhere in the package, the kernels, the trainer or the bench must be explained in ``docs/``."""
+    read = set()
+    for p in [q for q in PY if "/tests/" not in str(q)] + NATIVE:
+        for m in re.finditer(r"(?:environ(?:\.get)?\s*[\[(]\s*|getenv\s*\(\s*)\"(SCALETORCH_B200_[A-Z0-9_]+)\"", p.read_text(errors="ignore")):
+            read.add(m.group(1))
+    assert len(read) >= 20, sorted(read)
+    docs = "\n".join(p.read_text() for p in (ROOT / "docs").glob("*.md"))
+    missing = sorted(v for v in read if v not in docs)
+    assert not missing, missing

@@ -41,6 +41,7 @@ def _nvcc() -> str:
 
 
 def sources() -> list[Path]:
+    """The ``.cu`` / ``.cpp`` files that make up ``libscaletorch_b200.so``."""
     return sorted(p for p in CSRC.rglob("*.cu")) + sorted(p for p in CSRC.rglob("*.cpp"))
 
 
@@ -74,6 +75,7 @@ def _compile_one(src: Path, verbose: bool) -> tuple[Path, str]:
 
 
 def build(force: bool = False, verbose: bool = False) -> Path:
+    """Compile (``nvcc … -gencode arch=compute_100a,code=sm_100a -lineinfo``) and link the library in-tree; objects are cached by content hash unless ``force``."""
     BUILD.mkdir(parents=True, exist_ok=True)
     LIB_DIR.mkdir(parents=True, exist_ok=True)
     if force:

@@ -72,6 +72,7 @@ _LONG_RET = {
 
 
 def lib_path() -> Path:
+    """Where the in-tree library is expected (``scaletorch_b200/lib/libscaletorch_b200.so``)."""
     return _LIB_PATH
 
 
@@ -139,10 +140,12 @@ def use_native(t: torch.Tensor) -> bool:
 
 
 def stream_ptr() -> int:
+    """The current CUDA stream as an integer handle for the C ABI."""
     return torch.cuda.current_stream().cuda_stream
 
 
 def ptr(t: torch.Tensor | None) -> int | None:
+    """``data_ptr()`` of a tensor for the C ABI (``None`` stays ``None`` = null pointer)."""
     return None if t is None else t.data_ptr()
 
 
@@ -159,5 +162,6 @@ def call(name: str, *args) -> None:
 
 
 def call_long(name: str, *args) -> int:
+    """Call an entry point and return its integer result instead of treating it as a status code."""
     lib = load(required=True)
     return int(getattr(lib, name)(*args))

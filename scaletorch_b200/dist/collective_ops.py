@@ -81,6 +81,7 @@ def all_reduce(data: Tensor, op: str = "sum", group: ProcessGroup | None = None,
 
 
 def all_gather(data: Tensor, group: ProcessGroup | None = None) -> list[Tensor]:
+    """Every rank receives the list of all ranks' ``data`` (equal shapes), in rank order, on the input's device."""
     world = get_world_size(group)
     if world <= 1:
         return [data]
@@ -94,6 +95,7 @@ def all_gather(data: Tensor, group: ProcessGroup | None = None) -> list[Tensor]:
 
 
 def gather(data: Tensor, dst: int = 0, group: ProcessGroup | None = None) -> list[Tensor | None]:
+    """Rank ``dst`` (group-local) receives the list of all ranks' ``data``; the others get ``[]``.  NCCL has no gather, so it is an all-gather there."""
     world = get_world_size(group)
     if world <= 1:
         return [data]
@@ -111,6 +113,7 @@ def gather(data: Tensor, dst: int = 0, group: ProcessGroup | None = None) -> lis
 
 
 def broadcast(data: Tensor, src: int = 0, group: ProcessGroup | None = None) -> None:
+    """Overwrite ``data`` on every rank with the value held by group-local rank ``src`` (in place)."""
     if get_world_size(group) <= 1:
         return
     group = _group(group)
@@ -124,6 +127,7 @@ def broadcast(data: Tensor, src: int = 0, group: ProcessGroup | None = None) -> 
 
 def scatter(tensor_out: Tensor, scatter_list: list[Tensor] | None = None, src: int = 0,
             group: ProcessGroup | None = None) -> None:
+    """Group-local rank ``src`` sends ``scatter_list[i]`` to rank ``i``; every rank receives into ``tensor_out``."""
     world = get_world_size(group)
     if world <= 1:
         if scatter_list:
@@ -150,6 +154,7 @@ def scatter(tensor_out: Tensor, scatter_list: list[Tensor] | None = None, src: i
 
 
 def reduce(data: Tensor, dst: int = 0, op: str = "sum", group: ProcessGroup | None = None) -> None:
+    """Reduce ``data`` over the group into rank ``dst`` (in place there; other ranks' buffers are unspecified).  ``op`` = sum / mean / max / min / product."""
     world = get_world_size(group)
     if world <= 1:
         return
@@ -169,6 +174,7 @@ def reduce(data: Tensor, dst: int = 0, op: str = "sum", group: ProcessGroup | No
 
 def reduce_scatter(tensor_out: Tensor, input_list: list[Tensor] | None = None, op: str = "sum",
                    group: ProcessGroup | None = None) -> None:
+    """Rank ``i`` receives the reduction over ranks of ``input_list[i]`` in ``tensor_out`` (all-reduce + slice on gloo)."""
     world = get_world_size(group)
     if world <= 1:
         if input_list:
@@ -194,6 +200,7 @@ def reduce_scatter(tensor_out: Tensor, input_list: list[Tensor] | None = None, o
 
 def all_to_all(output_tensor_list: list[Tensor], input_tensor_list: list[Tensor],
                group: ProcessGroup | None = None) -> list[Tensor]:
+    """Rank ``r`` sends ``input_tensor_list[p]`` to peer ``p`` and receives ``output_tensor_list[p]`` from it (p2p emulation on gloo)."""
     world = get_world_size(group)
     if world <= 1:
         for o, i in zip(output_tensor_list, input_tensor_list):
@@ -270,6 +277,7 @@ def _all_reduce_coalesced(tensors: list[Tensor], bucket_size_mb: int = -1, op: s
 
 def all_reduce_params(params: list | GeneratorType, coalesce: bool = True, bucket_size_mb: int = -1,
                       op: str = "sum", group: ProcessGroup | None = None) -> None:
+    """All-reduce a collection of parameters in place, optionally coalesced into flat buckets of ``bucket_size_mb``."""
     if get_world_size(group) <= 1:
         return
     tensors = [p.data for p in params]

@@ -11,6 +11,7 @@ from .utils import barrier, get_rank, get_world_size
 
 
 def collect_results(results: list, size: int, device: str = "cpu", tmpdir: str | None = None) -> list | None:
+    """Gather per-rank partial result lists on rank 0, interleaved back into dataset order and cut to ``size``; via a shared directory (``cpu``) or object collectives (``gpu``)."""
     if device not in ("cpu", "gpu", "cuda"):
         raise NotImplementedError(f"device must be 'cpu' or 'gpu', but got {device}")
     if device == "cpu":
@@ -28,6 +29,7 @@ def _interleave(parts: list[list], size: int) -> list:
 
 
 def collect_results_cpu(result_part: list, size: int, tmpdir: str | None = None) -> list | None:
+    """``collect_results`` through pickle files in a directory every rank can see (created and broadcast by rank 0 when not given)."""
     rank, world = get_rank(), get_world_size()
     if world == 1:
         return result_part[:size]
@@ -54,6 +56,7 @@ def collect_results_cpu(result_part: list, size: int, tmpdir: str | None = None)
 
 
 def collect_results_gpu(result_part: list, size: int) -> list | None:
+    """``collect_results`` through ``all_gather_object``; returns the ordered list on rank 0 and ``None`` elsewhere."""
     rank, world = get_rank(), get_world_size()
     if world == 1:
         return result_part[:size]

@@ -50,6 +50,7 @@ def broadcast_object_list(data: list[Any], src: int = 0, group=None) -> None:
 
 
 def all_gather_object(data: Any, group=None) -> list[Any]:
+    """Every rank receives the list of all ranks' picklable ``data`` (sizes may differ per rank)."""
     world = get_world_size(group)
     if world <= 1:
         return [data]
@@ -67,6 +68,7 @@ def all_gather_object(data: Any, group=None) -> list[Any]:
 
 
 def gather_object(data: Any, dst: int = 0, group=None) -> list[Any] | None:
+    """Group-local rank ``dst`` receives the list of all ranks' picklable ``data``; the others get ``None``."""
     world = get_world_size(group)
     if world <= 1:
         return [data]

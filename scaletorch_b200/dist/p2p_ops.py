@@ -6,10 +6,12 @@ from torch import Tensor
 
 
 def isend(tensor: Tensor, dst: int, group=None, tag: int = 0):
+    """Non-blocking send of ``tensor`` to GLOBAL rank ``dst``; returns the work handle."""
     return torch_dist.isend(tensor, dst, group=group, tag=tag)
 
 
 def irecv(tensor: Tensor, src: int, group=None, tag: int = 0):
+    """Non-blocking receive into ``tensor`` from GLOBAL rank ``src``; returns the work handle."""
     return torch_dist.irecv(tensor, src, group=group, tag=tag)
 
 
@@ -23,6 +25,7 @@ def P2POp(op, tensor: Tensor, peer: int, group=None, tag: int = 0):
 
 
 def batch_isend_irecv(p2p_ops: list) -> list:
+    """Launch a list of ``P2POp`` as one batch (one NCCL group call) and return their work handles."""
     if not p2p_ops:
         return []
     return torch_dist.batch_isend_irecv(p2p_ops)

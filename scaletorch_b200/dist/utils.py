@@ -22,10 +22,12 @@ _LOCAL_PROCESS_GROUP: ProcessGroup | None = None
 
 
 def is_distributed() -> bool:
+    """True once ``torch.distributed`` is available and the default process group has been initialised."""
     return torch_dist.is_available() and torch_dist.is_initialized()
 
 
 def get_local_group() -> ProcessGroup | None:
+    """The process group of the ranks on this node (``init_local_group``); ``None`` outside a distributed run."""
     if not is_distributed():
         return None
     if _LOCAL_PROCESS_GROUP is None:
@@ -34,24 +36,29 @@ def get_local_group() -> ProcessGroup | None:
 
 
 def get_default_group() -> ProcessGroup | None:
+    """The world process group, or ``None`` outside a distributed run."""
     return torch_dist.distributed_c10d._get_default_group() if is_distributed() else None
 
 
 def cleanup_dist() -> None:
+    """Destroy the default process group if there is one (safe to call twice)."""
     if is_distributed():
         torch_dist.destroy_process_group()
 
 
 def new_group(ranks, **kwargs):
+    """``torch.distributed.new_group`` (collective over the world); ``None`` outside a distributed run."""
     return torch_dist.new_group(ranks=ranks, **kwargs) if is_distributed() else None
 
 
 def destroy_group(group) -> None:
+    """Destroy one sub-group; a no-op for ``None`` or outside a distributed run."""
     if is_distributed() and group is not None:
         torch_dist.destroy_process_group(group)
 
 
 def infer_launcher() -> str:
+    """Guess the launcher from the environment: ``pytorch`` (torchrun), ``slurm``, ``mpi`` or ``none``."""
     if "WORLD_SIZE" in os.environ:
         return "pytorch"
     if "SLURM_NTASKS" in os.environ:
@@ -135,30 +142,35 @@ def init_local_group(node_rank: int, num_gpus_per_node: int) -> None:
 
 
 def get_backend(group: ProcessGroup | None = None) -> str | None:
+    """Backend name of ``group`` (default: world), ``None`` outside a distributed run."""
     if not is_distributed():
         return None
     return torch_dist.get_backend(group or get_default_group())
 
 
 def get_world_size(group: ProcessGroup | None = None) -> int:
+    """Number of ranks in ``group`` (default: world); 1 outside a distributed run."""
     if not is_distributed():
         return 1
     return torch_dist.get_world_size(group or get_default_group())
 
 
 def get_rank(group: ProcessGroup | None = None) -> int:
+    """Rank of this process inside ``group`` (default: world); 0 outside a distributed run."""
     if not is_distributed():
         return 0
     return torch_dist.get_rank(group or get_default_group())
 
 
 def get_local_size() -> int:
+    """Number of ranks on this node; 1 outside a distributed run."""
     if not is_distributed():
         return 1
     return torch_dist.get_world_size(get_local_group())
 
 
 def get_local_rank() -> int:
+    """Rank of this process on its node (falls back to ``LOCAL_RANK`` when no local group was created)."""
     if not is_distributed():
         return 0
     if _LOCAL_PROCESS_GROUP is None:
@@ -167,14 +179,17 @@ def get_local_rank() -> int:
 
 
 def get_dist_info(group: ProcessGroup | None = None) -> tuple[int, int]:
+    """``(rank, world_size)`` of ``group``."""
     return get_rank(group), get_world_size(group)
 
 
 def is_main_process(group: ProcessGroup | None = None) -> bool:
+    """True on rank 0 of ``group``."""
     return get_rank(group) == 0
 
 
 def master_only(func: Callable) -> Callable:
+    """Decorator: run the function on rank 0 only, return ``None`` elsewhere."""
     @functools.wraps(func)
     def wrapper(*args, **kwargs):
         if is_main_process():
@@ -185,6 +200,7 @@ def master_only(func: Callable) -> Callable:
 
 
 def barrier(group: ProcessGroup | None = None) -> None:
+    """Block until every rank of ``group`` arrives; a no-op outside a distributed run."""
     if is_distributed():
         torch_dist.barrier(group or get_default_group())
 

@@ -28,10 +28,12 @@ DEFAULT_PARALLELISM_DISABLED = "0"
 
 
 def env_flag(name: str, default: str = "0") -> bool:
+    """True when environment variable ``name`` (default ``default``) is ``1``."""
     return os.environ.get(name, default) == "1"
 
 
 def env_int(name: str, default: int) -> int:
+    """Integer value of environment variable ``name``, ``default`` when unset."""
     try:
         return int(os.environ.get(name, default))
     except ValueError:

@@ -27,6 +27,7 @@ _AXES = ("dp", "pp", "cp", "ep", "tp")
 
 
 class ProcessGroupManager:
+    """The ``[DP, PP, CP, EP, TP]`` rank grid (TP fastest): this rank's coordinates, one process group per axis plus the CP x DP, PP x DP, gradient-sync and model-parallel groups, ring / pipeline neighbours, data rank for the loader."""
     def __init__(self, tp_size: int, cp_size: int, pp_size: int, dp_size: int, ep_size: int = 1,
                  ep_replicate_data: bool = False) -> None:
         if not is_distributed():
@@ -210,10 +211,12 @@ process_group_manager = ProcessGroupManagerProxy()
 
 def setup_process_group_manager(tp_size: int, cp_size: int, pp_size: int, dp_size: int, ep_size: int = 1,
                                 ep_replicate_data: bool = False) -> ProcessGroupManager:
+    """Create the manager (collective: every rank must call it with the same sizes) and install it behind the global ``process_group_manager`` proxy."""
     inst = ProcessGroupManager(tp_size, cp_size, pp_size, dp_size, ep_size, ep_replicate_data)
     process_group_manager._instance = inst
     return inst
 
 
 def get_process_group_manager() -> ProcessGroupManager | None:
+    """The installed manager, or ``None`` before ``setup_process_group_manager`` / in a single-process run."""
     return object.__getattribute__(process_group_manager, "_instance")

@@ -26,6 +26,7 @@ ALIGN = 128  # elements; keeps every parameter 256-byte aligned in bf16 (TMA / v
 
 @dataclass
 class ParamSlot:
+    """Where one parameter lives in the flat buffers: name, offset and length in elements, and its reduction segment."""
     name: str
     param: nn.Parameter
     offset: int
@@ -34,10 +35,12 @@ class ParamSlot:
 
 
 def is_expert_param(name: str) -> bool:
+    """True for parameters of MoE experts (reduced over DP x CP only, not over EP)."""
     return ".experts." in name
 
 
 class FlatParamStore:
+    """Re-homes every trainable parameter of a module as a view into one flat buffer (training dtype) and gives each a ``main_grad`` view into one flat fp32 gradient buffer; dense parameters first, expert parameters second."""
     def __init__(self, module: nn.Module, grad_dtype: torch.dtype = torch.float32, grad_alloc=None, param_alloc=None):
         """``grad_alloc(numel) -> fp32 tensor`` lets the caller place the gradient buffer in symmetric memory
         (data-parallel buckets are then reduced in place over NVLink); ``param_alloc(numel, dtype)`` does the same

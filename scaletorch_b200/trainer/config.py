@@ -18,6 +18,7 @@ _VALID_OPTIMIZERS = {"adamw", "adam", "sgd", "lamb"}
 
 @dataclass
 class DataArguments:
+    """Dataset and loader flags: dataset name or path, tokenizer, subset, split, worker counts, sample cap, pinned memory, synthetic data."""
     data_path: str = field(default="./data", metadata={"help": "Dataset download directory"})
     dataset_name: str = field(default="wikitext2", metadata={"help": "Dataset name or local directory"})
     tokenizer_name_or_path: str = field(default="facebook/opt-125m", metadata={"help": "Tokenizer name or path"})
@@ -32,6 +33,7 @@ class DataArguments:
 
 @dataclass
 class ModelArguments:
+    """Which model to build (name or path of an HF config / checkpoint), optional overrides of layer / head counts, attention switch, dtype."""
     model_name_or_path: str = field(default="facebook/opt-125m", metadata={"help": "Model name, local HF directory or a name under configs/"})
     num_hidden_layers: int | None = field(default=None, metadata={"help": "Override the number of hidden layers"})
     num_attention_heads: int | None = field(default=None, metadata={"help": "Override the number of attention heads"})
@@ -49,6 +51,7 @@ class ModelArguments:
 
 @dataclass
 class ParallelArguments:
+    """Sizes of the five parallel axes, the pipeline schedule, the backend, and the switches of the parallel implementations (sequence parallel, zig-zag CP, EP capacity and data replication, fused collectives, gradient wire dtype)."""
     tensor_parallel_size: int = field(default=1, metadata={"help": "Size of tensor parallelism"})
     pipeline_parallel_size: int = field(default=1, metadata={"help": "Size of pipeline parallelism"})
     data_parallel_size: int = field(default=1, metadata={"help": "Size of data parallelism"})
@@ -80,6 +83,7 @@ class ParallelArguments:
 
 @dataclass
 class LrSchedulerArguments:
+    """Learning-rate schedule: type, warm-up steps and the parameters of each decay family; validated in ``__post_init__``."""
     lr_scheduler_type: str = field(default="linear", metadata={"help": "Type of learning rate scheduler"})
     warmup_steps: int = field(default=0, metadata={"help": "Number of warmup steps"})
     T_max: int | None = field(default=None, metadata={"help": "Maximum number of iterations for cosine annealing"})
@@ -114,6 +118,7 @@ class LrSchedulerArguments:
 
 @dataclass
 class OptimizerArguments:
+    """Optimiser type, learning rate, betas, weight decay, fused-kernel switch."""
     optimizer_type: str = field(default="adamw", metadata={"help": "Type of optimizer"})
     weight_decay: float = field(default=0.0, metadata={"help": "Weight decay"})
     use_fused_adam: bool = field(default=True, metadata={"help": "Use the fused AdamW kernel over the flat parameter store"})
@@ -130,6 +135,7 @@ class OptimizerArguments:
 
 @dataclass
 class TrainingArguments:
+    """Batch geometry (micro-batch, sequence length, accumulation), stop criteria, seed, clipping, gradient checkpointing, ZeRO stage, native loader, CUDA-graph capture, lagged logging, CPU run, MoE aux loss."""
     batch_size: int = field(default=64, metadata={"help": "Training batch size"})
     test_batch_size: int = field(default=1000, metadata={"help": "Evaluation batch size"})
     micro_batch_size: int | None = field(default=None, metadata={"help": "Micro batch size"})
@@ -161,6 +167,7 @@ class TrainingArguments:
 
 @dataclass
 class CheckpointArguments:
+    """Where and how often to save, what to resume from, whether to load pretrained weights, background writing and save-on-signal."""
     work_dir: str = field(default="./work_dir", metadata={"help": "Directory to save checkpoints"})
     save_model_checkpoint: bool = field(default=True, metadata={"help": "Whether to save model checkpoints"})
     save_frequency: int = field(default=300, metadata={"help": "Checkpoint frequency in steps (0 = never)"})
@@ -177,6 +184,7 @@ class CheckpointArguments:
 
 @dataclass
 class LoggingArguments:
+    """wandb switches and names, the profiler window and trace directory, NVTX ranges, the step watchdog timeout."""
     use_wandb: bool = field(default=False, metadata={"help": "Log to Weights & Biases"})
     project_name: str = field(default="scaletorch", metadata={"help": "Project name for logging"})
     experiment_name: str | None = field(default=None, metadata={"help": "Experiment name for logging"})
@@ -222,6 +230,7 @@ class ScaleTorchArguments(DataArguments, ModelArguments, ParallelArguments, LrSc
 
 
 def validate_config(config: ScaleTorchArguments, world_size: int) -> None:
+    """Check that the parallel sizes multiply to ``world_size`` (raises ``ValueError`` otherwise)."""
     config.validate_world_size(world_size)
 
 
@@ -247,6 +256,7 @@ def resolve_model_config(name_or_path: str, quiet: bool = False):
 
 
 def main() -> None:  # pragma: no cover - CLI helper
+    """Parse the command line into ``ScaleTorchArguments`` and print the result (``python -m scaletorch_b200.trainer.config --help`` lists every flag)."""
     from transformers import HfArgumentParser
 
     (cfg,) = HfArgumentParser(ScaleTorchArguments).parse_args_into_dataclasses()

@@ -67,6 +67,7 @@ def initialize_distributed_training(config) -> tuple[int, int, int, torch.device
 
 
 def cleanup_distributed() -> None:
+    """Tear down in the order CUDA graphs require: release captured steps, destroy the parallel groups, then the default process group."""
     from .graphed import release_all
 
     release_all()                                   # captured steps first: see graphed.release_all

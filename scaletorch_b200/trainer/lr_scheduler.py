@@ -25,6 +25,7 @@ def register_scheduler(name: str, factory: Callable | None = None):
 
 
 def registered_schedulers() -> list[str]:
+    """Names accepted by ``--lr_scheduler_type`` (built-ins plus ``register_scheduler`` plug-ins)."""
     return sorted(_REGISTRY)
 
 
@@ -80,6 +81,7 @@ def _onecycle(optimizer, config, total_steps):
 
 
 def create_lr_scheduler(optimizer: Optimizer, config, total_steps: int | None = None) -> LRScheduler:
+    """Build the scheduler named by ``config.lr_scheduler_type`` for ``total_steps`` (default: ``config.total_train_steps``)."""
     total = total_steps or getattr(config, "total_train_steps", None) or 10_000
     name = config.lr_scheduler_type
     if name not in _REGISTRY:

@@ -13,6 +13,7 @@ from ..utils.misc import get_mfu, to_readable_format
 
 
 def is_logging_rank() -> bool:
+    """True on the one rank that prints the metrics line: tp = dp = cp = ep = 0 on the last pipeline stage (any rank when not distributed)."""
     if not pgm:
         return True
     return pgm.tp_rank == 0 and pgm.dp_rank == 0 and pgm.cp_rank == 0 and pgm.ep_rank == 0 and pgm.pp_is_last_stage
@@ -21,6 +22,7 @@ def is_logging_rank() -> bool:
 def format_metrics_line(step: int, loss: float, lr: float, grad_norm: float | None, global_batch_size: int,
                         tokens_per_second: float, tokens_per_second_per_gpu: float, trained_tokens: int,
                         max_tokens: int | None, mfu: float, memory_gb: float) -> str:
+    """The console line ``Step | Loss | LR | GradNorm | Global batch size | Tokens/s | Tokens/s/GPU | Tokens | MFU | Memory`` in the exact format the benchmark scripts parse."""
     parts = [
         f"Step: {step:<5d}",
         f"Loss: {loss:6.4f}",
@@ -39,6 +41,7 @@ def format_metrics_line(step: int, loss: float, lr: float, grad_norm: float | No
 def log_training_metrics(config: Any, model_config: Any, step: int, loss: float, lr: float, grad_norm: float | None,
                          step_duration: float, tokens_per_step: int, trained_tokens: int, num_params: int,
                          world_size: int, logger=None, wandb_run=None) -> dict[str, Any]:
+    """Compute throughput / MFU / memory for one step, print the metrics line on the logging rank, forward the dict to wandb when given, and return it."""
     tps = tokens_per_step / step_duration if step_duration > 0 else 0.0
     tps_gpu = tps / max(world_size, 1)
     mfu = get_mfu(tps_gpu, num_params, model_config, seq_len=config.sequence_length)

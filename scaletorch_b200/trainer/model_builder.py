@@ -28,6 +28,7 @@ MODEL_CLASSES = {"llama": Llama, "qwen3": Qwen3, "qwen3_moe": Qwen3MoE}
 
 
 def model_class_for(model_config):
+    """Model class for an HF config by its ``model_type`` (``llama``, ``qwen3``, ``qwen3_moe``; unknown types fall back to Llama)."""
     return MODEL_CLASSES.get(getattr(model_config, "model_type", "llama"), Llama)
 
 
@@ -120,6 +121,7 @@ def sync_replicated_parameters(model: torch.nn.Module) -> int:
 
 
 def unwrap(model):
+    """Strip ``.module`` wrappers (data parallel, pipeline stage) down to the bare model."""
     while hasattr(model, "module") and isinstance(model.module, torch.nn.Module):
         model = model.module
     return model

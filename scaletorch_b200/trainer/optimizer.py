@@ -24,6 +24,7 @@ def _small_all_reduce(t: torch.Tensor, group) -> None:
 
 
 class FusedAdamW(torch.optim.Optimizer):
+    """AdamW over a ``FlatParamStore``: sum-of-squares kernel, exact global-norm clip coefficient computed on the device (reduced over ``norm_group``, replicated parameters counted once), one update kernel over the flat buffers; LR and bias corrections live in device memory so the step replays from a CUDA graph."""
     def __init__(self, store: FlatParamStore, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8,
                  weight_decay: float = 0.01, max_grad_norm: float | None = None, norm_group=None,
                  norm_scale_tp_replicated: bool = True, _alloc_state: bool = True):

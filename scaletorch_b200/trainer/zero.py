@@ -44,6 +44,7 @@ class _Shard:
 
 
 class ZeroFusedAdamW(FusedAdamW):
+    """ZeRO-1 on c10d collectives: every rank updates its contiguous slice of the dense (and expert) segment and broadcasts the updated parameters; the CPU / gloo counterpart of ``PeerShardedAdamW``."""
     def __init__(self, store: FlatParamStore, dense_group=None, expert_group=None, **kw):
         super().__init__(store, _alloc_state=False, **kw)
         self.shards = [_Shard(0, store.dense_numel, dense_group, store.device)]

@@ -30,18 +30,22 @@ _CUDA_FALLBACK_FLOPS = 312e12
 
 @functools.lru_cache(maxsize=None)
 def get_device_type() -> str:
+    """``cuda`` when a GPU is visible, else ``cpu`` (cached; the reference's seven-way probe is reduced to the two targets built here)."""
     return "cuda" if torch.cuda.is_available() else "cpu"
 
 
 def is_accelerator_available() -> bool:
+    """True when a CUDA device is visible."""
     return get_device_type() == "cuda"
 
 
 def get_dist_backend() -> str:
+    """``nccl`` on CUDA, ``gloo`` on CPU."""
     return "nccl" if get_device_type() == "cuda" else "gloo"
 
 
 def get_visible_devices_keyword() -> str:
+    """Name of the environment variable that restricts visible devices (``CUDA_VISIBLE_DEVICES``)."""
     return "CUDA_VISIBLE_DEVICES"
 
 
@@ -51,12 +55,14 @@ def get_dist_info() -> tuple[int, int, int]:
 
 
 def get_current_device(use_cpu: bool = False) -> torch.device:
+    """This rank's device: ``cuda:<LOCAL_RANK mod device_count>``, or ``cpu`` when ``use_cpu`` or no GPU is visible."""
     if use_cpu or get_device_type() == "cpu":
         return torch.device("cpu")
     return torch.device("cuda", int(os.environ.get(ENV_LOCAL_RANK, 0)) % max(torch.cuda.device_count(), 1))
 
 
 def set_device(device: torch.device | int) -> None:
+    """Make ``device`` (a ``torch.device`` or a CUDA index) current; a no-op for CPU."""
     if isinstance(device, int):
         device = torch.device("cuda", device) if get_device_type() == "cuda" else torch.device("cpu")
     if device.type == "cuda":
@@ -64,43 +70,52 @@ def set_device(device: torch.device | int) -> None:
 
 
 def get_device_count() -> int:
+    """Number of visible CUDA devices (0 on a CPU-only machine)."""
     return torch.cuda.device_count() if get_device_type() == "cuda" else 0
 
 
 def synchronize() -> None:
+    """Wait for all queued work on the current CUDA device; a no-op on CPU."""
     if get_device_type() == "cuda":
         torch.cuda.synchronize()
 
 
 def empty_cache() -> None:
+    """Release the caching allocator's unused blocks; a no-op on CPU."""
     if get_device_type() == "cuda":
         torch.cuda.empty_cache()
 
 
 def memory_reserved() -> int:
+    """Bytes reserved by the caching allocator on the current device (0 on CPU)."""
     return torch.cuda.memory_reserved() if get_device_type() == "cuda" else 0
 
 
 def memory_allocated() -> int:
+    """Bytes currently allocated to tensors on the current device (0 on CPU)."""
     return torch.cuda.memory_allocated() if get_device_type() == "cuda" else 0
 
 
 def max_memory_allocated() -> int:
+    """Peak of ``memory_allocated`` since the last reset (0 on CPU)."""
     return torch.cuda.max_memory_allocated() if get_device_type() == "cuda" else 0
 
 
 def reset_peak_memory_stats() -> None:
+    """Restart the peak-memory statistics of the current device."""
     if get_device_type() == "cuda":
         torch.cuda.reset_peak_memory_stats()
 
 
 def is_bf16_supported() -> bool:
+    """Whether the compute dtype can be bf16 (always true on B200; true on CPU, where it is merely slow)."""
     if get_device_type() == "cuda":
         return torch.cuda.is_bf16_supported()
     return True  # CPU bf16 works (slowly); tests use fp32 explicitly
 
 
 def manual_seed_all(seed: int) -> None:
+    """Seed the CPU generator and every CUDA generator."""
     torch.manual_seed(seed)
     if get_device_type() == "cuda":
         torch.cuda.manual_seed_all(seed)

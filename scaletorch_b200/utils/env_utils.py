@@ -10,6 +10,7 @@ from .device import get_device_type
 
 
 def get_system_info() -> dict:
+    """Host / software / GPU diagnostics as a dict: hostname, platform, python, torch and CUDA versions, device count, name, memory and SM count."""
     info = {
         "hostname": socket.gethostname(),
         "platform": platform.platform(),
@@ -46,6 +47,7 @@ def init_dist_pytorch(backend: str | None = None, **kwargs) -> None:
 
 
 def cleanup_dist() -> None:
+    """Deprecated alias of ``scaletorch_b200.dist.cleanup_dist`` kept for the reference's import path."""
     from ..dist import cleanup_dist as _c
 
     _c()

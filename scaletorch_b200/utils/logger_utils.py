@@ -25,6 +25,7 @@ def _get_distributed_rank() -> int:
 
 
 class ColorfulFormatter(logging.Formatter):
+    """Formatter that stamps each record with the distributed rank and colours the line by level when writing to a terminal."""
     def __init__(self, *args, use_color: bool = True, **kwargs):
         super().__init__(*args, **kwargs)
         self.use_color = use_color
@@ -39,6 +40,7 @@ class ColorfulFormatter(logging.Formatter):
 
 def get_logger(name: str = "scaletorch_b200", log_file: str | None = None, log_level: int = logging.INFO,
                file_mode: str = "a") -> logging.Logger:
+    """Rank-aware logger (cached by name): rank 0 logs to stdout (and ``log_file``) at ``log_level``, other ranks only errors to stderr."""
     if name in _loggers:
         return _loggers[name]
     logger = logging.getLogger(name)

@@ -132,6 +132,7 @@ def get_num_params(model: torch.nn.Module) -> int:
 
 
 def assert_no_meta_tensors(model: torch.nn.Module) -> None:
+    """Raise if any parameter or buffer of ``model`` is still on the meta device (materialisation missed it)."""
     bad = [n for n, p in model.named_parameters() if p.device.type == "meta"]
     bad += [n for n, b in model.named_buffers() if b.device.type == "meta"]
     if bad:

@@ -33,6 +33,7 @@ except Exception:  # pragma: no cover
 
 
 class PerformanceMonitor:
+    """Per-iteration timing (CUDA events, optionally resolved one step late so that logging never synchronises), throughput, memory, NVML clocks / power / throttle reasons and CPU load; bounded history, JSON dump, summary table."""
     def __init__(self, config: Any = None, log_dir: str | None = None, device_index: int | None = None):
         self.config = config
         self.log_dir = log_dir or (getattr(config, "work_dir", None) or ".")

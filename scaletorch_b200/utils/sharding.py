@@ -12,6 +12,7 @@ import torch
 
 
 def shard_tensor(name: str, full: torch.Tensor, cfg, tp: int, tp_rank: int, ep: int, ep_rank: int) -> torch.Tensor:
+    """The slice of the full (local-layout) parameter ``name`` that rank ``(tp_rank, ep_rank)`` owns: head-aligned rows of the fused q|k|v, both halves of gate|up, columns of the row-parallel weights, vocabulary rows, a contiguous block of experts."""
     hd = getattr(cfg, "head_dim", None) or cfg.hidden_size // cfg.num_attention_heads
     nq, nkv = cfg.num_attention_heads, cfg.num_key_value_heads
 

@@ -20,12 +20,14 @@ _nvtx = os.environ.get("SCALETORCH_B200_NVTX", "0") == "1"
 
 
 def enable_nvtx(on: bool = True) -> None:
+    """Turn the ``nvtx_range`` annotations on or off at run time (initial value: ``SCALETORCH_B200_NVTX``)."""
     global _nvtx
     _nvtx = on
 
 
 @contextlib.contextmanager
 def nvtx_range(name: str):
+    """Context manager: an NVTX range around the block when annotations are enabled and CUDA is present, otherwise nothing."""
     if _nvtx and torch.cuda.is_available():
         torch.cuda.nvtx.range_push(name)
         try:

@@ -23,6 +23,7 @@ import time
 
 
 class StepWatchdog:
+    """Background thread that expects ``beat(step)`` at least every ``timeout_s`` seconds: writes a per-rank heartbeat file on every beat and, when the beats stop, dumps all thread stacks to ``hang_rank<r>.txt`` and exits the process with code 124 (or calls ``on_timeout``)."""
     def __init__(self, timeout_s: float, out_dir: str = ".", rank: int = 0, on_timeout=None, poll_s: float | None = None):
         self.timeout_s, self.out_dir, self.rank = float(timeout_s), out_dir, rank
         self.on_timeout = on_timeout
@@ -74,6 +75,7 @@ class StepWatchdog:
 
 
 def maybe_inject_fault(rank: int, step: int) -> None:
+    """Fault drill: when ``SCALETORCH_B200_FAULT_INJECT=<rank>:<step>[:raise|hang|exit]`` names this rank and step, raise, sleep forever or exit with code 17."""
     spec = os.environ.get("SCALETORCH_B200_FAULT_INJECT")
     if not spec:
         return

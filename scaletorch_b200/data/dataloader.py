@@ -32,6 +32,7 @@ class SyntheticTokens(torch.utils.data.Dataset):
 
 
 class MicroBatchDataLoader(DataLoader):
+    """Loader of ``{input_ids, target_ids, position_ids}`` micro-batches: a ``DistributedSampler`` over the DATA ranks, targets shifted by one token, each sample cut to this context-parallel rank's slice (contiguous or zig-zag), one batch of software prefetch, automatic epoch roll-over, and a resumable position (``state_dict`` / ``load_state_dict``)."""
     def __init__(self, micro_batch_size: int, sequence_length: int, dataset_name: str | None = None,
                  tokenizer_name_or_path: str | None = None, gradient_accumulation_steps: int = 1, device=None,
                  num_workers: int = 0, num_proc: int = 1, num_samples: int | None = None, split: str = "train",

@@ -21,6 +21,7 @@ _TOKENIZE_STRATEGIES: dict[str, TokenizeFn] = {}
 
 
 def register_tokenize_strategy(name: str, fn: TokenizeFn | None = None):
+    """Register ``fn`` as the tokenize strategy ``name`` (usable as a decorator when ``fn`` is omitted)."""
     def _reg(f: TokenizeFn) -> TokenizeFn:
         _TOKENIZE_STRATEGIES[name] = f
         return f
@@ -29,6 +30,7 @@ def register_tokenize_strategy(name: str, fn: TokenizeFn | None = None):
 
 
 def get_tokenize_strategy(name: str) -> TokenizeFn:
+    """Look up a registered tokenize strategy; ``KeyError`` lists the known names."""
     if name not in _TOKENIZE_STRATEGIES:
         raise KeyError(f"unknown tokenize strategy '{name}'; registered: {sorted(_TOKENIZE_STRATEGIES)}")
     return _TOKENIZE_STRATEGIES[name]
@@ -60,6 +62,7 @@ def tokenizer_pad_truncate(examples: dict[str, list], tokenizer: Any, sequence_l
 
 
 class DatasetProcessor:
+    """Tokenizer construction (built on rank 0 and broadcast), dataset loading (``load_from_disk`` for a directory, ``load_dataset`` otherwise) and tokenisation with a registered strategy through ``datasets.map``."""
     def __init__(self, tokenizer_name_or_path: str | None = None, tokenizer: Any = None, device=None):
         if tokenizer is None and tokenizer_name_or_path is None:
             raise ValueError("either tokenizer or tokenizer_name_or_path must be given")

@@ -83,6 +83,7 @@ N.register("stb_loader_destroy", [_P], restype=None)
 
 
 def native_loader_available() -> bool:
+    """True when the in-tree library exports the C++ token loader (``stb_loader_*``)."""
     lib = N.load()
     return lib is not None and hasattr(lib, "stb_loader_create")
 

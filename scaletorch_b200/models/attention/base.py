@@ -17,6 +17,7 @@ from ... import ops
 
 
 def validate_attention_inputs(hidden_state: torch.Tensor, attention_mask: torch.Tensor | None, hidden_size: int) -> None:
+    """Shape checks shared by the attention variants: ``hidden_state`` is ``[batch, seq, hidden_size]``, the mask has 2 to 4 dimensions."""
     if hidden_state.dim() != 3:
         raise ValueError(f"hidden_state must be [batch, seq, hidden], got {tuple(hidden_state.shape)}")
     if hidden_state.shape[-1] != hidden_size:
@@ -26,6 +27,7 @@ def validate_attention_inputs(hidden_state: torch.Tensor, attention_mask: torch.
 
 
 class BaseAttention(nn.Module, ABC):
+    """Common state and helpers of the stand-alone attention modules: head split / merge, mask broadcasting, and ``attend`` (flash kernel when possible, eager fp32 softmax when a mask, dropout or the weights are requested)."""
     def __init__(self, hidden_size: int, num_heads: int, dropout: float = 0.0, bias: bool = True) -> None:
         super().__init__()
         if hidden_size % num_heads != 0:

@@ -11,6 +11,7 @@ from .base import BaseAttention, validate_attention_inputs
 
 
 class GroupQueryAttention(BaseAttention):
+    """Grouped-query attention: ``num_heads`` query heads share ``num_kv_groups`` key / value heads (no K/V expansion on the kernel path)."""
     def __init__(self, hidden_size: int, num_heads: int, num_kv_groups: int, dropout: float = 0.1, bias: bool = True,
                  causal: bool = False):
         super().__init__(hidden_size, num_heads, dropout, bias)

@@ -7,6 +7,7 @@ from .base import BaseAttention, validate_attention_inputs
 
 
 class MultiHeadAttention(BaseAttention):
+    """Classic multi-head attention: one key / value head per query head."""
     def __init__(self, hidden_size: int, num_heads: int, dropout: float = 0.0, bias: bool = True, causal: bool = False):
         super().__init__(hidden_size, num_heads, dropout, bias)
         self.causal = causal

@@ -8,6 +8,7 @@ from .base import BaseAttention, validate_attention_inputs
 
 
 class MultiHeadLatentAttention(BaseAttention):
+    """Multi-head latent attention: queries through a ``q_latent_size`` bottleneck, keys and values expanded from one shared ``kv_latent_size`` latent (the tensor an inference cache would keep)."""
     def __init__(self, hidden_size: int, num_heads: int, q_latent_size: int, kv_latent_size: int, dropout: float = 0.0,
                  bias: bool = True, causal: bool = False):
         super().__init__(hidden_size, num_heads, dropout, bias)

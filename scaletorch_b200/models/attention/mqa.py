@@ -8,6 +8,7 @@ from .base import BaseAttention, validate_attention_inputs
 
 
 class MultiQueryAttention(BaseAttention):
+    """Multi-query attention: every query head attends over ONE shared key / value head."""
     def __init__(self, hidden_size: int, num_heads: int, dropout: float = 0.1, bias: bool = True, causal: bool = False):
         super().__init__(hidden_size, num_heads, dropout, bias)
         self.causal = causal

@@ -30,12 +30,14 @@ def register_attention_backend(name: str, fn: AttentionFn | None = None):
 
 
 def get_attention_backend(name: str) -> AttentionFn:
+    """The attention function registered as ``name`` (``ring``, ``flash``, ``sdpa`` or a plug-in); ``KeyError`` lists the known names."""
     if name not in _ATTENTION_BACKENDS:
         raise KeyError(f"unknown attention backend '{name}'; registered: {sorted(_ATTENTION_BACKENDS)}")
     return _ATTENTION_BACKENDS[name]
 
 
 def list_attention_backends() -> list[str]:
+    """Names of the registered attention back-ends, sorted."""
     return sorted(_ATTENTION_BACKENDS)
 
 

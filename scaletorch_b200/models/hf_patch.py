@@ -87,6 +87,7 @@ def apply_b200_patch() -> list[str]:
 
 
 def remove_b200_patch() -> None:
+    """Undo ``apply_b200_patch``: restore the original ``forward`` of every patched HuggingFace class."""
     for cls, fwd in _originals.items():
         cls.forward = fwd
     _originals.clear()

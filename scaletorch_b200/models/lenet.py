@@ -5,6 +5,7 @@ import torch.nn.functional as F
 
 
 class LeNet(nn.Module):
+    """Small CNN for 28 x 28 MNIST digits (two 3x3 convolutions, max-pool, two linear layers): the model of the DDP / FSDP examples."""
     def __init__(self, num_classes: int = 10):
         super().__init__()
         self.conv1 = nn.Conv2d(1, 32, 3, 1)

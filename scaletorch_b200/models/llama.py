@@ -10,6 +10,7 @@ from .transformer import DecoderLM
 
 
 class Llama(DecoderLM):
+    """Llama-family decoder: no QK-norm, ``rope_theta`` 5e5 by default, uniform fan-in initialisation."""
     model_type = "llama"
     qk_norm = False
     default_rope_theta = 500000.0

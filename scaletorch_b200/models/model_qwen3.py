@@ -11,6 +11,7 @@ from .transformer import DecoderLM
 
 
 class Qwen3(DecoderLM):
+    """Qwen3 dense decoder: explicit ``head_dim``, per-head q / k RMSNorm before RoPE, optional tied embeddings."""
     model_type = "qwen3"
     qk_norm = True
     default_rope_theta = 1000000.0

@@ -77,6 +77,7 @@ class MoEExperts(nn.Module):
 
 
 class MoELayer(nn.Module):
+    """Sparse MLP block: router -> top-k experts -> weighted sum.  Local experts run as a sort + grouped GEMM; with expert parallelism tokens travel through the peer-memory dispatch / combine kernels (or the differentiable all-to-all path on c10d)."""
     def __init__(self, config: Any, ctx: ParallelContext):
         super().__init__()
         self.ctx = ctx
@@ -203,6 +204,7 @@ class _SplitKeepGrad(torch.autograd.Function):
 
 
 class Qwen3MoE(DecoderLM):
+    """Qwen3-MoE decoder: Qwen3 attention with a ``MoELayer`` as the feed-forward of every sparse layer; ``get_aux_loss()`` sums the routers' load-balancing losses."""
     model_type = "qwen3_moe"
     qk_norm = True
     default_rope_theta = 1000000.0

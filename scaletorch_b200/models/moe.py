@@ -26,6 +26,7 @@ from ..ops.grouped import grouped_linear
 
 @dataclass
 class GPTConfig:
+    """nanoGPT-style hyper-parameters plus the MoE switches (which layers are sparse, experts, top-k, capacity, auxiliary / z losses, noisy routing); validated in ``__post_init__``."""
     block_size: int = 1024
     vocab_size: int = 50304
     n_layer: int = 12
@@ -79,6 +80,7 @@ class GPTConfig:
 
 
 class LayerNorm(nn.Module):
+    """LayerNorm with an optional bias (``F.layer_norm`` has no bias switch)."""
     def __init__(self, ndim: int, bias: bool) -> None:
         super().__init__()
         self.weight = nn.Parameter(torch.ones(ndim))
@@ -89,6 +91,7 @@ class LayerNorm(nn.Module):
 
 
 class CausalSelfAttention(nn.Module):
+    """Fused-qkv causal self-attention through ``ops.flash_attention``."""
     def __init__(self, config: GPTConfig) -> None:
         super().__init__()
         self.n_head, self.n_embd, self.dropout = config.n_head, config.n_embd, config.dropout
@@ -104,6 +107,7 @@ class CausalSelfAttention(nn.Module):
 
 
 class GELUMLP(nn.Module):
+    """The dense feed-forward block: 4x expansion, GELU, projection, dropout."""
     def __init__(self, config: GPTConfig) -> None:
         super().__init__()
         self.c_fc = nn.Linear(config.n_embd, 4 * config.n_embd, bias=config.bias)
@@ -115,6 +119,7 @@ class GELUMLP(nn.Module):
 
 
 class Block(nn.Module):
+    """Pre-norm transformer block with the dense MLP."""
     def __init__(self, config: GPTConfig) -> None:
         super().__init__()
         self.ln_1, self.ln_2 = LayerNorm(config.n_embd, config.bias), LayerNorm(config.n_embd, config.bias)
@@ -167,6 +172,7 @@ class MLPExperts(nn.Module):
 
 
 class Router(nn.Module):
+    """Noisy top-k router with a per-expert capacity ``floor(k * cf * T / E)``: returns gate weights, expert ids, the keep mask of pairs that fit their expert's queue (earlier choices first), the capacity and the auxiliary / z loss."""
     def __init__(self, config: GPTConfig) -> None:
         super().__init__()
         self.config = config
@@ -223,6 +229,7 @@ class Router(nn.Module):
 
 
 class MOELayer(nn.Module):
+    """Capacity-based MoE feed-forward: kept (token, expert) pairs are sorted by expert, run through the grouped expert MLP and scattered back with their gate weights; dropped pairs contribute zero."""
     def __init__(self, config: GPTConfig) -> None:
         super().__init__()
         self.router, self.experts = Router(config), MLPExperts(config)
@@ -248,6 +255,7 @@ class MOELayer(nn.Module):
 
 
 class MoEBlock(nn.Module):
+    """Pre-norm transformer block whose feed-forward is a ``MOELayer``; returns ``(x, aux_loss)``."""
     def __init__(self, config: GPTConfig) -> None:
         super().__init__()
         self.ln_1, self.ln_2 = LayerNorm(config.n_embd, config.bias), LayerNorm(config.n_embd, config.bias)
@@ -260,6 +268,7 @@ class MoEBlock(nn.Module):
 
 
 class GPT(nn.Module):
+    """The language model: token + position embeddings, dense and MoE blocks as configured, tied LM head; ``forward`` adds the routers' losses to the cross-entropy; ``generate``, ``crop_block_size``, ``estimate_mfu``."""
     def __init__(self, config: GPTConfig) -> None:
         super().__init__()
         self.config = config
@@ -343,12 +352,14 @@ class GPT(nn.Module):
 
 
 def analyze_moe_usage(model: GPT) -> dict[str, Any]:
+    """Which blocks of ``model`` are MoE blocks, how many, and the parameter count."""
     moe_layers = [i for i, b in enumerate(model.transformer.blocks) if isinstance(b, MoEBlock)]
     return {"total_layers": len(model.transformer.blocks), "moe_layers": moe_layers, "moe_layer_count": len(moe_layers),
             "total_parameters": model.get_num_params(), "uses_moe": len(moe_layers) > 0}
 
 
 def get_moe_layer_info(model: GPT, layer_idx: int) -> dict[str, Any] | None:
+    """Expert / router configuration and parameter counts of block ``layer_idx``; ``None`` if it is dense or out of range."""
     if layer_idx >= len(model.transformer.blocks):
         return None
     block = model.transformer.blocks[layer_idx]

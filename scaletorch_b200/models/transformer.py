@@ -34,6 +34,7 @@ from .attention_utils import RMSNorm, get_attention_backend, resolve_attention_b
 
 
 class Attention(nn.Module):
+    """Self-attention of the decoder: ONE fused q|k|v projection (column-parallel), optional per-head QK-norm fused with RoPE, flash / ring attention with native GQA, row-parallel output projection."""
     def __init__(self, config: Any, layer_idx: int, ctx: ParallelContext, *, qk_norm: bool, head_dim: int,
                  init_std: float | None):
         super().__init__()
@@ -107,6 +108,7 @@ class MLP(nn.Module):
 
 
 class DecoderLayer(nn.Module):
+    """Pre-norm decoder layer on the ``(h, delta)`` residual stream: the add of the previous branch output is fused into this layer's RMSNorm; the feed-forward is the SwiGLU MLP or the module passed as ``ffn`` (MoE)."""
     def __init__(self, config: Any, layer_idx: int, ctx: ParallelContext, *, qk_norm: bool, head_dim: int,
                  init_std: float | None, ffn: nn.Module | None = None):
         super().__init__()

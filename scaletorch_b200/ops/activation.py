@@ -14,6 +14,7 @@ from .. import _native as N
 
 
 def swiglu_ref(gu: torch.Tensor) -> torch.Tensor:
+    """PyTorch oracle: ``silu(gate) * up`` for ``gu = [gate | up]`` along the last dimension."""
     g, u = gu.chunk(2, dim=-1)
     return F.silu(g) * u
 
@@ -42,6 +43,7 @@ class _SwiGLU(torch.autograd.Function):
 
 
 def swiglu(gu: torch.Tensor) -> torch.Tensor:
+    """``silu(gate) * up`` on the fused gate|up GEMM output: the sm_100a kernel for contiguous bf16 CUDA tensors, the oracle otherwise."""
     if N.use_native(gu) and gu.dtype == torch.bfloat16 and gu.is_contiguous() and (gu.shape[-1] // 2) % 8 == 0:
         return _SwiGLU.apply(gu)
     return swiglu_ref(gu)

@@ -49,6 +49,7 @@ def attention_ref(q, k, v, causal=True, scale=None, q_offset: int = 0):
 
 
 def native_attention_fwd_available() -> bool:
+    """True when the in-tree library exports the flash-attention forward kernel."""
     lib = N.load()
     return lib is not None and hasattr(lib, "stb_flash_attn_fwd")
 

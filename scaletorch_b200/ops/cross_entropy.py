@@ -19,6 +19,7 @@ from .gemm import gemm, wgrad_into
 
 
 def cross_entropy_ref(logits: torch.Tensor, targets: torch.Tensor, ignore_index: int = -100) -> torch.Tensor:
+    """PyTorch oracle: mean cross-entropy of fp32-upcast logits over the targets that are not ``ignore_index``."""
     return F.cross_entropy(logits.float().view(-1, logits.shape[-1]), targets.reshape(-1), ignore_index=ignore_index)
 
 

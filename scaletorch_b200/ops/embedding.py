@@ -15,6 +15,7 @@ from .norm import _finish_param_grad, _param_grad_out
 
 
 def embedding_ref(ids: torch.Tensor, weight: torch.Tensor, vocab_start: int = 0) -> torch.Tensor:
+    """PyTorch oracle of the (vocabulary-parallel) lookup: rows of ``weight`` for ids inside ``[vocab_start, vocab_start + V)``, zeros for the others."""
     V = weight.shape[0]
     local = ids - vocab_start
     mask = (local >= 0) & (local < V)
@@ -70,6 +71,7 @@ class _Embedding(torch.autograd.Function):
 
 
 def embedding(ids: torch.Tensor, weight: torch.Tensor, vocab_start: int = 0) -> torch.Tensor:
+    """Embedding lookup with an optional vocabulary shard offset: gather / scatter-add kernels for bf16 CUDA weights, the oracle otherwise."""
     if N.use_native(weight) and weight.dtype == torch.bfloat16 and weight.shape[1] % 8 == 0:
         return _Embedding.apply(ids, weight, int(vocab_start))
     return embedding_ref(ids, weight, vocab_start)

@@ -38,6 +38,7 @@ def _offsets(tokens_per_expert: torch.Tensor) -> list[int]:
 
 
 def native_grouped_available() -> bool:
+    """True when the in-tree library exports the grouped (per-expert) GEMM."""
     lib = N.load()
     return lib is not None and hasattr(lib, "stb_grouped_gemm_bf16")
 
@@ -105,6 +106,7 @@ def _use_native(x_sorted, *weights) -> bool:
 
 
 def grouped_linear(x_sorted: torch.Tensor, weight: torch.Tensor, tokens_per_expert: torch.Tensor) -> torch.Tensor:
+    """``y[rows of expert e] = x[rows of expert e] @ weight[e].T`` for rows sorted by expert (``tokens_per_expert`` gives the segment lengths): the tcgen05 grouped GEMM on CUDA, a per-expert loop as the oracle."""
     if _use_native(x_sorted, weight):
         from .grouped_native import grouped_linear_native
 

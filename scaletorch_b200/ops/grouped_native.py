@@ -120,11 +120,13 @@ class _GroupedLinearPadded(torch.autograd.Function):
 
 
 def supported(weight: torch.Tensor) -> bool:
+    """Shape rule of the grouped GEMM: output features a multiple of 128, input features a multiple of 64."""
     _, Nn, K = weight.shape
     return Nn % 128 == 0 and K % 64 == 0
 
 
 def grouped_linear_native(x_sorted, weight, tokens_per_expert):
+    """Grouped linear through the padded expert-major layout (pad rows to 128 per expert, one kernel, un-pad); differentiable."""
     layout = GroupedLayout(tokens_per_expert, x_sorted.shape[0])
     return layout.unpad(_GroupedLinearPadded.apply(layout.pad(x_sorted), weight, layout))
 

@@ -20,6 +20,7 @@ N.register("stb_moe_router_bwd", [_P, _P, _P, _P, _P, _P, _F, _L, _I, _I, _P, _P
 
 
 def native_router_available(logits: torch.Tensor, k: int) -> bool:
+    """True when the fused router kernel applies: bf16 CUDA logits, at most 256 experts, ``k <= 16``."""
     lib = N.load() if logits.is_cuda else None
     return (lib is not None and hasattr(lib, "stb_moe_router_fwd") and N.use_native(logits)
             and logits.dtype == torch.bfloat16 and logits.shape[1] <= 256 and k <= 16)

@@ -44,12 +44,14 @@ def _finish_param_grad(param, dst, is_main):
 
 # --------------------------------------------------------------------------- oracle
 def rmsnorm_ref(x: torch.Tensor, w: torch.Tensor, eps: float) -> torch.Tensor:
+    """PyTorch oracle: ``w * (x * rsqrt(mean(x^2) + eps))`` with the statistics in fp32 and the cast before the weight multiply."""
     xf = x.float()
     xn = (xf * torch.rsqrt(xf.pow(2).mean(-1, keepdim=True) + eps)).to(x.dtype)
     return w * xn
 
 
 def rotate_half(x: torch.Tensor) -> torch.Tensor:
+    """``cat(-x2, x1)`` for ``x = cat(x1, x2)`` along the last dimension (the rotate-half RoPE convention)."""
     h = x.shape[-1] // 2
     return torch.cat((-x[..., h:], x[..., :h]), dim=-1)
 
@@ -147,6 +149,7 @@ class _AddRMSNorm(torch.autograd.Function):
 
 
 def rmsnorm(x: torch.Tensor, w: torch.Tensor, eps: float = 1e-6) -> torch.Tensor:
+    """RMSNorm over the last dimension: the fused kernel for bf16 CUDA tensors, the oracle otherwise."""
     if N.use_native(x) and x.dtype == torch.bfloat16:
         return _AddRMSNorm.apply(x.contiguous(), None, w, eps)
     return rmsnorm_ref(x, w, eps)

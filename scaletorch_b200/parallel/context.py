@@ -18,6 +18,7 @@ from .process_group import process_group_manager as pgm
 
 @dataclass
 class ParallelContext:
+    """Sizes, ranks and groups of the TP / CP / EP / PP / DP axes plus the resolved switches (sequence parallel, flash attention, fused collectives) that a model is built with."""
     tp_size: int = 1
     tp_rank: int = 0
     tp_group: Any = None
@@ -62,4 +63,5 @@ class ParallelContext:
 
 
 def single_device_context(**kw) -> ParallelContext:
+    """A context with every axis of size 1 (keyword arguments override fields)."""
     return ParallelContext(**kw)

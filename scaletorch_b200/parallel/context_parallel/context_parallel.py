@@ -57,6 +57,7 @@ def update_rows(out, lse, block_out, block_lse, q_lo: int):
 
 
 class RingAttentionFunc(torch.autograd.Function):
+    """Ring attention on c10d p2p: K/V blocks rotate around the CP ring while each rank runs block attention and merges ``(out, lse)``; the backward rotates K/V again together with the dK/dV accumulators.  Contiguous or zig-zag chunks; the CPU / fallback counterpart of ``fused_ring``."""
     @staticmethod
     def forward(ctx, q, k, v, sm_scale, is_causal, group, send_rank, recv_rank, cp_rank, cp_size):
         from . import zigzag

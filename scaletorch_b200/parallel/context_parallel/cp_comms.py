@@ -19,6 +19,7 @@ VERBOSE = os.environ.get(ENV_VERBOSE, "0") == "1"
 
 
 class ContextCommunicator:
+    """Send-to-next / receive-from-previous on the CP ring as a small state machine: ``send_recv`` queues pairs, ``commit`` launches them as one batch, ``wait`` completes them; misuse (commit twice, wait before commit) raises."""
     def __init__(self, msg: str = "", group=None, send_rank: int | None = None, recv_rank: int | None = None):
         self.msg = msg
         self._ops: list = []

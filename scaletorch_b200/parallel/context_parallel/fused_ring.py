@@ -62,6 +62,7 @@ def _stage_peer_blocks(g, steps, shape, n):
 
 
 def available(q: torch.Tensor, k: torch.Tensor, group) -> bool:
+    """True when the peer-memory ring applies: bf16 CUDA tensors with head_dim 128, the block kernels present, symmetric memory set up for the group and large enough for K/V and the fp32 dK/dV accumulators."""
     if not (q.is_cuda and q.dtype == torch.bfloat16 and q.shape[-1] == 128 and ops.native_attention_available()):
         return False
     if not symm.group_ready(group) or not symm.has_kernel("stb_flash_attn_bwd_block"):
@@ -151,4 +152,5 @@ class FusedRingAttention(torch.autograd.Function):
 
 
 def fused_ring_attention(q, k, v, sm_scale: float, is_causal: bool, group) -> torch.Tensor:
+    """Context-parallel attention over peer memory (see the module docstring); q / k / v are this rank's ``[B, S_local, H, D]`` chunks, the result is its chunk of the full-sequence attention."""
     return FusedRingAttention.apply(q, k.contiguous(), v.contiguous(), sm_scale, is_causal, group)

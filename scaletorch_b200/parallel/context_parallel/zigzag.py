@@ -26,10 +26,12 @@ ENV = "SCALETORCH_B200_CP_ZIGZAG"
 
 
 def enabled() -> bool:
+    """Whether the zig-zag split is active (``SCALETORCH_B200_CP_ZIGZAG=1``)."""
     return os.environ.get(ENV, "0") == "1"
 
 
 def set_enabled(on: bool) -> None:
+    """Switch the zig-zag split on or off for the loader, the RoPE positions and both ring implementations."""
     os.environ[ENV] = "1" if on else "0"
 
 

@@ -17,6 +17,7 @@ from ...runtime.flat_params import FlatParamStore, ParamSlot
 
 
 class Bucket:
+    """A contiguous range of the flat gradient buffer with the parameters that live in it: tracks which gradients are ready and launches the range's reduction (peer-memory kernel on the comm stream, or c10d) when the last one arrives."""
     def __init__(self, slots: list[ParamSlot], grad_flat: torch.Tensor, group, wire_dtype: torch.dtype = torch.float32,
                  grad_window=None, comm_stream=None, sm_budget: int = 32):
         self.slots = slots

@@ -113,6 +113,7 @@ class BasicDataParallel(_DPBase):
 
 
 class DataParallelBucket(_DPBase):
+    """Bucketed data parallelism over the flat gradient store: per-parameter hooks mark gradients ready, full buckets are reduced while backward continues, ``no_sync`` defers the reduction during gradient accumulation; with bf16 parameters on a peer-memory fabric the buckets are reduce-scattered for the sharded optimiser."""
     def __init__(self, module: nn.Module, bucket_size: int = 2**24, grad_type: torch.dtype | None = None,
                  group=None, expert_group=None, wire_dtype: torch.dtype | None = None):
         super().__init__(module)

@@ -77,6 +77,7 @@ class EPWindow:
 
 
 def get_window(group, rows_cap: int, hidden: int, num_experts: int) -> EPWindow:
+    """The cached symmetric receive / return window of an EP group for this capacity and shape (allocated collectively on first use)."""
     key = (id(group), rows_cap, hidden, num_experts)
     w = _windows.get(key)
     if w is None:
@@ -86,6 +87,7 @@ def get_window(group, rows_cap: int, hidden: int, num_experts: int) -> EPWindow:
 
 
 def reset() -> None:
+    """Forget the cached EP windows (called when the process groups are torn down)."""
     _windows.clear()
 
 
@@ -248,6 +250,7 @@ def fused_moe_ep(x: torch.Tensor, weights: torch.Tensor, idx: torch.Tensor, gate
 
 
 def available(group, x: torch.Tensor, gate_up_proj: torch.Tensor, down_proj: torch.Tensor) -> bool:
+    """True when the peer-memory EP path applies: bf16 CUDA activations, the push / pull and grouped-GEMM kernels present, expert shapes the grouped GEMM supports, symmetric memory ready for the group."""
     from ...ops.grouped_native import supported
     from ...runtime import symm
 

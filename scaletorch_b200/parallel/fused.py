@@ -57,35 +57,41 @@ def gemm_rs_available(x_full: torch.Tensor, group) -> bool:
 
 
 def gemm_ar_available(x: torch.Tensor, n_out: int, group) -> bool:
+    """Whether GEMM -> all-reduce through the window applies to ``x @ W`` with ``n_out`` output features (fits the region, 16-byte multiple, policy allows it)."""
     return (_ok(x, group) and symm.has_kernel("stb_allreduce_oneshot_bf16")
             and x.shape[0] * n_out * 2 <= symm.region_bytes(group) and (x.shape[0] * n_out) % 8 == 0
             and _policy("gemm_ar", _world(group)))
 
 
 def allreduce_available(t: torch.Tensor, group) -> bool:
+    """Whether the peer-memory all-reduce applies to ``t`` (bf16 CUDA, multiple of 8 elements, fits the region)."""
     return (_ok(t, group) and symm.has_kernel("stb_allreduce_oneshot_bf16") and t.numel() % 8 == 0
             and t.numel() * 2 <= symm.region_bytes(group))
 
 
 def all_gather_gemm(x2d, weight, group, b_mn: bool = False):
+    """``(x_full @ W.T, x_full)`` from this rank's row shard: the GEMM consumes peer shards as copy CTAs land them (``runtime.fused_ops.all_gather_gemm``)."""
     from ..runtime import fused_ops
 
     return fused_ops.all_gather_gemm(x2d, weight, group, b_mn=b_mn)
 
 
 def gemm_reduce_scatter(x2d, weight, group, b_mn: bool = False):
+    """This rank's row block of ``sum_over_ranks(x @ W.T)``: the GEMM epilogue reduce-adds each tile into its owner's buffer (``runtime.fused_ops.gemm_reduce_scatter``)."""
     from ..runtime import fused_ops
 
     return fused_ops.gemm_reduce_scatter(x2d, weight, group, b_mn=b_mn)
 
 
 def gemm_all_reduce(x2d, weight, group, b_mn: bool = False):
+    """``sum_over_ranks(x @ W.T)`` on every rank: GEMM into the window, then a one-shot / NVLS all-reduce kernel (``runtime.fused_ops.gemm_all_reduce``)."""
     from ..runtime import fused_ops
 
     return fused_ops.gemm_all_reduce(x2d, weight, group, b_mn=b_mn)
 
 
 def all_reduce_(t, group):
+    """Sum a bf16 tensor over the group through the symmetric window; returns a new tensor."""
     from ..runtime import fused_ops
 
     return fused_ops.all_reduce_(t, group)

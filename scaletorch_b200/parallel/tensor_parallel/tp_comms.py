@@ -146,26 +146,32 @@ class _ReduceScatterDim0(torch.autograd.Function):
 
 
 def copy_to_tensor_parallel_region(x, group):
+    """Identity in forward, all-reduce of the gradient in backward (input of a column-parallel layer)."""
     return _CopyToRegion.apply(x, group)
 
 
 def reduce_from_tensor_parallel_region(x, group):
+    """All-reduce in forward, identity in backward (output of a row-parallel layer)."""
     return _ReduceFromRegion.apply(x, group)
 
 
 def gather_from_tensor_parallel_region(x, group):
+    """All-gather along the last dimension in forward, this rank's slice of the gradient in backward."""
     return _GatherLastDim.apply(x, group)
 
 
 def all_reduce_sum_autograd(x, group):
+    """Sum over the group in forward; the backward hands every rank the upstream gradient unchanged (vocabulary-parallel loss statistics)."""
     return _AllReduceSum.apply(x, group)
 
 
 def gather_from_sequence_parallel_region(x, group):
+    """Sequence-parallel entry: all-gather along dim 0 in forward, reduce-scatter in backward."""
     return _AllGatherDim0.apply(x, group)
 
 
 def reduce_scatter_to_sequence_parallel_region(x, group):
+    """Sequence-parallel exit: reduce-scatter along dim 0 in forward, all-gather in backward."""
     return _ReduceScatterDim0.apply(x, group)
 
 

@@ -138,6 +138,7 @@ class SymmGroup:
 
 
 def get_group(group, window_bytes: int | None = None) -> SymmGroup:
+    """The cached ``SymmGroup`` (symmetric window, flag pages, multicast mapping) of a process group; allocated collectively on first use."""
     key = id(group)
     g = _groups.get(key)
     if g is None:
@@ -147,6 +148,7 @@ def get_group(group, window_bytes: int | None = None) -> SymmGroup:
 
 
 def reset() -> None:
+    """Forget the cached symmetric groups (called when the process groups are torn down)."""
     _groups.clear()
 
 
@@ -217,6 +219,7 @@ def gemm_all_reduce(x: torch.Tensor, weight: torch.Tensor, group, b_mn: bool = F
 
 
 def all_reduce_window_bf16(g: SymmGroup, offset_bytes: int, n: int, sm_budget: int = 0) -> torch.Tensor:
+    """Sum ``n`` bf16 elements at ``offset_bytes`` of every rank's window: in place through NVLS ``multimem`` when the group has a multicast mapping (returns a copy), otherwise one-shot peer loads into a fresh tensor."""
     if g.mc_ptr and n % 8 == 0 and not _no_multimem():
         # NVLS: in-switch reduction + broadcast in place on the window (each rank handles 1/world of the range)
         epoch = g.take_epochs(SLOT_AR, 2)

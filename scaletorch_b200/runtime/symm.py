@@ -14,11 +14,13 @@ DEFAULT_WINDOW_BYTES = int(os.environ.get("SCALETORCH_B200_SYMM_WINDOW_MB", "102
 
 
 def has_kernel(name: str) -> bool:
+    """True when the in-tree library is loaded and exports ``name``."""
     lib = N.load()
     return lib is not None and hasattr(lib, name)
 
 
 def enabled() -> bool:
+    """Whether the peer-memory paths may be used at all: CUDA present and ``SCALETORCH_B200_FUSED_COMM`` not 0."""
     return os.environ.get("SCALETORCH_B200_FUSED_COMM", "1") == "1" and torch.cuda.is_available()
 
 
@@ -47,12 +49,14 @@ def group_ready(group) -> bool:
 
 
 def region_bytes(group) -> int:
+    """Size in bytes of one region (all-gather / reduce-scatter / all-reduce / spare) of the group's symmetric window."""
     from . import fused_ops
 
     return fused_ops.get_group(group, DEFAULT_WINDOW_BYTES).region_bytes
 
 
 def reset() -> None:
+    """Drop the readiness cache and the symmetric groups (before the process groups are destroyed)."""
     from . import fused_ops
 
     _ready_groups.clear()

@@ -19,7 +19,6 @@ Reference: ``RingAttentionFunc`` with batched isend/irecv and eager per-block at
 from __future__ import annotations
 
 import torch
-import torch.distributed as dist
 
 from ... import ops
 from ...runtime import fused_ops as F

@@ -122,7 +122,6 @@ def test_gpt_moe():
 def test_hf_layout_export_load_roundtrip_keeps_weights(tmp_path):
     """export_hf_state_dict → safetensors → create_model(load_pretrained_weights) reproduces the same logits
     (the reference re-randomises after loading, SURVEY §2.7 #10)."""
-    import json
     import shutil
 
     from safetensors.torch import save_file

@@ -238,16 +238,68 @@ def validate_config(config: ScaleTorchArguments, world_size: int) -> None:
 _CONFIG_DIR = os.path.join(os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))), "configs")
 
 
-def resolve_model_config(name_or_path: str, quiet: bool = False):
-    """Returns a ``transformers.PretrainedConfig`` for a local HF directory, a vendored config under
-    ``configs/<name>/config.json`` (the GPU box has no network) or, last, the HF hub name."""
-    from transformers import AutoConfig
+# keys a config.json must spell out for the fast path below; anything less goes through ``AutoConfig`` so that the
+# family's class defaults fill the gaps exactly as HuggingFace would
+_DENSE_KEYS = ("hidden_size", "intermediate_size", "num_hidden_layers", "num_attention_heads", "num_key_value_heads",
+               "vocab_size", "max_position_embeddings", "rms_norm_eps", "tie_word_embeddings", "rope_theta")
+_COMPLETE_CONFIG_KEYS = {
+    "llama": _DENSE_KEYS,
+    "qwen3": _DENSE_KEYS + ("head_dim",),
+    "qwen3_moe": _DENSE_KEYS + ("head_dim", "num_experts", "num_experts_per_tok", "moe_intermediate_size", "norm_topk_prob",
+                                "decoder_sparse_step", "mlp_only_layers", "router_aux_loss_coef"),
+}
 
+
+class LocalModelConfig:
+    """The fields of a ``config.json`` as attributes (plus ``to_dict`` / ``get``), for model families this package builds.
+
+    ``AutoConfig.from_pretrained`` imports the family's modelling package and with it torchvision, scikit-learn and
+    ``torch._dynamo`` -- about ten seconds per process, on every rank of every launch.  The models here only read plain
+    fields, so a config file that spells out every field the family needs is used as it is."""
+
+    def __init__(self, values: dict, source: str):
+        self.__dict__.update(values)
+        self._name_or_path = source
+
+    def to_dict(self) -> dict:
+        return {k: v for k, v in self.__dict__.items() if not k.startswith("_")}
+
+    def get(self, key: str, default=None):
+        return self.__dict__.get(key, default)
+
+    def __repr__(self) -> str:
+        return f"LocalModelConfig({self._name_or_path}: {self.to_dict()})"
+
+
+def _complete_local_config(directory: str):
+    import json
+
+    with open(os.path.join(directory, "config.json")) as f:
+        values = json.load(f)
+    need = _COMPLETE_CONFIG_KEYS.get(values.get("model_type"))
+    if need is None or any(k not in values for k in need):
+        return None
+    return LocalModelConfig(values, directory)
+
+
+def resolve_model_config(name_or_path: str, quiet: bool = False):
+    """Returns the model configuration for a local HF directory, a vendored config under ``configs/<name>/config.json`` (the
+    GPU box has no network) or, last, the HF hub name: a :class:`LocalModelConfig` when the file spells out every field of
+    its family (all vendored configs do), otherwise the ``transformers.PretrainedConfig`` that ``AutoConfig`` builds
+    (``SCALETORCH_B200_HF_AUTOCONFIG=1`` forces that path)."""
     candidates = [name_or_path, os.path.join(_CONFIG_DIR, name_or_path), os.path.join(_CONFIG_DIR, os.path.basename(name_or_path.rstrip("/")))]
     for c in candidates:
         if os.path.isfile(os.path.join(c, "config.json")):
+            if os.environ.get("SCALETORCH_B200_HF_AUTOCONFIG", "0") != "1":
+                cfg = _complete_local_config(c)
+                if cfg is not None:
+                    return cfg
+            from transformers import AutoConfig
+
             return AutoConfig.from_pretrained(c)
     try:
+        from transformers import AutoConfig
+
         return AutoConfig.from_pretrained(name_or_path, local_files_only=True)
     except Exception as e:
         if not quiet:

@@ -2,6 +2,7 @@
 ``tests/trainer/test_config.py``, ``tests/trainer/test_lr_scheduler.py``)."""
 import dataclasses
 import math
+import os
 
 import pytest
 import torch
@@ -236,3 +237,43 @@ def test_help_renders():
 
     text = HfArgumentParser(K.ScaleTorchArguments).format_help()
     assert "--tensor_parallel_size" in text and "--cp_zigzag" in text
+
+
+def test_local_config_fast_path_agrees_with_autoconfig(tmp_path, monkeypatch):
+    """Vendored configs are read directly (no ``AutoConfig`` import chain); every field the models read must equal what
+    ``AutoConfig`` would have produced, and an incomplete ``config.json`` must still go through ``AutoConfig``."""
+    import json
+
+    from scaletorch_b200.trainer import config as K
+
+    names = sorted(os.listdir(K._CONFIG_DIR))
+    assert {"Qwen3-0.6B", "Qwen3-8B", "Qwen3-30B-A3B", "tiny-llama"} <= set(names)
+    fields = ("model_type", "hidden_size", "intermediate_size", "num_hidden_layers", "num_attention_heads", "num_key_value_heads",
+              "vocab_size", "max_position_embeddings", "rms_norm_eps", "tie_word_embeddings", "head_dim", "num_experts",
+              "num_experts_per_tok", "moe_intermediate_size", "norm_topk_prob", "decoder_sparse_step", "mlp_only_layers",
+              "router_aux_loss_coef", "eos_token_id")
+    for name in names:
+        fast = K.resolve_model_config(name)
+        assert isinstance(fast, K.LocalModelConfig), name
+        monkeypatch.setenv("SCALETORCH_B200_HF_AUTOCONFIG", "1")
+        slow = K.resolve_model_config(name)
+        monkeypatch.delenv("SCALETORCH_B200_HF_AUTOCONFIG")
+        assert not isinstance(slow, K.LocalModelConfig)
+        for f in fields:
+            a, b = getattr(fast, f, None), getattr(slow, f, None)
+            if f == "head_dim" and a is None:
+                a = fast.hidden_size // fast.num_attention_heads
+            assert a == b, (name, f, a, b)
+        theta = getattr(slow, "rope_theta", None) or (getattr(slow, "rope_parameters", None) or {}).get("rope_theta")
+        assert float(fast.rope_theta) == float(theta), name
+        assert fast.to_dict()["hidden_size"] == fast.hidden_size and fast.get("no_such_key", 7) == 7
+    # a file that leaves a family field to the class default is NOT taken by the fast path
+    d = json.load(open(os.path.join(K._CONFIG_DIR, "tiny-qwen3", "config.json")))
+    d.pop("rms_norm_eps")
+    (tmp_path / "config.json").write_text(json.dumps(d))
+    cfg = K.resolve_model_config(str(tmp_path))
+    assert not isinstance(cfg, K.LocalModelConfig) and cfg.rms_norm_eps == 1e-6
+    # unknown families too
+    d["model_type"] = "gpt2"
+    (tmp_path / "config.json").write_text(json.dumps(d))
+    assert K._complete_local_config(str(tmp_path)) is None

@@ -37,6 +37,11 @@ def _pop(argv: list[str], flag: str, default=None, cast=str):
 
 def main(argv=None) -> dict:
     argv = list(sys.argv[1:] if argv is None else argv)
+    if "-h" in argv or "--help" in argv:
+        print(__doc__)
+        print("generation flags: --prompt TEXT | --prompt_ids 1,2,3   --max_new_tokens N (16)   --temperature T (0 = greedy)   --top_k K\n"
+              "model / layout flags (the trainer's):\n")
+        HfArgumentParser(ScaleTorchArguments).parse_args_into_dataclasses(args=["--help"])
     prompt = _pop(argv, "--prompt")
     prompt_ids = _pop(argv, "--prompt_ids")
     max_new = _pop(argv, "--max_new_tokens", 16, int)

@@ -44,10 +44,16 @@ from scaletorch_b200.utils.monitor import PerformanceMonitor  # noqa: E402
 
 logger = get_logger("scaletorch_b200.train")
 
-try:  # optional
-    import wandb
-except Exception:  # pragma: no cover
-    wandb = None
+
+
+def _import_wandb():
+    """wandb is imported only when ``--use_wandb true`` asks for it: the import alone costs seconds on every rank."""
+    try:
+        import wandb
+    except Exception:  # pragma: no cover - optional dependency
+        rank_print("--use_wandb is set but wandb cannot be imported; continuing without it")
+        return None
+    return wandb
 
 
 def report_dropped_pairs(model, step: int) -> None:
@@ -161,7 +167,8 @@ def main(argv=None) -> None:
         tokens_per_step = data_loader.global_batch_size * config.sequence_length
         rank_print(f"init time: {time.time() - t0:.2f}s | Tokens per step: {to_readable_format(tokens_per_step)}",
                    is_print_rank=log_rank)
-        if log_rank and config.use_wandb and wandb is not None:
+        wandb = _import_wandb() if (log_rank and config.use_wandb) else None
+        if wandb is not None:
             run = wandb.init(project=config.project_name, name=f"{config.experiment_name}_{to_readable_format(tokens_per_step)}",
                              config={k: getattr(config, k) for k in ("tensor_parallel_size", "context_parallel_size",
                                      "pipeline_parallel_size", "data_parallel_size", "expert_parallel_size",

@@ -52,6 +52,15 @@ class FusedAdamW(torch.optim.Optimizer):
             self._hyper_dev = torch.zeros(4, dtype=torch.float32, device=store.device)
             self._hyper_host = torch.zeros(4, dtype=torch.float32, pin_memory=True)
 
+    def add_param_group(self, param_group) -> None:
+        """``Optimizer.add_param_group`` without its ``torch._dynamo.disable`` wrapper: the wrapper's first call imports
+        ``torch._dynamo`` (seconds on every rank of every launch) and nothing here is ever traced."""
+        plain = getattr(torch.optim.Optimizer.add_param_group, "__wrapped__", None)
+        if plain is None:
+            super().add_param_group(param_group)
+        else:
+            plain(self, param_group)
+
     def _local_sumsq(self) -> torch.Tensor:
         """This rank's share of the global Σg²: every parameter counted exactly once across the model-parallel group.
 

@@ -88,6 +88,14 @@ def _rebuild_rope(model: nn.Module) -> None:
             m.cos, m.sin = cos, sin
 
 
+def _to_empty(model: nn.Module, device: str | torch.device) -> None:
+    """``Module.to_empty`` with plain ``torch.empty`` per tensor.  ``to_empty`` calls ``empty_like`` on the META tensor, which
+    runs the Python reference implementation and imports the symbolic-shapes machinery: about three seconds on every rank
+    of every launch for uninitialised storage of the same shape and dtype."""
+    dev = torch.device(device)
+    model._apply(lambda t: torch.empty(t.shape, dtype=t.dtype, device=dev))
+
+
 def init_model_with_materialized_weights(model: nn.Module, model_config: Any, save_dir: str | None = None,
                                          load_weights: bool = False, device: str | torch.device = "cpu") -> nn.Module:
     """Materialises a meta-constructed model on ``device``.
@@ -98,7 +106,7 @@ def init_model_with_materialized_weights(model: nn.Module, model_config: Any, sa
     """
     single, weight_map = _find_safetensors(save_dir) if save_dir else (None, None)
     tied = _tied_pairs(model)
-    model.to_empty(device=device)
+    _to_empty(model, device)
     _retie(model, tied)
     _rebuild_rope(model)
     if not load_weights or (single is None and weight_map is None):

@@ -245,7 +245,7 @@ int stb_ce_stats_chunk(const void* logits, const long* targets, float* stats, in
                        int vocab_start, int merge, cudaStream_t stream);
 
 /* ZeRO-1 over symmetric memory (csrc/comm.cu).  Reference: torch DDP all-reduce + replicated AdamW,
- * scaletorch/parallel/data_parallel/*.py, scaletorch/trainer/*.py.
+ * the modules under scaletorch/parallel/data_parallel and scaletorch/trainer.
  *   stb_reduce_scatter_f32   each rank reduces the [own_lo, own_hi) slice of bucket [offset, offset + n) from all
  *                            peers' fp32 gradient windows (multimem.ld_reduce when multicast_ptr != NULL, peer loads
  *                            otherwise) into its own window, scaled.                                   2 epochs

@@ -56,3 +56,19 @@ def test_program_links_against_the_library(tmp_path):
     nm = subprocess.run(["nm", "-D", "--defined-only", LIB], capture_output=True, text=True).stdout
     exported = set(re.findall(r"\b(stb_[a-z0-9_]+)\b", nm))
     assert len(declared) >= 50 and declared <= exported, sorted(declared - exported)
+
+
+@needs_toolchain
+def test_c_example_compiles_and_links(tmp_path):
+    """``examples/c_abi/gemm_rmsnorm.c`` builds with strict warnings against the header, the library and the CUDA runtime."""
+    cudart = next((d for d in ("/usr/local/cuda/lib64", os.path.join(os.environ.get("CUDA_HOME", "/nonexistent"), "lib64"))
+                   if os.path.isfile(os.path.join(d, "libcudart.so"))), None)
+    if cudart is None or not os.path.isfile(LIB):
+        pytest.skip("needs libcudart and the built library")
+    exe = tmp_path / "gemm_rmsnorm"
+    cmd = ["gcc", "-std=c11", "-O1", "-Wall", "-Wextra", "-Werror", "-I", os.path.join(ROOT, "include"), "-I", CUDA_INC,
+           os.path.join(ROOT, "examples", "c_abi", "gemm_rmsnorm.c"), "-L", os.path.dirname(LIB), "-lscaletorch_b200",
+           "-Wl,-rpath," + os.path.dirname(LIB), "-L", cudart, "-lcudart", "-lm", "-o", str(exe)]
+    p = subprocess.run(cmd, capture_output=True, text=True)
+    assert p.returncode == 0, p.stderr[-3000:]
+    assert exe.is_file()

@@ -113,3 +113,19 @@ def test_register_and_stack_budgets(res_usage):
     known = ("flash_attn_fwd_kernel", "attn_bwd_fused_kernel")
     spilling = {k: v for k, v in res_usage.items() if v[1] > 0 and not any(n in k for n in known)}
     assert not spilling, spilling
+
+
+def test_committed_sass_index_describes_this_library(res_usage):
+    """``profiles/sass/INDEX.md`` (the evidence a reviewer reads) must have been generated from the library that is in the
+    tree: per kernel family the same number of instantiations with the same register and stack figures."""
+    index = open(os.path.join(ROOT, "profiles", "sass", "INDEX.md")).read()
+    by_family = {}
+    for m in re.finditer(r"^\| ([\w:]+) \| `[^`]*` \| \d+ \| (\d+) \| (\d+) \|", index, re.M):
+        by_family.setdefault(m.group(1), []).append((int(m.group(2)), int(m.group(3))))
+    assert len(by_family) >= 25, sorted(by_family)
+    names = list(res_usage)
+    pretty = subprocess.run(["c++filt"], input="\n".join(names), capture_output=True, text=True).stdout.splitlines()
+    assert len(pretty) == len(names)
+    for family, rows in by_family.items():                      # tools/dump_sass.py: a family is a substring of the demangled name
+        built = sorted(res_usage[n] for n, p in zip(names, pretty) if family in p)
+        assert built == sorted(rows), (family, built, sorted(rows))

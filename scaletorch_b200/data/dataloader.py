@@ -31,6 +31,32 @@ class SyntheticTokens(torch.utils.data.Dataset):
         return {"input_ids": torch.randint(0, self.vocab_size, (self.sequence_length + 1,), generator=g)}
 
 
+class TokenWindows(torch.utils.data.Dataset):
+    """Non-overlapping windows of ``sequence_length + 1`` ids from a flat token array (held-out evaluation data)."""
+
+    def __init__(self, tokens, sequence_length: int):
+        self.tokens, self.chunk = tokens, sequence_length + 1
+        self.n = len(tokens) // self.chunk
+        if self.n == 0:
+            raise ValueError(f"token file holds {len(tokens)} tokens; one window needs {self.chunk}")
+
+    def __len__(self) -> int:
+        return self.n
+
+    def __getitem__(self, i: int):
+        import numpy as np
+
+        w = self.tokens[i * self.chunk:(i + 1) * self.chunk]
+        return {"input_ids": torch.from_numpy(np.asarray(w, dtype=np.int64))}
+
+
+def load_tokens(path: str):
+    """Memory-map a flat token file: ``.npy`` (any integer dtype) or raw int32 ``.bin``."""
+    import numpy as np
+
+    return np.load(path, mmap_mode="r") if path.endswith(".npy") else np.memmap(path, dtype=np.int32, mode="r")
+
+
 class MicroBatchDataLoader(DataLoader):
     """Loader of ``{input_ids, target_ids, position_ids}`` micro-batches: a ``DistributedSampler`` over the DATA ranks, targets shifted by one token, each sample cut to this context-parallel rank's slice (contiguous or zig-zag), one batch of software prefetch, automatic epoch roll-over, and a resumable position (``state_dict`` / ``load_state_dict``)."""
     def __init__(self, micro_batch_size: int, sequence_length: int, dataset_name: str | None = None,

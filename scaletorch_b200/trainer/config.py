@@ -135,7 +135,7 @@ class OptimizerArguments:
 
 @dataclass
 class TrainingArguments:
-    """Batch geometry (micro-batch, sequence length, accumulation), stop criteria, seed, clipping, gradient checkpointing, ZeRO stage, native loader, CUDA-graph capture, lagged logging, CPU run, MoE aux loss."""
+    """Batch geometry (micro-batch, sequence length, accumulation), stop criteria, seed, clipping, gradient checkpointing, ZeRO stage, native loader, CUDA-graph capture, lagged logging, periodic evaluation, CPU run, MoE aux loss."""
     batch_size: int = field(default=64, metadata={"help": "Training batch size"})
     test_batch_size: int = field(default=1000, metadata={"help": "Evaluation batch size"})
     micro_batch_size: int | None = field(default=None, metadata={"help": "Micro batch size"})
@@ -152,6 +152,10 @@ class TrainingArguments:
     zero_stage: int = field(default=0, metadata={"help": "1 = shard AdamW state and update over the gradient-sync group (trainer/zero.py)"})
     use_cuda_graph: bool = field(default=False, metadata={"help": "Replay the whole step from a CUDA graph (trainer/graphed.py)"})
     log_lag: int = field(default=1, metadata={"help": "Log step i after enqueueing step i+lag (0 = synchronous logging)"})
+    eval_interval: int = field(default=0, metadata={"help": "Evaluate the held-out loss every N optimiser steps (0 = never; not offered with pipeline parallelism)"})
+    eval_batches: int = field(default=8, metadata={"help": "Micro-batches per data rank in one evaluation (the same batches every time)"})
+    eval_token_file: str | None = field(default=None, metadata={"help": "Flat int32 token file (.npy / raw .bin) with the held-out tokens; default: --eval_split of the dataset, or synthetic data with another seed"})
+    eval_split: str = field(default="validation", metadata={"help": "Dataset split used for evaluation when no --eval_token_file is given"})
     total_train_steps: int | None = field(default=None, metadata={"help": "Stop after this many steps"})
     use_cpu: bool = field(default=False, metadata={"help": "Run on CPU with the gloo backend"})
     aux_loss: bool = field(default=True, metadata={"help": "Add the MoE load-balancing loss to the training loss"})
@@ -163,6 +167,10 @@ class TrainingArguments:
             raise ValueError(f"micro_batch_size must be >= 1, got {self.micro_batch_size}")
         if self.sequence_length is not None and self.sequence_length < 1:
             raise ValueError(f"sequence_length must be >= 1, got {self.sequence_length}")
+        if self.eval_interval < 0:
+            raise ValueError(f"eval_interval must be >= 0, got {self.eval_interval}")
+        if self.eval_batches < 1:
+            raise ValueError(f"eval_batches must be >= 1, got {self.eval_batches}")
 
 
 @dataclass

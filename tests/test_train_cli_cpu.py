@@ -141,3 +141,52 @@ def test_async_checkpoint_cli(tmp_path):
         assert any(f.startswith("weights_") and f.endswith(".pth") for f in files) and not any(f.endswith(".tmp") for f in files)
     out2 = _run(common + ["--total_train_steps", "5", "--resume_path", str(tmp_path / "4")])
     assert [s for s, _ in _losses(out2)] == [5]
+
+
+def test_periodic_evaluation_cli(tmp_path):
+    """``--eval_interval``: evaluation lines appear at the right steps, every token of the held-out set is
+    counted once under TP2+SP and CP2, the held-out loss under CP2 (same initial weights, same global batch) equals the
+    single-process one, evaluation leaves the training
+    trajectory untouched, and a token file works as the held-out set."""
+    import numpy as np
+
+    ev = re.compile(r"Eval \| Step:\s*(\d+)\s*\| Loss:\s*([\d.]+).*?Tokens:\s*(\d+)")
+    common = ["--model_name_or_path", "tiny-qwen3", "--num_attention_heads", "4", "--num_key_value_heads", "2",
+              "--total_train_steps", "4", "--save_frequency", "0"]
+    evalf = ["--eval_interval", "2", "--eval_batches", "2"]
+    tok = tmp_path / "heldout.npy"
+    np.save(tok, np.random.default_rng(0).integers(0, 2048, size=65 * 9, dtype=np.int32))
+    jobs = [(common + ["--work_dir", str(tmp_path / "plain")], 1),
+            (common + evalf + ["--work_dir", str(tmp_path / "single")], 1),
+            (common + evalf + ["--work_dir", str(tmp_path / "tp2"), "--tensor_parallel_size", "2", "--sequence_parallel", "true"], 2),
+            (common + evalf + ["--work_dir", str(tmp_path / "cp2"), "--context_parallel_size", "2"], 2),
+            (common + evalf + ["--work_dir", str(tmp_path / "file"), "--eval_token_file", str(tok)], 1),
+            (common + evalf + ["--work_dir", str(tmp_path / "dp2"), "--data_parallel_size", "2", "--micro_batch_size", "1"], 2)]
+    plain, single, tp2, cp2, from_file, dp2 = _run_many(jobs)
+
+    def train_losses(out):
+        return _losses("\n".join(l for l in out.splitlines() if "Eval |" not in l))
+
+    assert not ev.findall(plain)
+    assert train_losses(single) == train_losses(plain) and len(train_losses(plain)) == 4    # evaluation does not perturb training
+    e1 = [(int(s), float(l), int(t)) for s, l, t in ev.findall(single)]
+    assert [s for s, _, _ in e1] == [2, 4] and all(t == 2 * 2 * 64 for _, _, t in e1), single[-1500:]
+    for name, out in (("tp2", tp2), ("cp2", cp2), ("dp2", dp2)):
+        e = [(int(s), float(l), int(t)) for s, l, t in ev.findall(out)]
+        assert [(s, t) for s, _, t in e] == [(s, t) for s, _, t in e1], (name, out[-1500:])
+        if name in ("cp2", "dp2"):                                 # same initial weights, same global batch: same model
+            assert all(abs(a[1] - b[1]) < 2e-3 for a, b in zip(e, e1)), (name, e, e1)
+        else:                                                      # tensor-parallel shards are seeded per rank: another model
+            assert all(0.0 < l < 12.0 for _, l, _ in e), (name, e)
+    ef = [(int(s), float(l), int(t)) for s, l, t in ev.findall(from_file)]
+    assert [s for s, _, _ in ef] == [2, 4] and ef[0][2] == 2 * 2 * 64 and all(0 < l < 12 for _, l, _ in ef)
+    assert train_losses(from_file) == train_losses(plain)
+
+
+def test_evaluation_flags_are_validated():
+    from scaletorch_b200.trainer import ScaleTorchArguments
+
+    with pytest.raises(ValueError, match="eval_interval"):
+        ScaleTorchArguments(model_name_or_path="tiny-llama", eval_interval=-1)
+    with pytest.raises(ValueError, match="eval_batches"):
+        ScaleTorchArguments(model_name_or_path="tiny-llama", eval_batches=0)

@@ -147,6 +147,31 @@ def build_data_loader(config, model_config, device):
         seed=config.seed)
 
 
+def build_eval_loader(config, model_config, device):
+    """The held-out loader of ``--eval_interval``: ``--eval_token_file`` windows, else the dataset's ``--eval_split``, else
+    (synthetic data) sequences drawn with another seed than the training stream.  Never shuffled; ``None`` when evaluation
+    is off or the layout has pipeline stages (the loss lives on the last stage only; evaluate a converted checkpoint)."""
+    if getattr(config, "eval_interval", 0) <= 0:
+        return None
+    if config.pipeline_parallel_size > 1:
+        rank_print("--eval_interval is ignored with pipeline parallelism (use tools/convert_checkpoint.py + tools/evaluate.py)")
+        return None
+    dataset = None
+    if config.eval_token_file:
+        from scaletorch_b200.data.dataloader import TokenWindows, load_tokens
+
+        dataset = TokenWindows(load_tokens(config.eval_token_file), config.sequence_length)
+    synthetic = dataset is None and (config.synthetic_data or getattr(config, "native_loader", False) and not config.dataset_name)
+    return MicroBatchDataLoader(
+        micro_batch_size=config.micro_batch_size, sequence_length=config.sequence_length,
+        dataset_name=config.dataset_name, tokenizer_name_or_path=config.tokenizer_name_or_path
+        if config.tokenizer_name_or_path != "facebook/opt-125m" else config.model_name_or_path,
+        device=device, num_workers=0, num_proc=config.num_proc, subset_name=config.subset_name, split=config.eval_split,
+        pin_memory=config.pin_memory, synthetic=synthetic, vocab_size=model_config.vocab_size, seed=config.seed + 7919,
+        num_samples=None if not synthetic else max(4096, 8 * config.eval_batches * config.micro_batch_size),
+        dataset=dataset, shuffle=False)
+
+
 def main(argv=None) -> None:
     world_size, monitor, run = 1, None, None
     try:
@@ -209,6 +234,15 @@ def main(argv=None) -> None:
         if config.use_cuda_graph and GraphedTrainStep.supported(config, optimizer, model):
             graphed = GraphedTrainStep(model, optimizer, config, device)
             rank_print("whole-step CUDA graph replay enabled", is_print_rank=log_rank)
+        from scaletorch_b200.trainer.evaluation import PeriodicEvaluator, format_eval_line
+
+        def report_eval(st, result):
+            rank_print(format_eval_line(st, result), is_print_rank=log_rank)
+            if run is not None:
+                run.log({"eval_loss": result["loss"], "eval_perplexity": result["perplexity"]}, step=st)
+
+        evaluator = PeriodicEvaluator(model, build_eval_loader(config, model_config, device), device,
+                                      getattr(config, "eval_interval", 0), getattr(config, "eval_batches", 8), report_eval)
         stopper = StopOnSignal(getattr(config, "save_on_signal", False), getattr(config, "signal_check_interval", 10), world_size)
         monitor.start()
         max_steps = config.total_train_steps or float("inf")
@@ -260,6 +294,11 @@ def main(argv=None) -> None:
             while len(pending) > log_lag:
                 flush_one()
             watchdog.beat(step)
+            if evaluator.due(step):
+                while pending:                            # the training line of this step goes out before the eval line
+                    flush_one()
+                evaluator.run(step)
+                watchdog.beat(step)
             if config.save_model_checkpoint and config.save_frequency > 0 and step % config.save_frequency == 0:
                 out_dir = Path(config.work_dir) / f"{step}"
                 ckpt.save_checkpoint(model, optimizer, step, trained_tokens, str(out_dir),

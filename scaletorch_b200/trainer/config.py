@@ -179,7 +179,8 @@ class CheckpointArguments:
     work_dir: str = field(default="./work_dir", metadata={"help": "Directory to save checkpoints"})
     save_model_checkpoint: bool = field(default=True, metadata={"help": "Whether to save model checkpoints"})
     save_frequency: int = field(default=300, metadata={"help": "Checkpoint frequency in steps (0 = never)"})
-    resume_path: str = field(default="", metadata={"help": "Checkpoint directory to resume from"})
+    resume_path: str = field(default="", metadata={"help": "Checkpoint directory to resume from; 'latest' = the newest complete checkpoint under --work_dir (none: start from scratch)"})
+    keep_last_checkpoints: int = field(default=0, metadata={"help": "Keep only the N newest complete checkpoints under --work_dir, delete older ones after each save (0 = keep all)"})
     save_on_signal: bool = field(default=False, metadata={"help": "On SIGTERM / SIGUSR1 (preemption) finish the current step, let all ranks agree, write a checkpoint and exit 0"})
     signal_check_interval: int = field(default=10, metadata={"help": "With --save_on_signal: ranks compare their stop flags every this many steps (one 8-byte gloo all-reduce)"})
     async_checkpoint: bool = field(default=False, metadata={"help": "Write checkpoints on a background thread: the step only pays for the copy of the state to host memory"})

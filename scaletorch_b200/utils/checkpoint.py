@@ -320,6 +320,63 @@ def export_hf_state_dict(model: nn.Module, model_config: Any) -> dict[str, torch
 
 
 # ------------------------------------------------------------------ training checkpoints
+def find_complete_checkpoints(work_dir: str) -> list[tuple[int, str]]:
+    """``[(step, path)]`` of the checkpoint directories ``work_dir/<step>`` that hold a full set of shard files, oldest
+    first.  A directory with a ``*.tmp`` file (a writer was interrupted) or with fewer ``weights_*.pth`` files than the
+    fullest one (some ranks had not written yet when the job died) does not count."""
+    found = []
+    if not os.path.isdir(work_dir):
+        return []
+    for name in os.listdir(work_dir):
+        path = os.path.join(work_dir, name)
+        if name.isdigit() and os.path.isdir(path):
+            files = os.listdir(path)
+            shards = [f for f in files if f.startswith("weights_") and f.endswith(".pth")]
+            if shards and not any(f.endswith(".tmp") for f in files):
+                found.append((int(name), path, len(shards)))
+    if not found:
+        return []
+    found.sort()
+    full = max(n for _, _, n in found)
+    return [(s, p) for s, p, n in found if n == full]
+
+
+def resolve_resume_path(resume_path: str, work_dir: str) -> str:
+    """``--resume_path latest`` (or ``auto``) -> the newest complete checkpoint under ``work_dir`` (``""`` = start from
+    scratch when there is none); any other value is returned unchanged."""
+    if resume_path not in ("latest", "auto"):
+        return resume_path
+    complete = find_complete_checkpoints(work_dir)
+    return complete[-1][1] if complete else ""
+
+
+def prune_checkpoints(work_dir: str, keep: int, protect: str | None = None) -> list[str]:
+    """Delete all but the ``keep`` newest COMPLETE checkpoints under ``work_dir`` (``keep <= 0``: keep everything).
+    ``protect`` (the directory being written right now) is never touched, and incomplete directories older than the newest
+    complete one are removed as debris.  Returns the deleted paths.  Call it from ONE process (global rank 0)."""
+    import shutil
+
+    if keep <= 0:
+        return []
+    complete = find_complete_checkpoints(work_dir)
+    doomed = [p for _, p in complete[:-keep]] if len(complete) > keep else []
+    if complete and os.path.isdir(work_dir):
+        newest = complete[-1][0]
+        keep_paths = {p for _, p in complete}
+        for name in os.listdir(work_dir):
+            path = os.path.join(work_dir, name)
+            if name.isdigit() and os.path.isdir(path) and path not in keep_paths and int(name) < newest:
+                doomed.append(path)
+    protect = os.path.abspath(protect) if protect else None
+    deleted = []
+    for path in doomed:
+        if protect and os.path.abspath(path) == protect:
+            continue
+        shutil.rmtree(path, ignore_errors=True)
+        deleted.append(path)
+    return deleted
+
+
 class CheckpointManager:
     """Per-(tp, pp, ep) ``torch.save`` checkpoints under ``work_dir/<step>/`` (reference ``checkpoint.py:467-560``)."""
 

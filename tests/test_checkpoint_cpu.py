@@ -396,3 +396,49 @@ def test_async_save_reports_write_errors(tmp_path, monkeypatch):
     with pytest.raises(RuntimeError, match="disk full"):
         ck.wait()
     ck.wait()                                                     # reported once
+
+
+def _fake_ckpt(root, step, shards=2, tmp=False):
+    d = root / str(step)
+    d.mkdir(parents=True)
+    for i in range(shards):
+        (d / f"weights_tp_rank_world_size={i}_2_pp_rank_world_size=0_1.pth").write_bytes(b"x")
+    if tmp:
+        (d / "weights_tp_rank_world_size=1_2_pp_rank_world_size=0_1.pth.tmp").write_bytes(b"x")
+    return str(d)
+
+
+def test_complete_checkpoint_discovery_latest_and_pruning(tmp_path):
+    from scaletorch_b200.utils.checkpoint import find_complete_checkpoints, prune_checkpoints, resolve_resume_path
+
+    assert find_complete_checkpoints(str(tmp_path / "nope")) == [] and resolve_resume_path("latest", str(tmp_path / "nope")) == ""
+    assert resolve_resume_path("/some/dir", str(tmp_path)) == "/some/dir" and resolve_resume_path("", str(tmp_path)) == ""
+    p2, p4, p6 = (_fake_ckpt(tmp_path, s) for s in (2, 4, 6))
+    half = _fake_ckpt(tmp_path, 8, shards=1)                      # one rank had not written yet
+    torn = _fake_ckpt(tmp_path, 10, tmp=True)                     # a writer was interrupted
+    (tmp_path / "logs").mkdir()
+    (tmp_path / "3").write_text("a file, not a checkpoint")
+    assert find_complete_checkpoints(str(tmp_path)) == [(2, p2), (4, p4), (6, p6)]
+    assert resolve_resume_path("latest", str(tmp_path)) == p6 and resolve_resume_path("auto", str(tmp_path)) == p6
+    assert prune_checkpoints(str(tmp_path), 0) == []
+    # keep the two newest complete ones; the directory being written is protected; newer incomplete ones are left alone
+    assert prune_checkpoints(str(tmp_path), 2, protect=torn) == [p2]
+    assert sorted(os.listdir(tmp_path)) == ["10", "3", "4", "6", "8", "logs"]
+    # an incomplete directory OLDER than the newest complete checkpoint is debris
+    old_torn = _fake_ckpt(tmp_path, 5, tmp=True)
+    assert prune_checkpoints(str(tmp_path), 2) == [old_torn]
+    assert prune_checkpoints(str(tmp_path), 1) == [p4] and find_complete_checkpoints(str(tmp_path)) == [(6, p6)]
+    assert os.path.isdir(half) and os.path.isdir(torn)
+
+
+def test_supervisor_and_trainer_agree_on_complete_checkpoints(tmp_path):
+    import importlib.util
+
+    from scaletorch_b200.utils.checkpoint import find_complete_checkpoints
+
+    spec = importlib.util.spec_from_file_location("supervise", os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools", "supervise.py"))
+    sup = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(sup)
+    for s, kw in ((2, {}), (4, {"shards": 1}), (6, {}), (8, {"tmp": True})):
+        _fake_ckpt(tmp_path, s, **kw)
+    assert sup.complete_checkpoints(str(tmp_path)) == find_complete_checkpoints(str(tmp_path)) == [(2, str(tmp_path / "2")), (6, str(tmp_path / "6"))]

@@ -190,3 +190,23 @@ def test_evaluation_flags_are_validated():
         ScaleTorchArguments(model_name_or_path="tiny-llama", eval_interval=-1)
     with pytest.raises(ValueError, match="eval_batches"):
         ScaleTorchArguments(model_name_or_path="tiny-llama", eval_batches=0)
+
+
+def test_checkpoint_retention_and_resume_latest(tmp_path):
+    """``--keep_last_checkpoints 2`` leaves the two newest checkpoints; ``--resume_path latest`` continues from the newest one
+    (and starts from scratch in an empty work directory) with the same losses as an uninterrupted run."""
+    common = ["--model_name_or_path", "tiny-llama", "--save_frequency", "2", "--log_lag", "0",
+              "--lr_scheduler_type", "step", "--step_size", "1000"]       # the schedule must not depend on total steps
+    full = _losses(_run(common + ["--total_train_steps", "10", "--work_dir", str(tmp_path / "full"), "--save_frequency", "0"]))
+    wd = tmp_path / "wd"
+    first = _run(common + ["--total_train_steps", "8", "--work_dir", str(wd), "--keep_last_checkpoints", "2",
+                           "--resume_path", "latest"])          # nothing to resume from yet: starts at step 1
+    assert [s for s, _ in _losses(first)] == list(range(1, 9))
+    assert sorted(d for d in os.listdir(wd) if d.isdigit()) == ["6", "8"], os.listdir(wd)
+    second = _run(common + ["--total_train_steps", "10", "--work_dir", str(wd), "--keep_last_checkpoints", "2",
+                            "--resume_path", "latest"])
+    assert "Loaded checkpoint at step 8" in second
+    got = _losses(second)
+    assert [s for s, _ in got] == [9, 10]
+    assert all(abs(a[1] - b[1]) < 2e-3 for a, b in zip(got, full[8:])), (got, full[8:])
+    assert sorted(d for d in os.listdir(wd) if d.isdigit()) == ["10", "8"]

@@ -31,7 +31,9 @@ import time
 
 
 def complete_checkpoints(work_dir: str) -> list[tuple[int, str]]:
-    """``[(step, path)]`` of checkpoint directories that hold a full set of shard files, oldest first."""
+    """``[(step, path)]`` of checkpoint directories that hold a full set of shard files, oldest first.  Same rule as
+    ``scaletorch_b200.utils.checkpoint.find_complete_checkpoints`` (``--resume_path latest``), restated here so that the
+    supervisor process never imports torch; ``tests/test_supervise_cpu.py`` checks that the two agree."""
     found = []
     if not os.path.isdir(work_dir):
         return found

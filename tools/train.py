@@ -209,6 +209,9 @@ def main(argv=None) -> None:
         ckpt = CheckpointManager(async_save=getattr(config, "async_checkpoint", False))
         monitor = PerformanceMonitor(config=config, log_dir=config.work_dir)
         trained_tokens, step = 0, 0
+        from scaletorch_b200.utils.checkpoint import prune_checkpoints, resolve_resume_path
+
+        config.resume_path = resolve_resume_path(config.resume_path, config.work_dir)   # 'latest' -> newest complete one
         if config.resume_path:
             step, trained_tokens = ckpt.load_checkpoint(model, optimizer, config.resume_path)
             sched_path = os.path.join(config.resume_path, "scheduler.pt")
@@ -305,6 +308,10 @@ def main(argv=None) -> None:
                                      extra={"data_loader": data_loader.state_dict()})
                 if log_rank:
                     torch.save(lr_scheduler.state_dict(), out_dir / "scheduler.pt")
+                if global_rank == 0 and getattr(config, "keep_last_checkpoints", 0) > 0:
+                    # older COMPLETE checkpoints only; the one being written (other ranks may still be at it) is protected
+                    for gone in prune_checkpoints(config.work_dir, config.keep_last_checkpoints, protect=str(out_dir)):
+                        logger.info("removed old checkpoint %s", gone)
             if step >= max_steps:
                 break
             if stopper.should_stop(step):

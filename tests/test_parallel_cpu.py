@@ -605,6 +605,18 @@ def _replica_worker(rank, world, name, layout):
                 n_rep += 1
     if tp > 1 or ep > 1:
         assert n_rep > 3 and n_shard > 1, (n_rep, n_shard)
+    # the memory planner cuts a meta model with the same functions: its per-rank parameter counts must be the real ones
+    import importlib.util
+    import os
+
+    spec = importlib.util.spec_from_file_location("plan_memory", os.path.join(os.path.dirname(os.path.dirname(
+        os.path.abspath(__file__))), "tools", "plan_memory.py"))
+    planner = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(planner)
+    want = planner.stage_parameters(mc, tp, pp, ep, pgm.pp_rank)
+    got_expert = sum(p.numel() for k, p in raw.named_parameters() if ".experts." in k)
+    got_dense = sum(p.numel() for k, p in raw.named_parameters() if ".experts." not in k)
+    assert (want["dense"], want["expert"]) == (got_dense, got_expert), (rank, want, got_dense, got_expert)
     if pp > 1 and mc.tie_word_embeddings:
         H, V = mc.hidden_size, mc.vocab_size // tp
         w = raw.embedding.weight if raw.is_first else (raw.final_proj.weight if raw.is_last else torch.zeros(V, H))

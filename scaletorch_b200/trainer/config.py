@@ -245,6 +245,7 @@ def validate_config(config: ScaleTorchArguments, world_size: int) -> None:
 
 # --------------------------------------------------------------------------- model config resolution
 _CONFIG_DIR = os.path.join(os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))), "configs")
+_PACKAGED_CONFIG_DIR = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "configs")   # pip-installed copy
 
 
 # keys a config.json must spell out for the fast path below; anything less goes through ``AutoConfig`` so that the
@@ -296,7 +297,8 @@ def resolve_model_config(name_or_path: str, quiet: bool = False):
     GPU box has no network) or, last, the HF hub name: a :class:`LocalModelConfig` when the file spells out every field of
     its family (all vendored configs do), otherwise the ``transformers.PretrainedConfig`` that ``AutoConfig`` builds
     (``SCALETORCH_B200_HF_AUTOCONFIG=1`` forces that path)."""
-    candidates = [name_or_path, os.path.join(_CONFIG_DIR, name_or_path), os.path.join(_CONFIG_DIR, os.path.basename(name_or_path.rstrip("/")))]
+    base = os.path.basename(name_or_path.rstrip("/"))
+    candidates = [name_or_path] + [os.path.join(d, n) for d in (_CONFIG_DIR, _PACKAGED_CONFIG_DIR) for n in (name_or_path, base)]
     for c in candidates:
         if os.path.isfile(os.path.join(c, "config.json")):
             if os.environ.get("SCALETORCH_B200_HF_AUTOCONFIG", "0") != "1":

@@ -19,6 +19,13 @@ class BuildWithNative(build_py):
             except Exception as e:  # no nvcc on this machine: install the Python layer only
                 print(f"warning: native library not built ({e}); CUDA ops will raise until it is")
         super().run()
+        # the vendored model configs live at the repository root; an installed package finds them under scaletorch_b200/configs
+        here = os.path.dirname(os.path.abspath(__file__))
+        src = os.path.join(here, "configs")
+        if os.path.isdir(src):
+            import shutil
+
+            shutil.copytree(src, os.path.join(self.build_lib, "scaletorch_b200", "configs"), dirs_exist_ok=True)
 
 
 setup(cmdclass={"build_py": BuildWithNative})

@@ -31,7 +31,11 @@ def test_parameter_counts_of_the_vendored_models():
 def test_headline_and_target_layouts_fit_and_one_gpu_32b_does_not():
     assert pm.plan("Qwen3-0.6B", micro_batch_size=2, sequence_length=2048)["fits"]
     assert pm.plan("Qwen3-8B", tp=2, cp=2, dp=2, sp=True, sequence_length=4096)["fits"]
-    assert pm.plan("Qwen3-30B-A3B", ep=8, sequence_length=4096)["fits"]
+    # dropless EP8 sizes every row-padded activation for the worst case (ep x T x k rows) in all 48 layers: it does not fit,
+    # which is what happened on the box -- the EP8 run in profiles/ used capacity factor 2.0, and that fits
+    assert not pm.plan("Qwen3-30B-A3B", ep=8, sequence_length=4096)["fits"]
+    assert pm.plan("Qwen3-30B-A3B", ep=8, sequence_length=4096, ep_capacity_factor=2.0)["fits"]
+    assert pm.plan("Qwen3-30B-A3B", ep=8, sequence_length=4096, gradient_checkpointing=True)["fits"]
     assert pm.plan("Qwen3-32B", tp=4, pp=2, ga=8, sp=True, sequence_length=4096)["fits"]
     big = pm.plan("Qwen3-32B", sequence_length=4096)
     assert not big["fits"] and big["stages"][0]["fraction_of_hbm"] > 2.0

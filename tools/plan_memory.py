@@ -62,7 +62,17 @@ def stage_parameters(cfg, tp: int, pp: int, ep: int, stage: int) -> dict:
     return {"dense": dense, "expert": expert}
 
 
-def layer_activation_bytes(cfg, tokens: int, tp: int, sp: bool, is_moe: bool) -> int:
+def ep_rows_cap(cfg, tokens: int, ep: int, capacity_factor: float | None) -> int:
+    """Rows of the expert-major padded layout on one EP rank (``fused_ep.fused_moe_ep``): dropless = the worst case
+    ``ep x T x k`` unless a capacity factor bounds it; every expert's segment is padded to 128 rows."""
+    k = cfg.num_experts_per_tok
+    cf = float(ep) if capacity_factor is None else min(float(capacity_factor), float(ep))
+    e_local = cfg.num_experts // ep
+    return (int(cf * tokens * k) + e_local * 127 + 127) // 128 * 128
+
+
+def layer_activation_bytes(cfg, tokens: int, tp: int, sp: bool, is_moe: bool, ep: int = 1,
+                           ep_capacity_factor: float | None = None) -> int:
     """Bytes one decoder layer keeps for backward for ``tokens`` local tokens (bf16 unless noted)."""
     H = cfg.hidden_size
     hd = getattr(cfg, "head_dim", None) or H // cfg.num_attention_heads
@@ -76,7 +86,8 @@ def layer_activation_bytes(cfg, tokens: int, tp: int, sp: bool, is_moe: bool) ->
     b += tokens * nq * hd * 2 + tokens * nq * 4               # attention output, LSE (fp32)
     if is_moe:
         k, inter = cfg.num_experts_per_tok, cfg.moe_intermediate_size
-        rows = tokens * k
+        # with expert parallelism the row-padded tensors have the STATIC capacity of the receive region, not T x k
+        rows = ep_rows_cap(cfg, tokens, ep, ep_capacity_factor) if ep > 1 else tokens * k
         b += tokens * cfg.num_experts * 4                     # router probabilities (fp32)
         b += rows * H * 2 * 2                                 # permuted expert inputs and outputs
         b += rows * 3 * inter * 2                             # gate|up output + SwiGLU output
@@ -87,7 +98,7 @@ def layer_activation_bytes(cfg, tokens: int, tp: int, sp: bool, is_moe: bool) ->
 
 
 def plan(model: str, tp=1, pp=1, cp=1, dp=1, ep=1, micro_batch_size=1, sequence_length=4096, ga=1, sp=False,
-         gradient_checkpointing=False, zero_stage=None, window_mb=1024, hbm_gb=180.0) -> dict:
+         gradient_checkpointing=False, zero_stage=None, window_mb=1024, hbm_gb=180.0, ep_capacity_factor=None) -> dict:
     cfg = resolve_model_config(model)
     if cfg.num_attention_heads % tp or cfg.num_key_value_heads % tp:
         raise SystemExit(f"tp={tp} must divide the head counts ({cfg.num_attention_heads} / {cfg.num_key_value_heads})")
@@ -113,8 +124,8 @@ def plan(model: str, tp=1, pp=1, cp=1, dp=1, ep=1, micro_batch_size=1, sequence_
         else:
             opt = 8 * P
         layer_ids = distribute_layers(cfg.num_hidden_layers, pp, s)
-        per_layer = [layer_activation_bytes(cfg, tokens, tp, sp, bool(E) and i not in mlp_only and (i + 1) % step == 0)
-                     for i in layer_ids]
+        per_layer = [layer_activation_bytes(cfg, tokens, tp, sp, bool(E) and i not in mlp_only and (i + 1) % step == 0, ep,
+                                            ep_capacity_factor) for i in layer_ids]
         in_flight = min(pp - s, ga) if pp > 1 else 1           # 1F1B: stage s holds up to pp - s micro-batches
         t_res = tokens // tp if sp else tokens
         if gradient_checkpointing:
@@ -128,8 +139,7 @@ def plan(model: str, tp=1, pp=1, cp=1, dp=1, ep=1, micro_batch_size=1, sequence_
         if cp > 1:
             windows += window_mb << 20                          # CP group window (K/V blocks, fp32 dK/dV accumulators)
         if ep > 1:
-            rows = ep * tokens * cfg.num_experts_per_tok        # dropless worst case: every pair of every rank lands here
-            windows += 2 * rows * cfg.hidden_size * 2           # receive + return regions
+            windows += 2 * ep_rows_cap(cfg, tokens, ep, ep_capacity_factor) * cfg.hidden_size * 2    # receive + return regions
         total = 2 * P + 4 * P + opt + act + logits + windows
         stages.append({"stage": s, "layers": len(layer_ids), "params": P, "params_expert": n["expert"],
                        "bytes": {"params_bf16": 2 * P, "grads_fp32": 4 * P, "adamw_state": int(opt), "activations_est": int(act),
@@ -142,6 +152,7 @@ def plan(model: str, tp=1, pp=1, cp=1, dp=1, ep=1, micro_batch_size=1, sequence_
             "sequence_parallel": sp, "gradient_checkpointing": gradient_checkpointing,
             "optimizer": ("zero1 (c10d)" if zero_stage == 1 else "zero1 on peer memory (dense sharded)" if peer_zero and zero_stage is None
                           else "replicated AdamW"),
+            "ep_capacity_factor": (None if ep == 1 else ("dropless" if ep_capacity_factor is None else ep_capacity_factor)),
             "hbm_gb": hbm_gb, "stages": stages, "worst_stage": worst["stage"], "fits": all(st["fits"] for st in stages)}
 
 
@@ -173,12 +184,14 @@ def main(argv=None) -> int:
     ap.add_argument("--sp", action="store_true", help="sequence parallelism (with tp > 1)")
     ap.add_argument("--gradient_checkpointing", action="store_true")
     ap.add_argument("--zero_stage", type=int, default=None, choices=(0, 1), help="default: what the trainer picks for the layout")
+    ap.add_argument("--ep_capacity_factor", type=float, default=None,
+                    help="receive capacity of the EP path as a multiple of tokens x top_k (default: dropless = ep)")
     ap.add_argument("--window_mb", type=int, default=int(os.environ.get("SCALETORCH_B200_SYMM_WINDOW_MB", "1024")))
     ap.add_argument("--hbm_gb", type=float, default=180.0)
     ap.add_argument("--json", action="store_true")
     a = ap.parse_args(argv)
     p = plan(a.model, a.tp, a.pp, a.cp, a.dp, a.ep, a.micro_batch_size, a.sequence_length, a.ga, a.sp and a.tp > 1,
-             a.gradient_checkpointing, a.zero_stage, a.window_mb, a.hbm_gb)
+             a.gradient_checkpointing, a.zero_stage, a.window_mb, a.hbm_gb, a.ep_capacity_factor)
     print(json.dumps(p) if a.json else render(p))
     return 0 if p["fits"] else 1
 

@@ -81,3 +81,18 @@ def test_invalid_layouts_are_refused_and_the_cli_prints_a_table(capsys):
     assert pm.main(["--model", "Qwen3-32B", "--json"]) == 1
     d = json.loads(capsys.readouterr().out)
     assert d["fits"] is False and d["layout"]["world"] == 1 and d["stages"][0]["layers"] == 64
+
+
+def test_suggest_lists_only_legal_layouts_that_fit():
+    found = pm.suggest("Qwen3-32B", 8, sequence_length=4096)
+    assert found and all(f["tp"] * f["pp"] * f["cp"] * f["ep"] * f["dp"] == 8 for f in found)
+    assert all(f["ep"] == 1 for f in found)                                  # a dense model has no expert axis
+    assert not any(f["dp"] == 8 for f in found)                              # 32B does not fit one GPU's 180 GB as pure DP
+    assert all(f["worst_fraction_of_hbm"] <= 1.0 for f in found)
+    assert found[0]["combination_covered_by_tests"] and found[0]["dp"] == max(f["dp"] for f in found)
+    assert {(f["tp"], f["pp"]) for f in found} >= {(4, 2), (8, 1), (2, 4)}
+    small = pm.suggest("Qwen3-0.6B", 8, micro_batch_size=2, sequence_length=2048)
+    assert small[0] == {**small[0], "dp": 8, "tp": 1, "pp": 1, "cp": 1, "ep": 1}
+    moe = pm.suggest("Qwen3-30B-A3B", 8, sequence_length=4096, ep_capacity_factor=2.0)
+    assert any(f["ep"] == 8 for f in moe) and all(128 % f["ep"] == 0 and f["tp"] <= 4 for f in moe)   # 4 kv heads bound tp
+    assert pm.main(["--model", "Qwen3-8B", "--suggest", "--gpus", "2", "--json"]) == 0

@@ -156,6 +156,44 @@ def plan(model: str, tp=1, pp=1, cp=1, dp=1, ep=1, micro_batch_size=1, sequence_
             "hbm_gb": hbm_gb, "stages": stages, "worst_stage": worst["stage"], "fits": all(st["fits"] for st in stages)}
 
 
+def suggest(model: str, gpus: int, **kw) -> list[dict]:
+    """Every layout of ``gpus`` GPUs (powers of two per axis) that is legal for the model and fits, most data-parallel
+    first (data parallelism is the cheapest axis on an NVSwitch node: docs/parallelism.md), then by memory.  A list of
+    candidates to measure, not a performance prediction."""
+    cfg = resolve_model_config(model)
+    E = getattr(cfg, "num_experts", 0) or 0
+    sizes = [n for n in (1, 2, 4, 8, 16, 32, 64) if n <= gpus]
+    found = []
+    for tp in sizes:
+        if cfg.num_attention_heads % tp or cfg.num_key_value_heads % tp:
+            continue
+        for pp in sizes:
+            if pp > cfg.num_hidden_layers:
+                continue
+            for cp in sizes:
+                if kw.get("sequence_length", 4096) % (2 * cp if cp > 1 else 1):
+                    continue
+                for ep in (sizes if E else [1]):
+                    if E and E % ep:
+                        continue
+                    used = tp * pp * cp * ep
+                    if used > gpus or gpus % used:
+                        continue
+                    dp = gpus // used
+                    try:
+                        p = plan(model, tp=tp, pp=pp, cp=cp, dp=dp, ep=ep, sp=tp > 1, **kw)
+                    except SystemExit:
+                        continue
+                    if p["fits"]:
+                        worst = max(st["fraction_of_hbm"] for st in p["stages"])
+                        # combinations whose training equality is pinned by tests/test_parallel_cpu.py (gloo) today
+                        covered = (cp == 1 and ep == 1) if pp > 1 else not (cp > 1 and ep > 1)
+                        found.append({"tp": tp, "pp": pp, "cp": cp, "ep": ep, "dp": dp, "worst_fraction_of_hbm": worst,
+                                      "optimizer": p["optimizer"], "combination_covered_by_tests": covered})
+    found.sort(key=lambda f: (not f["combination_covered_by_tests"], -f["dp"], f["tp"] * f["pp"] * f["cp"], f["worst_fraction_of_hbm"]))
+    return found
+
+
 def render(p: dict) -> str:
     lay = p["layout"]
     out = [f"{p['model']}  tp{lay['tp']} pp{lay['pp']} cp{lay['cp']} dp{lay['dp']} ep{lay['ep']} ({lay['world']} GPUs)  "
@@ -189,7 +227,21 @@ def main(argv=None) -> int:
     ap.add_argument("--window_mb", type=int, default=int(os.environ.get("SCALETORCH_B200_SYMM_WINDOW_MB", "1024")))
     ap.add_argument("--hbm_gb", type=float, default=180.0)
     ap.add_argument("--json", action="store_true")
+    ap.add_argument("--suggest", action="store_true", help="list every layout of --gpus GPUs that fits (ignores the axis flags)")
+    ap.add_argument("--gpus", type=int, default=8)
     a = ap.parse_args(argv)
+    if a.suggest:
+        found = suggest(a.model, a.gpus, micro_batch_size=a.micro_batch_size, sequence_length=a.sequence_length, ga=a.ga,
+                        gradient_checkpointing=a.gradient_checkpointing, zero_stage=a.zero_stage, window_mb=a.window_mb,
+                        hbm_gb=a.hbm_gb, ep_capacity_factor=a.ep_capacity_factor)
+        if a.json:
+            print(json.dumps(found))
+        else:
+            print(f"{a.model} on {a.gpus} GPUs, mbs {a.micro_batch_size} x S {a.sequence_length}: {len(found)} layouts fit in {a.hbm_gb:.0f} GB")
+            for f in found[:24]:
+                print(f"  dp{f['dp']:<3d} tp{f['tp']:<2d} pp{f['pp']:<2d} cp{f['cp']:<2d} ep{f['ep']:<2d}  worst stage {f['worst_fraction_of_hbm'] * 100:5.1f}% of HBM   {f['optimizer']}"
+                      + ("" if f["combination_covered_by_tests"] else "   (axis combination not covered by the equality tests)"))
+        return 0 if found else 1
     p = plan(a.model, a.tp, a.pp, a.cp, a.dp, a.ep, a.micro_batch_size, a.sequence_length, a.ga, a.sp and a.tp > 1,
              a.gradient_checkpointing, a.zero_stage, a.window_mb, a.hbm_gb, a.ep_capacity_factor)
     print(json.dumps(p) if a.json else render(p))

@@ -355,9 +355,9 @@ def _train_worker(rank, world, layout):
 
 
 @pytest.mark.parametrize("layout", [(2, 2, 1), (2, 1, 2), (1, 2, 2), (1, 2, 1, 2), (2, 1, 1, 2), (1, 2, 2, 1, 1),
-                                    (2, 1, 1, 2, 0, 1), (2, 1, 2, 1, 0, 0, 1), (2, 1, 1, 2, 0, 1, 1)],
+                                    (2, 1, 1, 2, 0, 1), (2, 1, 2, 1, 0, 0, 1), (2, 1, 1, 2, 0, 1, 1), (1, 1, 2, 2), (1, 1, 2, 2, 0, 1)],
                          ids=["tp2dp2", "tp2ep2", "dp2ep2", "cp2dp2", "tp2cp2", "dp2ep2-replicated", "tp2cp2-zigzag",
-                              "tp2ep2-recompute", "tp2cp2-zigzag-recompute"])
+                              "tp2ep2-recompute", "tp2cp2-zigzag-recompute", "cp2ep2", "cp2ep2-zigzag"])
 def test_mixed_layout_training_tracks_single_process(layout):
     run_distributed(_train_worker, 4, layout)
 
@@ -367,8 +367,8 @@ def test_3d_layout_tp2_cp2_dp2_tracks_single_process():
     run_distributed(_train_worker, 8, (2, 2, 1, 2))
 
 
-def _pp_train_worker(rank, world, tp, dp, tie):
-    """Pipeline stages (1F1B) combined with TP or DP, through clipped optimiser steps: the tied embedding / LM head lives on
+def _pp_train_worker(rank, world, tp, dp, tie, cp=1, ep=1):
+    """Pipeline stages (1F1B) combined with TP, DP or CP, through clipped optimiser steps: the tied embedding / LM head lives on
     both the first and the last stage and must be counted once in the global norm."""
     import re
 
@@ -381,12 +381,14 @@ def _pp_train_worker(rank, world, tp, dp, tie):
     from scaletorch_b200.trainer.optimizer import FusedAdamW
     from scaletorch_b200.utils.sharding import load_from_unsharded, shard_tensor
 
-    setup_process_group_manager(tp_size=tp, cp_size=1, pp_size=2, dp_size=dp)
-    cfg = TinyCfg(model_type="qwen3", num_hidden_layers=3, tie_word_embeddings=tie)
+    setup_process_group_manager(tp_size=tp, cp_size=cp, pp_size=2, dp_size=dp, ep_size=ep)
+    name = "qwen3_moe" if ep > 1 else "qwen3"
+    cfg = TinyCfg(model_type=name, num_hidden_layers=3, tie_word_embeddings=tie, router_aux_loss_coef=0.0)
     ctx = ParallelContext.from_pgm(sequence_parallel=tp > 1)
-    full, proto = _models(cfg, "qwen3", ctx)
+    full, proto = _models(cfg, name, ctx)
     par = PipelineParallel(proto, cfg)
-    load_from_unsharded(par, dict(full.named_parameters()), cfg, tp=tp, tp_rank=pgm.tp_rank, layer_ids=par.layer_ids)
+    load_from_unsharded(par, dict(full.named_parameters()), cfg, tp=tp, tp_rank=pgm.tp_rank, ep=ep, ep_rank=pgm.ep_rank,
+                        layer_ids=par.layer_ids)
     if tp > 1:
         mark_tp_partial_params(par, pgm.tp_group, ctx.sp)
     full_opt = FusedAdamW(get_store(full), lr=1e-2, weight_decay=0.0, max_grad_norm=0.05)
@@ -398,11 +400,11 @@ def _pp_train_worker(rank, world, tp, dp, tie):
     ga, mbs, S = 2, 2, 16
     torch.manual_seed(9)
     for step in range(3):
-        ids = torch.randint(0, cfg.vocab_size, (dp * ga * mbs, S + 1))
+        ids = torch.randint(0, cfg.vocab_size, (pgm.data_world_size * ga * mbs, S + 1))
         full_opt.zero_grad()
         full.loss(ids[:, :-1], ids[:, 1:]).backward()
         full_opt.step()
-        mine = ids[pgm.dp_rank * ga * mbs:(pgm.dp_rank + 1) * ga * mbs]
+        mine = ids[pgm.data_rank * ga * mbs:(pgm.data_rank + 1) * ga * mbs]      # EP ranks read distinct samples
 
         class Loader:
             gradient_accumulation_steps = ga
@@ -413,12 +415,16 @@ def _pp_train_worker(rank, world, tp, dp, tie):
             def __next__(self):
                 b = mine[self.i * mbs:(self.i + 1) * mbs]
                 self.i += 1
-                return {"input_ids": b[:, :-1].contiguous(), "target_ids": b[:, 1:].contiguous()}
+                x, y = b[:, :-1], b[:, 1:]
+                if cp > 1:                                       # contiguous context-parallel chunk of every sample
+                    n = S // cp
+                    x, y = x[:, pgm.cp_rank * n:(pgm.cp_rank + 1) * n], y[:, pgm.cp_rank * n:(pgm.cp_rank + 1) * n]
+                return {"input_ids": x.contiguous(), "target_ids": y.contiguous()}
 
         opt.zero_grad()
         if hasattr(model, "reset"):
             model.reset()
-        s_local = S // tp if ctx.sp else S
+        s_local = (S // tp if ctx.sp else S) // cp
         train_step_pipeline_1f1b(model, Loader(), (mbs, s_local, cfg.hidden_size), torch.device("cpu"), torch.float32)
         opt.step()
         assert abs(opt.grad_norm() - full_opt.grad_norm()) < 2e-3 * full_opt.grad_norm(), (
@@ -429,13 +435,15 @@ def _pp_train_worker(rank, world, tp, dp, tie):
         src = f"decoder_layers.{par.layer_ids[int(m.group(1))]}.{m.group(2)}" if m else n
         if src == "final_proj.weight" and tie:
             src = "embedding.weight"
-        want = shard_tensor(src, ref[src].detach(), cfg, tp, pgm.tp_rank, 1, 0)
+        want = shard_tensor(src, ref[src].detach(), cfg, tp, pgm.tp_rank, ep, pgm.ep_rank)
         assert rel_err(p.detach(), want) < 2e-3, f"{n}: {rel_err(p.detach(), want)}"
 
 
-@pytest.mark.parametrize("tp,dp,tie", [(1, 2, True), (2, 1, True), (2, 1, False)], ids=["pp2dp2-tied", "pp2tp2-tied", "pp2tp2"])
-def test_pipeline_mixed_layout_training_tracks_single_process(tp, dp, tie):
-    run_distributed(_pp_train_worker, 4, tp, dp, tie)
+@pytest.mark.parametrize("tp,dp,tie,cp,ep", [(1, 2, True, 1, 1), (2, 1, True, 1, 1), (2, 1, False, 1, 1), (1, 1, True, 2, 1),
+                                             (1, 1, False, 1, 2)],
+                         ids=["pp2dp2-tied", "pp2tp2-tied", "pp2tp2", "pp2cp2-tied", "pp2ep2"])
+def test_pipeline_mixed_layout_training_tracks_single_process(tp, dp, tie, cp, ep):
+    run_distributed(_pp_train_worker, 4, tp, dp, tie, cp, ep)
 
 
 # ------------------------------------------------------------------ HF checkpoint -> sharded parameters

@@ -367,6 +367,12 @@ def test_3d_layout_tp2_cp2_dp2_tracks_single_process():
     run_distributed(_train_worker, 8, (2, 2, 1, 2))
 
 
+@pytest.mark.parametrize("layout", [(2, 2, 2), (1, 2, 2, 2), (2, 1, 2, 2, 0, 1)], ids=["tp2dp2ep2", "dp2ep2cp2", "tp2ep2cp2-zigzag"])
+def test_3d_moe_layouts_track_single_process(layout):
+    """MoE triples on eight CPU processes: expert parallelism combined with two more axes."""
+    run_distributed(_train_worker, 8, layout)
+
+
 def _pp_train_worker(rank, world, tp, dp, tie, cp=1, ep=1):
     """Pipeline stages (1F1B) combined with TP, DP or CP, through clipped optimiser steps: the tied embedding / LM head lives on
     both the first and the last stage and must be counted once in the global norm."""

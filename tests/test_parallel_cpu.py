@@ -452,6 +452,13 @@ def test_pipeline_mixed_layout_training_tracks_single_process(tp, dp, tie, cp, e
     run_distributed(_pp_train_worker, 4, tp, dp, tie, cp, ep)
 
 
+@pytest.mark.parametrize("tp,dp,cp,ep", [(2, 2, 1, 1), (2, 1, 2, 1), (1, 2, 1, 2), (2, 1, 1, 2), (1, 2, 2, 1), (1, 1, 2, 2)],
+                         ids=["pp2tp2dp2", "pp2tp2cp2", "pp2dp2ep2", "pp2tp2ep2", "pp2dp2cp2", "pp2cp2ep2"])
+def test_pipeline_3d_layouts_track_single_process(tp, dp, cp, ep):
+    """Pipeline stages with two more axes on eight CPU processes (the shape of the reference's TP-PP-DP benchmark rows)."""
+    run_distributed(_pp_train_worker, 8, tp, dp, ep == 1, cp, ep)
+
+
 # ------------------------------------------------------------------ HF checkpoint -> sharded parameters
 def _hf_load_worker(rank, world, model_dir, layout, name):
     """Every rank materialises its TP / EP / PP shard from one HF-layout safetensors file; the shards must equal the

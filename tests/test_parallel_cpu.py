@@ -9,6 +9,22 @@ from dist_utils import TinyCfg, rel_err, run_distributed
 TOL = 2e-4
 
 
+def _big_host() -> bool:
+    """Sixteen / thirty-two single-threaded ranks want a few cores and ~0.4 GB each."""
+    import os
+
+    try:
+        import psutil
+
+        mem_ok = psutil.virtual_memory().available > 20e9
+    except Exception:
+        mem_ok = True
+    return (os.cpu_count() or 1) >= 8 and mem_ok
+
+
+_needs_big_host = pytest.mark.skipif(not _big_host(), reason="16- and 32-rank layouts need >= 8 cores and >= 20 GB of free memory")
+
+
 def _models(cfg, cls_name, ctx):
     from scaletorch_b200.models import Llama, Qwen3, Qwen3MoE
     from scaletorch_b200.parallel.context import ParallelContext
@@ -373,6 +389,12 @@ def test_3d_moe_layouts_track_single_process(layout):
     run_distributed(_train_worker, 8, layout)
 
 
+@_needs_big_host
+def test_4d_layout_tp2_cp2_dp2_ep2_tracks_single_process():
+    """All four non-pipeline axes at once on sixteen CPU processes (zig-zag CP, MoE)."""
+    run_distributed(_train_worker, 16, (2, 2, 2, 2, 0, 1))
+
+
 def _pp_train_worker(rank, world, tp, dp, tie, cp=1, ep=1):
     """Pipeline stages (1F1B) combined with TP, DP or CP, through clipped optimiser steps: the tied embedding / LM head lives on
     both the first and the last stage and must be counted once in the global norm."""
@@ -457,6 +479,19 @@ def test_pipeline_mixed_layout_training_tracks_single_process(tp, dp, tie, cp, e
 def test_pipeline_3d_layouts_track_single_process(tp, dp, cp, ep):
     """Pipeline stages with two more axes on eight CPU processes (the shape of the reference's TP-PP-DP benchmark rows)."""
     run_distributed(_pp_train_worker, 8, tp, dp, ep == 1, cp, ep)
+
+
+@_needs_big_host
+@pytest.mark.parametrize("tp,dp,cp,ep", [(2, 2, 2, 1), (2, 2, 1, 2)], ids=["pp2tp2dp2cp2", "pp2tp2dp2ep2"])
+def test_pipeline_4d_layouts_track_single_process(tp, dp, cp, ep):
+    """Pipeline stages with three more axes on sixteen CPU processes."""
+    run_distributed(_pp_train_worker, 16, tp, dp, ep == 1, cp, ep)
+
+
+@_needs_big_host
+def test_all_five_axes_at_once_track_single_process():
+    """PP2 x TP2 x CP2 x DP2 x EP2 on thirty-two CPU processes: the full ``[DP, PP, CP, EP, TP]`` grid."""
+    run_distributed(_pp_train_worker, 32, 2, 2, False, 2, 2)
 
 
 # ------------------------------------------------------------------ HF checkpoint -> sharded parameters

@@ -152,6 +152,7 @@ class TrainingArguments:
     zero_stage: int = field(default=0, metadata={"help": "1 = shard AdamW state and update over the gradient-sync group (trainer/zero.py)"})
     use_cuda_graph: bool = field(default=False, metadata={"help": "Replay the whole step from a CUDA graph (trainer/graphed.py)"})
     log_lag: int = field(default=1, metadata={"help": "Log step i after enqueueing step i+lag (0 = synchronous logging)"})
+    nonfinite_loss: str = field(default="abort", metadata={"help": "What to do when the logged loss is NaN / Inf: 'abort' (exit non-zero so that a supervisor resumes from the last checkpoint) or 'warn' (keep going, as the reference does)"})
     eval_interval: int = field(default=0, metadata={"help": "Evaluate the held-out loss every N optimiser steps (0 = never; not offered with pipeline parallelism)"})
     eval_batches: int = field(default=8, metadata={"help": "Micro-batches per data rank in one evaluation (the same batches every time)"})
     eval_token_file: str | None = field(default=None, metadata={"help": "Flat int32 token file (.npy / raw .bin) with the held-out tokens; default: --eval_split of the dataset, or synthetic data with another seed"})
@@ -167,6 +168,8 @@ class TrainingArguments:
             raise ValueError(f"micro_batch_size must be >= 1, got {self.micro_batch_size}")
         if self.sequence_length is not None and self.sequence_length < 1:
             raise ValueError(f"sequence_length must be >= 1, got {self.sequence_length}")
+        if self.nonfinite_loss not in ("abort", "warn"):
+            raise ValueError(f"nonfinite_loss must be 'abort' or 'warn', got {self.nonfinite_loss!r}")
         if self.eval_interval < 0:
             raise ValueError(f"eval_interval must be >= 0, got {self.eval_interval}")
         if self.eval_batches < 1:

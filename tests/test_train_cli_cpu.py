@@ -210,3 +210,20 @@ def test_checkpoint_retention_and_resume_latest(tmp_path):
     assert [s for s, _ in got] == [9, 10]
     assert all(abs(a[1] - b[1]) < 2e-3 for a, b in zip(got, full[8:])), (got, full[8:])
     assert sorted(d for d in os.listdir(wd) if d.isdigit()) == ["10", "8"]
+
+
+def test_nonfinite_loss_aborts_before_a_checkpoint_is_written(tmp_path):
+    """An exploding run stops with a non-zero exit code and a message that names the step; no checkpoint of the broken
+    weights is published; ``--nonfinite_loss warn`` keeps the reference's behaviour (log and continue)."""
+    boom = ["--model_name_or_path", "tiny-llama", "--learning_rate", "1e30", "--max_grad_norm", "0", "--total_train_steps", "6",
+            "--save_frequency", "2"]
+    out = _run(boom + ["--work_dir", str(tmp_path / "abort")], expect_rc=1)
+    m = re.search(r"non-finite loss \((nan|inf)\) at step (\d+)", out)
+    assert m and int(m.group(2)) == 2, out[-1500:]
+    assert not any(d.isdigit() for d in os.listdir(tmp_path / "abort")), os.listdir(tmp_path / "abort")
+    out = _run(boom + ["--work_dir", str(tmp_path / "warn"), "--nonfinite_loss", "warn", "--save_frequency", "0"])
+    assert "WARNING: non-finite loss" in out and len(_losses(out.replace("nan", "0.0"))) >= 1
+    from scaletorch_b200.trainer import ScaleTorchArguments
+
+    with pytest.raises(ValueError, match="nonfinite_loss"):
+        ScaleTorchArguments(model_name_or_path="tiny-llama", nonfinite_loss="ignore")

@@ -258,6 +258,13 @@ def main(argv=None) -> None:
             stats = monitor.resolve_iteration(handle)
             loss = loss_reader.pop()
             gn = norm_reader.pop() if gn == "reader" else gn
+            if loss != loss or loss in (float("inf"), float("-inf")):
+                # every rank reads the same (averaged) loss, so every rank takes the same branch
+                msg = f"non-finite loss ({loss}) at step {st}"
+                if getattr(config, "nonfinite_loss", "abort") == "abort":
+                    raise FloatingPointError(msg + ": aborting (--nonfinite_loss warn continues instead); resume from the "
+                                             "last checkpoint with a lower learning rate or inspect the data of this step")
+                rank_print("WARNING: " + msg, is_print_rank=log_rank)
             log_training_metrics(config, model_config, st, loss, lr_, gn, stats["iteration_time"], tokens_per_step, tokens_,
                                  num_params, world_size, logger=logger, wandb_run=run)
             if st % 50 == 0:
@@ -303,6 +310,8 @@ def main(argv=None) -> None:
                 evaluator.run(step)
                 watchdog.beat(step)
             if config.save_model_checkpoint and config.save_frequency > 0 and step % config.save_frequency == 0:
+                while pending:                            # know this step's loss before publishing its weights (non-finite -> abort)
+                    flush_one()
                 out_dir = Path(config.work_dir) / f"{step}"
                 ckpt.save_checkpoint(model, optimizer, step, trained_tokens, str(out_dir),
                                      extra={"data_loader": data_loader.state_dict()})
@@ -315,6 +324,8 @@ def main(argv=None) -> None:
             if step >= max_steps:
                 break
             if stopper.should_stop(step):
+                while pending:
+                    flush_one()
                 out_dir = Path(config.work_dir) / f"{step}"
                 if not (config.save_model_checkpoint and config.save_frequency > 0 and step % config.save_frequency == 0):
                     ckpt.save_checkpoint(model, optimizer, step, trained_tokens, str(out_dir),

@@ -482,13 +482,6 @@ def test_pipeline_3d_layouts_track_single_process(tp, dp, cp, ep):
 
 
 @_needs_big_host
-@pytest.mark.parametrize("tp,dp,cp,ep", [(2, 2, 2, 1), (2, 2, 1, 2)], ids=["pp2tp2dp2cp2", "pp2tp2dp2ep2"])
-def test_pipeline_4d_layouts_track_single_process(tp, dp, cp, ep):
-    """Pipeline stages with three more axes on sixteen CPU processes."""
-    run_distributed(_pp_train_worker, 16, tp, dp, ep == 1, cp, ep)
-
-
-@_needs_big_host
 def test_all_five_axes_at_once_track_single_process():
     """PP2 x TP2 x CP2 x DP2 x EP2 on thirty-two CPU processes: the full ``[DP, PP, CP, EP, TP]`` grid."""
     run_distributed(_pp_train_worker, 32, 2, 2, False, 2, 2)

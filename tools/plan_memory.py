@@ -188,9 +188,8 @@ def suggest(model: str, gpus: int, **kw) -> list[dict]:
                         worst = max(st["fraction_of_hbm"] for st in p["stages"])
                         # combinations whose training equality is pinned by tests/test_parallel_cpu.py (gloo) today
                         axes = {n for n, v in (("tp", tp), ("pp", pp), ("cp", cp), ("ep", ep), ("dp", dp)) if v > 1}
-                        # pairs, triples, the quadruples around TP x DP and all five axes together are pinned by tests
-                        covered = (len(axes) <= 3 or axes in ({"tp", "cp", "dp", "ep"}, {"pp", "tp", "dp", "cp"}, {"pp", "tp", "dp", "ep"})
-                                   or len(axes) == 5)
+                        # pairs, triples, TP x CP x DP x EP and all five axes together are pinned by tests
+                        covered = len(axes) <= 3 or axes == {"tp", "cp", "dp", "ep"} or len(axes) == 5
                         found.append({"tp": tp, "pp": pp, "cp": cp, "ep": ep, "dp": dp, "worst_fraction_of_hbm": worst,
                                       "optimizer": p["optimizer"], "combination_covered_by_tests": covered})
     found.sort(key=lambda f: (not f["combination_covered_by_tests"], -f["dp"], f["tp"] * f["pp"] * f["cp"], f["worst_fraction_of_hbm"]))

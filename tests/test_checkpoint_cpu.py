@@ -442,3 +442,48 @@ def test_supervisor_and_trainer_agree_on_complete_checkpoints(tmp_path):
     for s, kw in ((2, {}), (4, {"shards": 1}), (6, {}), (8, {"tmp": True})):
         _fake_ckpt(tmp_path, s, **kw)
     assert sup.complete_checkpoints(str(tmp_path)) == find_complete_checkpoints(str(tmp_path)) == [(2, str(tmp_path / "2")), (6, str(tmp_path / "6"))]
+
+
+def test_inspect_checkpoint_reports_and_gates(tmp_path, capsys):
+    """tools/inspect_checkpoint.py: a healthy checkpoint passes (exit 0) and is described; a missing shard, a leftover
+    temporary file or a NaN weight make it fail (exit 1) with the reason in the report."""
+    import importlib.util
+    import shutil
+
+    spec = importlib.util.spec_from_file_location("inspect_checkpoint", os.path.join(os.path.dirname(os.path.dirname(
+        os.path.abspath(__file__))), "tools", "inspect_checkpoint.py"))
+    ic = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(ic)
+    torch.manual_seed(0)
+    m = nn.Sequential(nn.Linear(4, 4), nn.Linear(4, 2))
+    opt = torch.optim.AdamW(m.parameters(), lr=1e-2)
+    m(torch.randn(3, 4)).sum().backward()
+    opt.step()
+    good = tmp_path / "7"
+    path = C.CheckpointManager().save_checkpoint(m, opt, 7, 7000, str(good), extra={"data_loader": {"batches_served": 14}})
+    assert ic.main([str(good)]) == 0
+    out = capsys.readouterr().out
+    assert "step 7, 7000 tokens" in out and "shards 1 / 1" in out and "OK: complete and finite" in out and "'batches_served': 14" in out
+    info = ic.inspect(str(good), list_tensors=True)
+    assert info["total_parameters_over_shards"] == sum(p.numel() for p in m.parameters()) == 30
+    assert {t["name"] for t in info["shards"][0]["tensors"]} == set(m.state_dict()) and info["shards"][0]["optimizer_bytes"] > 0
+    # the same file claimed to be shard 0 of a TP2 layout: shard 1 is missing
+    half = tmp_path / "8"
+    half.mkdir()
+    shutil.copy(path, half / "weights_tp_rank_world_size=0_2_pp_rank_world_size=0_1.pth")
+    assert ic.main([str(half), "--json"]) == 1
+    d = json.loads(capsys.readouterr().out)
+    assert d["missing_shards"] == [[1, 0, 0]] and d["shards_expected"] == 2
+    # a writer that died
+    torn = tmp_path / "9"
+    shutil.copytree(good, torn)
+    (torn / (os.path.basename(path) + ".tmp")).write_bytes(b"x")
+    assert ic.main([str(torn)]) == 1 and "TEMPORARY FILES" in capsys.readouterr().out
+    # diverged weights
+    with torch.no_grad():
+        m[0].weight[0, 0] = float("nan")
+    bad = tmp_path / "10"
+    C.CheckpointManager().save_checkpoint(m, opt, 10, 10000, str(bad))
+    assert ic.main([str(bad)]) == 1 and "NON-FINITE: ['0.weight']" in capsys.readouterr().out
+    with pytest.raises(SystemExit):
+        ic.inspect(str(tmp_path))

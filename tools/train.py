@@ -259,7 +259,8 @@ def main(argv=None) -> None:
             loss = loss_reader.pop()
             gn = norm_reader.pop() if gn == "reader" else gn
             if loss != loss or loss in (float("inf"), float("-inf")):
-                # every rank reads the same (averaged) loss, so every rank takes the same branch
+                # ranks that log a loss read the same averaged value and take the same branch; with pipeline stages only the
+                # last one sees it, and the launcher ends the other ranks when that one exits
                 msg = f"non-finite loss ({loss}) at step {st}"
                 if getattr(config, "nonfinite_loss", "abort") == "abort":
                     raise FloatingPointError(msg + ": aborting (--nonfinite_loss warn continues instead); resume from the "

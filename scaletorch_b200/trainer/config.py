@@ -183,6 +183,7 @@ class CheckpointArguments:
     save_model_checkpoint: bool = field(default=True, metadata={"help": "Whether to save model checkpoints"})
     save_frequency: int = field(default=300, metadata={"help": "Checkpoint frequency in steps (0 = never)"})
     resume_path: str = field(default="", metadata={"help": "Checkpoint directory to resume from; 'latest' = the newest complete checkpoint under --work_dir (none: start from scratch)"})
+    resume_reshard: bool = field(default=False, metadata={"help": "Allow --resume_path to point at a checkpoint written under another TP / PP / EP layout: the weights are merged and re-cut for this layout, step / token counters and the data position carry over, the optimiser moments restart from zero"})
     keep_last_checkpoints: int = field(default=0, metadata={"help": "Keep only the N newest complete checkpoints under --work_dir, delete older ones after each save (0 = keep all)"})
     save_on_signal: bool = field(default=False, metadata={"help": "On SIGTERM / SIGUSR1 (preemption) finish the current step, let all ranks agree, write a checkpoint and exit 0"})
     signal_check_interval: int = field(default=10, metadata={"help": "With --save_on_signal: ranks compare their stop flags every this many steps (one 8-byte gloo all-reduce)"})

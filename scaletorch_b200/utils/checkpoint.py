@@ -377,6 +377,50 @@ def prune_checkpoints(work_dir: str, keep: int, protect: str | None = None) -> l
     return deleted
 
 
+_SHARD_NAME = re.compile(r"weights_tp_rank_world_size=(\d+)_(\d+)_pp_rank_world_size=(\d+)_(\d+)(?:_ep_rank_world_size=(\d+)_(\d+))?\.pth$")
+
+
+def find_shards(ckpt_dir: str) -> tuple[dict[tuple[int, int, int], str], tuple[int, int, int]]:
+    """``{(tp_rank, pp_rank, ep_rank): path}`` and the layout ``(tp, pp, ep)`` found in ``ckpt_dir``."""
+    found: dict[tuple[int, int, int], str] = {}
+    layout = None
+    for f in sorted(os.listdir(ckpt_dir)):
+        m = _SHARD_NAME.match(f)
+        if not m:
+            continue
+        tr, tp, pr, pp = (int(m.group(i)) for i in range(1, 5))
+        er, ep = (int(m.group(5)), int(m.group(6))) if m.group(5) is not None else (0, 1)
+        if layout is None:
+            layout = (tp, pp, ep)
+        elif layout != (tp, pp, ep):
+            raise ValueError(f"{ckpt_dir} mixes layouts {layout} and {(tp, pp, ep)}")
+        found[(tr, pr, er)] = os.path.join(ckpt_dir, f)
+    if layout is None:
+        raise FileNotFoundError(f"no weights_tp_rank_world_size=*.pth files in {ckpt_dir}")
+    return found, layout
+
+
+def merge_checkpoint(ckpt_dir: str, model_config) -> tuple[dict[str, torch.Tensor], dict]:
+    """Returns ``(unsharded model state dict, meta)``; ``meta`` carries the step / token counters and the source layout."""
+    from .sharding import merge_shards
+
+    paths, (tp, pp, ep) = find_shards(ckpt_dir)
+    want = tp * pp * ep
+    if len(paths) != want:
+        raise FileNotFoundError(f"{ckpt_dir} holds {len(paths)} of the {want} shard files of its tp{tp} pp{pp} ep{ep} layout")
+    states, meta = {}, {}
+    for coord, path in paths.items():
+        blob = torch.load(path, map_location="cpu", weights_only=False)
+        states[coord] = blob["model"]
+        meta = {"trained_steps": int(blob.get("trained_steps", 0)), "trained_tokens": int(blob.get("trained_tokens", 0))}
+        dl = (blob.get("extra") or {}).get("data_loader")
+        if dl:
+            meta["data_loader"] = dl                    # position of the sample stream (layout-independent form inside)
+    full = merge_shards(states, model_config, tp, pp, ep)
+    meta["source_layout"] = {"tp": tp, "pp": pp, "ep": ep}
+    return full, meta
+
+
 class CheckpointManager:
     """Per-(tp, pp, ep) ``torch.save`` checkpoints under ``work_dir/<step>/`` (reference ``checkpoint.py:467-560``)."""
 
@@ -462,6 +506,27 @@ class CheckpointManager:
             self._writer.join()
             self._writer = None
         self._raise_writer_error()
+
+    def layout_matches(self, load_dir: str) -> bool:
+        """Whether ``load_dir`` was written under this run's (tp, pp, ep) layout."""
+        _, layout = find_shards(load_dir)
+        return layout == (self.tp_size, self.pp_size, self.ep_size)
+
+    def load_resharded(self, model: nn.Module, load_dir: str, model_config) -> tuple[int, int]:
+        """Resume the WEIGHTS of a checkpoint written under another (tp, pp, ep) layout: every rank merges the shard files
+        into the unsharded state (``merge_checkpoint``) and cuts its own slice (``load_from_unsharded``), pipeline stage
+        included.  Step and token counters and the data position (kept in samples, hence layout-independent) carry over;
+        the optimiser moments do NOT -- they are laid out per source rank -- and restart from zero, which the caller
+        must announce.  The reference cannot resume across layouts at all (``checkpoint.py:467-560``)."""
+        from .sharding import load_from_unsharded
+
+        full, meta = merge_checkpoint(load_dir, model_config)
+        raw = self._unwrap(model)
+        load_from_unsharded(raw, full, model_config, tp=self.tp_size, tp_rank=self.tp_rank, ep=self.ep_size, ep_rank=self.ep_rank,
+                            layer_ids=getattr(raw, "layer_ids", None))
+        self.last_extra = {"data_loader": meta["data_loader"]} if "data_loader" in meta else None
+        self.last_source_layout = meta["source_layout"]
+        return meta["trained_steps"], meta["trained_tokens"]
 
     def load_checkpoint(self, model: nn.Module, optimizer, load_dir: str, restore_rng: bool = True) -> tuple[int, int]:
         path = os.path.join(load_dir, self._filename())

@@ -21,7 +21,6 @@ from __future__ import annotations
 import argparse
 import json
 import os
-import re
 import shutil
 import sys
 
@@ -31,46 +30,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
 from scaletorch_b200.trainer.config import resolve_model_config  # noqa: E402
 from scaletorch_b200.utils.checkpoint import hf_state_from_unsharded  # noqa: E402
-from scaletorch_b200.utils.sharding import merge_shards  # noqa: E402
-
-_NAME = re.compile(r"weights_tp_rank_world_size=(\d+)_(\d+)_pp_rank_world_size=(\d+)_(\d+)(?:_ep_rank_world_size=(\d+)_(\d+))?\.pth$")
-
-
-def find_shards(ckpt_dir: str) -> tuple[dict[tuple[int, int, int], str], tuple[int, int, int]]:
-    """``{(tp_rank, pp_rank, ep_rank): path}`` and the layout ``(tp, pp, ep)`` found in ``ckpt_dir``."""
-    found: dict[tuple[int, int, int], str] = {}
-    layout = None
-    for f in sorted(os.listdir(ckpt_dir)):
-        m = _NAME.match(f)
-        if not m:
-            continue
-        tr, tp, pr, pp = (int(m.group(i)) for i in range(1, 5))
-        er, ep = (int(m.group(5)), int(m.group(6))) if m.group(5) is not None else (0, 1)
-        if layout is None:
-            layout = (tp, pp, ep)
-        elif layout != (tp, pp, ep):
-            raise ValueError(f"{ckpt_dir} mixes layouts {layout} and {(tp, pp, ep)}")
-        found[(tr, pr, er)] = os.path.join(ckpt_dir, f)
-    if layout is None:
-        raise FileNotFoundError(f"no weights_tp_rank_world_size=*.pth files in {ckpt_dir}")
-    return found, layout
-
-
-def merge_checkpoint(ckpt_dir: str, model_config) -> tuple[dict[str, torch.Tensor], dict]:
-    """Returns ``(unsharded model state dict, meta)``; ``meta`` carries the step / token counters and the source layout."""
-    paths, (tp, pp, ep) = find_shards(ckpt_dir)
-    states, meta = {}, {}
-    for coord, path in paths.items():
-        blob = torch.load(path, map_location="cpu", weights_only=False)
-        states[coord] = blob["model"]
-        meta = {"trained_steps": int(blob.get("trained_steps", 0)), "trained_tokens": int(blob.get("trained_tokens", 0))}
-        dl = (blob.get("extra") or {}).get("data_loader")
-        if dl:
-            meta["data_loader"] = dl                    # position of the sample stream (layout-independent form inside)
-    full = merge_shards(states, model_config, tp, pp, ep)
-    meta["source_layout"] = {"tp": tp, "pp": pp, "ep": ep}
-    return full, meta
-
+from scaletorch_b200.utils.checkpoint import find_shards, merge_checkpoint  # noqa: E402,F401
 
 def main(argv=None) -> int:
     ap = argparse.ArgumentParser(description=__doc__.split("\n\n")[0])

@@ -212,8 +212,18 @@ def main(argv=None) -> None:
         from scaletorch_b200.utils.checkpoint import prune_checkpoints, resolve_resume_path
 
         config.resume_path = resolve_resume_path(config.resume_path, config.work_dir)   # 'latest' -> newest complete one
-        if config.resume_path:
+        if config.resume_path and not ckpt.layout_matches(config.resume_path):
+            if not getattr(config, "resume_reshard", False):
+                raise SystemExit(f"{config.resume_path} was written under another TP / PP / EP layout; pass --resume_reshard true to "
+                                 "merge and re-cut its weights for this layout (optimiser moments restart from zero)")
+            step, trained_tokens = ckpt.load_resharded(model, config.resume_path, model_config)
+            rank_print(f"WARNING: resharded the weights of {config.resume_path} from {ckpt.last_source_layout} to this layout; "
+                       "the AdamW moments restart from zero", is_print_rank=log_rank)
+            if hasattr(optimizer, "step_count"):
+                optimizer.step_count = 0                   # fresh moments need fresh bias corrections
+        elif config.resume_path:
             step, trained_tokens = ckpt.load_checkpoint(model, optimizer, config.resume_path)
+        if config.resume_path:
             sched_path = os.path.join(config.resume_path, "scheduler.pt")
             if os.path.exists(sched_path):
                 lr_scheduler.load_state_dict(torch.load(sched_path, weights_only=False))

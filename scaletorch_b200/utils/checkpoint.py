@@ -409,15 +409,29 @@ def merge_checkpoint(ckpt_dir: str, model_config) -> tuple[dict[str, torch.Tenso
     if len(paths) != want:
         raise FileNotFoundError(f"{ckpt_dir} holds {len(paths)} of the {want} shard files of its tp{tp} pp{pp} ep{ep} layout")
     states, meta = {}, {}
+    moments: dict[str, dict] | None = {"exp_avg": {}, "exp_avg_sq": {}}
+    optimizer_step = 0
     for coord, path in paths.items():
         blob = torch.load(path, map_location="cpu", weights_only=False)
         states[coord] = blob["model"]
+        opt, slots = blob.get("optimizer"), blob.get("optimizer_slots")
+        if moments is not None and slots and isinstance(opt, dict) and torch.is_tensor(opt.get("exp_avg")):
+            for key in ("exp_avg", "exp_avg_sq"):
+                flat = opt[key]
+                moments[key][coord] = {n: flat[o:o + k].view(shape) for n, o, k, shape in slots}
+            optimizer_step = int(opt.get("step", 0))
+        else:
+            moments = None                              # a shard without a slot table: the moments cannot be re-cut
         meta = {"trained_steps": int(blob.get("trained_steps", 0)), "trained_tokens": int(blob.get("trained_tokens", 0))}
         dl = (blob.get("extra") or {}).get("data_loader")
         if dl:
             meta["data_loader"] = dl                    # position of the sample stream (layout-independent form inside)
     full = merge_shards(states, model_config, tp, pp, ep)
     meta["source_layout"] = {"tp": tp, "pp": pp, "ep": ep}
+    if moments is not None:
+        # AdamW moments have the shapes of their parameters: the same merge rules apply, name by name
+        meta["moments"] = {key: merge_shards(moments[key], model_config, tp, pp, ep) for key in moments}
+        meta["optimizer_step"] = optimizer_step
     return full, meta
 
 
@@ -474,6 +488,10 @@ class CheckpointManager:
                     "cuda": torch.cuda.get_rng_state() if torch.cuda.is_available() else None},
             "layout": {"tp": self.tp_size, "pp": self.pp_size, "ep": self.ep_size},
         }
+        store = getattr(optimizer, "store", None)
+        if store is not None and hasattr(store, "slots"):
+            # where each parameter's moments sit in the flat exp_avg / exp_avg_sq: lets another layout re-cut them by name
+            payload["optimizer_slots"] = [(sl.name, int(sl.offset), int(sl.numel), tuple(sl.param.shape)) for sl in store.slots]
         if extra:
             payload["extra"] = extra
         self.wait()                                   # at most one save in flight (and surface an earlier failure)
@@ -512,11 +530,13 @@ class CheckpointManager:
         _, layout = find_shards(load_dir)
         return layout == (self.tp_size, self.pp_size, self.ep_size)
 
-    def load_resharded(self, model: nn.Module, load_dir: str, model_config) -> tuple[int, int]:
+    def load_resharded(self, model: nn.Module, load_dir: str, model_config, optimizer=None) -> tuple[int, int]:
         """Resume the WEIGHTS of a checkpoint written under another (tp, pp, ep) layout: every rank merges the shard files
         into the unsharded state (``merge_checkpoint``) and cuts its own slice (``load_from_unsharded``), pipeline stage
-        included.  Step and token counters and the data position (kept in samples, hence layout-independent) carry over;
-        the optimiser moments do NOT -- they are laid out per source rank -- and restart from zero, which the caller
+        included.  Step and token counters and the data position (kept in samples, hence layout-independent) carry over.
+        The AdamW moments have the shapes of their parameters, so when the checkpoint carries the slot table of its flat
+        optimiser state (``optimizer_slots``, written since this feature exists) they are merged and re-cut by the same
+        rules and loaded into ``optimizer`` (``self.moments_resharded``); otherwise they restart from zero, which the caller
         must announce.  The reference cannot resume across layouts at all (``checkpoint.py:467-560``)."""
         from .sharding import load_from_unsharded
 
@@ -526,6 +546,25 @@ class CheckpointManager:
                             layer_ids=getattr(raw, "layer_ids", None))
         self.last_extra = {"data_loader": meta["data_loader"]} if "data_loader" in meta else None
         self.last_source_layout = meta["source_layout"]
+        self.moments_resharded = False
+        store = getattr(optimizer, "store", None)
+        if optimizer is not None and "moments" in meta and store is not None and hasattr(store, "slots"):
+            from .sharding import shard_tensor
+
+            layer_ids = getattr(raw, "layer_ids", None)
+            sd = {"step": meta["optimizer_step"], "param_groups": []}
+            for key in ("exp_avg", "exp_avg_sq"):
+                flat = torch.zeros(store.total_numel, dtype=torch.float32)
+                for sl in store.slots:
+                    m = re.match(r"decoder_layers\.(\d+)\.(.*)", sl.name)
+                    src = f"decoder_layers.{layer_ids[int(m.group(1))]}.{m.group(2)}" if (m and layer_ids is not None) else sl.name
+                    if src not in meta["moments"][key] and src == "final_proj.weight":
+                        src = "embedding.weight"           # tied embeddings
+                    piece = shard_tensor(src, meta["moments"][key][src], model_config, self.tp_size, self.tp_rank, self.ep_size, self.ep_rank)
+                    flat[sl.offset:sl.offset + sl.numel] = piece.reshape(-1).float()
+                sd[key] = flat
+            optimizer.load_state_dict(sd)
+            self.moments_resharded = True
         return meta["trained_steps"], meta["trained_tokens"]
 
     def load_checkpoint(self, model: nn.Module, optimizer, load_dir: str, restore_rng: bool = True) -> tuple[int, int]:

@@ -231,23 +231,24 @@ def test_nonfinite_loss_aborts_before_a_checkpoint_is_written(tmp_path):
 
 def test_resume_across_layouts_with_resharding(tmp_path):
     """A checkpoint written under TP2+SP is resumed in ONE process, and a single-process checkpoint under PP2: refused without
-    ``--resume_reshard true``; with it, the first resumed step has the loss of the uninterrupted run (it depends on the weights
-    and on the data position only, both carried over), and the job says that the optimiser moments restart."""
+    ``--resume_reshard true``; with it, the resumed steps have the losses of the uninterrupted run: weights, data position AND
+    the AdamW moments (re-cut by name through the slot table stored in the checkpoint) carry over."""
     model = ["--model_name_or_path", "tiny-qwen3", "--num_attention_heads", "4", "--num_key_value_heads", "2", "--log_lag", "0",
              "--lr_scheduler_type", "step", "--step_size", "1000"]
     tp2 = ["--tensor_parallel_size", "2", "--sequence_parallel", "true"]
     a, straight = _run_many([
         (model + tp2 + ["--total_train_steps", "3", "--save_frequency", "3", "--work_dir", str(tmp_path / "tp2")], 2),
-        (model + tp2 + ["--total_train_steps", "4", "--save_frequency", "0", "--work_dir", str(tmp_path / "straight")], 2)])
-    want4 = dict(_losses(straight))[4]
+        (model + tp2 + ["--total_train_steps", "5", "--save_frequency", "0", "--work_dir", str(tmp_path / "straight")], 2)])
+    want = dict(_losses(straight))
     refused = _run(model + ["--total_train_steps", "4", "--save_frequency", "0", "--work_dir", str(tmp_path / "one"),
                             "--resume_path", str(tmp_path / "tp2" / "3")], expect_rc=1)
     assert "--resume_reshard true" in refused
     out = _run(model + ["--total_train_steps", "5", "--save_frequency", "5", "--work_dir", str(tmp_path / "one"),
                         "--resume_path", str(tmp_path / "tp2" / "3"), "--resume_reshard", "true"])
-    assert "resharded the weights" in out and "{'tp': 2, 'pp': 1, 'ep': 1}" in out and "Loaded checkpoint at step 3" in out
+    assert "resharded the weights and AdamW moments" in out and "{'tp': 2, 'pp': 1, 'ep': 1}" in out and "Loaded checkpoint at step 3" in out
     got = dict(_losses(out))
-    assert sorted(got) == [4, 5] and abs(got[4] - want4) < 2e-3, (got, want4)
+    # step 4 depends on the weights and the data position, step 5 also on the re-cut AdamW moments and the step count
+    assert sorted(got) == [4, 5] and abs(got[4] - want[4]) < 2e-3 and abs(got[5] - want[5]) < 2e-3, (got, want)
     # and onwards: the single-process checkpoint of step 5 continues under pipeline parallelism
     out = _run(model + ["--total_train_steps", "6", "--save_frequency", "0", "--work_dir", str(tmp_path / "pp2"),
                         "--pipeline_parallel_size", "2", "--gradient_accumulation_steps", "1",

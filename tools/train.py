@@ -216,11 +216,15 @@ def main(argv=None) -> None:
             if not getattr(config, "resume_reshard", False):
                 raise SystemExit(f"{config.resume_path} was written under another TP / PP / EP layout; pass --resume_reshard true to "
                                  "merge and re-cut its weights for this layout (optimiser moments restart from zero)")
-            step, trained_tokens = ckpt.load_resharded(model, config.resume_path, model_config)
-            rank_print(f"WARNING: resharded the weights of {config.resume_path} from {ckpt.last_source_layout} to this layout; "
-                       "the AdamW moments restart from zero", is_print_rank=log_rank)
-            if hasattr(optimizer, "step_count"):
-                optimizer.step_count = 0                   # fresh moments need fresh bias corrections
+            step, trained_tokens = ckpt.load_resharded(model, config.resume_path, model_config, optimizer)
+            if ckpt.moments_resharded:
+                rank_print(f"resharded the weights and AdamW moments of {config.resume_path} from {ckpt.last_source_layout} to this "
+                           "layout", is_print_rank=log_rank)
+            else:
+                rank_print(f"WARNING: resharded the weights of {config.resume_path} from {ckpt.last_source_layout} to this layout; "
+                           "the AdamW moments restart from zero", is_print_rank=log_rank)
+                if hasattr(optimizer, "step_count"):
+                    optimizer.step_count = 0               # fresh moments need fresh bias corrections
         elif config.resume_path:
             step, trained_tokens = ckpt.load_checkpoint(model, optimizer, config.resume_path)
         if config.resume_path:

@@ -189,3 +189,16 @@ def test_real_tp2_pp2_run_converts_and_continues_in_one_process(tmp_path):
     # carries the position over in samples): the loss on the NEXT, unseen batches stays where the run had brought it.
     # (Restarting the data at sample 0 would show ~4.0 here: the tiny model has memorised the batches it trained on.)
     assert abs(cont[0][1] - par[-1][1]) < 0.5, (par, cont)
+    # Without the converter: --resume_reshard reads the four shard files directly and re-cuts weights AND AdamW moments
+    # (tied embedding on both pipeline ends, TP-sliced projections), so the single process continues the trajectory of
+    # the TP2 x PP2 run itself.
+    from test_train_cli_cpu import _run_many
+
+    par_args = model + const_lr + ["--tensor_parallel_size", "2", "--pipeline_parallel_size", "2", "--gradient_accumulation_steps", "2",
+                                   "--total_train_steps", "8", "--work_dir", str(tmp_path / "straight"), "--save_frequency", "0"]
+    one_args = ["--model_name_or_path", str(cfg_dir)] + const_lr + ["--gradient_accumulation_steps", "2", "--total_train_steps", "8",
+                "--work_dir", str(tmp_path / "direct"), "--save_frequency", "0", "--resume_path", str(work / "6"), "--resume_reshard", "true"]
+    straight_out, direct_out = _run_many([(par_args, 4), (one_args, 1)])
+    straight, direct = dict(_losses(straight_out)), dict(_losses(direct_out))
+    assert "resharded the weights and AdamW moments" in direct_out and sorted(direct) == [7, 8]
+    assert all(abs(direct[s] - straight[s]) < 2e-3 for s in (7, 8)), (direct, {s: straight[s] for s in (7, 8)})

@@ -230,27 +230,41 @@ def test_nonfinite_loss_aborts_before_a_checkpoint_is_written(tmp_path):
 
 
 def test_resume_across_layouts_with_resharding(tmp_path):
-    """A checkpoint written under TP2+SP is resumed in ONE process, and a single-process checkpoint under PP2: refused without
-    ``--resume_reshard true``; with it, the resumed steps have the losses of the uninterrupted run: weights, data position AND
-    the AdamW moments (re-cut by name through the slot table stored in the checkpoint) carry over."""
-    model = ["--model_name_or_path", "tiny-qwen3", "--num_attention_heads", "4", "--num_key_value_heads", "2", "--log_lag", "0",
-             "--lr_scheduler_type", "step", "--step_size", "1000"]
+    """A checkpoint written under TP2+SP, and one written under EP2 (MoE), are resumed in ONE process; a single-process
+    checkpoint under PP2: refused without ``--resume_reshard true``; with it, the resumed steps have the losses of the
+    uninterrupted run: weights, data position AND the AdamW moments (re-cut by name through the slot table stored in the
+    checkpoint; expert moments included) carry over."""
+    const = ["--log_lag", "0", "--lr_scheduler_type", "step", "--step_size", "1000"]
+    dense = ["--model_name_or_path", "tiny-qwen3", "--num_attention_heads", "4", "--num_key_value_heads", "2"] + const
+    moe = ["--model_name_or_path", "tiny-qwen3-moe"] + const
     tp2 = ["--tensor_parallel_size", "2", "--sequence_parallel", "true"]
-    a, straight = _run_many([
-        (model + tp2 + ["--total_train_steps", "3", "--save_frequency", "3", "--work_dir", str(tmp_path / "tp2")], 2),
-        (model + tp2 + ["--total_train_steps", "5", "--save_frequency", "0", "--work_dir", str(tmp_path / "straight")], 2)])
-    want = dict(_losses(straight))
-    refused = _run(model + ["--total_train_steps", "4", "--save_frequency", "0", "--work_dir", str(tmp_path / "one"),
-                            "--resume_path", str(tmp_path / "tp2" / "3")], expect_rc=1)
+    ep2 = ["--expert_parallel_size", "2", "--micro_batch_size", "1"]          # two data ranks x 1 = the single process's batch of 2
+    _, straight, _, straight_moe = _run_many([
+        (dense + tp2 + ["--total_train_steps", "3", "--save_frequency", "3", "--work_dir", str(tmp_path / "tp2")], 2),
+        (dense + tp2 + ["--total_train_steps", "5", "--save_frequency", "0", "--work_dir", str(tmp_path / "straight")], 2),
+        (moe + ep2 + ["--total_train_steps", "3", "--save_frequency", "3", "--work_dir", str(tmp_path / "ep2")], 2),
+        (moe + ep2 + ["--total_train_steps", "5", "--save_frequency", "0", "--work_dir", str(tmp_path / "straight_moe")], 2)])
+    want, want_moe = dict(_losses(straight)), dict(_losses(straight_moe))
+    resume = ["--total_train_steps", "5", "--save_frequency", "5"]
+    jobs = [(dense + ["--total_train_steps", "4", "--save_frequency", "0", "--work_dir", str(tmp_path / "refused"),
+                      "--resume_path", str(tmp_path / "tp2" / "3")], 1),
+            (dense + resume + ["--work_dir", str(tmp_path / "one"), "--resume_path", str(tmp_path / "tp2" / "3"), "--resume_reshard", "true"], 1),
+            (moe + resume + ["--work_dir", str(tmp_path / "one_moe"), "--resume_path", str(tmp_path / "ep2" / "3"), "--resume_reshard", "true"], 1)]
+    from concurrent.futures import ThreadPoolExecutor
+
+    with ThreadPoolExecutor(max_workers=3) as ex:
+        futs = [ex.submit(_run, a, n, None, 600, rc) for (a, n), rc in zip(jobs, (1, 0, 0))]
+        refused, out, out_moe = [f.result() for f in futs]
     assert "--resume_reshard true" in refused
-    out = _run(model + ["--total_train_steps", "5", "--save_frequency", "5", "--work_dir", str(tmp_path / "one"),
-                        "--resume_path", str(tmp_path / "tp2" / "3"), "--resume_reshard", "true"])
     assert "resharded the weights and AdamW moments" in out and "{'tp': 2, 'pp': 1, 'ep': 1}" in out and "Loaded checkpoint at step 3" in out
     got = dict(_losses(out))
     # step 4 depends on the weights and the data position, step 5 also on the re-cut AdamW moments and the step count
     assert sorted(got) == [4, 5] and abs(got[4] - want[4]) < 2e-3 and abs(got[5] - want[5]) < 2e-3, (got, want)
+    got_moe = dict(_losses(out_moe))
+    assert "{'tp': 1, 'pp': 1, 'ep': 2}" in out_moe and sorted(got_moe) == [4, 5]
+    assert all(abs(got_moe[s] - want_moe[s]) < 2e-3 for s in (4, 5)), (got_moe, want_moe)
     # and onwards: the single-process checkpoint of step 5 continues under pipeline parallelism
-    out = _run(model + ["--total_train_steps", "6", "--save_frequency", "0", "--work_dir", str(tmp_path / "pp2"),
+    out = _run(dense + ["--total_train_steps", "6", "--save_frequency", "0", "--work_dir", str(tmp_path / "pp2"),
                         "--pipeline_parallel_size", "2", "--gradient_accumulation_steps", "1",
                         "--resume_path", str(tmp_path / "one" / "5"), "--resume_reshard", "true"], nproc=2)
     assert "resharded the weights" in out and [s for s, _ in _losses(out)] == [6]

@@ -53,7 +53,7 @@ def inspect(path: str, list_tensors: bool = False) -> dict:
                  "parameters": sum(t.numel() for _, t in params), "parameter_bytes": sum(t.numel() * t.element_size() for _, t in params),
                  "optimizer_bytes": sum(t.numel() * t.element_size() for _, t in opt), "nonfinite_tensors": bad,
                  "layout_recorded": ck.get("layout"), "data_loader": (ck.get("extra") or {}).get("data_loader"),
-                 "has_rng": bool(ck.get("rng"))}
+                 "has_rng": bool(ck.get("rng")), "moments_can_be_recut": bool(ck.get("optimizer_slots"))}
         if list_tensors:
             entry["tensors"] = [{"name": n, "shape": list(t.shape), "dtype": str(t.dtype).replace("torch.", "")} for n, t in params]
         shards.append(entry)
@@ -77,7 +77,9 @@ def render(info: dict) -> str:
            f"  shards {info['shards_found']} / {info['shards_expected']}" + (f"  MISSING {info['missing_shards']}" if info["missing_shards"] else "")
            + (f"  TEMPORARY FILES {info['temporary_files']}" if info["temporary_files"] else "")
            + ("" if info["consistent_step"] else "  SHARDS DISAGREE ON THE STEP"),
-           f"  scheduler state: {'yes' if info['scheduler_state'] else 'no'}   data position: {info['shards'][0]['data_loader']}"]
+           f"  scheduler state: {'yes' if info['scheduler_state'] else 'no'}   data position: {info['shards'][0]['data_loader']}",
+           "  resume under another layout (--resume_reshard): weights"
+           + (" and AdamW moments" if all(s["moments_can_be_recut"] for s in info["shards"]) else " only (no optimiser slot table in these files)")]
     for s in info["shards"]:
         out.append(f"  tp{s['tp_rank']} pp{s['pp_rank']} ep{s['ep_rank']}: {s['parameters'] / 1e6:9.2f} M parameters, {s['parameter_bytes'] / 1e6:9.1f} MB weights, "
                    f"{s['optimizer_bytes'] / 1e6:9.1f} MB optimiser state" + (f"  NON-FINITE: {s['nonfinite_tensors'][:3]}" if s["nonfinite_tensors"] else ""))

@@ -153,7 +153,7 @@ class TrainingArguments:
     use_cuda_graph: bool = field(default=False, metadata={"help": "Replay the whole step from a CUDA graph (trainer/graphed.py)"})
     log_lag: int = field(default=1, metadata={"help": "Log step i after enqueueing step i+lag (0 = synchronous logging)"})
     nonfinite_loss: str = field(default="abort", metadata={"help": "What to do when the logged loss is NaN / Inf: 'abort' (exit non-zero so that a supervisor resumes from the last checkpoint) or 'warn' (keep going, as the reference does)"})
-    eval_interval: int = field(default=0, metadata={"help": "Evaluate the held-out loss every N optimiser steps (0 = never; not offered with pipeline parallelism)"})
+    eval_interval: int = field(default=0, metadata={"help": "Evaluate the held-out loss every N optimiser steps (0 = never; with pipeline stages the pass runs forward-only through the pipeline)"})
     eval_batches: int = field(default=8, metadata={"help": "Micro-batches per data rank in one evaluation (the same batches every time)"})
     eval_token_file: str | None = field(default=None, metadata={"help": "Flat int32 token file (.npy / raw .bin) with the held-out tokens; default: --eval_split of the dataset, or synthetic data with another seed"})
     eval_split: str = field(default="validation", metadata={"help": "Dataset split used for evaluation when no --eval_token_file is given"})

@@ -25,11 +25,23 @@ from ..parallel.process_group import process_group_manager as pgm
 
 
 @torch.no_grad()
-def evaluate_loss(model, loader, device, max_batches: int | None = None) -> dict:
-    """Sum of token losses and token count over this rank's next ``max_batches`` batches (default: one epoch)."""
+def evaluate_loss(model, loader, device, max_batches: int | None = None, tensor_shapes=None, dtype=None) -> dict:
+    """Sum of token losses and token count over this rank's next ``max_batches`` batches (default: one epoch).
+
+    With pipeline stages (``tensor_shapes`` = the activation shape the stages exchange, as in training) the pass is
+    forward-only through the pipeline: every stage receives, runs its layers and sends on; the last stage holds the loss
+    and the token count, the other stages report zeros."""
     raw = model.module if hasattr(model, "module") else model
+    while hasattr(raw, "module") and isinstance(raw.module, torch.nn.Module):
+        raw = raw.module
     was_training = raw.training
     raw.eval()
+    pipelined = bool(pgm) and pgm.pp_world_size > 1
+    if pipelined:
+        from ..parallel.pipeline_parallel.pp_comms import pipeline_communicate, post_recv
+
+        if tensor_shapes is None or dtype is None:
+            raise ValueError("evaluation under pipeline parallelism needs tensor_shapes and dtype")
     try:
         n_batches = len(loader) if max_batches is None else min(len(loader), max_batches)
         loss_sum = torch.zeros((), dtype=torch.float64, device=device)
@@ -38,6 +50,17 @@ def evaluate_loss(model, loader, device, max_batches: int | None = None) -> dict
         for _ in range(n_batches):
             b = next(loader)
             x, y = b["input_ids"].to(device, non_blocking=True), b["target_ids"].to(device, non_blocking=True)
+            if pipelined:
+                recv = post_recv("recv_forward", tensor_shapes, device, dtype)
+                hidden = recv.wait() if recv is not None else None
+                out = raw(input_ids=x if raw.is_first else None, hidden_states=hidden)
+                if raw.is_last:
+                    n = int((y != -100).sum())
+                    loss_sum += raw.loss_from_hidden(out, y, loss_scale=1.0).double() * n
+                    tokens += n
+                else:
+                    pipeline_communicate("send_forward", tensor=out, device=device, dtype=dtype)
+                continue
             n = int((y != -100).sum())
             loss_sum += raw.loss(x, y).double() * n          # mean over the batch's tokens -> sum
             tokens += n
@@ -64,8 +87,9 @@ class PeriodicEvaluator:
     """Every ``interval`` optimiser steps: rewind the held-out loader, run :func:`evaluate_loss` over ``batches`` batches per
     rank, reduce, and hand the result to ``report(step, result)``.  ``interval <= 0`` disables it."""
 
-    def __init__(self, model, loader, device, interval: int, batches: int, report=None):
+    def __init__(self, model, loader, device, interval: int, batches: int, report=None, tensor_shapes=None, dtype=None):
         self.model, self.loader, self.device = model, loader, device
+        self.tensor_shapes, self.dtype = tensor_shapes, dtype
         self.interval, self.batches, self.report = int(interval), int(batches), report
         self.history: list[tuple[int, dict[str, Any]]] = []
 
@@ -76,7 +100,8 @@ class PeriodicEvaluator:
         if self.device.type == "cuda":
             torch.cuda.synchronize()                        # the step (possibly a graph replay on a side stream) is complete
         self.loader.load_state_dict({"batches_served": 0})   # same held-out batches every time
-        result = reduce_eval_stats(evaluate_loss(self.model, self.loader, self.device, self.batches), self.device)
+        result = reduce_eval_stats(evaluate_loss(self.model, self.loader, self.device, self.batches, self.tensor_shapes,
+                                                 self.dtype), self.device)
         self.history.append((step, result))
         if self.report is not None:
             self.report(step, result)

@@ -269,3 +269,21 @@ def test_resume_across_layouts_with_resharding(tmp_path):
                         "--resume_path", str(tmp_path / "one" / "5"), "--resume_reshard", "true"], nproc=2)
     assert "resharded the weights" in out and [s for s, _ in _losses(out)] == [6]
     assert abs(dict(_losses(out))[6] - got[5]) < 1.0          # same model a step later: the loss stays where it was
+
+
+def test_periodic_evaluation_through_pipeline_stages(tmp_path):
+    """``--eval_interval`` with pipeline parallelism: the forward-only pass through the stages gives the held-out loss of the
+    same weights evaluated in one process (both runs resume the same single-process checkpoint; the PP2 run re-cuts it)."""
+    ev = re.compile(r"Eval \| Step:\s*(\d+)\s*\| Loss:\s*([\d.]+).*?Tokens:\s*(\d+)")
+    model = ["--model_name_or_path", "tiny-qwen3", "--num_attention_heads", "4", "--num_key_value_heads", "2", "--log_lag", "0",
+             "--lr_scheduler_type", "step", "--step_size", "1000"]
+    _run(model + ["--total_train_steps", "2", "--save_frequency", "2", "--work_dir", str(tmp_path / "base")])
+    resume = ["--total_train_steps", "4", "--save_frequency", "0", "--eval_interval", "2", "--eval_batches", "2",
+              "--resume_path", str(tmp_path / "base" / "2")]
+    one, pp2 = _run_many([(model + resume + ["--work_dir", str(tmp_path / "one")], 1),
+                          (model + resume + ["--work_dir", str(tmp_path / "pp2"), "--pipeline_parallel_size", "2",
+                                             "--resume_reshard", "true"], 2)])
+    e1 = [(int(s), float(l), int(t)) for s, l, t in ev.findall(one)]
+    e2 = [(int(s), float(l), int(t)) for s, l, t in ev.findall(pp2)]
+    assert [(s, t) for s, _, t in e1] == [(4, 2 * 2 * 64)] == [(s, t) for s, _, t in e2], (one[-800:], pp2[-800:])
+    assert abs(e1[0][1] - e2[0][1]) < 2e-3, (e1, e2)

@@ -9,7 +9,8 @@ Takes the trainer's flags (``ScaleTorchArguments``) plus ``--max_batches``.  Dat
 ``--tokenizer_name_or_path``, or ``--synthetic_data true``.  Every data-parallel rank evaluates its shard of the windows;
 token counts and summed losses meet in ONE ``all_reduce_dict`` at the end (``scaletorch_b200.dist``), rank 0 prints one
 JSON line: ``{"loss", "perplexity", "tokens", "batches", "tokens_per_s"}``.  Tensor / context parallel layouts work as in
-training (the loss is already reduced over them); pipeline-parallel evaluation is not offered.
+training (the loss is already reduced over them); the stand-alone tool does not take pipeline
+layouts (the trainer's ``--eval_interval`` does).
 """
 from __future__ import annotations
 

@@ -150,11 +150,8 @@ def build_data_loader(config, model_config, device):
 def build_eval_loader(config, model_config, device):
     """The held-out loader of ``--eval_interval``: ``--eval_token_file`` windows, else the dataset's ``--eval_split``, else
     (synthetic data) sequences drawn with another seed than the training stream.  Never shuffled; ``None`` when evaluation
-    is off or the layout has pipeline stages (the loss lives on the last stage only; evaluate a converted checkpoint)."""
+    is off."""
     if getattr(config, "eval_interval", 0) <= 0:
-        return None
-    if config.pipeline_parallel_size > 1:
-        rank_print("--eval_interval is ignored with pipeline parallelism (use tools/convert_checkpoint.py + tools/evaluate.py)")
         return None
     dataset = None
     if config.eval_token_file:
@@ -259,7 +256,8 @@ def main(argv=None) -> None:
                 run.log({"eval_loss": result["loss"], "eval_perplexity": result["perplexity"]}, step=st)
 
         evaluator = PeriodicEvaluator(model, build_eval_loader(config, model_config, device), device,
-                                      getattr(config, "eval_interval", 0), getattr(config, "eval_batches", 8), report_eval)
+                                      getattr(config, "eval_interval", 0), getattr(config, "eval_batches", 8), report_eval,
+                                      tensor_shapes=tensor_shapes, dtype=dtype)
         stopper = StopOnSignal(getattr(config, "save_on_signal", False), getattr(config, "signal_check_interval", 10), world_size)
         monitor.start()
         max_steps = config.total_train_steps or float("inf")

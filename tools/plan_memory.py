@@ -232,6 +232,11 @@ def main(argv=None) -> int:
     ap.add_argument("--suggest", action="store_true", help="list every layout of --gpus GPUs that fits (ignores the axis flags)")
     ap.add_argument("--gpus", type=int, default=8)
     a = ap.parse_args(argv)
+    try:
+        resolve_model_config(a.model)
+    except RuntimeError as e:
+        vendored = sorted(os.listdir(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "configs")))
+        raise SystemExit(f"plan_memory.py: {str(e).splitlines()[0]}\nvendored configs: {', '.join(vendored)}")
     if a.suggest:
         found = suggest(a.model, a.gpus, micro_batch_size=a.micro_batch_size, sequence_length=a.sequence_length, ga=a.ga,
                         gradient_checkpointing=a.gradient_checkpointing, zero_stage=a.zero_stage, window_mb=a.window_mb,
